@@ -1,0 +1,102 @@
+"""Module-level worker functions for the multi-process tests (importable by spawn)."""
+import os
+import time
+
+import torch
+
+
+def w_rank_info(tag):
+    from databricks_distributed_deep_learning_b200.parallel import process_group as pg
+
+    got = pg.all_gather_object((pg.rank(), tag))
+    return {"rank": pg.rank(), "world": pg.world_size(), "gathered": got, "env_rank": os.environ["RANK"]}
+
+
+def w_fail_on_rank(bad_rank):
+    from databricks_distributed_deep_learning_b200.parallel import process_group as pg
+
+    if pg.rank() == bad_rank:
+        raise ValueError(f"boom from rank {pg.rank()}")
+    time.sleep(30)  # siblings would hang here; the parent must kill them
+    return "survived"
+
+
+def w_die_on_rank(bad_rank):
+    from databricks_distributed_deep_learning_b200.parallel import process_group as pg
+
+    if pg.rank() == bad_rank:
+        os._exit(7)  # simulated crash mid-step: no traceback, no report
+    time.sleep(30)
+    return "survived"
+
+
+def w_no_pg():
+    return int(os.environ["WORLD_SIZE"]) * 10 + int(os.environ["RANK"])
+
+
+def _make_resnet18():
+    from databricks_distributed_deep_learning_b200.models import resnet18
+
+    torch.manual_seed(1234)
+    return resnet18(num_classes=10, small_input=True)
+
+
+def w_ddp_resnet18(steps, per_rank_batch, bucket_cap_mb, use_no_sync=False):
+    """BASELINE.json:7 - ResNet-18, 32x32 synthetic, DDP over gloo, world_size=2."""
+    import torch.nn.functional as F
+
+    from databricks_distributed_deep_learning_b200 import DDP
+    from databricks_distributed_deep_learning_b200.parallel import process_group as pg
+    from databricks_distributed_deep_learning_b200.utils.data import cifar_shape_loader
+
+    torch.set_num_threads(2)
+    rank, world = pg.rank(), pg.world_size()
+    model = _make_resnet18()
+    if rank != 0:  # perturb: the init broadcast must repair this
+        with torch.no_grad():
+            for p in model.parameters():
+                p.add_(1.0)
+    # BN in eval mode so that the 2-rank run is exactly comparable to one process with the
+    # concatenated batch (batch statistics would differ by construction)
+    model.eval()
+    ddp = DDP(model, bucket_cap_mb=bucket_cap_mb)
+    opt = torch.optim.SGD(ddp.parameters(), lr=0.05)
+    loader = cifar_shape_loader(per_rank_batch, rank=rank, world_size=world, seed=3, steps=steps, pin_memory=False)
+    losses = []
+    for x, y in loader:
+        ddp.zero_grad()
+        if use_no_sync:
+            h = per_rank_batch // 2
+            with ddp.no_sync():
+                (F.cross_entropy(ddp(x[:h]), y[:h]) * 0.5).backward()
+            (F.cross_entropy(ddp(x[h:]), y[h:]) * 0.5).backward()
+            losses.append(0.0)
+        else:
+            loss = F.cross_entropy(ddp(x), y)
+            loss.backward()
+            losses.append(float(loss.detach()))
+        opt.step()
+    flat = torch.cat([p.detach().reshape(-1) for p in ddp.module.parameters()])
+    gathered = pg.all_gather_object(flat)
+    keys = list(ddp.state_dict().keys())
+    return {"params": gathered, "losses": losses, "keys": keys, "nbuckets": len(ddp.buckets)}
+
+
+def single_process_resnet18(steps, per_rank_batch, world):
+    import torch.nn.functional as F
+
+    from databricks_distributed_deep_learning_b200.utils.data import cifar_shape_loader
+
+    torch.set_num_threads(2)
+    model = _make_resnet18().eval()
+    opt = torch.optim.SGD(model.parameters(), lr=0.05)
+    loaders = [iter(cifar_shape_loader(per_rank_batch, rank=r, world_size=world, seed=3, steps=steps, pin_memory=False))
+               for r in range(world)]
+    for _ in range(steps):
+        batches = [next(l) for l in loaders]
+        x = torch.cat([b[0] for b in batches])
+        y = torch.cat([b[1] for b in batches])
+        opt.zero_grad()
+        F.cross_entropy(model(x), y).backward()
+        opt.step()
+    return torch.cat([p.detach().reshape(-1) for p in model.parameters()])
