@@ -1,0 +1,374 @@
+// BatchNorm (training) + residual add + ReLU on NHWC bf16 activations, forward and backward
+// (the BN/ReLU half of K9 "conv-BN-ReLU"; workload: the 53 BatchNorm2d of
+// the reference's ResNet-50, notebooks/cv/onnx_experiments.py:19).
+//
+// The activation is a [M = N*H*W, C] matrix with C contiguous.  A thread owns one
+// 8-channel (16-byte) column group for its whole life: the grid's total thread count is a
+// multiple of C/8, so striding over the flat vector index never changes a thread's
+// channels and per-channel constants stay in registers.
+//
+//   forward : stats pass   (read x)                      -> per-block partial sum / sumsq
+//             finalize     (C threads)                   -> mean, invstd, running stats, scale/shift
+//             apply pass   (read x [+res], write y)      -> y = relu(x*scale + shift [+ res])
+//   backward: reduce pass  (read dy, y, x [write g])     -> partial sum(g), sum(g*xhat)
+//             finalize                                   -> dgamma, dbeta, coefficients
+//             apply pass   (read g|dy,y and x, write dx) -> dx
+//
+// versus stock eager (BN kernel, ReLU kernel, add kernel, each a full read+write), the
+// forward moves 2R+1W (+1R residual) instead of up to 5R+3W.  All cross-block reductions
+// go through a scratch buffer folded in fixed order: deterministic, no atomics.
+#include "../include/b200ddl.h"
+#include "common.cuh"
+
+namespace {
+
+constexpr int kBnMaxThreads = 256;
+constexpr int kBnGridCap = DDL_SM_COUNT * 2;
+constexpr int kUnroll = 4;
+
+struct BnGeom {
+    int vec_cols;  // C / 8
+    int threads;   // multiple of vec_cols, <= 256
+    int grid;
+    size_t nvec;   // M * C / 8
+};
+
+int make_geom(long long M, int C, BnGeom* g) {
+    DDL_REQUIRE(C % 8 == 0 && C >= 8 && C <= 2048, "bn: channels %d must be a multiple of 8 and <= 2048", C);
+    DDL_REQUIRE(M >= 1, "bn: empty activation");
+    g->vec_cols = C / 8;
+    g->threads = (kBnMaxThreads / g->vec_cols) * g->vec_cols;
+    g->nvec = (size_t)M * g->vec_cols;
+    long long want = (long long)((g->nvec + (size_t)g->threads * kUnroll - 1) / ((size_t)g->threads * kUnroll));
+    g->grid = (int)(want < 1 ? 1 : (want > kBnGridCap ? kBnGridCap : want));
+    return 0;
+}
+
+// block-level fold of per-thread [2][8] accumulators over the threads that share a column
+// group; result for column group vc lands in partial[block][which][vc*8 + j]
+__device__ __forceinline__ void fold_to_partials(const float (&a)[8], const float (&b)[8], int vec_cols, int C,
+                                                 float* __restrict__ partial_block, float* sh /*[threads][17]*/) {
+    float* mine = sh + threadIdx.x * 17;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        mine[j] = a[j];
+        mine[8 + j] = b[j];
+    }
+    __syncthreads();
+    // thread t < vec_cols*16 handles (vc = t / 16, slot = t % 16)
+    for (int t = threadIdx.x; t < vec_cols * 16; t += blockDim.x) {
+        const int vc = t >> 4, slot = t & 15;
+        float acc = 0.f;
+        for (int r = vc; r < (int)blockDim.x; r += vec_cols) acc += sh[r * 17 + slot];
+        const int which = slot >> 3, j = slot & 7;
+        partial_block[which * C + vc * 8 + j] = acc;
+    }
+}
+
+__global__ void __launch_bounds__(kBnMaxThreads) bn_stats_kernel(const bf16* __restrict__ x, size_t nvec, int vec_cols, int C,
+                                                                 float* __restrict__ partials) {
+    extern __shared__ float sh[];
+    float s[8], q[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t v0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v0 < nvec; v0 += stride * kUnroll) {
+        uint4 u[kUnroll];
+#pragma unroll
+        for (int k = 0; k < kUnroll; ++k)
+            if (v0 + k * stride < nvec) u[k] = ld_stream_v4(x + (v0 + k * stride) * 8);
+#pragma unroll
+        for (int k = 0; k < kUnroll; ++k)
+            if (v0 + k * stride < nvec) {
+                float f[8];
+                bf16x8_to_float(u[k], f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    s[j] += f[j];
+                    q[j] += f[j] * f[j];
+                }
+            }
+    }
+    fold_to_partials(s, q, vec_cols, C, partials + (size_t)blockIdx.x * 2 * C, sh);
+}
+
+// mean/var from partials; running-stat update (unbiased var, like torch); scale/shift
+__global__ void bn_fwd_finalize_kernel(const float* __restrict__ partials, int nblocks, long long M, int C,
+                                       const bf16* __restrict__ gamma, const bf16* __restrict__ beta,
+                                       float* __restrict__ running_mean, float* __restrict__ running_var, float momentum, float eps,
+                                       float* __restrict__ mean_out, float* __restrict__ invstd_out, float* __restrict__ scale_out,
+                                       float* __restrict__ shift_out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    float s = 0.f, q = 0.f;
+    for (int b = 0; b < nblocks; ++b) {
+        s += partials[(size_t)b * 2 * C + c];
+        q += partials[(size_t)b * 2 * C + C + c];
+    }
+    const float inv_m = 1.f / (float)M;
+    const float mean = s * inv_m;
+    float var = q * inv_m - mean * mean;
+    var = var < 0.f ? 0.f : var;
+    const float invstd = rsqrtf(var + eps);
+    mean_out[c] = mean;
+    invstd_out[c] = invstd;
+    const float g = gamma ? __bfloat162float(gamma[c]) : 1.f, b = beta ? __bfloat162float(beta[c]) : 0.f;
+    scale_out[c] = g * invstd;
+    shift_out[c] = b - mean * g * invstd;
+    if (running_mean) {
+        const float unbiased = M > 1 ? var * ((float)M / (float)(M - 1)) : var;
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+    }
+}
+
+// scale/shift from running statistics (eval mode)
+__global__ void bn_eval_coeff_kernel(int C, const bf16* __restrict__ gamma, const bf16* __restrict__ beta,
+                                     const float* __restrict__ running_mean, const float* __restrict__ running_var, float eps,
+                                     float* __restrict__ scale_out, float* __restrict__ shift_out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float invstd = rsqrtf(running_var[c] + eps);
+    const float g = gamma ? __bfloat162float(gamma[c]) : 1.f, b = beta ? __bfloat162float(beta[c]) : 0.f;
+    scale_out[c] = g * invstd;
+    shift_out[c] = b - running_mean[c] * g * invstd;
+}
+
+template <bool kRelu, bool kRes>
+__global__ void __launch_bounds__(kBnMaxThreads) bn_apply_kernel(const bf16* __restrict__ x, const bf16* __restrict__ res,
+                                                                 const float* __restrict__ scale, const float* __restrict__ shift,
+                                                                 bf16* __restrict__ y, size_t nvec, int vec_cols) {
+    const int vc = (int)(((size_t)blockIdx.x * blockDim.x + threadIdx.x) % vec_cols);
+    float sc[8], sf[8];
+    *reinterpret_cast<float4*>(&sc[0]) = *reinterpret_cast<const float4*>(scale + vc * 8);
+    *reinterpret_cast<float4*>(&sc[4]) = *reinterpret_cast<const float4*>(scale + vc * 8 + 4);
+    *reinterpret_cast<float4*>(&sf[0]) = *reinterpret_cast<const float4*>(shift + vc * 8);
+    *reinterpret_cast<float4*>(&sf[4]) = *reinterpret_cast<const float4*>(shift + vc * 8 + 4);
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t v0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v0 < nvec; v0 += stride * kUnroll) {
+        uint4 u[kUnroll], r[kUnroll];
+#pragma unroll
+        for (int k = 0; k < kUnroll; ++k)
+            if (v0 + k * stride < nvec) {
+                u[k] = ld_stream_v4(x + (v0 + k * stride) * 8);
+                if (kRes) r[k] = ld_stream_v4(res + (v0 + k * stride) * 8);
+            }
+#pragma unroll
+        for (int k = 0; k < kUnroll; ++k)
+            if (v0 + k * stride < nvec) {
+                float f[8];
+                bf16x8_to_float(u[k], f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] = f[j] * sc[j] + sf[j];
+                if (kRes) {
+                    float g[8];
+                    bf16x8_to_float(r[k], g);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) f[j] += g[j];
+                }
+                if (kRelu) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+                }
+                st_global_v4(y + (v0 + k * stride) * 8, float_to_bf16x8(f));
+            }
+    }
+}
+
+// backward pass 1: g = dy * (y > 0); partial sum(g), sum(g * (x - mean)); optionally write g
+template <bool kRelu, bool kWriteG>
+__global__ void __launch_bounds__(kBnMaxThreads) bn_bwd_reduce_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y,
+                                                                      const bf16* __restrict__ x, const float* __restrict__ mean,
+                                                                      bf16* __restrict__ g_out, size_t nvec, int vec_cols, int C,
+                                                                      float* __restrict__ partials) {
+    extern __shared__ float sh[];
+    const int vc = (int)(((size_t)blockIdx.x * blockDim.x + threadIdx.x) % vec_cols);
+    float mu[8], s[8], q[8];
+    *reinterpret_cast<float4*>(&mu[0]) = *reinterpret_cast<const float4*>(mean + vc * 8);
+    *reinterpret_cast<float4*>(&mu[4]) = *reinterpret_cast<const float4*>(mean + vc * 8 + 4);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t v0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v0 < nvec; v0 += stride * kUnroll) {
+        uint4 ud[kUnroll], uy[kUnroll], ux[kUnroll];
+#pragma unroll
+        for (int k = 0; k < kUnroll; ++k)
+            if (v0 + k * stride < nvec) {
+                ud[k] = ld_stream_v4(dy + (v0 + k * stride) * 8);
+                if (kRelu) uy[k] = ld_stream_v4(y + (v0 + k * stride) * 8);
+                ux[k] = ld_stream_v4(x + (v0 + k * stride) * 8);
+            }
+#pragma unroll
+        for (int k = 0; k < kUnroll; ++k)
+            if (v0 + k * stride < nvec) {
+                float d[8], xx[8];
+                bf16x8_to_float(ud[k], d);
+                bf16x8_to_float(ux[k], xx);
+                if (kRelu) {
+                    float yy[8];
+                    bf16x8_to_float(uy[k], yy);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) d[j] = yy[j] > 0.f ? d[j] : 0.f;
+                }
+                if (kWriteG) st_global_v4(g_out + (v0 + k * stride) * 8, float_to_bf16x8(d));
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    s[j] += d[j];
+                    q[j] += d[j] * (xx[j] - mu[j]);
+                }
+            }
+    }
+    fold_to_partials(s, q, vec_cols, C, partials + (size_t)blockIdx.x * 2 * C, sh);
+}
+
+// dgamma, dbeta and the coefficients of pass 2:  dx = a * (g - b - (x - mean) * c)
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partials, int nblocks, long long M, int C,
+                                       const bf16* __restrict__ gamma, const float* __restrict__ invstd, void* __restrict__ dgamma,
+                                       void* __restrict__ dbeta, int grad_dtype, float* __restrict__ coef /*[3][C]*/) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    float sg = 0.f, sgx = 0.f;
+    for (int b = 0; b < nblocks; ++b) {
+        sg += partials[(size_t)b * 2 * C + c];
+        sgx += partials[(size_t)b * 2 * C + C + c];
+    }
+    const float is = invstd[c];
+    const float g = gamma ? __bfloat162float(gamma[c]) : 1.f;
+    const float dgam = sgx * is, dbet = sg;
+    if (dgamma) {
+        if (grad_dtype == DDL_F32) ((float*)dgamma)[c] = dgam; else ((bf16*)dgamma)[c] = __float2bfloat16(dgam);
+    }
+    if (dbeta) {
+        if (grad_dtype == DDL_F32) ((float*)dbeta)[c] = dbet; else ((bf16*)dbeta)[c] = __float2bfloat16(dbet);
+    }
+    const float inv_m = 1.f / (float)M;
+    coef[c] = g * is;
+    coef[C + c] = sg * inv_m;
+    coef[2 * C + c] = sgx * inv_m * is * is;
+}
+
+// backward pass 2.  kFromG: g was materialised by pass 1 (residual blocks); else recompute
+// the ReLU mask from y.
+template <bool kRelu, bool kFromG>
+__global__ void __launch_bounds__(kBnMaxThreads) bn_bwd_apply_kernel(const bf16* __restrict__ dy_or_g, const bf16* __restrict__ y,
+                                                                     const bf16* __restrict__ x, const float* __restrict__ mean,
+                                                                     const float* __restrict__ coef, bf16* __restrict__ dx, size_t nvec,
+                                                                     int vec_cols, int C) {
+    const int vc = (int)(((size_t)blockIdx.x * blockDim.x + threadIdx.x) % vec_cols);
+    float mu[8], a[8], b[8], cc[8];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        *reinterpret_cast<float4*>(&mu[4 * h]) = *reinterpret_cast<const float4*>(mean + vc * 8 + 4 * h);
+        *reinterpret_cast<float4*>(&a[4 * h]) = *reinterpret_cast<const float4*>(coef + vc * 8 + 4 * h);
+        *reinterpret_cast<float4*>(&b[4 * h]) = *reinterpret_cast<const float4*>(coef + C + vc * 8 + 4 * h);
+        *reinterpret_cast<float4*>(&cc[4 * h]) = *reinterpret_cast<const float4*>(coef + 2 * C + vc * 8 + 4 * h);
+    }
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t v0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v0 < nvec; v0 += stride * kUnroll) {
+        uint4 ud[kUnroll], uy[kUnroll], ux[kUnroll];
+#pragma unroll
+        for (int k = 0; k < kUnroll; ++k)
+            if (v0 + k * stride < nvec) {
+                ud[k] = ld_stream_v4(dy_or_g + (v0 + k * stride) * 8);
+                if (kRelu && !kFromG) uy[k] = ld_stream_v4(y + (v0 + k * stride) * 8);
+                ux[k] = ld_stream_v4(x + (v0 + k * stride) * 8);
+            }
+#pragma unroll
+        for (int k = 0; k < kUnroll; ++k)
+            if (v0 + k * stride < nvec) {
+                float d[8], xx[8], o[8];
+                bf16x8_to_float(ud[k], d);
+                bf16x8_to_float(ux[k], xx);
+                if (kRelu && !kFromG) {
+                    float yy[8];
+                    bf16x8_to_float(uy[k], yy);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) d[j] = yy[j] > 0.f ? d[j] : 0.f;
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] = a[j] * (d[j] - b[j] - (xx[j] - mu[j]) * cc[j]);
+                st_global_v4(dx + (v0 + k * stride) * 8, float_to_bf16x8(o));
+            }
+    }
+}
+
+size_t smem_bytes(const BnGeom& g) { return (size_t)g.threads * 17 * sizeof(float); }
+
+}  // namespace
+
+// scratch layout: [grid][2][C] partials, then [3][C] coefficients
+DDL_API size_t ddl_bn_scratch_bytes(long long M, int C) {
+    BnGeom g;
+    if (make_geom(M, C, &g)) return 0;
+    return ((size_t)g.grid * 2 * C + 3 * (size_t)C) * sizeof(float);
+}
+
+DDL_API int ddl_bn_apply(const void* x, const void* residual, const float* scale, const float* shift, void* y, long long M, int C,
+                         int relu, void* stream_) {
+    BnGeom g;
+    if (int e = make_geom(M, C, &g)) return e;
+    cudaStream_t s = (cudaStream_t)stream_;
+    const bf16 *xp = (const bf16*)x, *rp = (const bf16*)residual;
+    bf16* yp = (bf16*)y;
+    if (relu && rp) bn_apply_kernel<true, true><<<g.grid, g.threads, 0, s>>>(xp, rp, scale, shift, yp, g.nvec, g.vec_cols);
+    else if (relu) bn_apply_kernel<true, false><<<g.grid, g.threads, 0, s>>>(xp, rp, scale, shift, yp, g.nvec, g.vec_cols);
+    else if (rp) bn_apply_kernel<false, true><<<g.grid, g.threads, 0, s>>>(xp, rp, scale, shift, yp, g.nvec, g.vec_cols);
+    else bn_apply_kernel<false, false><<<g.grid, g.threads, 0, s>>>(xp, rp, scale, shift, yp, g.nvec, g.vec_cols);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+DDL_API int ddl_bn_act_fwd_train(const void* x, const void* residual, const void* gamma, const void* beta, float* running_mean,
+                                 float* running_var, void* y, float* mean, float* invstd, float* scale, float* shift, void* scratch,
+                                 size_t scratch_bytes, long long M, int C, float eps, float momentum, int relu, void* stream_) {
+    BnGeom g;
+    if (int e = make_geom(M, C, &g)) return e;
+    DDL_REQUIRE(x && y && mean && invstd && scale && shift && scratch, "bn fwd: null pointer");
+    DDL_REQUIRE(scratch_bytes >= ddl_bn_scratch_bytes(M, C), "bn fwd: scratch too small");
+    cudaStream_t s = (cudaStream_t)stream_;
+    float* partials = (float*)scratch;
+    bn_stats_kernel<<<g.grid, g.threads, smem_bytes(g), s>>>((const bf16*)x, g.nvec, g.vec_cols, C, partials);
+    DDL_LAUNCH_CHECK();
+    bn_fwd_finalize_kernel<<<ddl_ceil_div(C, 128), 128, 0, s>>>(partials, g.grid, M, C, (const bf16*)gamma, (const bf16*)beta, running_mean,
+                                                               running_var, momentum, eps, mean, invstd, scale, shift);
+    DDL_LAUNCH_CHECK();
+    return ddl_bn_apply(x, residual, scale, shift, y, M, C, relu, stream_);
+}
+
+DDL_API int ddl_bn_act_fwd_eval(const void* x, const void* residual, const void* gamma, const void* beta, const float* running_mean,
+                                const float* running_var, void* y, float* scale, float* shift, long long M, int C, float eps, int relu,
+                                void* stream_) {
+    DDL_REQUIRE(x && y && running_mean && running_var && scale && shift, "bn eval: null pointer");
+    bn_eval_coeff_kernel<<<ddl_ceil_div(C, 128), 128, 0, (cudaStream_t)stream_>>>(C, (const bf16*)gamma, (const bf16*)beta, running_mean,
+                                                                                 running_var, eps, scale, shift);
+    DDL_LAUNCH_CHECK();
+    return ddl_bn_apply(x, residual, scale, shift, y, M, C, relu, stream_);
+}
+
+DDL_API int ddl_bn_act_bwd(const void* dy, const void* y, const void* x, const void* gamma, const float* mean, const float* invstd,
+                           void* dx, void* dres, void* dgamma, void* dbeta, int param_grad_dtype, void* scratch, size_t scratch_bytes,
+                           long long M, int C, int relu, void* stream_) {
+    BnGeom g;
+    if (int e = make_geom(M, C, &g)) return e;
+    DDL_REQUIRE(dy && x && mean && invstd && dx && scratch, "bn bwd: null pointer");
+    DDL_REQUIRE(!relu || y, "bn bwd: relu needs the saved output");
+    DDL_REQUIRE(scratch_bytes >= ddl_bn_scratch_bytes(M, C), "bn bwd: scratch too small");
+    cudaStream_t s = (cudaStream_t)stream_;
+    float* partials = (float*)scratch;
+    float* coef = partials + (size_t)g.grid * 2 * C;
+    const bf16 *dyp = (const bf16*)dy, *yp = (const bf16*)y, *xp = (const bf16*)x;
+    // g must be materialised when it is itself an output (gradient of the residual branch)
+    const bool write_g = dres != nullptr && relu;
+    if (relu && write_g) bn_bwd_reduce_kernel<true, true><<<g.grid, g.threads, smem_bytes(g), s>>>(dyp, yp, xp, mean, (bf16*)dres, g.nvec, g.vec_cols, C, partials);
+    else if (relu) bn_bwd_reduce_kernel<true, false><<<g.grid, g.threads, smem_bytes(g), s>>>(dyp, yp, xp, mean, nullptr, g.nvec, g.vec_cols, C, partials);
+    else bn_bwd_reduce_kernel<false, false><<<g.grid, g.threads, smem_bytes(g), s>>>(dyp, yp, xp, mean, nullptr, g.nvec, g.vec_cols, C, partials);
+    DDL_LAUNCH_CHECK();
+    bn_bwd_finalize_kernel<<<ddl_ceil_div(C, 128), 128, 0, s>>>(partials, g.grid, M, C, (const bf16*)gamma, invstd, dgamma, dbeta,
+                                                               param_grad_dtype, coef);
+    DDL_LAUNCH_CHECK();
+    if (write_g) bn_bwd_apply_kernel<true, true><<<g.grid, g.threads, 0, s>>>((const bf16*)dres, yp, xp, mean, coef, (bf16*)dx, g.nvec, g.vec_cols, C);
+    else if (relu) bn_bwd_apply_kernel<true, false><<<g.grid, g.threads, 0, s>>>(dyp, yp, xp, mean, coef, (bf16*)dx, g.nvec, g.vec_cols, C);
+    else bn_bwd_apply_kernel<false, false><<<g.grid, g.threads, 0, s>>>(dyp, yp, xp, mean, coef, (bf16*)dx, g.nvec, g.vec_cols, C);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}

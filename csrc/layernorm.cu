@@ -1,0 +1,386 @@
+// Fused (dropout +) residual-add + LayerNorm, forward and backward (K10),
+// plus the fused embedding-gather + LayerNorm used at the bottom of BERT (part of K14).
+//
+// bf16 in / bf16 out, fp32 statistics.  One warp owns one row (hidden 768 / 1024 -> 3 / 4
+// 16-byte vectors per lane, the whole row lives in registers, two-pass variance).
+// Backward writes dz and accumulates dgamma / dbeta in registers across all rows a warp
+// visits, then reduces per block into a [blocks, 2, H] fp32 scratch that a second kernel
+// folds in a fixed order (deterministic, no atomics).
+// Dropout masks come from a stateless hash of (seed, element index): nothing is stored and
+// backward regenerates the same mask.  The reference has no such op.
+#include "../include/b200ddl.h"
+#include "common.cuh"
+
+namespace {
+
+constexpr int kWarpsPerBlock = 8;
+constexpr int kLnThreads = kWarpsPerBlock * 32;
+
+struct DropCfg {
+    uint64_t seed;               // per-call-site salt (host value)
+    const uint64_t* seed_dev;    // optional device word mixed in at run time (changes per graph replay)
+    uint32_t thr;                // drop iff byte < thr   (p = thr / 256)
+    float scale;                 // 1 / (1 - thr/256)
+};
+
+__device__ __forceinline__ void resolve_seed(DropCfg& d) {
+    if (d.thr && d.seed_dev) d.seed ^= (*d.seed_dev + 0x632BE59BD9B4E019ull) * 0x9E3779B97F4A7C15ull;
+}
+
+__device__ __forceinline__ void apply_dropout8(float (&f)[8], const DropCfg& d, uint64_t idx8) {
+    const uint32_t keep = keep_mask8(d.seed, idx8, d.thr);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = ((keep >> j) & 1u) ? f[j] * d.scale : 0.f;
+}
+
+// z = dropout(x) + residual ; y = LN(z) * gamma + beta
+template <int VPL>
+__global__ void __launch_bounds__(kLnThreads) add_ln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ residual,
+                                                                const bf16* __restrict__ gamma, const bf16* __restrict__ beta,
+                                                                bf16* __restrict__ z_out, bf16* __restrict__ y,
+                                                                float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                                                                int rows, int H, float eps, DropCfg drop) {
+    resolve_seed(drop);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nv = H >> 3;
+    const float inv_h = 1.f / (float)H;
+    for (long long row = (long long)blockIdx.x * kWarpsPerBlock + warp; row < rows; row += (long long)gridDim.x * kWarpsPerBlock) {
+        float v[VPL][8];
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < VPL; ++k) {
+            const int c = lane + 32 * k;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[k][j] = 0.f;
+            if (c < nv) {
+                const size_t off = (size_t)row * H + c * 8;
+                bf16x8_to_float(ld_stream_v4(x + off), v[k]);
+                if (drop.thr) apply_dropout8(v[k], drop, ((size_t)row * nv + c));
+                if (residual) {
+                    float r[8];
+                    bf16x8_to_float(ld_stream_v4(residual + off), r);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) v[k][j] += r[j];
+                }
+                if (z_out) {
+                    // round once so that backward sees exactly what forward normalised
+                    const uint4 q = float_to_bf16x8(v[k]);
+                    st_global_v4(z_out + off, q);
+                    bf16x8_to_float(q, v[k]);
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) s += v[k][j];
+            }
+        }
+        const float mean = warp_sum(s) * inv_h;
+        float q = 0.f;
+#pragma unroll
+        for (int k = 0; k < VPL; ++k) {
+            if (lane + 32 * k < nv) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float d = v[k][j] - mean;
+                    q += d * d;
+                }
+            }
+        }
+        const float rstd = rsqrtf(warp_sum(q) * inv_h + eps);
+        if (lane == 0) {
+            mean_out[row] = mean;
+            rstd_out[row] = rstd;
+        }
+#pragma unroll
+        for (int k = 0; k < VPL; ++k) {
+            const int c = lane + 32 * k;
+            if (c < nv) {
+                float g[8], b[8], o[8];
+                bf16x8_to_float(ld_global_v4(gamma + c * 8), g);
+                bf16x8_to_float(ld_global_v4(beta + c * 8), b);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] = (v[k][j] - mean) * rstd * g[j] + b[j];
+                st_global_v4(y + (size_t)row * H + c * 8, float_to_bf16x8(o));
+            }
+        }
+    }
+}
+
+// dz = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * gamma
+// dx = dz * keep * scale (only when dropout is active; else dx aliases dz on the host side)
+template <int VPL>
+__global__ void __launch_bounds__(kLnThreads) ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z,
+                                                            const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
+                                                            const bf16* __restrict__ gamma, bf16* __restrict__ dz,
+                                                            bf16* __restrict__ dx, float* __restrict__ partials, int rows, int H,
+                                                            DropCfg drop) {
+    resolve_seed(drop);
+    __shared__ float red[kWarpsPerBlock][32 * 8 + 1];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nv = H >> 3;
+    const float inv_h = 1.f / (float)H;
+    float dgam[VPL][8], dbet[VPL][8], gam[VPL][8];
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+        const int c = lane + 32 * k;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dgam[k][j] = dbet[k][j] = gam[k][j] = 0.f;
+        if (c < nv) bf16x8_to_float(ld_global_v4(gamma + c * 8), gam[k]);
+    }
+    for (long long row = (long long)blockIdx.x * kWarpsPerBlock + warp; row < rows; row += (long long)gridDim.x * kWarpsPerBlock) {
+        const float mean = mean_in[row], rstd = rstd_in[row];
+        float g[VPL][8], xh[VPL][8];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < VPL; ++k) {
+            const int c = lane + 32 * k;
+            if (c < nv) {
+                const size_t off = (size_t)row * H + c * 8;
+                float d[8], zz[8];
+                bf16x8_to_float(ld_stream_v4(dy + off), d);
+                bf16x8_to_float(ld_stream_v4(z + off), zz);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    xh[k][j] = (zz[j] - mean) * rstd;
+                    g[k][j] = d[j] * gam[k][j];
+                    s1 += g[k][j];
+                    s2 += g[k][j] * xh[k][j];
+                    dgam[k][j] += d[j] * xh[k][j];
+                    dbet[k][j] += d[j];
+                }
+            }
+        }
+        const float c1 = warp_sum(s1) * inv_h, c2 = warp_sum(s2) * inv_h;
+#pragma unroll
+        for (int k = 0; k < VPL; ++k) {
+            const int c = lane + 32 * k;
+            if (c < nv) {
+                const size_t off = (size_t)row * H + c * 8;
+                float o[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] = rstd * (g[k][j] - c1 - xh[k][j] * c2);
+                st_global_v4(dz + off, float_to_bf16x8(o));
+                if (dx != nullptr && drop.thr) {
+                    apply_dropout8(o, drop, ((size_t)row * nv + c));
+                    st_global_v4(dx + off, float_to_bf16x8(o));
+                }
+            }
+        }
+    }
+    // block reduction of dgamma / dbeta partials: [blocks][2][H]
+    float* out = partials + (size_t)blockIdx.x * 2 * H;
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+#pragma unroll
+        for (int k = 0; k < VPL; ++k) {
+            __syncthreads();
+#pragma unroll
+            for (int j = 0; j < 8; ++j) red[warp][lane * 8 + j] = which == 0 ? dgam[k][j] : dbet[k][j];
+            __syncthreads();
+            // 256 threads fold 8 warps x 256 columns
+            const int col = threadIdx.x;  // 0..255 -> (lane = col/8, j = col%8)
+            float acc = 0.f;
+#pragma unroll
+            for (int w = 0; w < kWarpsPerBlock; ++w) acc += red[w][col];
+            const int c = (col >> 3) + 32 * k;
+            if (c < nv) out[which * H + c * 8 + (col & 7)] = acc;
+        }
+    }
+}
+
+__global__ void ln_bwd_finalize_kernel(const float* __restrict__ partials, int nblocks, int H, bf16* __restrict__ dgamma,
+                                       bf16* __restrict__ dbeta, float* __restrict__ dgamma_f32, float* __restrict__ dbeta_f32) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 2 * H) return;
+    float acc = 0.f;
+    for (int b = 0; b < nblocks; ++b) acc += partials[(size_t)b * 2 * H + i];
+    if (i < H) {
+        if (dgamma) dgamma[i] = __float2bfloat16(acc);
+        if (dgamma_f32) dgamma_f32[i] = acc;
+    } else {
+        if (dbeta) dbeta[i - H] = __float2bfloat16(acc);
+        if (dbeta_f32) dbeta_f32[i - H] = acc;
+    }
+}
+
+// BERT embeddings: y = LN(word[ids] + pos[s] + type[tt]) (+ dropout on the output)
+template <int VPL>
+__global__ void __launch_bounds__(kLnThreads) embed_ln_fwd_kernel(const long long* __restrict__ ids, const long long* __restrict__ tts,
+                                                                  const bf16* __restrict__ word, const bf16* __restrict__ pos,
+                                                                  const bf16* __restrict__ type, const bf16* __restrict__ gamma,
+                                                                  const bf16* __restrict__ beta, bf16* __restrict__ z_out,
+                                                                  bf16* __restrict__ y, float* __restrict__ mean_out,
+                                                                  float* __restrict__ rstd_out, int rows, int S, int H, float eps,
+                                                                  DropCfg drop) {
+    resolve_seed(drop);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nv = H >> 3;
+    const float inv_h = 1.f / (float)H;
+    for (long long row = (long long)blockIdx.x * kWarpsPerBlock + warp; row < rows; row += (long long)gridDim.x * kWarpsPerBlock) {
+        const long long id = ids[row], tt = tts ? tts[row] : 0;
+        const int s = (int)(row % S);
+        float v[VPL][8];
+        float sum = 0.f;
+#pragma unroll
+        for (int k = 0; k < VPL; ++k) {
+            const int c = lane + 32 * k;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[k][j] = 0.f;
+            if (c < nv) {
+                float a[8], b[8], t[8];
+                bf16x8_to_float(ld_global_v4(word + (size_t)id * H + c * 8), a);
+                bf16x8_to_float(ld_global_v4(pos + (size_t)s * H + c * 8), b);
+                bf16x8_to_float(ld_global_v4(type + (size_t)tt * H + c * 8), t);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[k][j] = a[j] + b[j] + t[j];
+                const uint4 q = float_to_bf16x8(v[k]);
+                st_global_v4(z_out + (size_t)row * H + c * 8, q);
+                bf16x8_to_float(q, v[k]);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) sum += v[k][j];
+            }
+        }
+        const float mean = warp_sum(sum) * inv_h;
+        float q = 0.f;
+#pragma unroll
+        for (int k = 0; k < VPL; ++k)
+            if (lane + 32 * k < nv) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float d = v[k][j] - mean;
+                    q += d * d;
+                }
+            }
+        const float rstd = rsqrtf(warp_sum(q) * inv_h + eps);
+        if (lane == 0) {
+            mean_out[row] = mean;
+            rstd_out[row] = rstd;
+        }
+#pragma unroll
+        for (int k = 0; k < VPL; ++k) {
+            const int c = lane + 32 * k;
+            if (c < nv) {
+                float g[8], b[8], o[8];
+                bf16x8_to_float(ld_global_v4(gamma + c * 8), g);
+                bf16x8_to_float(ld_global_v4(beta + c * 8), b);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] = (v[k][j] - mean) * rstd * g[j] + b[j];
+                if (drop.thr) apply_dropout8(o, drop, ((size_t)row * nv + c));
+                st_global_v4(y + (size_t)row * H + c * 8, float_to_bf16x8(o));
+            }
+        }
+    }
+}
+
+// elementwise dropout backward / forward on bf16 (used for the embedding output mask)
+__global__ void dropout_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, size_t n8, DropCfg drop) {
+    resolve_seed(drop);
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+        float f[8];
+        bf16x8_to_float(ld_stream_v4(in + i * 8), f);
+        apply_dropout8(f, drop, i);
+        st_global_v4(out + i * 8, float_to_bf16x8(f));
+    }
+}
+
+DropCfg make_drop(float p, unsigned long long seed, const unsigned long long* seed_dev = nullptr) {
+    DropCfg d;
+    d.seed = seed;
+    d.seed_dev = (const uint64_t*)seed_dev;
+    int thr = (int)(p * 256.f + 0.5f);
+    if (thr < 0) thr = 0;
+    if (thr > 255) thr = 255;
+    d.thr = (uint32_t)thr;
+    d.scale = 1.f / (1.f - (float)thr / 256.f);
+    return d;
+}
+
+int ln_grid(int rows) {
+    int blocks = ddl_ceil_div(rows, kWarpsPerBlock);
+    const int cap = DDL_SM_COUNT * 2;
+    return blocks > cap ? cap : (blocks < 1 ? 1 : blocks);
+}
+
+#define LN_DISPATCH(H, CALL)                                  \
+    do {                                                      \
+        const int _nv = (H) / 8;                              \
+        if (_nv <= 32) { constexpr int VPL = 1; CALL; }       \
+        else if (_nv <= 64) { constexpr int VPL = 2; CALL; }  \
+        else if (_nv <= 96) { constexpr int VPL = 3; CALL; }  \
+        else if (_nv <= 128) { constexpr int VPL = 4; CALL; } \
+        else if (_nv <= 192) { constexpr int VPL = 6; CALL; } \
+        else { constexpr int VPL = 8; CALL; }                 \
+    } while (0)
+
+}  // namespace
+
+DDL_API float ddl_dropout_effective_p(float p) {
+    const DropCfg d = make_drop(p, 0);
+    return (float)d.thr / 256.f;
+}
+
+DDL_API int ddl_add_layernorm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* z_out, void* y,
+                                  float* mean, float* rstd, int rows, int H, float eps, float dropout_p, unsigned long long seed,
+                                  const unsigned long long* seed_dev, void* stream_) {
+    DDL_REQUIRE(H % 8 == 0 && H >= 8 && H <= 2048, "layernorm: hidden size %d must be a multiple of 8 and <= 2048", H);
+    DDL_REQUIRE(x && gamma && beta && y && mean && rstd, "layernorm fwd: null pointer");
+    if (rows == 0) return 0;
+    const DropCfg d = make_drop(dropout_p, seed, seed_dev);
+    const int grid = ln_grid(rows);
+    cudaStream_t s = (cudaStream_t)stream_;
+    LN_DISPATCH(H, (add_ln_fwd_kernel<VPL><<<grid, kLnThreads, 0, s>>>((const bf16*)x, (const bf16*)residual, (const bf16*)gamma,
+                                                                      (const bf16*)beta, (bf16*)z_out, (bf16*)y, mean, rstd, rows, H, eps, d)));
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+DDL_API size_t ddl_layernorm_bwd_scratch_bytes(int rows, int H) { return (size_t)ln_grid(rows) * 2 * H * sizeof(float); }
+
+DDL_API int ddl_layernorm_bwd(const void* dy, const void* z, const float* mean, const float* rstd, const void* gamma, void* dz,
+                              void* dx, void* dgamma, void* dbeta, int param_grad_dtype, void* scratch, size_t scratch_bytes, int rows,
+                              int H, float dropout_p, unsigned long long seed, const unsigned long long* seed_dev, void* stream_) {
+    DDL_REQUIRE(H % 8 == 0 && H >= 8 && H <= 2048, "layernorm: hidden size %d must be a multiple of 8 and <= 2048", H);
+    DDL_REQUIRE(dy && z && mean && rstd && gamma && dz && scratch, "layernorm bwd: null pointer");
+    DDL_REQUIRE(scratch_bytes >= ddl_layernorm_bwd_scratch_bytes(rows, H), "layernorm bwd: scratch too small (%zu < %zu)", scratch_bytes,
+                ddl_layernorm_bwd_scratch_bytes(rows, H));
+    if (rows == 0) return 0;
+    const DropCfg d = make_drop(dropout_p, seed, seed_dev);
+    const int grid = ln_grid(rows);
+    cudaStream_t s = (cudaStream_t)stream_;
+    LN_DISPATCH(H, (ln_bwd_kernel<VPL><<<grid, kLnThreads, 0, s>>>((const bf16*)dy, (const bf16*)z, mean, rstd, (const bf16*)gamma, (bf16*)dz,
+                                                                  (bf16*)dx, (float*)scratch, rows, H, d)));
+    DDL_LAUNCH_CHECK();
+    const bool f32 = param_grad_dtype == DDL_F32;
+    ln_bwd_finalize_kernel<<<ddl_ceil_div(2 * H, 256), 256, 0, s>>>((const float*)scratch, grid, H, f32 ? nullptr : (bf16*)dgamma,
+                                                                    f32 ? nullptr : (bf16*)dbeta, f32 ? (float*)dgamma : nullptr,
+                                                                    f32 ? (float*)dbeta : nullptr);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+DDL_API int ddl_embed_layernorm_fwd(const long long* ids, const long long* token_types, const void* word, const void* pos,
+                                    const void* type, const void* gamma, const void* beta, void* z_out, void* y, float* mean,
+                                    float* rstd, int rows, int S, int H, float eps, float dropout_p, unsigned long long seed,
+                                    const unsigned long long* seed_dev, void* stream_) {
+    DDL_REQUIRE(H % 8 == 0 && H >= 8 && H <= 2048, "embed_layernorm: hidden size %d must be a multiple of 8 and <= 2048", H);
+    DDL_REQUIRE(ids && word && pos && type && gamma && beta && z_out && y && mean && rstd, "embed_layernorm: null pointer");
+    if (rows == 0) return 0;
+    const DropCfg d = make_drop(dropout_p, seed, seed_dev);
+    const int grid = ln_grid(rows);
+    cudaStream_t s = (cudaStream_t)stream_;
+    LN_DISPATCH(H, (embed_ln_fwd_kernel<VPL><<<grid, kLnThreads, 0, s>>>(ids, token_types, (const bf16*)word, (const bf16*)pos, (const bf16*)type,
+                                                                        (const bf16*)gamma, (const bf16*)beta, (bf16*)z_out, (bf16*)y, mean,
+                                                                        rstd, rows, S, H, eps, d)));
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+DDL_API int ddl_dropout(const void* in, void* out, size_t numel, float dropout_p, unsigned long long seed,
+                        const unsigned long long* seed_dev, void* stream_) {
+    DDL_REQUIRE(numel % 8 == 0, "ddl_dropout: numel must be a multiple of 8");
+    if (numel == 0) return 0;
+    const DropCfg d = make_drop(dropout_p, seed, seed_dev);
+    int blocks = ddl_ceil_div((long long)(numel / 8), 256);
+    if (blocks > DDL_SM_COUNT * 8) blocks = DDL_SM_COUNT * 8;
+    dropout_kernel<<<blocks, 256, 0, (cudaStream_t)stream_>>>((const bf16*)in, (bf16*)out, numel / 8, d);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}

@@ -1,0 +1,194 @@
+"""Training engine: the public "train this model data-parallel" API.
+
+``Trainer`` wires together the pieces a ``train_fn`` would otherwise assemble by hand:
+model -> bf16 compute copy with fp32 masters -> :class:`DistributedDataParallel` (flat
+symmetric-memory buckets, peer-memory all-reduce overlapped with backward) ->
+:class:`FusedAdamW` -> optional whole-step CUDA graph (forward, backward, bucket
+reductions on the comm stream, optimizer; one ``cudaGraphLaunch`` per step instead of
+thousands of kernel launches).  Inputs arrive from pinned host memory through a
+double-buffered copy stream; the loss of every step is copied back to pinned host memory.
+
+On CPU (gloo plumbing config, BASELINE.json:7) the same class runs eagerly in fp32.
+The reference has no training loop; requirements are BASELINE.json:5,7-10.
+"""
+from __future__ import annotations
+
+from typing import Any, Callable, Dict, Iterable, List, Optional
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .optim import FusedAdamW
+from .parallel import process_group as pg
+from .parallel.ddp import DistributedDataParallel
+
+
+def _default_loss(model: nn.Module, batch, fused: bool) -> torch.Tensor:
+    if isinstance(batch, dict):
+        loss, _ = model(**batch)
+        return loss
+    x, y = batch
+    logits = model(x)
+    if fused and logits.is_cuda:
+        from .ops import functional as OF
+
+        return OF.cross_entropy(logits, y)
+    return F.cross_entropy(logits.float(), y)
+
+
+class Trainer:
+    """One object per rank.
+
+    Parameters
+    ----------
+    model:        an ``nn.Module`` on CPU (moved/cast here).  Models from :mod:`.models`
+                  switch to their fused implementation when ``impl="fused"``.
+    lr, betas, eps, weight_decay: AdamW hyper-parameters.
+    dtype:        compute dtype on GPU (bf16; masters and moments stay fp32).
+    use_graph:    capture the whole step in a CUDA graph after ``graph_warmup`` eager steps.
+    comm:         "auto" | "p2p" | "torch" - gradient path (see :func:`..parallel.comm.default_comm`).
+    overlap_optimizer: run each bucket's AdamW on the comm stream right after its reduction.
+    """
+
+    def __init__(self, model: nn.Module, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.01,
+                 device: Optional[torch.device] = None, dtype: torch.dtype = torch.bfloat16, impl: str = "fused",
+                 use_graph: bool = True, graph_warmup: int = 3, comm: str = "auto", bucket_cap_mb: float = 25.0,
+                 overlap_optimizer: bool = True, loss_fn: Optional[Callable[[nn.Module, Any], torch.Tensor]] = None,
+                 broadcast_buffers: bool = False, channels_last: bool = True):
+        self.device = device or pg.device()
+        self.cuda = self.device.type == "cuda"
+        self.fused = impl == "fused" and self.cuda
+        if hasattr(model, "set_impl"):
+            model.set_impl("fused" if self.fused else "torch")
+        if self.cuda:
+            model = model.to(self.device, dtype)
+            if channels_last and any(isinstance(m, nn.Conv2d) for m in model.modules()):
+                model = model.to(memory_format=torch.channels_last)
+                for m in model.modules():  # running statistics stay fp32
+                    if isinstance(m, nn.modules.batchnorm._BatchNorm) and m.running_mean is not None:
+                        m.running_mean.data = m.running_mean.data.float()
+                        m.running_var.data = m.running_var.data.float()
+        else:
+            model = model.to(self.device)
+        self.model = model
+        self.ddp = DistributedDataParallel(model, bucket_cap_mb=bucket_cap_mb, comm=comm, flatten_params=True,
+                                           broadcast_buffers=broadcast_buffers)
+        self.opt = FusedAdamW(self.ddp, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay,
+                              overlap=overlap_optimizer and self.cuda)
+        self.loss_fn = loss_fn
+        self.use_graph = use_graph and self.cuda
+        self.graph_warmup = graph_warmup
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.static_batch = None
+        self.static_loss: Optional[torch.Tensor] = None
+        self.steps_done = 0
+        self._copy_stream = torch.cuda.Stream(self.device) if self.cuda else None
+        self._staging: List[Any] = []
+        self._stage_events: List[torch.cuda.Event] = []
+        self._loss_ring: Optional[torch.Tensor] = None
+
+    # ---- one optimisation step on device-resident inputs ----------------------------------
+    def _step_impl(self, batch) -> torch.Tensor:
+        self.ddp.zero_grad()
+        loss = self.loss_fn(self.ddp, batch) if self.loss_fn else _default_loss(self.ddp, batch, self.fused)
+        loss.backward()
+        self.opt.step()
+        if self.fused:
+            from .ops import functional as OF
+
+            OF.advance_seed(self.device)
+        return loss.detach()
+
+    def _alloc_like(self, batch):
+        if isinstance(batch, dict):
+            return {k: torch.empty_like(v, device=self.device) for k, v in batch.items()}
+        return tuple(torch.empty_like(v, device=self.device) for v in batch)
+
+    @staticmethod
+    def _copy_into(dst, src, non_blocking=True):
+        if isinstance(src, dict):
+            for k, v in src.items():
+                dst[k].copy_(v, non_blocking=non_blocking)
+        else:
+            for d, s in zip(dst, src):
+                d.copy_(s, non_blocking=non_blocking)
+
+    def _ensure_static(self, batch) -> None:
+        if self.static_batch is None:
+            self.static_batch = self._alloc_like(batch)
+            self._staging = [self._alloc_like(batch) for _ in range(2)]
+            self._stage_events = [torch.cuda.Event() for _ in range(2)]
+            self._consumed = [torch.cuda.Event() for _ in range(2)]
+            self._loss_ring = torch.zeros(1024, dtype=torch.float32).pin_memory()
+
+    def _capture(self) -> None:
+        s = torch.cuda.Stream(self.device)
+        s.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(s):
+            for _ in range(self.graph_warmup):
+                self._step_impl(self.static_batch)
+        torch.cuda.current_stream(self.device).wait_stream(s)
+        torch.cuda.synchronize(self.device)
+        pg.barrier()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.static_loss = self._step_impl(self.static_batch)
+        torch.cuda.synchronize(self.device)
+        pg.barrier()
+
+    # ---- public API ------------------------------------------------------------------------
+    def step(self, batch) -> torch.Tensor:
+        """One step.  ``batch`` holds host (ideally pinned) or device tensors.  Returns the
+        loss as a device scalar (no host synchronisation here)."""
+        if not self.cuda:
+            self.steps_done += 1
+            return self._step_impl(batch)
+        self._ensure_static(batch)
+        slot = self.steps_done % 2
+        cur = torch.cuda.current_stream(self.device)
+        # host -> staging on the copy stream, staging -> static inputs on the compute stream
+        if self.steps_done >= 2:  # this staging slot was last read by step k-2's D2D copy
+            self._copy_stream.wait_event(self._consumed[slot])
+        with torch.cuda.stream(self._copy_stream):
+            self._copy_into(self._staging[slot], batch)
+            self._stage_events[slot].record(self._copy_stream)
+        cur.wait_event(self._stage_events[slot])
+        self._copy_into(self.static_batch, self._staging[slot])
+        self._consumed[slot].record(cur)
+        if self.use_graph:
+            if self.graph is None:
+                self._capture()
+            self.graph.replay()
+            loss = self.static_loss
+        else:
+            loss = self._step_impl(self.static_batch)
+        self._loss_ring[self.steps_done % 1024].copy_(loss, non_blocking=True)
+        self.steps_done += 1
+        return loss
+
+    def prefetch_hint(self) -> None:
+        """(reserved) hook for loaders that want to start the next copy early."""
+
+    def loss_history(self, last: int = 1) -> List[float]:
+        """Host values of the last ``last`` losses (synchronises)."""
+        if not self.cuda:
+            return []
+        torch.cuda.synchronize(self.device)
+        n = min(last, self.steps_done, 1024)
+        return [float(self._loss_ring[(self.steps_done - n + i) % 1024]) for i in range(n)]
+
+    def fit(self, loader: Iterable, steps: Optional[int] = None, log_every: int = 0, logger=None) -> Dict[str, Any]:
+        losses = []
+        for i, batch in enumerate(loader):
+            if steps is not None and i >= steps:
+                break
+            loss = self.step(batch)
+            if not self.cuda:
+                losses.append(float(loss))
+            if log_every and (i + 1) % log_every == 0 and logger is not None:
+                val = self.loss_history(1)[0] if self.cuda else losses[-1]
+                logger.log(step=i + 1, loss=val)
+        if self.cuda:
+            losses = self.loss_history(min(self.steps_done, 1024))
+        return {"steps": self.steps_done, "losses": losses}

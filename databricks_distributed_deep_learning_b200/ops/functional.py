@@ -1,0 +1,294 @@
+"""Autograd-aware wrappers around the native sm_100a kernels (target layer T5).
+
+Every function here launches hand-written kernels from ``libb200ddl.so`` through the C ABI
+(``include/b200ddl.h``).  There is no eager fallback on CUDA tensors: if the library is
+missing the call raises.  The plain-PyTorch expression of each op (used as the fp32 oracle
+in ``tests/``) is given in each docstring.
+"""
+from __future__ import annotations
+
+import itertools
+from typing import Optional
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+from torch.autograd.function import once_differentiable
+
+from . import _lib as L
+
+# ----------------------------------------------------------------------------- RNG state
+_salt_counter = itertools.count(1)
+_seed_words = {}
+
+
+def seed_word(device: torch.device) -> torch.Tensor:
+    """Device-resident uint64 mixed into every dropout mask; bump it once per step (works
+    under CUDA-graph replay, where host-side seeds would be frozen)."""
+    key = (device.type, device.index)
+    if key not in _seed_words:
+        _seed_words[key] = torch.zeros(1, dtype=torch.int64, device=device)
+    return _seed_words[key]
+
+
+def advance_seed(device: torch.device) -> None:
+    seed_word(device).add_(1)
+
+
+def manual_seed(seed: int, device: torch.device) -> None:
+    seed_word(device).fill_(int(seed))
+
+
+def _next_salt() -> int:
+    return (next(_salt_counter) * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
+
+
+def _scratch(nbytes: int, device) -> torch.Tensor:
+    return torch.empty(max(nbytes, 16), dtype=torch.uint8, device=device)
+
+
+def _req_bf16(*ts):
+    for t in ts:
+        if t is not None and t.dtype != torch.bfloat16:
+            raise L.DdlError(f"native op needs bfloat16 tensors, got {t.dtype}")
+
+
+# ----------------------------------------------------------------------------- cross entropy
+class _CrossEntropy(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, labels, ignore_index):
+        logits = logits.contiguous()
+        B, Cn = logits.shape
+        row = torch.empty(B, dtype=torch.float32, device=logits.device)
+        loss = torch.empty((), dtype=torch.float32, device=logits.device)
+        dlogits = torch.empty_like(logits)
+        L.call("ddl_cross_entropy", logits.data_ptr(), L.dtype_code(logits.dtype), labels.data_ptr(), row.data_ptr(),
+               loss.data_ptr(), dlogits.data_ptr(), B, Cn, 1.0 / B, int(ignore_index), L.stream_ptr(logits.device))
+        ctx.save_for_backward(dlogits)
+        return loss
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, grad_out):
+        (dlogits,) = ctx.saved_tensors
+        return dlogits * grad_out.to(dlogits.dtype), None, None
+
+
+def cross_entropy(logits: torch.Tensor, labels: torch.Tensor, ignore_index: int = -100) -> torch.Tensor:
+    """``F.cross_entropy(logits.float(), labels)`` (mean).  Loss and d(logits) come out of one
+    pass over the logits (K12).  Rows equal to ``ignore_index`` contribute 0 and the mean is
+    over all rows."""
+    return _CrossEntropy.apply(logits, labels.contiguous(), ignore_index)
+
+
+# ----------------------------------------------------------------------------- layer norm
+class _AddLayerNorm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, residual, gamma, beta, eps, p):
+        _req_bf16(x, residual, gamma, beta)
+        x = x.contiguous()
+        rows, H = x.shape
+        dev = x.device
+        need_z = residual is not None or p > 0
+        z = torch.empty_like(x) if need_z else None
+        y = torch.empty_like(x)
+        mean = torch.empty(rows, dtype=torch.float32, device=dev)
+        rstd = torch.empty(rows, dtype=torch.float32, device=dev)
+        salt = _next_salt() if p > 0 else 0
+        sw = seed_word(dev) if p > 0 else None
+        L.call("ddl_add_layernorm_fwd", x.data_ptr(), L.ptr(None if residual is None else residual.contiguous()), gamma.data_ptr(),
+               beta.data_ptr(), L.ptr(z), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(), rows, H, float(eps), float(p), salt,
+               L.ptr(sw), L.stream_ptr(dev))
+        ctx.save_for_backward(z if need_z else x, mean, rstd, gamma)
+        ctx.p, ctx.salt, ctx.has_res = p, salt, residual is not None
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        z, mean, rstd, gamma = ctx.saved_tensors
+        rows, H = z.shape
+        dev = z.device
+        dy = dy.contiguous()
+        dz = torch.empty_like(z)
+        dx = torch.empty_like(z) if ctx.p > 0 else None
+        dgamma, dbeta = torch.empty_like(gamma), torch.empty_like(gamma)
+        nbytes = L.lib().ddl_layernorm_bwd_scratch_bytes(rows, H)
+        scratch = _scratch(nbytes, dev)
+        sw = seed_word(dev) if ctx.p > 0 else None
+        L.call("ddl_layernorm_bwd", dy.data_ptr(), z.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(), dz.data_ptr(),
+               L.ptr(dx), dgamma.data_ptr(), dbeta.data_ptr(), L.DDL_BF16, scratch.data_ptr(), scratch.numel(), rows, H,
+               float(ctx.p), ctx.salt, L.ptr(sw), L.stream_ptr(dev))
+        return (dx if dx is not None else dz), (dz if ctx.has_res else None), dgamma, dbeta, None, None
+
+
+def dropout_add_layernorm(x, residual, gamma, beta, eps: float = 1e-12, p: float = 0.0) -> torch.Tensor:
+    """``F.layer_norm(F.dropout(x, p) + residual, (H,), gamma, beta, eps)`` on [rows, H] bf16 (K10)."""
+    return _AddLayerNorm.apply(x, residual, gamma, beta, eps, p)
+
+
+def layernorm(x, gamma, beta, eps: float = 1e-12) -> torch.Tensor:
+    return _AddLayerNorm.apply(x, None, gamma, beta, eps, 0.0)
+
+
+class _EmbedLayerNorm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ids, tts, word, pos, typ, gamma, beta, eps, p):
+        _req_bf16(word, pos, typ, gamma, beta)
+        B, S = ids.shape
+        H = word.shape[1]
+        dev = word.device
+        rows = B * S
+        z = torch.empty(rows, H, dtype=torch.bfloat16, device=dev)
+        y = torch.empty_like(z)
+        mean = torch.empty(rows, dtype=torch.float32, device=dev)
+        rstd = torch.empty(rows, dtype=torch.float32, device=dev)
+        salt = _next_salt() if p > 0 else 0
+        sw = seed_word(dev) if p > 0 else None
+        ids, tts = ids.contiguous(), tts.contiguous()
+        L.call("ddl_embed_layernorm_fwd", ids.data_ptr(), tts.data_ptr(), word.data_ptr(), pos.data_ptr(), typ.data_ptr(),
+               gamma.data_ptr(), beta.data_ptr(), z.data_ptr(), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(), rows, S, H, float(eps),
+               float(p), salt, L.ptr(sw), L.stream_ptr(dev))
+        ctx.save_for_backward(ids, tts, z, mean, rstd, gamma)
+        ctx.p, ctx.salt, ctx.sizes = p, salt, (word.shape[0], pos.shape[0], typ.shape[0], B, S)
+        return y.view(B, S, H)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        ids, tts, z, mean, rstd, gamma = ctx.saved_tensors
+        V, P, T, B, S = ctx.sizes
+        rows, H = z.shape
+        dev = z.device
+        dy = dy.contiguous().view(rows, H)
+        if ctx.p > 0:
+            masked = torch.empty_like(dy)
+            L.call("ddl_dropout", dy.data_ptr(), masked.data_ptr(), dy.numel(), float(ctx.p), ctx.salt, seed_word(dev).data_ptr(),
+                   L.stream_ptr(dev))
+            dy = masked
+        dz = torch.empty_like(z)
+        dgamma, dbeta = torch.empty_like(gamma), torch.empty_like(gamma)
+        scratch = _scratch(L.lib().ddl_layernorm_bwd_scratch_bytes(rows, H), dev)
+        L.call("ddl_layernorm_bwd", dy.data_ptr(), z.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(), dz.data_ptr(),
+               None, dgamma.data_ptr(), dbeta.data_ptr(), L.DDL_BF16, scratch.data_ptr(), scratch.numel(), rows, H, 0.0, 0, None,
+               L.stream_ptr(dev))
+        # scatter-adds into the three tables: fp32 accumulation, then one cast (small next to the GEMMs)
+        dzf = dz.float()
+        dword = torch.zeros(V, H, dtype=torch.float32, device=dev).index_add_(0, ids.view(-1), dzf)
+        dpos = dzf.view(B, S, H).sum(0)
+        dpos_full = torch.zeros(P, H, dtype=torch.float32, device=dev)
+        dpos_full[:S] = dpos
+        dtype_ = torch.zeros(T, H, dtype=torch.float32, device=dev).index_add_(0, tts.view(-1), dzf)
+        bf = torch.bfloat16
+        return None, None, dword.to(bf), dpos_full.to(bf), dtype_.to(bf), dgamma, dbeta, None, None
+
+
+def embed_layernorm(ids, token_type_ids, word, pos, typ, gamma, beta, eps: float, p: float) -> torch.Tensor:
+    """``dropout(LN(word[ids] + pos[arange(S)] + typ[tt]))`` -> [B, S, H] bf16."""
+    return _EmbedLayerNorm.apply(ids, token_type_ids, word, pos, typ, gamma, beta, eps, p)
+
+
+# ----------------------------------------------------------------------------- batch norm
+class _BnAct(torch.autograd.Function):
+    """x: NCHW-shaped tensor in channels_last memory (i.e. an NHWC matrix [M, C])."""
+
+    @staticmethod
+    def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu):
+        _req_bf16(x, residual, gamma, beta)
+        N, Cc, H, W = x.shape
+        if not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        if residual is not None and not residual.is_contiguous(memory_format=torch.channels_last):
+            residual = residual.contiguous(memory_format=torch.channels_last)
+        M = N * H * W
+        dev = x.device
+        y = torch.empty_like(x, memory_format=torch.channels_last)
+        scale = torch.empty(Cc, dtype=torch.float32, device=dev)
+        shift = torch.empty(Cc, dtype=torch.float32, device=dev)
+        st = L.stream_ptr(dev)
+        if training:
+            mean = torch.empty(Cc, dtype=torch.float32, device=dev)
+            invstd = torch.empty(Cc, dtype=torch.float32, device=dev)
+            scratch = _scratch(L.lib().ddl_bn_scratch_bytes(M, Cc), dev)
+            L.call("ddl_bn_act_fwd_train", x.data_ptr(), L.ptr(residual), gamma.data_ptr(), beta.data_ptr(), L.ptr(running_mean),
+                   L.ptr(running_var), y.data_ptr(), mean.data_ptr(), invstd.data_ptr(), scale.data_ptr(), shift.data_ptr(),
+                   scratch.data_ptr(), scratch.numel(), M, Cc, float(eps), float(momentum), int(relu), st)
+            ctx.save_for_backward(x, y if relu else None, gamma, mean, invstd)
+        else:
+            L.call("ddl_bn_act_fwd_eval", x.data_ptr(), L.ptr(residual), gamma.data_ptr(), beta.data_ptr(), running_mean.data_ptr(),
+                   running_var.data_ptr(), y.data_ptr(), scale.data_ptr(), shift.data_ptr(), M, Cc, float(eps), int(relu), st)
+            ctx.save_for_backward(x, y if relu else None, gamma, scale, None)
+        ctx.training, ctx.relu, ctx.has_res, ctx.M = training, relu, residual is not None, M
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        x, y, gamma, mean, invstd = ctx.saved_tensors
+        if not ctx.training:
+            raise L.DdlError("backward through eval-mode fused BatchNorm is not supported; use impl='torch' for frozen BN")
+        Cc = x.shape[1]
+        dev = x.device
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dx = torch.empty_like(x, memory_format=torch.channels_last)
+        dres = None
+        if ctx.has_res:
+            dres = torch.empty_like(x, memory_format=torch.channels_last) if ctx.relu else dy
+        dgamma, dbeta = torch.empty_like(gamma), torch.empty_like(gamma)
+        scratch = _scratch(L.lib().ddl_bn_scratch_bytes(ctx.M, Cc), dev)
+        L.call("ddl_bn_act_bwd", dy.data_ptr(), L.ptr(y), x.data_ptr(), gamma.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+               dx.data_ptr(), L.ptr(dres) if ctx.relu else None, dgamma.data_ptr(), dbeta.data_ptr(), L.DDL_BF16, scratch.data_ptr(),
+               scratch.numel(), ctx.M, Cc, int(ctx.relu), L.stream_ptr(dev))
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None
+
+
+def bn_act(x, bn: nn.BatchNorm2d, relu: bool = True, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``relu(batch_norm(x) + residual)`` with torch's training/eval semantics (running stats
+    updated with the unbiased variance and ``bn.momentum``)."""
+    training = bn.training or bn.running_mean is None
+    if training and bn.num_batches_tracked is not None:
+        bn.num_batches_tracked.add_(1)
+    return _BnAct.apply(x, residual, bn.weight, bn.bias, bn.running_mean, bn.running_var, training,
+                        0.1 if bn.momentum is None else bn.momentum, bn.eps, relu)
+
+
+def to_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
+    return x.to(dtype=torch.bfloat16, memory_format=torch.channels_last)
+
+
+def conv_bn_act(x, conv: nn.Conv2d, bn: nn.BatchNorm2d, relu: bool = True, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """conv -> BN -> (+residual) -> ReLU on NHWC bf16.  The convolution itself is the library
+    call (cuDNN through ATen) except for 1x1/stride-1 convolutions, which are GEMMs and run on
+    the tcgen05 kernel when it is built in; BN statistics, normalise, residual add and ReLU
+    are the native kernels in ``csrc/bn_act.cu``."""
+    y = conv2d(x, conv)
+    return bn_act(y, bn, relu=relu, residual=residual)
+
+
+def conv2d(x, conv: nn.Conv2d) -> torch.Tensor:
+    return F.conv2d(x, conv.weight, None, conv.stride, conv.padding, conv.dilation, conv.groups)
+
+
+# ----------------------------------------------------------------------------- linear / attention
+def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, activation: Optional[str] = None) -> torch.Tensor:
+    """``act(x @ weight.T + bias)``; dispatches to the tcgen05 GEMM (``ops/gemm.py``) for bf16
+    operands whose shapes fit its tiles, otherwise to the library GEMM."""
+    from . import gemm
+
+    if gemm.usable(x, weight):
+        return gemm.linear(x, weight, bias, activation)
+    y = F.linear(x, weight, bias)
+    if activation == "gelu":
+        y = F.gelu(y)
+    elif activation == "relu":
+        y = F.relu(y)
+    return y
+
+
+def attention_qkvpacked(qkv: torch.Tensor, seqlens: Optional[torch.Tensor], p: float = 0.0) -> torch.Tensor:
+    """Self attention on packed projections ``qkv`` [B, S, 3, h, d] with right-padding given by
+    ``seqlens`` [B]; returns [B, S, h*d]."""
+    from . import attention
+
+    return attention.attention_qkvpacked(qkv, seqlens, p)

@@ -1,0 +1,120 @@
+/* libb200ddl - C ABI of the hand-written sm_100a kernels and the native runtime.
+ *
+ * Every entry point returns 0 on success or a non-zero cudaError_t value; the message is
+ * available from ddl_last_error() (thread local).  Pointers are device pointers unless the
+ * name says otherwise; `stream` is a cudaStream_t passed as void*.  Nothing here allocates
+ * device memory except ddl_symm_alloc: scratch buffers are passed in by the caller, which
+ * keeps every kernel launch capturable in a CUDA graph.
+ *
+ * "reference" in the comments below = /root/reference/notebooks/cv/onnx_experiments.py, the
+ * only code file of the upstream repository.  It contains no native
+ * code and no distributed code, so most entry points cite BASELINE.json instead.
+ */
+#ifndef B200DDL_H
+#define B200DDL_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { DDL_F32 = 0, DDL_BF16 = 1 };
+enum { DDL_ALGO_AUTO = 0, DDL_ALGO_ONESHOT = 1, DDL_ALGO_TWOSHOT = 2, DDL_ALGO_NVLS = 3 };
+enum { DDL_ACT_NONE = 0, DDL_ACT_GELU = 1, DDL_ACT_RELU = 2 };
+
+#define DDL_COMM_MAX_BLOCKS 160
+
+/* ---- runtime (csrc/runtime.cu) ------------------------------------------------------ */
+const char* ddl_last_error(void);
+int ddl_version(void);
+int ddl_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, size_t* total_mem);
+/* symmetric heap slab: cudaMalloc + zero fill; handle export/import over CUDA IPC
+ * (target layer T1; BASELINE.json:5 "load and store directly from peer GPUs") */
+int ddl_symm_alloc(size_t bytes, void** ptr);
+int ddl_symm_free(void* ptr);
+int ddl_ipc_export(void* ptr, unsigned char* handle64);
+int ddl_ipc_open(const unsigned char* handle64, void** ptr);
+int ddl_ipc_close(void* ptr);
+int ddl_can_access_peer(int device, int peer, int* ok);
+int ddl_stream_sync(void* stream);
+
+/* ---- peer-memory collectives (csrc/collectives.cu) ---------------------------------- */
+typedef struct {
+    void* signal_pads[8]; /* peer-mapped address of every rank's signal pad (one channel) */
+    void* epoch;          /* local device memory, ddl_comm_epoch_bytes(), zero-initialised */
+    int rank;
+    int world;
+} ddl_comm_t;
+
+size_t ddl_comm_signal_pad_bytes(void);
+size_t ddl_comm_epoch_bytes(void);
+size_t ddl_allreduce_oneshot_max_bytes(int dtype, int num_blocks);
+/* All-reduce (mean when scale = 1/world) fused with the output cast.  in_ptrs[r] / out_ptrs[r]
+ * are this message's address inside rank r's heap as mapped into THIS process.
+ * K1 one-shot, K2 two-shot, K3 NVLS multimem (needs multicast addresses mc_in/mc_out).
+ * BASELINE.json:5; the reference has no collective. */
+int ddl_allreduce(const ddl_comm_t* comm, void* const* in_ptrs, void* const* out_ptrs, size_t numel, int in_dtype, int out_dtype,
+                  float scale, int algo, void* mc_in, void* mc_out, int num_blocks, void* stream);
+int ddl_allgather(const ddl_comm_t* comm, void* const* shard_ptrs, void* out_full, size_t shard_bytes, int num_blocks, void* stream);
+int ddl_reducescatter(const ddl_comm_t* comm, void* const* full_ptrs, void* out_shard, size_t shard_numel, int in_dtype,
+                      int out_dtype, float scale, int num_blocks, void* stream);
+/* K7: reduce-scatter fused with the sharded AdamW update (BASELINE.json:5, FSDP mode).
+ * hyper = device float[8]: {lr, beta1, beta2, eps, weight_decay, step, -, -}. */
+int ddl_reducescatter_adamw(const ddl_comm_t* comm, void* const* full_ptrs, size_t shard_numel, int in_dtype, float scale,
+                            float* master, float* m, float* v, void* param_out_bf16, const float* hyper, int num_blocks,
+                            void* stream);
+int ddl_broadcast(const ddl_comm_t* comm, void* const* buf_ptrs, int root, size_t bytes, int num_blocks, void* stream);
+int ddl_barrier(const ddl_comm_t* comm, void* stream);
+
+/* ---- fused AdamW (csrc/optim.cu), K13 ---------------------------------------------- */
+int ddl_adamw(const void* grad, int grad_dtype, float* master, float* m, float* v, void* param_out, int param_dtype, size_t numel,
+              const float* hyper, float grad_scale, void* stream);
+int ddl_adamw_tick(float* hyper, void* stream); /* hyper[5] += 1 (step counter), graph friendly */
+
+/* ---- LayerNorm family (csrc/layernorm.cu), K10 ------------------------------------- */
+float ddl_dropout_effective_p(float p); /* p rounded to a multiple of 1/256 */
+/* z = dropout(x) + residual ; y = LN(z)*gamma + beta.  residual, z_out may be NULL. */
+int ddl_add_layernorm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* z_out, void* y,
+                          float* mean, float* rstd, int rows, int H, float eps, float dropout_p, unsigned long long seed,
+                          const unsigned long long* seed_dev, void* stream);
+size_t ddl_layernorm_bwd_scratch_bytes(int rows, int H);
+/* dz (grad of z) always; dx = dropout-masked dz only when dropout_p > 0 and dx != NULL.
+ * dgamma/dbeta in param_grad_dtype.  scratch: ddl_layernorm_bwd_scratch_bytes(rows, H). */
+int ddl_layernorm_bwd(const void* dy, const void* z, const float* mean, const float* rstd, const void* gamma, void* dz, void* dx,
+                      void* dgamma, void* dbeta, int param_grad_dtype, void* scratch, size_t scratch_bytes, int rows, int H,
+                      float dropout_p, unsigned long long seed, const unsigned long long* seed_dev, void* stream);
+int ddl_embed_layernorm_fwd(const long long* ids, const long long* token_types, const void* word, const void* pos,
+                            const void* type, const void* gamma, const void* beta, void* z_out, void* y, float* mean, float* rstd,
+                            int rows, int S, int H, float eps, float dropout_p, unsigned long long seed,
+                            const unsigned long long* seed_dev, void* stream);
+int ddl_dropout(const void* in, void* out, size_t numel, float dropout_p, unsigned long long seed,
+                const unsigned long long* seed_dev, void* stream);
+
+/* ---- cross-entropy (csrc/cross_entropy.cu), K12 ------------------------------------ */
+/* row_loss[rows] fp32; mean_loss (optional) = mean(row_loss); dlogits (optional) =
+ * (softmax - onehot) * grad_scale in the logits' dtype.  The reference only computes a
+ * display softmax (reference:85-88, :174). */
+int ddl_cross_entropy(const void* logits, int dtype, const long long* labels, float* row_loss, float* mean_loss, void* dlogits,
+                      int rows, int classes, float grad_scale, long long ignore_index, void* stream);
+
+/* ---- BatchNorm + residual + ReLU, NHWC bf16 (csrc/bn_act.cu), K9 epilogue half ------ */
+size_t ddl_bn_scratch_bytes(long long M, int C);
+int ddl_bn_apply(const void* x, const void* residual, const float* scale, const float* shift, void* y, long long M, int C, int relu,
+                 void* stream);
+int ddl_bn_act_fwd_train(const void* x, const void* residual, const void* gamma, const void* beta, float* running_mean,
+                         float* running_var, void* y, float* mean, float* invstd, float* scale, float* shift, void* scratch,
+                         size_t scratch_bytes, long long M, int C, float eps, float momentum, int relu, void* stream);
+int ddl_bn_act_fwd_eval(const void* x, const void* residual, const void* gamma, const void* beta, const float* running_mean,
+                        const float* running_var, void* y, float* scale, float* shift, long long M, int C, float eps, int relu,
+                        void* stream);
+/* dres (optional) receives the gradient of the residual branch (= ReLU-masked dy). */
+int ddl_bn_act_bwd(const void* dy, const void* y, const void* x, const void* gamma, const float* mean, const float* invstd, void* dx,
+                   void* dres, void* dgamma, void* dbeta, int param_grad_dtype, void* scratch, size_t scratch_bytes, long long M,
+                   int C, int relu, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DDL_H */

@@ -1,0 +1,176 @@
+"""Worker functions for the multi-GPU tests (one process per GPU)."""
+import torch
+
+
+def _pg():
+    from databricks_distributed_deep_learning_b200.parallel import process_group as pg
+
+    return pg
+
+
+def w_allreduce_variants():
+    from databricks_distributed_deep_learning_b200.parallel.collectives import PeerMemoryComm
+
+    pg = _pg()
+    dev = pg.device()
+    rank, world = pg.rank(), pg.world_size()
+    comm = PeerMemoryComm(dev)
+    report = {"ok": True, "cases": []}
+    for dtype in (torch.bfloat16, torch.float32):
+        for n in (1024, 8 * 1024 * 3, 1 << 20, (1 << 22) + 8192):
+            n = n // (8 * world) * (8 * world)
+            buf = comm.alloc_flat(n, dtype, dev)
+            for algo in ("oneshot", "twoshot"):
+                if algo == "oneshot" and n * buf.element_size() > 2 << 20:
+                    continue
+                for rep in range(3):  # back-to-back launches exercise epoch reuse
+                    g = torch.Generator(device="cpu").manual_seed(100 + rep)
+                    full = torch.randn(world, n, generator=g)
+                    buf.copy_(full[rank].to(dtype))
+                    pg.barrier()
+                    comm.all_reduce_mean_(buf, algo=algo)
+                    torch.cuda.synchronize()
+                    ref = full.to(dtype).float().mean(0)
+                    err = (buf.float().cpu() - ref).abs().max().item()
+                    tol = 2e-2 if dtype == torch.bfloat16 else 1e-5
+                    ok = err < tol
+                    report["cases"].append((str(dtype), n, algo, rep, err))
+                    report["ok"] &= ok
+                    pg.barrier()
+        # fused cast: fp32 in -> bf16 out (out of place)
+    n = 8 * world * 4096
+    src = comm.alloc_flat(n, torch.float32, dev)
+    dst = comm.alloc_flat(n, torch.bfloat16, dev)
+    for algo in ("oneshot", "twoshot"):
+        g = torch.Generator(device="cpu").manual_seed(7)
+        full = torch.randn(world, n, generator=g)
+        src.copy_(full[rank])
+        dst.zero_()
+        pg.barrier()
+        comm.all_reduce_mean_(src, out=dst, algo=algo)
+        torch.cuda.synchronize()
+        err = (dst.float().cpu() - full.mean(0)).abs().max().item()
+        report["cases"].append(("f32->bf16", n, algo, 0, err))
+        report["ok"] &= err < 2e-2
+        pg.barrier()
+    gathered = pg.all_gather_object(report["ok"])
+    report["ok"] = all(gathered)
+    return report
+
+
+def w_other_collectives():
+    from databricks_distributed_deep_learning_b200.parallel.collectives import PeerMemoryComm
+
+    pg = _pg()
+    dev = pg.device()
+    rank, world = pg.rank(), pg.world_size()
+    comm = PeerMemoryComm(dev)
+    ok = True
+    notes = []
+    n = 8 * 5000
+    shard = comm.alloc_flat(n, torch.bfloat16, dev)
+    shard.copy_(torch.full((n,), float(rank + 1)).to(torch.bfloat16))
+    full = torch.empty(world * n, dtype=torch.bfloat16, device=dev)
+    pg.barrier()
+    comm.all_gather_into(full, shard)
+    torch.cuda.synchronize()
+    for r in range(world):
+        ok &= bool((full[r * n:(r + 1) * n].float() == r + 1).all())
+    notes.append(("allgather", ok))
+    fullg = comm.alloc_flat(world * n, torch.float32, dev)
+    g = torch.Generator(device="cpu").manual_seed(5)
+    data = torch.randn(world, world * n, generator=g)
+    fullg.copy_(data[rank])
+    out = torch.empty(n, dtype=torch.float32, device=dev)
+    pg.barrier()
+    comm.reduce_scatter_mean_into(out, fullg)
+    torch.cuda.synchronize()
+    ref = data.mean(0)[rank * n:(rank + 1) * n]
+    ok &= bool((out.cpu() - ref).abs().max() < 1e-5)
+    notes.append(("reducescatter", ok))
+    # fused reduce-scatter + AdamW vs unfused
+    master = torch.randn(n, device=dev)
+    m = torch.zeros(n, device=dev)
+    v = torch.zeros(n, device=dev)
+    pout = torch.empty(n, dtype=torch.bfloat16, device=dev)
+    hyper = torch.tensor([1e-2, 0.9, 0.999, 1e-8, 0.01, 1.0, 0, 0], device=dev)
+    ref_p = torch.nn.Parameter(master.clone())
+    opt = torch.optim.AdamW([ref_p], lr=1e-2, weight_decay=0.01)
+    pg.barrier()
+    comm.reduce_scatter_adamw_(fullg, master, m, v, pout, hyper)
+    torch.cuda.synchronize()
+    ref_p.grad = out.clone()
+    opt.step()
+    ok &= bool(torch.allclose(master, ref_p.data, rtol=1e-5, atol=1e-5))
+    ok &= bool(torch.allclose(pout.float(), ref_p.data, rtol=1e-2, atol=1e-2))
+    notes.append(("rs_adamw", ok))
+    # broadcast (symmetric and staged)
+    b = comm.alloc_flat(4096, torch.float32, dev)
+    b.fill_(float(rank))
+    pg.barrier()
+    comm.broadcast_(b, src=0)
+    torch.cuda.synchronize()
+    ok &= bool((b == 0).all())
+    t = torch.full((1000,), float(rank + 3), device=dev)
+    comm.broadcast_(t, src=0)
+    torch.cuda.synchronize()
+    ok &= bool((t == 3).all())
+    notes.append(("broadcast", ok))
+    comm.barrier()
+    torch.cuda.synchronize()
+    return {"ok": all(pg.all_gather_object(ok)), "notes": notes}
+
+
+def _make_model():
+    from databricks_distributed_deep_learning_b200.models import resnet18
+
+    torch.manual_seed(11)
+    return resnet18(num_classes=10, small_input=True)
+
+
+def w_ddp_equivalence(steps):
+    """Our wrapper (peer-memory all-reduce) vs stock DDP + NCCL: same parameters after K steps."""
+    import torch.nn.functional as F
+
+    from databricks_distributed_deep_learning_b200 import DDP
+    from databricks_distributed_deep_learning_b200.utils.data import cifar_shape_loader
+
+    pg = _pg()
+    dev = pg.device()
+    rank, world = pg.rank(), pg.world_size()
+    ours = DDP(_make_model().to(dev), bucket_cap_mb=1.0, comm="p2p")
+    stock = torch.nn.parallel.DistributedDataParallel(_make_model().to(dev), device_ids=[dev.index], bucket_cap_mb=1.0)
+    o1 = torch.optim.SGD(ours.parameters(), lr=0.05)
+    o2 = torch.optim.SGD(stock.parameters(), lr=0.05)
+    loader = cifar_shape_loader(16, rank=rank, world_size=world, seed=5, steps=steps, pin_memory=False)
+    maxdiff = 0.0
+    for x, y in loader:
+        x, y = x.to(dev), y.to(dev)
+        ours.zero_grad()
+        F.cross_entropy(ours(x), y).backward()
+        o1.step()
+        o2.zero_grad()
+        F.cross_entropy(stock(x), y).backward()
+        o2.step()
+    for a, b in zip(ours.module.parameters(), stock.module.parameters()):
+        maxdiff = max(maxdiff, (a - b).abs().max().item())
+    flat = torch.cat([p.detach().reshape(-1) for p in ours.module.parameters()]).cpu()
+    same = all(torch.equal(flat, o) for o in pg.all_gather_object(flat))
+    ok = maxdiff < 2e-3 and same
+    return {"ok": all(pg.all_gather_object(ok)), "maxdiff": maxdiff, "ranks_identical": same, "comm": ours.comm.name}
+
+
+def w_trainer_graph_sync(steps):
+    from databricks_distributed_deep_learning_b200.engine import Trainer
+    from databricks_distributed_deep_learning_b200.utils.data import cifar_shape_loader
+
+    pg = _pg()
+    dev = pg.device()
+    rank, world = pg.rank(), pg.world_size()
+    tr = Trainer(_make_model(), lr=1e-3, device=dev, use_graph=True, bucket_cap_mb=1.0)
+    loader = cifar_shape_loader(16, rank=rank, world_size=world, seed=9, steps=steps)
+    out = tr.fit(loader)
+    flat = torch.cat([p.detach().float().reshape(-1) for p in tr.model.parameters()]).cpu()
+    same = all(torch.equal(flat, o) for o in pg.all_gather_object(flat))
+    finite = all(l == l for l in out["losses"])
+    return {"ok": same and finite, "losses": out["losses"], "comm": tr.ddp.comm.name}

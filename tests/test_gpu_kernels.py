@@ -1,0 +1,266 @@
+"""Numerics of the native sm_100a kernels vs plain PyTorch fp32 references (SURVEY.md §4.2
+"Kernel numerics (GPU)")."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def _seed():
+    torch.manual_seed(0)
+
+
+def _OF():
+    from databricks_distributed_deep_learning_b200.ops import functional as OF
+
+    return OF
+
+
+def test_library_loads_and_counts_launches():
+    from databricks_distributed_deep_learning_b200.ops import _lib as L
+
+    assert L.lib().ddl_version() >= 100
+    sm = __import__("ctypes").c_int()
+    L.check(L.lib().ddl_device_info(0, sm, None, None, None))
+    assert sm.value >= 100
+
+
+@pytest.mark.parametrize("B,C,dtype", [(256, 1000, torch.bfloat16), (64, 10, torch.float32), (33, 2, torch.bfloat16),
+                                       (8, 5000, torch.float32)])
+def test_cross_entropy_fwd_bwd(B, C, dtype):
+    OF = _OF()
+    logits = (torch.randn(B, C, device="cuda") * 3).to(dtype).requires_grad_()
+    labels = torch.randint(0, C, (B,), device="cuda")
+    loss = OF.cross_entropy(logits, labels)
+    loss.backward()
+    ref_in = logits.detach().float().requires_grad_()
+    ref = F.cross_entropy(ref_in, labels)
+    ref.backward()
+    assert torch.allclose(loss, ref, rtol=1e-4, atol=1e-4), (float(loss), float(ref))
+    tol = 1e-6 if dtype == torch.float32 else 2e-2 / B
+    assert torch.allclose(logits.grad.float(), ref_in.grad, rtol=2e-2, atol=max(tol, 1e-6))
+
+
+@pytest.mark.parametrize("rows,H", [(512, 768), (300, 1024), (64, 128), (17, 2048), (40, 136)])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_add_layernorm_fwd_bwd(rows, H, with_res):
+    OF = _OF()
+    bf = torch.bfloat16
+    x = torch.randn(rows, H, device="cuda").to(bf).requires_grad_()
+    res = torch.randn(rows, H, device="cuda").to(bf).requires_grad_() if with_res else None
+    g = (1 + 0.1 * torch.randn(H, device="cuda")).to(bf).requires_grad_()
+    b = (0.1 * torch.randn(H, device="cuda")).to(bf).requires_grad_()
+    y = OF.dropout_add_layernorm(x, res, g, b, 1e-12, 0.0)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xf, gf, bfv = x.detach().float().requires_grad_(), g.detach().float().requires_grad_(), b.detach().float().requires_grad_()
+    rf = res.detach().float().requires_grad_() if with_res else None
+    z = xf + rf if with_res else xf
+    if with_res:
+        z = z.to(bf).float() + (z - z.detach())  # kernel rounds z to bf16 once (straight-through)
+    yr = F.layer_norm(z, (H,), gf, bfv, 1e-12)
+    yr.backward(dy.float())
+    assert torch.allclose(y.float(), yr, rtol=2e-2, atol=2e-2)
+    assert torch.allclose(x.grad.float(), xf.grad, rtol=3e-2, atol=3e-2)
+    if with_res:
+        assert torch.allclose(res.grad.float(), rf.grad, rtol=3e-2, atol=3e-2)
+    # column sums over `rows` bf16-rounded terms: compare with a tolerance that scales
+    scale = dy.float().abs().sum(0).max().item()
+    assert (g.grad.float() - gf.grad).abs().max().item() < 2e-2 * scale
+    assert (b.grad.float() - bfv.grad).abs().max().item() < 2e-2 * scale
+
+
+def test_layernorm_dropout_mask_is_consistent_between_fwd_and_bwd():
+    OF = _OF()
+    bf = torch.bfloat16
+    rows, H, p = 256, 768, 0.1
+    x = torch.ones(rows, H, device="cuda", dtype=bf).requires_grad_()
+    res = torch.zeros(rows, H, device="cuda", dtype=bf).requires_grad_()
+    g = torch.ones(H, device="cuda", dtype=bf)
+    b = torch.zeros(H, device="cuda", dtype=bf)
+    from databricks_distributed_deep_learning_b200.ops import _lib as L
+
+    # recover the mask from z = dropout(1) + 0
+    import databricks_distributed_deep_learning_b200.ops.functional as OFm
+
+    y = OFm._AddLayerNorm.apply(x, res, g, b, 1e-12, p)
+    z = y.grad_fn.saved_tensors[0] if hasattr(y.grad_fn, "saved_tensors") else None
+    assert z is not None
+    keep = z.float() > 0
+    frac = 1 - keep.float().mean().item()
+    p_eff = L.lib().ddl_dropout_effective_p(p)
+    assert abs(frac - p_eff) < 0.01, (frac, p_eff)
+    assert torch.allclose(z.float()[keep], torch.full_like(z.float()[keep], 1 / (1 - p_eff)), rtol=1e-2)
+    y.backward(torch.randn_like(y))
+    # gradient wrt x must be exactly zero where the element was dropped, and non-zero (a.s.) elsewhere
+    assert (x.grad.float()[~keep] == 0).all()
+    assert (x.grad.float()[keep] != 0).float().mean() > 0.99
+    # advancing the device seed word changes the mask
+    OF.advance_seed(x.device)
+    y2 = OFm._AddLayerNorm.apply(x, res, g, b, 1e-12, p)
+    z2 = y2.grad_fn.saved_tensors[0]
+    assert (z2.float() > 0).ne(keep).any()
+
+
+def test_embed_layernorm():
+    OF = _OF()
+    bf = torch.bfloat16
+    B, S, H, V = 4, 64, 768, 1000
+    word = (torch.randn(V, H, device="cuda") * 0.05).to(bf).requires_grad_()
+    pos = (torch.randn(512, H, device="cuda") * 0.05).to(bf).requires_grad_()
+    typ = (torch.randn(2, H, device="cuda") * 0.05).to(bf).requires_grad_()
+    g = torch.ones(H, device="cuda", dtype=bf).requires_grad_()
+    b = torch.zeros(H, device="cuda", dtype=bf).requires_grad_()
+    ids = torch.randint(0, V, (B, S), device="cuda")
+    tts = torch.randint(0, 2, (B, S), device="cuda")
+    y = OF.embed_layernorm(ids, tts, word, pos, typ, g, b, 1e-12, 0.0)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    wf, pf, tf = (t.detach().float().requires_grad_() for t in (word, pos, typ))
+    z = wf[ids] + pf[:S][None] + tf[tts]
+    yr = F.layer_norm(z, (H,), g.detach().float(), b.detach().float(), 1e-12)
+    yr.backward(dy.float())
+    assert torch.allclose(y.float(), yr, rtol=3e-2, atol=3e-2)
+    assert torch.allclose(word.grad.float(), wf.grad, rtol=5e-2, atol=5e-2)
+    assert torch.allclose(pos.grad.float(), pf.grad, rtol=5e-2, atol=8e-2)
+    assert torch.allclose(typ.grad.float(), tf.grad, rtol=5e-2, atol=0.5)
+
+
+@pytest.mark.parametrize("N,C,HW", [(8, 64, 56), (4, 256, 14), (2, 2048, 7), (16, 128, 28), (3, 24, 5)])
+@pytest.mark.parametrize("relu,with_res", [(True, False), (True, True), (False, False), (False, True)])
+def test_bn_act_train_fwd_bwd(N, C, HW, relu, with_res):
+    OF = _OF()
+    bf = torch.bfloat16
+    bn = torch.nn.BatchNorm2d(C).cuda()
+    with torch.no_grad():
+        bn.weight.copy_(1 + 0.2 * torch.randn(C))
+        bn.bias.copy_(0.2 * torch.randn(C))
+    ref_bn = torch.nn.BatchNorm2d(C).cuda()
+    ref_bn.load_state_dict(bn.state_dict())
+    bn.weight.data = bn.weight.data.to(bf)
+    bn.bias.data = bn.bias.data.to(bf)
+    ref_bn.weight.data = bn.weight.data.float()
+    ref_bn.bias.data = bn.bias.data.float()
+    x = (torch.randn(N, C, HW, HW, device="cuda") * 2 + 0.5).to(bf).contiguous(memory_format=torch.channels_last).requires_grad_()
+    res = torch.randn(N, C, HW, HW, device="cuda").to(bf).contiguous(memory_format=torch.channels_last).requires_grad_() if with_res else None
+    y = OF.bn_act(x, bn, relu=relu, residual=res)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xf = x.detach().float().requires_grad_()
+    rf = res.detach().float().requires_grad_() if with_res else None
+    yr = ref_bn(xf)
+    if with_res:
+        yr = yr + rf
+    if relu:
+        yr = F.relu(yr)
+    yr.backward(dy.float())
+    assert y.is_contiguous(memory_format=torch.channels_last)
+    assert torch.allclose(y.float(), yr, rtol=2e-2, atol=3e-2)
+    assert torch.allclose(bn.running_mean, ref_bn.running_mean, rtol=1e-3, atol=1e-3)
+    assert torch.allclose(bn.running_var, ref_bn.running_var, rtol=1e-2, atol=1e-3)
+    assert int(bn.num_batches_tracked) == 1
+    # dx: differences come from bf16 rounding of y at the ReLU boundary and of dx itself
+    err = (x.grad.float() - xf.grad).abs()
+    assert err.mean().item() < 5e-3 and err.max().item() < 0.25, (err.mean().item(), err.max().item())
+    if with_res:
+        assert torch.allclose(res.grad.float(), rf.grad, rtol=2e-2, atol=2e-2) or \
+            ((res.grad.float() - rf.grad).abs() > 2e-2).float().mean() < 1e-3
+    M = N * HW * HW
+    assert (bn.weight.grad.float() - ref_bn.weight.grad).abs().max().item() < 2e-2 * M ** 0.5 + 0.05 * ref_bn.weight.grad.abs().max().item()
+    assert (bn.bias.grad.float() - ref_bn.bias.grad).abs().max().item() < 2e-2 * M ** 0.5 + 0.05 * ref_bn.bias.grad.abs().max().item()
+
+
+def test_bn_act_eval_matches_torch():
+    OF = _OF()
+    bf = torch.bfloat16
+    C = 64
+    bn = torch.nn.BatchNorm2d(C).cuda()
+    bn.running_mean.normal_()
+    bn.running_var.uniform_(0.5, 2)
+    ref = torch.nn.BatchNorm2d(C).cuda().eval()
+    ref.load_state_dict(bn.state_dict())
+    bn.weight.data = bn.weight.data.to(bf)
+    bn.bias.data = bn.bias.data.to(bf)
+    bn.eval()
+    x = torch.randn(4, C, 14, 14, device="cuda").to(bf).contiguous(memory_format=torch.channels_last)
+    with torch.no_grad():
+        y = OF.bn_act(x, bn, relu=True)
+        yr = F.relu(ref(x.float()))
+    assert torch.allclose(y.float(), yr, rtol=2e-2, atol=2e-2)
+
+
+@pytest.mark.parametrize("gdtype,pdtype", [(torch.bfloat16, torch.bfloat16), (torch.float32, torch.float32),
+                                           (torch.float32, torch.bfloat16)])
+def test_fused_adamw_matches_torch(gdtype, pdtype):
+    from databricks_distributed_deep_learning_b200.ops import _lib as L
+
+    n = 8 * 12345
+    w0 = torch.randn(n, device="cuda")
+    master = w0.clone()
+    m = torch.zeros(n, device="cuda")
+    v = torch.zeros(n, device="cuda")
+    pout = torch.empty(n, device="cuda", dtype=pdtype)
+    hyper = torch.tensor([1e-2, 0.9, 0.999, 1e-8, 0.01, 1.0, 0, 0], device="cuda")
+    ref_p = torch.nn.Parameter(w0.clone())
+    ref = torch.optim.AdamW([ref_p], lr=1e-2, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01)
+    for step in range(5):
+        g = torch.randn(n, device="cuda").to(gdtype)
+        L.call("ddl_adamw", g.data_ptr(), L.dtype_code(gdtype), master.data_ptr(), m.data_ptr(), v.data_ptr(), pout.data_ptr(),
+               L.dtype_code(pdtype), n, hyper.data_ptr(), 1.0, L.stream_ptr())
+        L.call("ddl_adamw_tick", hyper.data_ptr(), L.stream_ptr())
+        ref_p.grad = g.float()
+        ref.step()
+    assert float(hyper[5]) == 6.0
+    assert torch.allclose(master, ref_p.data, rtol=1e-5, atol=1e-5), (master - ref_p.data).abs().max()
+    assert torch.allclose(pout.float(), ref_p.data, rtol=1e-2 if pdtype == torch.bfloat16 else 1e-5, atol=1e-2 if pdtype == torch.bfloat16 else 1e-5)
+
+
+def test_trainer_graph_matches_eager_resnet18():
+    """Whole-step CUDA graph (fwd + bwd + bucketed reduce + fused AdamW) == eager execution."""
+    from databricks_distributed_deep_learning_b200.engine import Trainer
+    from databricks_distributed_deep_learning_b200.models import resnet18
+
+    dev = torch.device("cuda", 0)
+    x = torch.randn(16, 3, 32, 32).pin_memory()
+    y = torch.randint(0, 10, (16,)).pin_memory()
+    losses = {}
+    for graph in (False, True):
+        torch.manual_seed(1)
+        tr = Trainer(resnet18(num_classes=10, small_input=True), lr=1e-3, device=dev, use_graph=graph, graph_warmup=0, bucket_cap_mb=1.0)
+        losses[graph] = [float(tr.step((x, y))) for _ in range(6)]
+    assert losses[True][-1] < losses[True][0]
+    for a, b in zip(losses[False], losses[True]):
+        assert abs(a - b) < 0.05 * max(1.0, abs(a)), (losses[False], losses[True])
+
+
+def test_fused_resnet_matches_torch_impl_one_step():
+    """Fused NHWC/bf16 ResNet forward+backward vs the ATen implementation of the same module."""
+    from databricks_distributed_deep_learning_b200.models import resnet18
+
+    torch.manual_seed(2)
+    a = resnet18(num_classes=10, small_input=True).cuda().to(torch.bfloat16).to(memory_format=torch.channels_last)
+    b = resnet18(num_classes=10, small_input=True).cuda()
+    b.load_state_dict({k: v.float() for k, v in a.state_dict().items()})
+    for m in a.modules():
+        if isinstance(m, torch.nn.BatchNorm2d):
+            m.running_mean.data = m.running_mean.data.float()
+            m.running_var.data = m.running_var.data.float()
+    a.set_impl("fused")
+    x = torch.randn(32, 3, 32, 32, device="cuda")
+    y = torch.randint(0, 10, (32,), device="cuda")
+    OF = _OF()
+    la = OF.cross_entropy(a(x), y)
+    la.backward()
+    lb = F.cross_entropy(b(x), y)
+    lb.backward()
+    assert abs(float(la) - float(lb)) < 0.05, (float(la), float(lb))
+    ga = a.fc.weight.grad.float()
+    gb = b.fc.weight.grad
+    cos = F.cosine_similarity(ga.flatten(), gb.flatten(), dim=0).item()
+    assert cos > 0.98, cos
+    ga = a.conv1.weight.grad.float()
+    gb = b.conv1.weight.grad
+    cos = F.cosine_similarity(ga.flatten(), gb.flatten(), dim=0).item()
+    assert cos > 0.9, cos
