@@ -59,7 +59,7 @@ def test_add_layernorm_fwd_bwd(rows, H, with_res):
     rf = res.detach().float().requires_grad_() if with_res else None
     z = xf + rf if with_res else xf
     if with_res:
-        z = z.to(bf).float() + (z - z.detach())  # kernel rounds z to bf16 once (straight-through)
+        z = z + (z.to(bf).float() - z).detach()  # kernel rounds z to bf16 once (straight-through)
     yr = F.layer_norm(z, (H,), gf, bfv, 1e-12)
     yr.backward(dy.float())
     assert torch.allclose(y.float(), yr, rtol=2e-2, atol=2e-2)
@@ -123,9 +123,12 @@ def test_embed_layernorm():
     yr = F.layer_norm(z, (H,), g.detach().float(), b.detach().float(), 1e-12)
     yr.backward(dy.float())
     assert torch.allclose(y.float(), yr, rtol=3e-2, atol=3e-2)
-    assert torch.allclose(word.grad.float(), wf.grad, rtol=5e-2, atol=5e-2)
-    assert torch.allclose(pos.grad.float(), pf.grad, rtol=5e-2, atol=8e-2)
-    assert torch.allclose(typ.grad.float(), tf.grad, rtol=5e-2, atol=0.5)
+    def rel(a, b):  # error relative to the tensor's scale (rstd ~ 10 here, so grads are O(10))
+        return ((a.float() - b).abs().max() / b.abs().max()).item()
+
+    assert rel(word.grad, wf.grad) < 2e-2, rel(word.grad, wf.grad)
+    assert rel(pos.grad, pf.grad) < 2e-2, rel(pos.grad, pf.grad)
+    assert rel(typ.grad, tf.grad) < 2e-2, rel(typ.grad, tf.grad)
 
 
 @pytest.mark.parametrize("N,C,HW", [(8, 64, 56), (4, 256, 14), (2, 2048, 7), (16, 128, 28), (3, 24, 5)])
