@@ -372,3 +372,59 @@ DDL_API int ddl_bn_act_bwd(const void* dy, const void* y, const void* x, const v
     DDL_LAUNCH_CHECK();
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------
+// Allocation-free variant of ddl_bn_act_fwd_train.
+//
+// Who needs it: a host program that has handed the whole GPU to its own pre-sized arena (a
+// serving process, an embedded runtime with a fixed memory budget) has nothing left to
+// cudaMalloc from, and a latency-critical loop cannot afford the device-wide
+// synchronisation that cudaMalloc / cudaFree imply.  Such callers can provide inputs and
+// outputs but no scratch buffer.  For them the cross-block partial sums live in the
+// file-scope array below, which is part of the loaded module: every GPU that loads the
+// library holds DDL_BN_NOALLOC_MAX_BYTES (2 MiB) of it until the process exits.
+//
+// Rules for the caller:
+//  * The first call on each device resolves the array's device address with
+//    cudaGetSymbolAddress (the name `g_bn_noalloc_scratch` is only a host-side stand-in in
+//    host code, not an address a kernel may be given).  That set-up call must be made with
+//    the device current and should happen before any stream capture begins.
+//  * Sizes whose scratch need (ddl_bn_scratch_bytes(M, C)) exceeds the array are rejected
+//    with cudaErrorInvalidValue and a message in ddl_last_error().
+//  * All calls on a device share the one array, and it keeps whatever the last call left
+//    in it.  Nothing has to start at zero: every word a call reads (per-block partial sums,
+//    then the folded coefficients) is written earlier in the same call, so stale contents
+//    are harmless.  Two calls that overlap on the GPU (different streams, or different host
+//    threads) race on the array and corrupt each other's statistics: serialise them.
+//  * No cudaMalloc / cudaFree / allocating library routine is called on this path.
+#define DDL_BN_NOALLOC_MAX_FLOATS (DDL_BN_NOALLOC_MAX_BYTES / sizeof(float))
+static __device__ __align__(256) float g_bn_noalloc_scratch[DDL_BN_NOALLOC_MAX_FLOATS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_bn_noalloc_ptr[kMaxDevices] = {};  // per-device address of g_bn_noalloc_scratch
+}  // namespace
+
+DDL_API int ddl_bn_act_fwd_train_noalloc(const void* x, const void* residual, const void* gamma, const void* beta,
+                                         float* running_mean, float* running_var, void* y, float* mean, float* invstd, float* scale,
+                                         float* shift, long long M, int C, float eps, float momentum, int relu, void* stream_) {
+    const size_t need = ddl_bn_scratch_bytes(M, C);
+    DDL_REQUIRE(need != 0, "bn noalloc: unsupported shape M=%lld C=%d (C must be a multiple of 8, <= 2048; M >= 1)", M, C);
+    DDL_REQUIRE(need <= (size_t)DDL_BN_NOALLOC_MAX_BYTES,
+                "bn noalloc: M=%lld C=%d needs %zu bytes of scratch, more than the built-in %zu; use ddl_bn_act_fwd_train with a "
+                "caller-provided scratch buffer",
+                M, C, need, (size_t)DDL_BN_NOALLOC_MAX_BYTES);
+    int dev = -1;
+    DDL_CHECK(cudaGetDevice(&dev));
+    DDL_REQUIRE(dev >= 0 && dev < kMaxDevices, "bn noalloc: device ordinal %d out of range", dev);
+    void* ptr = __atomic_load_n(&g_bn_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+    if (ptr == nullptr) {
+        // once per device, with that device current; idempotent, so a race between two host
+        // threads only resolves the same address twice
+        DDL_CHECK(cudaGetSymbolAddress((void**)&ptr, g_bn_noalloc_scratch));
+        DDL_REQUIRE(ptr != nullptr, "bn noalloc: cudaGetSymbolAddress returned a null address");
+        __atomic_store_n(&g_bn_noalloc_ptr[dev], ptr, __ATOMIC_RELEASE);
+    }
+    return ddl_bn_act_fwd_train(x, residual, gamma, beta, running_mean, running_var, y, mean, invstd, scale, shift, ptr,
+                                (size_t)DDL_BN_NOALLOC_MAX_BYTES, M, C, eps, momentum, relu, stream_);
+}

@@ -109,6 +109,21 @@ int ddl_bn_act_fwd_train(const void* x, const void* residual, const void* gamma,
 int ddl_bn_act_fwd_eval(const void* x, const void* residual, const void* gamma, const void* beta, const float* running_mean,
                         const float* running_var, void* y, float* scale, float* shift, long long M, int C, float eps, int relu,
                         void* stream);
+/* Allocation-free variant of ddl_bn_act_fwd_train: same arguments minus the scratch buffer.
+ * No counterpart in the reference (it has no native code at all).  It exists for callers
+ * that cannot allocate device memory - a process whose own arena already owns the whole
+ * GPU, or a latency-critical loop that must not hit cudaMalloc's device-wide sync.  The
+ * scratch is a 2 MiB array inside the library image (held by every GPU that loads the
+ * library until exit); shapes needing more (ddl_bn_scratch_bytes(M, C) >
+ * DDL_BN_NOALLOC_MAX_BYTES; every M fits when C <= 512, wider C only for small M -
+ * ask ddl_bn_scratch_bytes) are rejected.  The first call on a device looks up the array's
+ * address: make that call with the device current and before any stream capture.  All
+ * calls share the array; calls that overlap on the GPU race - serialise them.  Nothing in
+ * it needs zeroing between calls. */
+#define DDL_BN_NOALLOC_MAX_BYTES (2u << 20)
+int ddl_bn_act_fwd_train_noalloc(const void* x, const void* residual, const void* gamma, const void* beta, float* running_mean,
+                                 float* running_var, void* y, float* mean, float* invstd, float* scale, float* shift, long long M,
+                                 int C, float eps, float momentum, int relu, void* stream);
 /* dres (optional) receives the gradient of the residual branch (= ReLU-masked dy). */
 int ddl_bn_act_bwd(const void* dy, const void* y, const void* x, const void* gamma, const float* mean, const float* invstd, void* dx,
                    void* dres, void* dgamma, void* dbeta, int param_grad_dtype, void* scratch, size_t scratch_bytes, long long M,
