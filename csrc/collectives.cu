@@ -137,41 +137,91 @@ __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(Ctx c, Peer
 // Rank r owns slice r: pull-reduce it from all peers (inbound links), then push the
 // result to all peers (outbound links).  Both NVLink directions are busy at once; bytes
 // per GPU per direction = (W-1)/W * S, the bandwidth-optimal volume without switch help.
-template <typename Tin, typename Tout, int UNR>
+// A peer load takes ~2 us round trip, so bandwidth comes from bytes in flight: every thread
+// first issues ALL loads of its UNR granules from ALL W ranks (UNR*W = 16 independent 16-byte
+// requests for bf16), and only then starts adding.  W is a compile-time constant so that the
+// load batch is fully unrolled (W = 0 selects the generic run-time loop).
+template <typename T>
+__device__ __forceinline__ void g8_load_raw(const char* base, size_t g, uint4 (&raw)[G8<T>::kBytes / 16]) {
+#pragma unroll
+    for (int i = 0; i < G8<T>::kBytes / 16; ++i) raw[i] = ld_relaxed_sys_v4(base + g * G8<T>::kBytes + i * 16);
+}
+template <typename T>
+__device__ __forceinline__ void g8_accumulate(const uint4 (&raw)[G8<T>::kBytes / 16], float (&acc)[8]) {
+    if constexpr (sizeof(T) == 2) {
+        float f[8];
+        bf16x8_to_float(raw[0], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+    } else {
+        acc[0] += __uint_as_float(raw[0].x); acc[1] += __uint_as_float(raw[0].y); acc[2] += __uint_as_float(raw[0].z); acc[3] += __uint_as_float(raw[0].w);
+        acc[4] += __uint_as_float(raw[1].x); acc[5] += __uint_as_float(raw[1].y); acc[6] += __uint_as_float(raw[1].z); acc[7] += __uint_as_float(raw[1].w);
+    }
+}
+
+template <typename Tin, typename Tout, int W, int UNR>
 __global__ void __launch_bounds__(kThreads) allreduce_twoshot_kernel(Ctx c, PeerPtrs in, PeerPtrs out, size_t n8, float scale) {
     uint32_t epoch = epoch_begin(c);
-    const size_t slice = n8 / c.world;  // host guarantees divisibility
+    const int world = W > 0 ? W : c.world;
+    const size_t slice = n8 / world;  // host guarantees divisibility
     const size_t base = slice * c.rank;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
+    constexpr int kVec = G8<Tin>::kBytes / 16;
     block_barrier(c, epoch, false);
     for (size_t g0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g0 < slice; g0 += stride * UNR) {
-        float acc[UNR][8];
+        if constexpr (W > 0) {
+            uint4 raw[UNR][W][kVec];
 #pragma unroll
-        for (int k = 0; k < UNR; ++k) {
-            const size_t g = g0 + k * stride;
+            for (int k = 0; k < UNR; ++k) {
+                const size_t g = g0 + k * stride;
+                if (g < slice) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[k][j] = 0.f;
-            if (g < slice) {
-                for (int r = 0; r < c.world; ++r) {
-                    int peer = c.rank + r;
-                    if (peer >= c.world) peer -= c.world;
-                    float f[8];
-                    G8<Tin>::load(in.p[peer], base + g, f);
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) acc[k][j] += f[j];
+                    for (int r = 0; r < W; ++r) {
+                        int peer = c.rank + r;
+                        if (peer >= W) peer -= W;
+                        g8_load_raw<Tin>(in.p[peer], base + g, raw[k][r]);
+                    }
                 }
             }
-        }
+            // reduce + push granule by granule: the raw registers die as they are consumed
 #pragma unroll
-        for (int k = 0; k < UNR; ++k) {
-            const size_t g = g0 + k * stride;
-            if (g < slice) {
+            for (int k = 0; k < UNR; ++k) {
+                const size_t g = g0 + k * stride;
+                if (g < slice) {
+                    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-                for (int j = 0; j < 8; ++j) acc[k][j] *= scale;
-                for (int r = 0; r < c.world; ++r) {
-                    int peer = c.rank + r;
-                    if (peer >= c.world) peer -= c.world;
-                    G8<Tout>::store(out.p[peer], base + g, acc[k]);
+                    for (int r = 0; r < W; ++r) g8_accumulate<Tin>(raw[k][r], acc);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[j] *= scale;
+#pragma unroll
+                    for (int r = 0; r < W; ++r) {
+                        int peer = c.rank + r;
+                        if (peer >= W) peer -= W;
+                        G8<Tout>::store(out.p[peer], base + g, acc);
+                    }
+                }
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < UNR; ++k) {
+                const size_t g = g0 + k * stride;
+                if (g < slice) {
+                    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                    for (int r = 0; r < world; ++r) {
+                        int peer = c.rank + r;
+                        if (peer >= world) peer -= world;
+                        float f[8];
+                        G8<Tin>::load(in.p[peer], base + g, f);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[j] *= scale;
+                    for (int r = 0; r < world; ++r) {
+                        int peer = c.rank + r;
+                        if (peer >= world) peer -= world;
+                        G8<Tout>::store(out.p[peer], base + g, acc);
+                    }
                 }
             }
         }
@@ -462,21 +512,30 @@ DDL_API int ddl_allreduce(const ddl_comm_t* comm, void* const* in_ptrs, void* co
 #undef ONE
     } else if (algo == DDL_ALGO_TWOSHOT) {
         DDL_REQUIRE(in_dtype == out_dtype || in_ptrs[c.rank] != out_ptrs[c.rank], "two-shot with a dtype change cannot be in place");
-        const int nb = clamp_blocks(num_blocks, n8 / c.world, kThreads * 2);
-#define TWO(TI, TO) allreduce_twoshot_kernel<TI, TO, 2><<<nb, kThreads, 0, stream>>>(c, in, out, n8, scale)
+        const int nb = clamp_blocks(num_blocks, n8 / c.world, kThreads * 4);
+#define TWO_W(TI, TO, W_, U_) allreduce_twoshot_kernel<TI, TO, W_, U_><<<nb, kThreads, 0, stream>>>(c, in, out, n8, scale)
+#define TWO(TI, TO)                                   \
+    do {                                              \
+        constexpr int kV = sizeof(TI) == 2 ? 1 : 2;   \
+        if (c.world == 2) TWO_W(TI, TO, 2, 8 / kV);   \
+        else if (c.world == 4) TWO_W(TI, TO, 4, 4 / kV); \
+        else if (c.world == 8) TWO_W(TI, TO, 8, 2 / kV); \
+        else TWO_W(TI, TO, 0, 2);                     \
+    } while (0)
         if (in_dtype == DDL_BF16 && out_dtype == DDL_BF16) TWO(bf16, bf16);
         else if (in_dtype == DDL_F32 && out_dtype == DDL_BF16) TWO(float, bf16);
         else if (in_dtype == DDL_F32 && out_dtype == DDL_F32) TWO(float, float);
         else TWO(bf16, float);
+#undef TWO_W
 #undef TWO
     } else if (algo == DDL_ALGO_NVLS) {
         DDL_REQUIRE(mc_in && mc_out, "NVLS all-reduce needs multicast addresses (not exposed on this host?)");
         DDL_REQUIRE(in_dtype == out_dtype, "NVLS all-reduce keeps the dtype");
         const size_t n16 = in_bytes / 16;
         DDL_REQUIRE(n16 % c.world == 0, "NVLS all-reduce: size not divisible");
-        const int nb = clamp_blocks(num_blocks, n16 / c.world, kThreads * 4);
-        if (in_dtype == DDL_BF16) allreduce_nvls_kernel<true, 4><<<nb, kThreads, 0, stream>>>(c, (char*)mc_in, (char*)mc_out, n16, scale);
-        else allreduce_nvls_kernel<false, 4><<<nb, kThreads, 0, stream>>>(c, (char*)mc_in, (char*)mc_out, n16, scale);
+        const int nb = clamp_blocks(num_blocks, n16 / c.world, kThreads * 8);
+        if (in_dtype == DDL_BF16) allreduce_nvls_kernel<true, 8><<<nb, kThreads, 0, stream>>>(c, (char*)mc_in, (char*)mc_out, n16, scale);
+        else allreduce_nvls_kernel<false, 8><<<nb, kThreads, 0, stream>>>(c, (char*)mc_in, (char*)mc_out, n16, scale);
     } else {
         DDL_REQUIRE(false, "unknown all-reduce algorithm %d", algo);
     }

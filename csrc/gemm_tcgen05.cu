@@ -1,0 +1,552 @@
+// bf16 GEMM on the 5th-generation tensor cores: tcgen05.mma with TMEM accumulators, TMA
+// operand loads, mbarrier pipelines, warp-specialised persistent CTAs (K8, SURVEY.md §2.E.3;
+// BASELINE.json:5 "tcgen05/TMEM GEMM").  Written directly in PTX; descriptor layouts follow
+// the canonical UMMA layouts (K-major / MN-major, 128-byte swizzle).
+//
+//      C[M, N] = epilogue( A[M, K] . B[N, K]^T )          fp32 accumulation in TMEM
+//
+// Operand storage (row-major in global memory, bf16):
+//      A: [M, K] (K-major)   or  [K, M] (MN-major, `a_mn`)
+//      B: [N, K] (K-major)   or  [K, N] (MN-major, `b_mn`)
+// which covers the three GEMMs of a linear layer without any transpose kernel:
+//      forward  y  = x W^T        A = x  [M,K]  K-major      B = W  [N,K] K-major
+//      dgrad    dx = dy W         A = dy [M,N]  K-major      B = W  stored [K=N, N=Kin]  MN-major
+//      wgrad    dW = dy^T x       A = dy stored [K=tok, M=N] MN-major,  B = x stored [K=tok, N=Kin] MN-major
+//
+// CTA = 10 warps: warp 0 TMA producer, warp 1 MMA issuer + TMEM owner, warps 2-9 epilogue
+// (two warps per TMEM lane quarter, each taking half of the tile's columns).  Tile
+// 128 x BN (BN = 128 | 256) x 64, UMMA 128 x BN x 16, `kStages` smem stages, two TMEM
+// accumulator stages so the epilogue of tile i overlaps the mainloop of tile i+1.
+//
+// Epilogues (fused, per BASELINE.json:5): bias add, exact (erf) GELU with the pre-activation
+// kept for backward, dGELU multiply, residual / accumulate add, bf16 store; split-K with
+// fp32 `red.global.add` into a caller-zeroed buffer for the skinny wgrad shapes.
+#include <cuda.h>
+
+#include <mutex>
+#include <unordered_map>
+
+#include "../include/b200ddl.h"
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle span
+constexpr int UMMA_K = 16;
+constexpr int kEpiWarps = 8;
+constexpr int kThreads = (2 + kEpiWarps) * 32;
+
+// ---------------------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(smem_dst)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc]
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// arrive on an mbarrier once all previously issued MMAs of this thread have completed
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// 32 lanes x 32 columns of fp32: thread i of the warp gets row (lane base + i), 32 consecutive columns
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+          "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+          "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ void red_add_f32x4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// ---------------------------------------------------------------------------- descriptors
+// Shared-memory matrix descriptor, 128-byte swizzle (layout type 2), version 1 (Blackwell).
+//   K-major : rows of 128 B (64 bf16 along K), 8-row groups 1024 B apart (SBO); LBO unused (1).
+//   MN-major: rows of 128 B (64 bf16 along M/N), 8 k-rows = 1024 B (SBO), next 64-wide MN
+//             block `lbo_bytes` further on (LBO).
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;  // descriptor version
+    d |= (uint64_t)2 << 61;  // SWIZZLE_128B
+    return d;
+}
+// Instruction descriptor (kind::f16): D fp32, A/B bf16, majorness bits, N>>3 at [17,23), M>>4 at [24,29)
+__host__ __device__ constexpr uint32_t make_idesc(int m, int n, bool a_mn, bool b_mn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn ? 1u : 0u) << 15) | ((b_mn ? 1u : 0u) << 16) | ((uint32_t)(n >> 3) << 17) |
+           ((uint32_t)(m >> 4) << 24);
+}
+
+// ---------------------------------------------------------------------------- epilogue math
+__device__ __forceinline__ float erf_fast(float x) {
+    // Abramowitz-Stegun 7.1.26, |err| < 1.5e-7 (far below bf16 resolution)
+    const float ax = fabsf(x);
+    const float t = __fdividef(1.f, fmaf(0.3275911f, ax, 1.f));
+    float p = fmaf(1.061405429f, t, -1.453152027f);
+    p = fmaf(p, t, 1.421413741f);
+    p = fmaf(p, t, -0.284496736f);
+    p = fmaf(p, t, 0.254829592f);
+    const float r = 1.f - p * t * __expf(-ax * ax);
+    return copysignf(r, x);
+}
+__device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.f + erf_fast(x * 0.70710678f)); }
+__device__ __forceinline__ float dgelu_f(float x) {
+    const float cdf = 0.5f * (1.f + erf_fast(x * 0.70710678f));
+    return cdf + x * 0.39894228f * __expf(-0.5f * x * x);
+}
+
+struct GemmParams {
+    int M, N, K;
+    bf16* C;           // [M, ldc]
+    long long ldc;
+    const bf16* bias;  // [N] or null
+    const bf16* residual;  // [M, ldc] or null: added to the result (also used as "accumulate into grad")
+    bf16* aux;         // EPI_GELU: pre-activation out [M, ldc];  EPI_DGELU: pre-activation in
+    float* acc_f32;    // split-K: fp32 [M, N] accumulation target (caller-zeroed), ld = N
+    int epilogue;      // DDL_EPI_*
+    int split_k;
+    int num_m_blocks, num_n_blocks, k_blocks_total;
+};
+
+template <int BN, bool A_MN, bool B_MN, int kStages>
+struct SmemLayout {
+    static constexpr int kABytes = BM * BK * 2;
+    static constexpr int kBBytes = BN * BK * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kBarOffset = kStages * kStageBytes;
+    static constexpr int kTotal = kBarOffset + 256 + 1024;  // barriers + alignment slack
+};
+
+template <int BN, bool A_MN, bool B_MN, int kStages>
+__global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a,
+                                                                const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
+    using L = SmemLayout<BN, A_MN, B_MN, kStages>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
+    uint64_t* empty_bar = full_bar + kStages;
+    uint64_t* tmem_full = empty_bar + kStages;   // [2]
+    uint64_t* tmem_empty = tmem_full + 2;         // [2]
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    constexpr uint32_t kTmemCols = 2 * BN;  // two accumulator stages (256 or 512 columns)
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full[s], 1);
+            mbar_init(&tmem_empty[s], kEpiWarps);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_ptr_smem, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    const int tiles_mn = p.num_m_blocks * p.num_n_blocks;
+    const int num_tiles = tiles_mn * p.split_k;
+    const int kb_per_split = (p.k_blocks_total + p.split_k - 1) / p.split_k;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int ks = tile / tiles_mn, mn = tile % tiles_mn;
+                const int m_blk = mn / p.num_n_blocks, n_blk = mn % p.num_n_blocks;
+                const int kb0 = ks * kb_per_split;
+                const int kb1 = min(kb0 + kb_per_split, p.k_blocks_total);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* sa = smem + stage * L::kStageBytes;
+                    uint8_t* sb = sa + L::kABytes;
+                    mbar_expect_tx(&full_bar[stage], L::kStageBytes);
+                    if (A_MN) {
+#pragma unroll
+                        for (int j = 0; j < BM / 64; ++j) tma_load_2d(sa + j * (BK * 128), &tma_a, &full_bar[stage], m_blk * BM + j * 64, kb * BK);
+                    } else {
+                        tma_load_2d(sa, &tma_a, &full_bar[stage], kb * BK, m_blk * BM);
+                    }
+                    if (B_MN) {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j) tma_load_2d(sb + j * (BK * 128), &tma_b, &full_bar[stage], n_blk * BN + j * 64, kb * BK);
+                    } else {
+                        tma_load_2d(sb, &tma_b, &full_bar[stage], kb * BK, n_blk * BN);
+                    }
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc(BM, BN, A_MN, B_MN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc_stage = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int ks = tile / tiles_mn;
+                const int kb0 = ks * kb_per_split;
+                const int kb1 = min(kb0 + kb_per_split, p.k_blocks_total);
+                mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc_stage * BN;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
+                    const uint32_t sb = sa + L::kABytes;
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) {
+                        // K-major: +32 B per 16 elements inside the 128 B swizzle span
+                        // MN-major: +2 k-groups (8 rows of 128 B each) = 2048 B
+                        const uint64_t da = A_MN ? make_smem_desc(sa + k * 2048, BK * 128, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
+                        const uint64_t db = B_MN ? make_smem_desc(sb + k * 2048, BK * 128, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
+                        umma_bf16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[stage]);  // frees the smem stage once these MMAs retire
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&tmem_full[acc_stage]);  // accumulator complete -> epilogue
+                if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
+            }
+        }
+    } else {
+        // ===================== epilogue warps =====================
+        const int ew = warp - 2;              // 0..7
+        const int quarter = warp & 3;         // TMEM lane quarter this warp may access
+        const int half = ew >> 2;             // which half of the tile's columns
+        constexpr int kColsPerWarp = BN / 2;
+        int acc_stage = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const int mn = tile % tiles_mn;
+            const int m_blk = mn / p.num_n_blocks, n_blk = mn % p.num_n_blocks;
+            mbar_wait(&tmem_full[acc_stage], acc_phase);
+            tc_fence_after();
+            const int row = m_blk * BM + quarter * 32 + lane;
+            const bool row_ok = row < p.M;
+#pragma unroll 1
+            for (int c = 0; c < kColsPerWarp; c += 32) {
+                const int col0 = n_blk * BN + half * kColsPerWarp + c;
+                uint32_t r[32];
+                const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc_stage * BN + half * kColsPerWarp + c);
+                tmem_ld_32x32(taddr, r);
+                tmem_ld_wait();
+                if (row_ok && col0 < p.N) {
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                    if (p.split_k > 1) {
+                        float* dst = p.acc_f32 + (size_t)row * p.N + col0;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4)
+                            if (col0 + j < p.N) red_add_f32x4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+                    } else {
+                        const size_t off = (size_t)row * p.ldc + col0;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 8) {
+                            if (col0 + j >= p.N) break;
+                            float* w = &v[j];
+                            if (p.bias) {
+                                float b[8];
+                                bf16x8_to_float(ld_global_v4(p.bias + col0 + j), b);
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) w[q] += b[q];
+                            }
+                            if (p.epilogue == DDL_EPI_GELU) {
+                                float pre[8];
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) pre[q] = w[q];
+                                if (p.aux) {
+                                    const uint4 pq = float_to_bf16x8(pre);
+                                    st_global_v4(p.aux + off + j, pq);
+                                    bf16x8_to_float(pq, pre);  // backward sees the rounded pre-activation
+                                }
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) w[q] = gelu_f(pre[q]);
+                            } else if (p.epilogue == DDL_EPI_DGELU) {
+                                float pre[8];
+                                bf16x8_to_float(ld_global_v4(p.aux + off + j), pre);
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) w[q] *= dgelu_f(pre[q]);
+                            } else if (p.epilogue == DDL_EPI_RELU) {
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) w[q] = fmaxf(w[q], 0.f);
+                            }
+                            if (p.residual) {
+                                float rs[8];
+                                bf16x8_to_float(ld_global_v4(p.residual + off + j), rs);
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) w[q] += rs[q];
+                            }
+                            float o[8];
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) o[q] = w[q];
+                            st_global_v4(p.C + off + j, float_to_bf16x8(o));
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);
+            if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// fp32 split-K accumulator -> bf16 (+ optional accumulate into existing bf16)
+__global__ void f32_to_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, size_t n8, int accumulate) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+        float f[8];
+        *reinterpret_cast<float4*>(&f[0]) = *reinterpret_cast<const float4*>(in + i * 8);
+        *reinterpret_cast<float4*>(&f[4]) = *reinterpret_cast<const float4*>(in + i * 8 + 4);
+        if (accumulate) {
+            float g[8];
+            bf16x8_to_float(ld_global_v4(out + i * 8), g);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] += g[j];
+        }
+        st_global_v4(out + i * 8, float_to_bf16x8(f));
+    }
+}
+
+// column sums of a bf16 [rows, cols] matrix (bias gradient): out[c] = sum_r x[r, c]
+__global__ void __launch_bounds__(256) colsum_partial_kernel(const bf16* __restrict__ x, int rows, int cols, long long ld,
+                                                             float* __restrict__ partials) {
+    // block handles a 256-column-vector slab? simpler: thread = one 8-column group, grid.y splits rows
+    const int vc = blockIdx.x * blockDim.x + threadIdx.x;
+    if (vc * 8 >= cols) return;
+    float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int r = blockIdx.y; r < rows; r += gridDim.y) {
+        float f[8];
+        bf16x8_to_float(ld_stream_v4(x + (size_t)r * ld + vc * 8), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s[j] += f[j];
+    }
+    float* o = partials + (size_t)blockIdx.y * cols + vc * 8;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = s[j];
+}
+__global__ void colsum_final_kernel(const float* __restrict__ partials, int nparts, int cols, bf16* __restrict__ out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cols) return;
+    float a = 0.f;
+    for (int i = 0; i < nparts; ++i) a += partials[(size_t)i * cols + c];
+    out[c] = __float2bfloat16(a);
+}
+
+// ---------------------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode = nullptr;
+std::once_flag g_encode_once;
+
+int get_encode() {
+    std::call_once(g_encode_once, [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            g_encode = (EncodeTiledFn)fn;
+    });
+    DDL_REQUIRE(g_encode != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
+    return 0;
+}
+
+// 2-D bf16 row-major tensor [rows, cols] with pitch `ld` elements; box = [box_rows, 64 cols], 128B swizzle
+int make_map(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld, int box_rows) {
+    DDL_REQUIRE(((uintptr_t)ptr & 15) == 0, "gemm: operand pointer must be 16-byte aligned");
+    DDL_REQUIRE((ld * 2) % 16 == 0, "gemm: operand pitch (%lld elements) must be a multiple of 8", ld);
+    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1u, 1u};
+    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DDL_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (rows %lld cols %lld ld %lld box %d)", (int)r, rows,
+                cols, ld, box_rows);
+    return 0;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t stream) {
+    constexpr int kStages = BN == 256 ? 4 : 6;
+    using L = SmemLayout<BN, A_MN, B_MN, kStages>;
+    auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, kStages>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        DDL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+        attr_set = true;
+    }
+    kern<<<grid, kThreads, L::kTotal, stream>>>(ta, tb, p);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+int g_sm_count = 0;
+
+}  // namespace
+
+DDL_API int ddl_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb, void* C, long long ldc, int M,
+                          int N, int K, const void* bias, const void* residual, void* aux, int epilogue, int split_k, float* acc_f32,
+                          int block_n, void* stream_) {
+    if (int e = get_encode()) return e;
+    DDL_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem");
+    DDL_REQUIRE(N % 8 == 0 && K % 8 == 0, "gemm: N (%d) and K (%d) must be multiples of 8", N, K);
+    DDL_REQUIRE(!a_mn || M % 8 == 0, "gemm: MN-major A needs M %% 8 == 0");
+    DDL_REQUIRE(ldc % 8 == 0, "gemm: ldc must be a multiple of 8");
+    DDL_REQUIRE(split_k >= 1, "gemm: split_k must be >= 1");
+    DDL_REQUIRE(split_k == 1 || (acc_f32 != nullptr && epilogue == DDL_EPI_NONE && !bias && !residual),
+                "gemm: split-K writes raw fp32 partial sums (no epilogue) into acc_f32");
+    DDL_REQUIRE(split_k > 1 || C != nullptr, "gemm: null output");
+    DDL_REQUIRE(epilogue != DDL_EPI_DGELU || aux != nullptr, "gemm: dGELU epilogue needs the pre-activation in aux");
+    if (g_sm_count == 0) {
+        int dev = 0;
+        DDL_CHECK(cudaGetDevice(&dev));
+        DDL_CHECK(cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev));
+    }
+    const int BN = block_n == 128 ? 128 : (block_n == 256 ? 256 : (N % 256 == 0 || N > 1024 ? 256 : 128));
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K;
+    p.C = (bf16*)C; p.ldc = ldc;
+    p.bias = (const bf16*)bias; p.residual = (const bf16*)residual; p.aux = (bf16*)aux;
+    p.acc_f32 = acc_f32; p.epilogue = epilogue; p.split_k = split_k;
+    p.num_m_blocks = (M + BM - 1) / BM;
+    p.num_n_blocks = (N + BN - 1) / BN;
+    p.k_blocks_total = (K + BK - 1) / BK;
+    DDL_REQUIRE(split_k <= p.k_blocks_total, "gemm: split_k %d exceeds the number of K blocks %d", split_k, p.k_blocks_total);
+    {
+        // no empty K slices: an empty slice would publish an accumulator nobody wrote
+        const int per = (p.k_blocks_total + split_k - 1) / split_k;
+        p.split_k = (p.k_blocks_total + per - 1) / per;
+    }
+    CUtensorMap ta, tb;
+    // K-major operand [R=M|N, K]: box 64 (K) x BM|BN rows.  MN-major operand stored [K, M|N]: box 64 (MN) x 64 (K) rows.
+    if (int e = a_mn ? make_map(&ta, A, K, M, lda, BK) : make_map(&ta, A, M, K, lda, BM)) return e;
+    if (int e = b_mn ? make_map(&tb, B, K, N, ldb, BK) : make_map(&tb, B, N, K, ldb, BN)) return e;
+    const int tiles = p.num_m_blocks * p.num_n_blocks * p.split_k;
+    const int grid = tiles < g_sm_count ? tiles : g_sm_count;
+    cudaStream_t s = (cudaStream_t)stream_;
+#define GO(BN_, AM, BMN) return launch<BN_, AM, BMN>(ta, tb, p, grid, s)
+    if (BN == 256) {
+        if (!a_mn && !b_mn) GO(256, false, false);
+        if (!a_mn && b_mn) GO(256, false, true);
+        if (a_mn && b_mn) GO(256, true, true);
+        GO(256, true, false);
+    } else {
+        if (!a_mn && !b_mn) GO(128, false, false);
+        if (!a_mn && b_mn) GO(128, false, true);
+        if (a_mn && b_mn) GO(128, true, true);
+        GO(128, true, false);
+    }
+#undef GO
+}
+
+DDL_API int ddl_f32_to_bf16(const float* in, void* out, size_t numel, int accumulate, void* stream_) {
+    DDL_REQUIRE(numel % 8 == 0, "ddl_f32_to_bf16: numel must be a multiple of 8");
+    if (numel == 0) return 0;
+    int blocks = ddl_ceil_div((long long)(numel / 8), 256);
+    if (blocks > DDL_SM_COUNT * 8) blocks = DDL_SM_COUNT * 8;
+    f32_to_bf16_kernel<<<blocks, 256, 0, (cudaStream_t)stream_>>>(in, (bf16*)out, numel / 8, accumulate);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+DDL_API size_t ddl_colsum_scratch_bytes(int rows, int cols) {
+    int parts = rows < 128 ? rows : 128;
+    return (size_t)parts * cols * sizeof(float);
+}
+
+DDL_API int ddl_colsum_bf16(const void* x, int rows, int cols, long long ld, void* out, void* scratch, size_t scratch_bytes, void* stream_) {
+    DDL_REQUIRE(cols % 8 == 0 && ld % 8 == 0, "ddl_colsum_bf16: cols and ld must be multiples of 8");
+    DDL_REQUIRE(scratch_bytes >= ddl_colsum_scratch_bytes(rows, cols), "ddl_colsum_bf16: scratch too small");
+    const int parts = rows < 128 ? rows : 128;
+    dim3 grid(ddl_ceil_div(cols / 8, 256), parts);
+    cudaStream_t s = (cudaStream_t)stream_;
+    colsum_partial_kernel<<<grid, 256, 0, s>>>((const bf16*)x, rows, cols, ld, (float*)scratch);
+    DDL_LAUNCH_CHECK();
+    colsum_final_kernel<<<ddl_ceil_div(cols, 256), 256, 0, s>>>((const float*)scratch, parts, cols, (bf16*)out);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}

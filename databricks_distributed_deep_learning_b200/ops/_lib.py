@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(_HERE, "libb200ddl.so")
 DDL_F32, DDL_BF16 = 0, 1
 ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS = 0, 1, 2, 3
 ACT_NONE, ACT_GELU, ACT_RELU = 0, 1, 2
-COMM_MAX_BLOCKS = 160
+COMM_MAX_BLOCKS = 320
 
 _lib: Optional[C.CDLL] = None
 launch_count = 0  # number of native kernel-launching calls issued from Python (bench "gpu_launches")
@@ -68,6 +68,10 @@ _PROTOS = {
     "ddl_bn_act_fwd_train": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _ll, _i, _f, _f, _i, _vp], _i),
     "ddl_bn_act_fwd_eval": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _f, _i, _vp], _i),
     "ddl_bn_act_bwd": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _ll, _i, _i, _vp], _i),
+    "ddl_gemm_bf16": ([_vp, _i, _ll, _vp, _i, _ll, _vp, _ll, _i, _i, _i, _vp, _vp, _vp, _i, _i, _vp, _i, _vp], _i),
+    "ddl_f32_to_bf16": ([_vp, _vp, _sz, _i, _vp], _i),
+    "ddl_colsum_scratch_bytes": ([_i, _i], _sz),
+    "ddl_colsum_bf16": ([_vp, _i, _i, _ll, _vp, _vp, _sz, _vp], _i),
 }
 # entry points added by later translation units register themselves here
 OPTIONAL_PROTOS = {}

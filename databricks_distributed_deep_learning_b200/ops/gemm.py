@@ -1,12 +1,172 @@
-"""tcgen05/TMEM GEMM front end (K8) - filled in by csrc/gemm_tcgen05.cu."""
+"""tcgen05 / TMEM / TMA GEMM front end (K8) and the linear-layer autograd
+functions built on it (``csrc/gemm_tcgen05.cu``).
+
+``gemm_nt`` is the raw call: ``C[M,N] = epilogue(A . B^T)`` with either operand K-major or
+MN-major, so that forward, dgrad and wgrad of a linear layer all run on the same kernel
+without transposes:
+
+    forward  y  = x W^T + b          A = x  [M,K]           B = W [N,K]
+    dgrad    dx = dy W               A = dy [M,N]           B = W read as [K=N, N=Kin] (MN-major)
+    wgrad    dW = dy^T x             A = dy read as [K=tok, M=N], B = x read as [K=tok, N=Kin]
+                                     (both MN-major; split-K with fp32 red.add for skinny outputs)
+
+:func:`linear` fuses bias / GELU / residual into the epilogue; :func:`ffn` is the whole
+transformer MLP (GEMM+bias+GELU -> GEMM+bias) with dGELU fused into the dgrad epilogue.
+"""
 from __future__ import annotations
 
+from typing import Optional
+
 import torch
+from torch.autograd.function import once_differentiable
+
+from . import _lib as L
+
+EPI_NONE, EPI_GELU, EPI_DGELU, EPI_RELU = 0, 1, 2, 3
+_NUM_SMS = 148
+
+
+def available() -> bool:
+    try:
+        return hasattr(L.lib(), "ddl_gemm_bf16")
+    except L.DdlError:
+        return False
 
 
 def usable(x: torch.Tensor, weight: torch.Tensor) -> bool:
-    return False
+    """Shapes/dtypes the tcgen05 kernel takes: bf16, CUDA, inner dims multiples of 8."""
+    return (x.is_cuda and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16 and x.dim() == 2
+            and x.shape[1] % 8 == 0 and weight.shape[0] % 8 == 0 and x.shape[0] >= 1 and available())
 
 
-def linear(x, weight, bias=None, activation=None):
-    raise NotImplementedError
+def gemm_nt(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool = False, b_mn: bool = False,
+            bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None, aux: Optional[torch.Tensor] = None,
+            epilogue: int = EPI_NONE, out: Optional[torch.Tensor] = None, split_k: int = 1, block_n: int = 0) -> torch.Tensor:
+    """C[M,N] = epilogue(A . B^T).  ``a``/``b`` are 2-D row-major bf16 tensors holding the operand
+    as [M,K]/[N,K] (default) or as [K,M]/[K,N] (``a_mn``/``b_mn``)."""
+    dev = a.device
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+    acc = None
+    if split_k > 1:
+        acc = torch.zeros(M, N, dtype=torch.float32, device=dev)
+    L.call("ddl_gemm_bf16", a.data_ptr(), int(a_mn), a.stride(0), b.data_ptr(), int(b_mn), b.stride(0), out.data_ptr(), out.stride(0),
+           M, N, K, L.ptr(bias), L.ptr(residual), L.ptr(aux), epilogue, split_k, L.ptr(acc), block_n, L.stream_ptr(dev))
+    if split_k > 1:
+        L.call("ddl_f32_to_bf16", acc.data_ptr(), out.data_ptr(), M * N, 0, L.stream_ptr(dev))
+    return out
+
+
+def pick_split_k(M: int, N: int, K: int, block_n: int = 256) -> int:
+    """Split the reduction when the output has too few tiles to fill 148 SMs."""
+    tiles = ((M + 127) // 128) * ((N + block_n - 1) // block_n)
+    kblocks = (K + 63) // 64
+    if tiles >= _NUM_SMS or kblocks < 8:
+        return 1
+    best, best_eff = 1, tiles / _NUM_SMS
+    for s in range(2, 17):
+        if s * 4 > kblocks:
+            break
+        t = tiles * s
+        eff = t / (((t + _NUM_SMS - 1) // _NUM_SMS) * _NUM_SMS)
+        if eff > best_eff + 0.05:
+            best, best_eff = s, eff
+    return best
+
+
+def colsum(x: torch.Tensor) -> torch.Tensor:
+    """Column sums of a [rows, cols] bf16 matrix (bias gradient), deterministic."""
+    rows, cols = x.shape
+    out = torch.empty(cols, dtype=torch.bfloat16, device=x.device)
+    nbytes = L.lib().ddl_colsum_scratch_bytes(rows, cols)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+    L.call("ddl_colsum_bf16", x.data_ptr(), rows, cols, x.stride(0), out.data_ptr(), scratch.data_ptr(), nbytes, L.stream_ptr(x.device))
+    return out
+
+
+def _wgrad(dy: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    """dW[N, Kin] = dy^T x  with dy [tok, N], x [tok, Kin]."""
+    tok, N = dy.shape
+    Kin = x.shape[1]
+    return gemm_nt(dy, x, N, Kin, tok, a_mn=True, b_mn=True, split_k=pick_split_k(N, Kin, tok))
+
+
+class _Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, residual, act):
+        x = x.contiguous()
+        M, K = x.shape
+        N = weight.shape[0]
+        epi = {None: EPI_NONE, "gelu": EPI_GELU, "relu": EPI_RELU}[act]
+        pre = torch.empty(M, N, dtype=torch.bfloat16, device=x.device) if act == "gelu" else None
+        y = gemm_nt(x, weight, M, N, K, bias=bias, residual=residual, aux=pre, epilogue=epi)
+        ctx.save_for_backward(x, weight, pre if act == "gelu" else (y if act == "relu" else None))
+        ctx.act, ctx.has_bias, ctx.has_res = act, bias is not None, residual is not None
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        x, weight, saved = ctx.saved_tensors
+        dy = dy.contiguous()
+        M, K = x.shape
+        N = weight.shape[0]
+        dres = dy if ctx.has_res else None
+        if ctx.act == "gelu":
+            # elementwise dGELU on the incoming gradient (the fused form lives in `ffn`)
+            dy = _dgelu_mul(dy, saved)
+        elif ctx.act == "relu":
+            dy = dy * (saved > 0)
+        dx = gemm_nt(dy, weight, M, K, N, b_mn=True) if ctx.needs_input_grad[0] else None
+        dw = _wgrad(dy, x) if ctx.needs_input_grad[1] else None
+        db = colsum(dy) if ctx.has_bias and ctx.needs_input_grad[2] else None
+        return dx, dw, db, dres, None
+
+
+def _dgelu_mul(dy: torch.Tensor, pre: torch.Tensor) -> torch.Tensor:
+    p = pre.float()
+    cdf = 0.5 * (1 + torch.erf(p * 0.70710678))
+    return (dy.float() * (cdf + p * torch.exp(-0.5 * p * p) * 0.39894228)).to(dy.dtype)
+
+
+def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, activation: Optional[str] = None,
+           residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``act(x @ weight.T + bias) + residual`` on [M, K] bf16 rows, all in one kernel."""
+    return _Linear.apply(x, weight, bias, residual, activation)
+
+
+class _FFN(torch.autograd.Function):
+    """out = gelu(x W1^T + b1) W2^T + b2 (+ residual).  Five GEMM launches in backward, with
+    dGELU fused into the epilogue of the dgrad of the second linear."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2, residual):
+        x = x.contiguous()
+        M, H = x.shape
+        I = w1.shape[0]
+        pre = torch.empty(M, I, dtype=torch.bfloat16, device=x.device)
+        h = gemm_nt(x, w1, M, I, H, bias=b1, aux=pre, epilogue=EPI_GELU)
+        y = gemm_nt(h, w2, M, w2.shape[0], I, bias=b2, residual=residual)
+        ctx.save_for_backward(x, w1, w2, pre, h)
+        ctx.has_res = residual is not None
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        x, w1, w2, pre, h = ctx.saved_tensors
+        dy = dy.contiguous()
+        M, H = x.shape
+        I = w1.shape[0]
+        O = w2.shape[0]
+        dw2 = _wgrad(dy, h)
+        db2 = colsum(dy)
+        dpre = gemm_nt(dy, w2, M, I, O, b_mn=True, aux=pre, epilogue=EPI_DGELU)  # (dy W2) * gelu'(pre)
+        dw1 = _wgrad(dpre, x)
+        db1 = colsum(dpre)
+        dx = gemm_nt(dpre, w1, M, H, I, b_mn=True)
+        return dx, dw1, db1, dw2, db2, (dy if ctx.has_res else None)
+
+
+def ffn(x, w1, b1, w2, b2, residual=None) -> torch.Tensor:
+    return _FFN.apply(x, w1, b1, w2, b2, residual)

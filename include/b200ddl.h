@@ -23,8 +23,9 @@ extern "C" {
 enum { DDL_F32 = 0, DDL_BF16 = 1 };
 enum { DDL_ALGO_AUTO = 0, DDL_ALGO_ONESHOT = 1, DDL_ALGO_TWOSHOT = 2, DDL_ALGO_NVLS = 3 };
 enum { DDL_ACT_NONE = 0, DDL_ACT_GELU = 1, DDL_ACT_RELU = 2 };
+enum { DDL_EPI_NONE = 0, DDL_EPI_GELU = 1, DDL_EPI_DGELU = 2, DDL_EPI_RELU = 3 };
 
-#define DDL_COMM_MAX_BLOCKS 160
+#define DDL_COMM_MAX_BLOCKS 320
 
 /* ---- runtime (csrc/runtime.cu) ------------------------------------------------------ */
 const char* ddl_last_error(void);
@@ -128,6 +129,24 @@ int ddl_bn_act_fwd_train_noalloc(const void* x, const void* residual, const void
 int ddl_bn_act_bwd(const void* dy, const void* y, const void* x, const void* gamma, const float* mean, const float* invstd, void* dx,
                    void* dres, void* dgamma, void* dbeta, int param_grad_dtype, void* scratch, size_t scratch_bytes, long long M,
                    int C, int relu, void* stream);
+
+/* ---- tcgen05 / TMEM / TMA GEMM (csrc/gemm_tcgen05.cu), K8 ------------------------------ */
+/* C[M,N] = epilogue(A . B^T), bf16 operands, fp32 accumulation in tensor memory.
+ * A is [M,K] row-major (a_mn = 0) or stored as [K,M] (a_mn = 1); B is [N,K] (b_mn = 0) or stored
+ * as [K,N] (b_mn = 1); lda/ldb/ldc are row pitches in elements (multiples of 8).
+ * Epilogue, in order: + bias[N]; DDL_EPI_GELU (exact GELU; pre-activation written to aux when
+ * given) | DDL_EPI_DGELU (multiply by GELU'(aux)) | DDL_EPI_RELU; + residual[M,ldc]; bf16 store.
+ * split_k > 1: raw fp32 partial sums are red.add-ed into acc_f32[M,N] (caller zeroes it), no
+ * epilogue; finish with ddl_f32_to_bf16.  block_n: 0 = auto, 128 or 256.
+ * BASELINE.json:5 ("tcgen05/TMEM GEMM ... TMA-fed tiles"); the reference has no GEMM of its own
+ * (its only matrix product is the library-run fc layer of ResNet-50, reference:19). */
+int ddl_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb, void* C, long long ldc, int M, int N,
+                  int K, const void* bias, const void* residual, void* aux, int epilogue, int split_k, float* acc_f32, int block_n,
+                  void* stream);
+int ddl_f32_to_bf16(const float* in, void* out, size_t numel, int accumulate, void* stream);
+size_t ddl_colsum_scratch_bytes(int rows, int cols);
+/* out[c] = sum_r x[r,c] (bias gradients), deterministic two-stage fold */
+int ddl_colsum_bf16(const void* x, int rows, int cols, long long ld, void* out, void* scratch, size_t scratch_bytes, void* stream);
 
 #ifdef __cplusplus
 }

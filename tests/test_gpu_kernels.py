@@ -267,3 +267,108 @@ def test_fused_resnet_matches_torch_impl_one_step():
     gb = b.conv1.weight.grad
     cos = F.cosine_similarity(ga.flatten(), gb.flatten(), dim=0).item()
     assert cos > 0.9, cos
+
+
+# ----------------------------------------------------------------------------- tcgen05 GEMM
+def _gemm():
+    from databricks_distributed_deep_learning_b200.ops import gemm
+
+    return gemm
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (256, 256, 128), (384, 768, 768), (1000, 2304, 768), (128, 3072, 768),
+                                   (4096, 768, 3072), (77, 256, 200), (130, 136, 72)])
+@pytest.mark.parametrize("block_n", [128, 256])
+def test_gemm_tn_matches_fp32(M, N, K, block_n):
+    g = _gemm()
+    a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+    b = torch.randn(N, K, device="cuda").to(torch.bfloat16)
+    c = g.gemm_nt(a, b, M, N, K, block_n=block_n)
+    ref = a.float() @ b.float().t()
+    err = (c.float() - ref).abs().max().item()
+    assert err < 2e-2 * K ** 0.5 + 1e-2 * ref.abs().max().item(), err
+    assert torch.allclose(c.float(), ref, rtol=2e-2, atol=0.5)
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("M,N,K", [(256, 256, 128), (768, 768, 1024), (2304, 768, 640), (128, 136, 64)])
+def test_gemm_mn_major_operands(a_mn, b_mn, M, N, K):
+    g = _gemm()
+    a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+    b = torch.randn(N, K, device="cuda").to(torch.bfloat16)
+    a_store = a.t().contiguous() if a_mn else a
+    b_store = b.t().contiguous() if b_mn else b
+    c = g.gemm_nt(a_store, b_store, M, N, K, a_mn=a_mn, b_mn=b_mn)
+    ref = a.float() @ b.float().t()
+    assert torch.allclose(c.float(), ref, rtol=2e-2, atol=0.5), (c.float() - ref).abs().max().item()
+
+
+@pytest.mark.parametrize("split_k", [2, 5, 8])
+def test_gemm_split_k(split_k):
+    g = _gemm()
+    M, N, K = 768, 768, 4096
+    a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+    b = torch.randn(N, K, device="cuda").to(torch.bfloat16)
+    c = g.gemm_nt(a.t().contiguous(), b.t().contiguous(), M, N, K, a_mn=True, b_mn=True, split_k=split_k)
+    ref = a.float() @ b.float().t()
+    assert torch.allclose(c.float(), ref, rtol=2e-2, atol=1.0), (c.float() - ref).abs().max().item()
+
+
+def test_gemm_epilogues():
+    g = _gemm()
+    M, N, K = 512, 768, 256
+    a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+    b = (torch.randn(N, K, device="cuda") * 0.1).to(torch.bfloat16)
+    bias = torch.randn(N, device="cuda").to(torch.bfloat16)
+    res = torch.randn(M, N, device="cuda").to(torch.bfloat16)
+    base = a.float() @ b.float().t() + bias.float()
+    c = g.gemm_nt(a, b, M, N, K, bias=bias, residual=res)
+    assert torch.allclose(c.float(), base + res.float(), rtol=2e-2, atol=5e-2)
+    pre = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    c = g.gemm_nt(a, b, M, N, K, bias=bias, aux=pre, epilogue=g.EPI_GELU)
+    assert torch.allclose(pre.float(), base, rtol=2e-2, atol=5e-2)
+    assert torch.allclose(c.float(), F.gelu(pre.float()), rtol=2e-2, atol=2e-2)
+    c = g.gemm_nt(a, b, M, N, K, aux=pre, epilogue=g.EPI_DGELU)
+    p = pre.float().requires_grad_()
+    F.gelu(p).sum().backward()
+    assert torch.allclose(c.float(), (a.float() @ b.float().t()) * p.grad, rtol=3e-2, atol=5e-2)
+
+
+@pytest.mark.parametrize("act", [None, "gelu"])
+def test_linear_autograd_matches_torch(act):
+    g = _gemm()
+    M, K, N = 640, 768, 1024
+    x = torch.randn(M, K, device="cuda").to(torch.bfloat16).requires_grad_()
+    w = (torch.randn(N, K, device="cuda") * 0.05).to(torch.bfloat16).requires_grad_()
+    b = torch.randn(N, device="cuda").to(torch.bfloat16).requires_grad_()
+    y = g.linear(x, w, b, act)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xf, wf, bf_ = (t.detach().float().requires_grad_() for t in (x, w, b))
+    yr = F.linear(xf, wf, bf_)
+    if act == "gelu":
+        yr = F.gelu(yr)
+    yr.backward(dy.float())
+    rel = lambda u, v: ((u.float() - v).abs().max() / v.abs().max()).item()
+    assert rel(y, yr) < 2e-2 and rel(x.grad, xf.grad) < 2e-2 and rel(w.grad, wf.grad) < 2e-2 and rel(b.grad, bf_.grad) < 2e-2, \
+        (rel(y, yr), rel(x.grad, xf.grad), rel(w.grad, wf.grad), rel(b.grad, bf_.grad))
+
+
+def test_ffn_autograd_matches_torch():
+    g = _gemm()
+    M, H, I = 512, 768, 3072
+    x = torch.randn(M, H, device="cuda").to(torch.bfloat16).requires_grad_()
+    w1 = (torch.randn(I, H, device="cuda") * 0.03).to(torch.bfloat16).requires_grad_()
+    b1 = (torch.randn(I, device="cuda") * 0.1).to(torch.bfloat16).requires_grad_()
+    w2 = (torch.randn(H, I, device="cuda") * 0.03).to(torch.bfloat16).requires_grad_()
+    b2 = (torch.randn(H, device="cuda") * 0.1).to(torch.bfloat16).requires_grad_()
+    res = torch.randn(M, H, device="cuda").to(torch.bfloat16).requires_grad_()
+    y = g.ffn(x, w1, b1, w2, b2, res)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    fs = [t.detach().float().requires_grad_() for t in (x, w1, b1, w2, b2, res)]
+    yr = F.linear(F.gelu(F.linear(fs[0], fs[1], fs[2])), fs[3], fs[4]) + fs[5]
+    yr.backward(dy.float())
+    rel = lambda u, v: ((u.float() - v).abs().max() / v.abs().max()).item()
+    errs = [rel(y, yr)] + [rel(t.grad, f.grad) for t, f in zip((x, w1, b1, w2, b2, res), fs)]
+    assert max(errs) < 3e-2, errs
