@@ -1,0 +1,610 @@
+// Self-attention for BERT (head_dim 64, sequence 128..512, right-padding mask, dropout) on the
+// 5th-generation tensor cores (K11; BASELINE.json:5 "softmax/attention").
+//
+// Layout: the QKV projection leaves one packed matrix  qkv[B*S, 3H]  (row = token; columns
+// q|k|v, each H = heads*64 wide).  Every operand tile this kernel touches is a [128 rows x 64
+// columns] bf16 box of that matrix, fetched by ONE tensor map with the 128-byte swizzle, so
+// the same shared-memory tile serves as a K-major operand (reduction over head_dim) and as an
+// MN-major operand (reduction over sequence positions).  Output ctx[B*S, H]; backward writes
+// the packed gradient dqkv[B*S, 3H] directly (no concatenation pass).
+//
+// Forward, one CTA per (batch, head, 128-query tile), 128 threads (thread = query row):
+//   TMA   : Q tile, K tiles, V tiles (only the tiles below the sequence's valid length)
+//   MMA 1 : S = Q K^T                      tcgen05.mma SS, fp32 accumulators in TMEM [0, Skv)
+//   soft  : row max / exp2 / row sum on TMEM rows (tcgen05.ld), dropout, P -> bf16 written back
+//           over the S columns it came from (tcgen05.st)
+//   MMA 2 : O = P V                        tcgen05.mma TS: A = P from TMEM, B = V tiles (MN-major)
+//   epil. : O / rowsum -> bf16 ctx, LSE saved for backward
+//
+// Backward, one CTA per (batch, head, 128-key tile), looping over query tiles; everything is
+// computed transposed (rows = keys) so that P^T and dS^T come out of the softmax threads as
+// K-major A operands, and the very same dS^T tile read MN-major is the A operand of dQ:
+//   S^T = K Q^T, dP^T = V dO^T  ->  P^T, dS^T (bf16, swizzled smem)  ->
+//   dV += P^T dO, dK += dS^T Q (TMEM accumulators across query tiles), dQ = dS K (per tile;
+//   written straight to dqkv when the sequence has one key tile, else red.add into fp32).
+#include <math.h>
+
+#include <mutex>
+
+#include "../include/b200ddl.h"
+#include "common.cuh"
+#include "tcgen05.cuh"
+
+using namespace tc;
+
+namespace {
+
+constexpr int D = 64;          // head dim
+constexpr int TILE = 128;      // query / key tile
+constexpr int kTileBytes = TILE * D * 2;  // 16 KB
+constexpr float kLog2e = 1.4426950408889634f;
+
+struct AttnParams {
+    int B, S, heads, H;        // H = heads * 64
+    const int* seqlens;        // [B] valid lengths (right padding) or null
+    bf16* ctx;                 // [B*S, H]
+    float* lse;                // [B, heads, S]  (natural log of the softmax denominator, incl. max)
+    float scale;               // 1/sqrt(64)
+    uint32_t drop_thr;         // byte threshold (p = thr/256), 0 = no dropout
+    float drop_scale;          // 1/(1-p)
+    uint64_t seed;
+    const uint64_t* seed_dev;
+    // backward
+    const float* dvec;         // [B, heads, S] rowsum(dO * O)
+    bf16* dqkv;                // [B*S, 3H]
+    float* dq_acc;             // [B*S, H] fp32, only when S > 128
+};
+
+// 4 dropout decisions (bits) for elements (q, kv4*4 .. kv4*4+3) of head `bh`
+__device__ __forceinline__ uint32_t drop_keep4(uint64_t seed, uint32_t bh, uint32_t q, uint32_t kv4, uint32_t S, uint32_t thr) {
+    const uint64_t idx = ((uint64_t)bh * S + q) * (S >> 2) + kv4;
+    const uint32_t h = hash_u32(seed, idx);
+    uint32_t m = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) m |= (((h >> (8 * i)) & 0xffu) >= thr ? 1u : 0u) << i;
+    return m;
+}
+
+__device__ __forceinline__ uint64_t resolve_seed(uint64_t seed, const uint64_t* seed_dev, uint32_t thr) {
+    if (thr && seed_dev) seed ^= (*seed_dev + 0x632BE59BD9B4E019ull) * 0x9E3779B97F4A7C15ull;
+    return seed;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// ------------------------------------------------------------------------------------------------
+// forward
+// ------------------------------------------------------------------------------------------------
+template <int kMaxKvTiles>
+__global__ void __launch_bounds__(128, 1) attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* sQ = smem;
+    uint8_t* sK = sQ + kTileBytes;
+    uint8_t* sV = sK + kMaxKvTiles * kTileBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sV + kMaxKvTiles * kTileBytes);  // [0] load, [1] S ready, [2] O ready
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q_tile = blockIdx.x, hd = blockIdx.y, b = blockIdx.z;
+    const int kv_len = p.seqlens ? min(max(p.seqlens[b], 1), p.S) : p.S;
+    const int n_kv = (kv_len + TILE - 1) / TILE;
+    constexpr uint32_t kTmemCols = kMaxKvTiles == 1 ? 256 : 512;
+    const uint32_t o_col = (kMaxKvTiles * TILE < 512) ? (uint32_t)(kMaxKvTiles * TILE) : 256u;
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&tma_qkv);
+        for (int i = 0; i < 3; ++i) mbar_init(&bars[i], 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc(tmem_ptr_smem, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    const int row0 = b * p.S + q_tile * TILE;
+    if (threadIdx.x == 0) {
+        mbar_expect_tx(&bars[0], (uint32_t)((1 + 2 * n_kv) * kTileBytes));
+        tma_load_2d(sQ, &tma_qkv, &bars[0], hd * D, row0);
+        for (int j = 0; j < n_kv; ++j) {
+            tma_load_2d(sK + j * kTileBytes, &tma_qkv, &bars[0], p.H + hd * D, b * p.S + j * TILE);
+            tma_load_2d(sV + j * kTileBytes, &tma_qkv, &bars[0], 2 * p.H + hd * D, b * p.S + j * TILE);
+        }
+        // ---- MMA 1: S = Q K^T
+        mbar_wait(&bars[0], 0);
+        tc_fence_after();
+        constexpr uint32_t idesc_s = make_idesc(TILE, TILE, false, false);
+        for (int j = 0; j < n_kv; ++j) {
+#pragma unroll
+            for (int k = 0; k < D / 16; ++k) {
+                const uint64_t da = make_smem_desc(smem_u32(sQ) + k * 32, 16, 1024);
+                const uint64_t db = make_smem_desc(smem_u32(sK + j * kTileBytes) + k * 32, 16, 1024);
+                umma_bf16(tmem_base + j * TILE, da, db, idesc_s, k > 0 ? 1u : 0u);
+            }
+        }
+        umma_commit(&bars[1]);
+    }
+
+    // ---- softmax: thread = query row, its TMEM lane is (warp*32 + lane)
+    const int r = threadIdx.x;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+    const float sl2 = p.scale * kLog2e;
+    const uint64_t seed = resolve_seed(p.seed, p.seed_dev, p.drop_thr);
+    mbar_wait(&bars[1], 0);
+    __syncwarp();
+    tc_fence_after();
+    const int n_chunks = n_kv * (TILE / 32);
+    float mx = -INFINITY;
+    for (int c = 0; c < n_chunks; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(lane_addr + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            if (c * 32 + j < kv_len) mx = fmaxf(mx, __uint_as_float(v[j]));
+    }
+    const float mxs = mx * sl2;
+    float sum = 0.f;
+    const uint32_t bh = (uint32_t)(b * p.heads + hd);
+    const uint32_t q_idx = (uint32_t)(q_tile * TILE + r);
+    for (int c = 0; c < n_chunks; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(lane_addr + c * 32, v);
+        tmem_ld_wait();
+        uint32_t packed[16];
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4) {
+            float e[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const int col = c * 32 + j4 * 4 + t;
+                e[t] = col < kv_len ? exp2f(__uint_as_float(v[j4 * 4 + t]) * sl2 - mxs) : 0.f;
+                sum += e[t];
+            }
+            if (p.drop_thr) {
+                const uint32_t keep = drop_keep4(seed, bh, q_idx, (uint32_t)(c * 8 + j4), (uint32_t)p.S, p.drop_thr);
+#pragma unroll
+                for (int t = 0; t < 4; ++t) e[t] = ((keep >> t) & 1u) ? e[t] : 0.f;
+            }
+            packed[j4 * 2] = pack_bf16x2(e[0], e[1]);
+            packed[j4 * 2 + 1] = pack_bf16x2(e[2], e[3]);
+        }
+        // P (bf16 pairs) overwrites S columns [16c, 16c+16): already consumed (16c+15 <= 32c+31)
+        tmem_st_32x16(lane_addr + c * 16, packed);
+    }
+    tmem_st_wait();
+    tc_fence_before();
+    __syncthreads();
+
+    if (threadIdx.x == 0) {
+        tc_fence_after();
+        // ---- MMA 2: O = P V   (A from TMEM, B = V tile read MN-major: N = head_dim contiguous, K = key rows)
+        constexpr uint32_t idesc_o = make_idesc(TILE, D, false, true);
+        for (int j = 0; j < n_kv; ++j) {
+#pragma unroll
+            for (int k = 0; k < TILE / 16; ++k) {
+                const uint64_t db = make_smem_desc(smem_u32(sV + j * kTileBytes) + k * 2048, 8192, 1024);
+                umma_bf16_ts(tmem_base + o_col, tmem_base + j * (TILE / 2) + k * 8, db, idesc_o, (j > 0 || k > 0) ? 1u : 0u);
+            }
+        }
+        umma_commit(&bars[2]);
+    }
+    mbar_wait(&bars[2], 0);
+    __syncwarp();
+    tc_fence_after();
+    {
+        const float inv = (p.drop_thr ? p.drop_scale : 1.f) / sum;
+        bf16* out = p.ctx + (size_t)(row0 + r) * p.H + hd * D;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            uint32_t v[32];
+            tmem_ld_32x32(lane_addr + o_col + c * 32, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+                float o[8];
+#pragma unroll
+                for (int t = 0; t < 8; ++t) o[t] = __uint_as_float(v[j + t]) * inv;
+                st_global_v4(out + c * 32 + j, float_to_bf16x8(o));
+            }
+        }
+        if (p.lse) p.lse[((size_t)b * p.heads + hd) * p.S + q_tile * TILE + r] = mx * p.scale + __logf(sum);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// D[b, h, s] = sum_d dO[b, s, h, d] * O[b, s, h, d]
+__global__ void attn_dvec_kernel(const bf16* __restrict__ dO, const bf16* __restrict__ O, float* __restrict__ dvec, int B, int S, int heads) {
+    const size_t total = (size_t)B * S * heads;
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= total) return;
+    const int hd = (int)(t % heads);
+    const size_t tok = t / heads;
+    const int s = (int)(tok % S), b = (int)(tok / S);
+    const bf16* a = dO + tok * heads * D + hd * D;
+    const bf16* o = O + tok * heads * D + hd * D;
+    float acc = 0.f;
+#pragma unroll
+    for (int j = 0; j < D; j += 8) {
+        float x[8], y[8];
+        bf16x8_to_float(ld_global_v4(a + j), x);
+        bf16x8_to_float(ld_global_v4(o + j), y);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) acc += x[q] * y[q];
+    }
+    dvec[((size_t)b * heads + hd) * S + s] = acc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward
+// ------------------------------------------------------------------------------------------------
+// write 8 bf16 (one 16-byte chunk) of row `row`, logical chunk `chunk` (0..15 across 128 columns)
+// into a [128 x 128] bf16 tile stored as two [128 x 64] K-major 128B-swizzled blocks
+__device__ __forceinline__ void st_swizzled_chunk(uint8_t* tile, int row, int chunk, uint4 v) {
+    const int blk = chunk >> 3, cc = chunk & 7;
+    uint8_t* dst = tile + blk * kTileBytes + row * 128 + ((cc ^ (row & 7)) << 4);
+    *reinterpret_cast<uint4*>(dst) = v;
+}
+
+__global__ void __launch_bounds__(128, 1) attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
+                                                          const __grid_constant__ CUtensorMap tma_do, const AttnParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* sK = smem;                      // [128 kv x 64]
+    uint8_t* sV = sK + kTileBytes;
+    uint8_t* sQ = sV + kTileBytes;           // [128 q x 64]
+    uint8_t* sdO = sQ + kTileBytes;
+    uint8_t* sPt = sdO + kTileBytes;         // P^T  [128 kv x 128 q], two swizzled 64-column blocks
+    uint8_t* sdSt = sPt + 2 * kTileBytes;    // dS^T
+    float* sLse = reinterpret_cast<float*>(sdSt + 2 * kTileBytes);  // [128]
+    float* sDv = sLse + TILE;                                       // [128]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sDv + TILE);      // [0] kv load, [1] q load, [2] S/dP ready, [3] grads ready
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int kv_tile = blockIdx.x, hd = blockIdx.y, b = blockIdx.z;
+    const int kv_len = p.seqlens ? min(max(p.seqlens[b], 1), p.S) : p.S;
+    const int n_q = p.S / TILE;
+    const bool single = p.S == TILE;
+    // TMEM columns: S^T [0,128) dP^T [128,256) dV [256,320) dK [320,384) dQ [384,448)
+    constexpr uint32_t kTmemCols = 512, cST = 0, cDP = 128, cDV = 256, cDK = 320, cDQ = 384;
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&tma_qkv);
+        tma_prefetch_desc(&tma_do);
+        for (int i = 0; i < 4; ++i) mbar_init(&bars[i], 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc(tmem_ptr_smem, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+
+    const int kv_row0 = b * p.S + kv_tile * TILE;
+    const int r = threadIdx.x;                      // this thread's key row inside the tile
+    const int kv_idx = kv_tile * TILE + r;
+    const bool kv_valid = kv_idx < kv_len;
+    const bool tile_empty = kv_tile * TILE >= kv_len;  // fully padded key tile: gradients are zero
+    const float sl2 = p.scale * kLog2e;
+    const uint64_t seed = resolve_seed(p.seed, p.seed_dev, p.drop_thr);
+    const uint32_t bh = (uint32_t)(b * p.heads + hd);
+
+    if (!tile_empty) {
+        if (threadIdx.x == 0) {
+            mbar_expect_tx(&bars[0], 2 * kTileBytes);
+            tma_load_2d(sK, &tma_qkv, &bars[0], p.H + hd * D, kv_row0);
+            tma_load_2d(sV, &tma_qkv, &bars[0], 2 * p.H + hd * D, kv_row0);
+        }
+        uint32_t ph = 0;
+        for (int qi = 0; qi < n_q; ++qi) {
+            const int q_row0 = b * p.S + qi * TILE;
+            if (threadIdx.x == 0) {
+                mbar_expect_tx(&bars[1], 2 * kTileBytes);
+                tma_load_2d(sQ, &tma_qkv, &bars[1], hd * D, q_row0);
+                tma_load_2d(sdO, &tma_do, &bars[1], hd * D, q_row0);
+            }
+            sLse[r] = p.lse[((size_t)b * p.heads + hd) * p.S + qi * TILE + r] * kLog2e;
+            sDv[r] = p.dvec[((size_t)b * p.heads + hd) * p.S + qi * TILE + r];
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                if (qi == 0) mbar_wait(&bars[0], 0);
+                mbar_wait(&bars[1], ph);
+                tc_fence_after();
+                constexpr uint32_t idesc = make_idesc(TILE, TILE, false, false);
+#pragma unroll
+                for (int k = 0; k < D / 16; ++k) {  // S^T = K Q^T
+                    umma_bf16(tmem_base + cST, make_smem_desc(smem_u32(sK) + k * 32, 16, 1024), make_smem_desc(smem_u32(sQ) + k * 32, 16, 1024),
+                              idesc, k > 0 ? 1u : 0u);
+                }
+#pragma unroll
+                for (int k = 0; k < D / 16; ++k) {  // dP^T = V dO^T
+                    umma_bf16(tmem_base + cDP, make_smem_desc(smem_u32(sV) + k * 32, 16, 1024), make_smem_desc(smem_u32(sdO) + k * 32, 16, 1024),
+                              idesc, k > 0 ? 1u : 0u);
+                }
+                umma_commit(&bars[2]);
+            }
+            mbar_wait(&bars[2], ph);
+            __syncwarp();
+            tc_fence_after();
+            // ---- softmax backward on row `r` (a key), columns = queries of this tile
+#pragma unroll 1
+            for (int c = 0; c < TILE / 32; ++c) {
+                uint32_t s[32], dp[32];
+                tmem_ld_32x32(lane_addr + cST + c * 32, s);
+                tmem_ld_32x32(lane_addr + cDP + c * 32, dp);
+                tmem_ld_wait();
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    float pt[8], ds[8];
+#pragma unroll
+                    for (int t = 0; t < 8; ++t) {
+                        const int qc = c * 32 + g * 8 + t;
+                        float pv = kv_valid ? exp2f(__uint_as_float(s[g * 8 + t]) * sl2 - sLse[qc]) : 0.f;
+                        float dpv = __uint_as_float(dp[g * 8 + t]);
+                        float pdrop = pv;
+                        if (p.drop_thr) {
+                            const uint32_t keep = drop_keep4(seed, bh, (uint32_t)(qi * TILE + qc), (uint32_t)(kv_idx >> 2), (uint32_t)p.S, p.drop_thr);
+                            const bool kept = (keep >> (kv_idx & 3)) & 1u;
+                            pdrop = kept ? pv * p.drop_scale : 0.f;
+                            dpv = kept ? dpv * p.drop_scale : 0.f;
+                        }
+                        pt[t] = pdrop;
+                        ds[t] = pv * (dpv - sDv[qc]) * p.scale;
+                    }
+                    st_swizzled_chunk(sPt, r, c * 4 + g, float_to_bf16x8(pt));
+                    st_swizzled_chunk(sdSt, r, c * 4 + g, float_to_bf16x8(ds));
+                }
+            }
+            fence_proxy_async();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
+            tc_fence_before();
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                tc_fence_after();
+                constexpr uint32_t idesc_kmaj_bmn = make_idesc(TILE, D, false, true);
+                constexpr uint32_t idesc_amn_bmn = make_idesc(TILE, D, true, true);
+                // dV += P^T dO ; dK += dS^T Q : A K-major [kv x q] (two 64-column blocks), B MN-major (N = d, K = q rows)
+#pragma unroll
+                for (int k = 0; k < TILE / 16; ++k) {
+                    const uint32_t a_off = (k >> 2) * kTileBytes + (k & 3) * 32;
+                    umma_bf16(tmem_base + cDV, make_smem_desc(smem_u32(sPt) + a_off, 16, 1024),
+                              make_smem_desc(smem_u32(sdO) + k * 2048, 8192, 1024), idesc_kmaj_bmn, (qi > 0 || k > 0) ? 1u : 0u);
+                }
+#pragma unroll
+                for (int k = 0; k < TILE / 16; ++k) {
+                    const uint32_t a_off = (k >> 2) * kTileBytes + (k & 3) * 32;
+                    umma_bf16(tmem_base + cDK, make_smem_desc(smem_u32(sdSt) + a_off, 16, 1024),
+                              make_smem_desc(smem_u32(sQ) + k * 2048, 8192, 1024), idesc_kmaj_bmn, (qi > 0 || k > 0) ? 1u : 0u);
+                }
+                // dQ = dS K : A = dS^T tile read MN-major (M = q contiguous: 64-wide blocks kTileBytes apart, K = kv rows),
+                //             B = K tile read MN-major (N = d, K = kv rows)
+#pragma unroll
+                for (int k = 0; k < TILE / 16; ++k) {
+                    umma_bf16(tmem_base + cDQ, make_smem_desc(smem_u32(sdSt) + k * 2048, kTileBytes, 1024),
+                              make_smem_desc(smem_u32(sK) + k * 2048, 8192, 1024), idesc_amn_bmn, k > 0 ? 1u : 0u);
+                }
+                umma_commit(&bars[3]);
+            }
+            mbar_wait(&bars[3], ph);
+            __syncwarp();
+            tc_fence_after();
+            // dQ rows = queries (TMEM lane = query index inside the tile)
+            {
+                const size_t tok = (size_t)q_row0 + r;
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(lane_addr + cDQ + c * 32, v);
+                    tmem_ld_wait();
+                    if (single) {
+                        bf16* dst = p.dqkv + tok * 3 * p.H + hd * D + c * 32;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 8) {
+                            float o[8];
+#pragma unroll
+                            for (int t = 0; t < 8; ++t) o[t] = __uint_as_float(v[j + t]);
+                            st_global_v4(dst + j, float_to_bf16x8(o));
+                        }
+                    } else {
+                        float* dst = p.dq_acc + tok * p.H + hd * D + c * 32;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4)
+                            red_add_f32x4(dst + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                                          __uint_as_float(v[j + 3]));
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncthreads();  // TMEM S/dP/dQ columns and the Q/dO/P^T/dS^T tiles are free again
+            ph ^= 1;
+        }
+    }
+    // ---- dK, dV rows = keys
+    {
+        const size_t tok = (size_t)kv_row0 + r;
+        bf16* dk = p.dqkv + tok * 3 * p.H + p.H + hd * D;
+        bf16* dv = p.dqkv + tok * 3 * p.H + 2 * p.H + hd * D;
+        if (tile_empty) {
+            const uint4 z = make_uint4(0, 0, 0, 0);
+#pragma unroll
+            for (int j = 0; j < D; j += 8) {
+                st_global_v4(dk + j, z);
+                st_global_v4(dv + j, z);
+            }
+        } else {
+            tc_fence_after();
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                uint32_t a[32], g[32];
+                tmem_ld_32x32(lane_addr + cDK + c * 32, a);
+                tmem_ld_32x32(lane_addr + cDV + c * 32, g);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                    float o[8], w[8];
+#pragma unroll
+                    for (int t = 0; t < 8; ++t) {
+                        o[t] = __uint_as_float(a[j + t]);
+                        w[t] = __uint_as_float(g[j + t]);
+                    }
+                    st_global_v4(dk + c * 32 + j, float_to_bf16x8(o));
+                    st_global_v4(dv + c * 32 + j, float_to_bf16x8(w));
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// dq_acc [tokens, H] fp32 -> q part of dqkv [tokens, 3H] bf16
+__global__ void attn_dq_convert_kernel(const float* __restrict__ acc, bf16* __restrict__ dqkv, size_t tokens, int H) {
+    const int vc = H >> 3;
+    const size_t total = tokens * vc;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const size_t tok = t / vc;
+        const int c8 = (int)(t % vc);
+        float f[8];
+        *reinterpret_cast<float4*>(&f[0]) = *reinterpret_cast<const float4*>(acc + tok * H + c8 * 8);
+        *reinterpret_cast<float4*>(&f[4]) = *reinterpret_cast<const float4*>(acc + tok * H + c8 * 8 + 4);
+        st_global_v4(dqkv + tok * 3 * H + c8 * 8, float_to_bf16x8(f));
+    }
+}
+
+// ---------------------------------------------------------------------------- host
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode = nullptr;
+std::once_flag g_once;
+
+int make_tile_map(CUtensorMap* map, const void* ptr, long long rows, long long cols) {
+    std::call_once(g_once, [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            g_encode = (EncodeTiledFn)fn;
+    });
+    DDL_REQUIRE(g_encode != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
+    DDL_REQUIRE(((uintptr_t)ptr & 15) == 0 && cols % 8 == 0, "attention: operand must be 16-byte aligned with a pitch multiple of 8");
+    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t gstride[1] = {(cuuint64_t)cols * 2};
+    cuuint32_t box[2] = {64u, 128u};
+    cuuint32_t estr[2] = {1u, 1u};
+    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DDL_REQUIRE(r == CUDA_SUCCESS, "attention: cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return 0;
+}
+
+int fill_params(AttnParams* p, int B, int S, int heads, const int* seqlens, float dropout_p, unsigned long long seed,
+                const unsigned long long* seed_dev) {
+    DDL_REQUIRE(S % TILE == 0 && S >= TILE && S <= 512, "attention: sequence length %d must be a multiple of 128 in [128, 512]", S);
+    DDL_REQUIRE(B >= 1 && heads >= 1, "attention: bad shape");
+    p->B = B; p->S = S; p->heads = heads; p->H = heads * D;
+    p->seqlens = seqlens;
+    p->scale = 0.125f;
+    int thr = (int)(dropout_p * 256.f + 0.5f);
+    thr = thr < 0 ? 0 : (thr > 255 ? 255 : thr);
+    p->drop_thr = (uint32_t)thr;
+    p->drop_scale = 1.f / (1.f - (float)thr / 256.f);
+    p->seed = seed;
+    p->seed_dev = (const uint64_t*)seed_dev;
+    p->ctx = nullptr; p->lse = nullptr; p->dvec = nullptr; p->dqkv = nullptr; p->dq_acc = nullptr;
+    return 0;
+}
+
+template <int KV>
+int launch_fwd(const CUtensorMap& map, const AttnParams& p, cudaStream_t s) {
+    constexpr int smem = (1 + 2 * KV) * kTileBytes + 64 + 1024;
+    static bool set = false;
+    if (!set) {
+        DDL_CHECK(cudaFuncSetAttribute(attn_fwd_kernel<KV>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        set = true;
+    }
+    dim3 grid(p.S / TILE, p.heads, p.B);
+    attn_fwd_kernel<KV><<<grid, 128, smem, s>>>(map, p);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace
+
+DDL_API int ddl_attention_fwd(const void* qkv, const int* seqlens, void* ctx, float* lse, int B, int S, int heads, float dropout_p,
+                              unsigned long long seed, const unsigned long long* seed_dev, void* stream_) {
+    AttnParams p;
+    if (int e = fill_params(&p, B, S, heads, seqlens, dropout_p, seed, seed_dev)) return e;
+    DDL_REQUIRE(qkv && ctx && lse, "attention fwd: null pointer");
+    p.ctx = (bf16*)ctx;
+    p.lse = lse;
+    CUtensorMap map;
+    if (int e = make_tile_map(&map, qkv, (long long)B * S, 3LL * p.H)) return e;
+    cudaStream_t s = (cudaStream_t)stream_;
+    switch (S / TILE) {
+        case 1: return launch_fwd<1>(map, p, s);
+        case 2: return launch_fwd<2>(map, p, s);
+        case 3: return launch_fwd<3>(map, p, s);
+        default: return launch_fwd<4>(map, p, s);
+    }
+}
+
+DDL_API size_t ddl_attention_bwd_scratch_bytes(int B, int S, int heads) {
+    size_t n = (size_t)B * heads * S * sizeof(float);                       // D vector
+    if (S > TILE) n += (size_t)B * S * heads * D * sizeof(float);           // fp32 dQ accumulator
+    return n;
+}
+
+DDL_API int ddl_attention_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse, const int* seqlens, void* dqkv,
+                              void* scratch, size_t scratch_bytes, int B, int S, int heads, float dropout_p, unsigned long long seed,
+                              const unsigned long long* seed_dev, void* stream_) {
+    AttnParams p;
+    if (int e = fill_params(&p, B, S, heads, seqlens, dropout_p, seed, seed_dev)) return e;
+    DDL_REQUIRE(qkv && ctx && dctx && lse && dqkv && scratch, "attention bwd: null pointer");
+    DDL_REQUIRE(scratch_bytes >= ddl_attention_bwd_scratch_bytes(B, S, heads), "attention bwd: scratch too small");
+    cudaStream_t s = (cudaStream_t)stream_;
+    float* dvec = (float*)scratch;
+    float* dq_acc = S > TILE ? dvec + (size_t)B * heads * S : nullptr;
+    p.lse = const_cast<float*>(lse);
+    p.dvec = dvec;
+    p.dqkv = (bf16*)dqkv;
+    p.dq_acc = dq_acc;
+    const size_t rows = (size_t)B * S * heads;
+    attn_dvec_kernel<<<(unsigned)((rows + 127) / 128), 128, 0, s>>>((const bf16*)dctx, (const bf16*)ctx, dvec, B, S, heads);
+    DDL_LAUNCH_CHECK();
+    if (dq_acc) DDL_CHECK(cudaMemsetAsync(dq_acc, 0, (size_t)B * S * p.H * sizeof(float), s));
+    CUtensorMap mq, md;
+    if (int e = make_tile_map(&mq, qkv, (long long)B * S, 3LL * p.H)) return e;
+    if (int e = make_tile_map(&md, dctx, (long long)B * S, (long long)p.H)) return e;
+    constexpr int smem = 8 * kTileBytes + 2 * TILE * 4 + 64 + 1024;
+    static bool set = false;
+    if (!set) {
+        DDL_CHECK(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        set = true;
+    }
+    dim3 grid(S / TILE, heads, B);
+    attn_bwd_kernel<<<grid, 128, smem, s>>>(mq, md, p);
+    DDL_LAUNCH_CHECK();
+    if (dq_acc) {
+        const size_t total = (size_t)B * S * (p.H / 8);
+        int blocks = (int)((total + 255) / 256);
+        if (blocks > DDL_SM_COUNT * 8) blocks = DDL_SM_COUNT * 8;
+        attn_dq_convert_kernel<<<blocks, 256, 0, s>>>(dq_acc, (bf16*)dqkv, (size_t)B * S, p.H);
+        DDL_LAUNCH_CHECK();
+    }
+    return 0;
+}

@@ -24,10 +24,10 @@
 #include <cuda.h>
 
 #include <mutex>
-#include <unordered_map>
 
 #include "../include/b200ddl.h"
 #include "common.cuh"
+#include "tcgen05.cuh"
 
 namespace {
 
@@ -37,106 +37,7 @@ constexpr int UMMA_K = 16;
 constexpr int kEpiWarps = 8;
 constexpr int kThreads = (2 + kEpiWarps) * 32;
 
-// ---------------------------------------------------------------------------- PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_LOOP:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE;\n"
-        "bra WAIT_LOOP;\n"
-        "DONE:\n"
-        "}\n" ::"r"(smem_u32(bar)),
-        "r"(parity)
-        : "memory");
-}
-__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(smem_dst)),
-        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
-        : "memory");
-}
-__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
-}
-
-__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-// D[tmem] (+)= A[smem desc] * B[smem desc]
-__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
-        "}\n" ::"r"(d_tmem),
-        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-// arrive on an mbarrier once all previously issued MMAs of this thread have completed
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-// 32 lanes x 32 columns of fp32: thread i of the warp gets row (lane base + i), 32 consecutive columns
-__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
-          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
-          "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
-          "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-        : "r"(taddr)
-        : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-__device__ __forceinline__ void red_add_f32x4(float* p, float a, float b, float c, float d) {
-    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
-}
-
-// ---------------------------------------------------------------------------- descriptors
-// Shared-memory matrix descriptor, 128-byte swizzle (layout type 2), version 1 (Blackwell).
-//   K-major : rows of 128 B (64 bf16 along K), 8-row groups 1024 B apart (SBO); LBO unused (1).
-//   MN-major: rows of 128 B (64 bf16 along M/N), 8 k-rows = 1024 B (SBO), next 64-wide MN
-//             block `lbo_bytes` further on (LBO).
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
-    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
-    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
-    d |= (uint64_t)1 << 46;  // descriptor version
-    d |= (uint64_t)2 << 61;  // SWIZZLE_128B
-    return d;
-}
-// Instruction descriptor (kind::f16): D fp32, A/B bf16, majorness bits, N>>3 at [17,23), M>>4 at [24,29)
-__host__ __device__ constexpr uint32_t make_idesc(int m, int n, bool a_mn, bool b_mn) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn ? 1u : 0u) << 15) | ((b_mn ? 1u : 0u) << 16) | ((uint32_t)(n >> 3) << 17) |
-           ((uint32_t)(m >> 4) << 24);
-}
+using namespace tc;
 
 // ---------------------------------------------------------------------------- epilogue math
 __device__ __forceinline__ float erf_fast(float x) {
@@ -390,28 +291,52 @@ __global__ void f32_to_bf16_kernel(const float* __restrict__ in, bf16* __restric
 }
 
 // column sums of a bf16 [rows, cols] matrix (bias gradient): out[c] = sum_r x[r, c]
+// block = 32 column-vectors (512 contiguous bytes per warp) x 8 rows; grid.y splits the rows
 __global__ void __launch_bounds__(256) colsum_partial_kernel(const bf16* __restrict__ x, int rows, int cols, long long ld,
                                                              float* __restrict__ partials) {
-    // block handles a 256-column-vector slab? simpler: thread = one 8-column group, grid.y splits rows
-    const int vc = blockIdx.x * blockDim.x + threadIdx.x;
-    if (vc * 8 >= cols) return;
+    __shared__ float sh[8][32 * 8 + 1];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int vc = blockIdx.x * 32 + tx;
+    const bool ok = vc * 8 < cols;
     float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int r = blockIdx.y; r < rows; r += gridDim.y) {
-        float f[8];
-        bf16x8_to_float(ld_stream_v4(x + (size_t)r * ld + vc * 8), f);
+    if (ok) {
+        for (int r = blockIdx.y * 8 + ty; r < rows; r += gridDim.y * 8 * 2) {
+            uint4 u0 = ld_stream_v4(x + (size_t)r * ld + vc * 8), u1;
+            const int r1 = r + gridDim.y * 8;
+            const bool has1 = r1 < rows;
+            if (has1) u1 = ld_stream_v4(x + (size_t)r1 * ld + vc * 8);
+            float f[8];
+            bf16x8_to_float(u0, f);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) s[j] += f[j];
+            for (int j = 0; j < 8; ++j) s[j] += f[j];
+            if (has1) {
+                bf16x8_to_float(u1, f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) s[j] += f[j];
+            }
+        }
     }
-    float* o = partials + (size_t)blockIdx.y * cols + vc * 8;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) o[j] = s[j];
+    for (int j = 0; j < 8; ++j) sh[ty][tx * 8 + j] = s[j];
+    __syncthreads();
+    const int col = threadIdx.x;  // 0..255 = (tx, j)
+    float a = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) a += sh[w][col];
+    const int c = blockIdx.x * 256 + col;
+    if (c < cols) partials[(size_t)blockIdx.y * cols + c] = a;
 }
 __global__ void colsum_final_kernel(const float* __restrict__ partials, int nparts, int cols, bf16* __restrict__ out) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= cols) return;
+    // 8 threads per column group fold `nparts` rows in parallel, then a shuffle folds the 8
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int c = t >> 3, sub = t & 7;
     float a = 0.f;
-    for (int i = 0; i < nparts; ++i) a += partials[(size_t)i * cols + c];
-    out[c] = __float2bfloat16(a);
+    if (c < cols)
+        for (int i = sub; i < nparts; i += 8) a += partials[(size_t)i * cols + c];
+    a += __shfl_xor_sync(0xffffffffu, a, 1);
+    a += __shfl_xor_sync(0xffffffffu, a, 2);
+    a += __shfl_xor_sync(0xffffffffu, a, 4);
+    if (c < cols && sub == 0) out[c] = __float2bfloat16(a);
 }
 
 // ---------------------------------------------------------------------------- host side
@@ -533,20 +458,25 @@ DDL_API int ddl_f32_to_bf16(const float* in, void* out, size_t numel, int accumu
     return 0;
 }
 
-DDL_API size_t ddl_colsum_scratch_bytes(int rows, int cols) {
-    int parts = rows < 128 ? rows : 128;
-    return (size_t)parts * cols * sizeof(float);
+static int colsum_parts(int rows, int cols) {
+    const int col_tiles = (cols / 8 + 31) / 32;
+    int parts = (DDL_SM_COUNT * 6 + col_tiles - 1) / col_tiles;  // ~6 blocks per SM in total
+    const int max_parts = (rows + 15) / 16;
+    if (parts > max_parts) parts = max_parts;
+    return parts < 1 ? 1 : parts;
 }
+
+DDL_API size_t ddl_colsum_scratch_bytes(int rows, int cols) { return (size_t)colsum_parts(rows, cols) * cols * sizeof(float); }
 
 DDL_API int ddl_colsum_bf16(const void* x, int rows, int cols, long long ld, void* out, void* scratch, size_t scratch_bytes, void* stream_) {
     DDL_REQUIRE(cols % 8 == 0 && ld % 8 == 0, "ddl_colsum_bf16: cols and ld must be multiples of 8");
     DDL_REQUIRE(scratch_bytes >= ddl_colsum_scratch_bytes(rows, cols), "ddl_colsum_bf16: scratch too small");
-    const int parts = rows < 128 ? rows : 128;
-    dim3 grid(ddl_ceil_div(cols / 8, 256), parts);
+    const int parts = colsum_parts(rows, cols);
+    dim3 grid((cols / 8 + 31) / 32, parts);
     cudaStream_t s = (cudaStream_t)stream_;
     colsum_partial_kernel<<<grid, 256, 0, s>>>((const bf16*)x, rows, cols, ld, (float*)scratch);
     DDL_LAUNCH_CHECK();
-    colsum_final_kernel<<<ddl_ceil_div(cols, 256), 256, 0, s>>>((const float*)scratch, parts, cols, (bf16*)out);
+    colsum_final_kernel<<<ddl_ceil_div((long long)cols * 8, 256), 256, 0, s>>>((const float*)scratch, parts, cols, (bf16*)out);
     DDL_LAUNCH_CHECK();
     return 0;
 }

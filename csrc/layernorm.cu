@@ -107,43 +107,55 @@ __global__ void __launch_bounds__(kLnThreads) add_ln_fwd_kernel(const bf16* __re
 // dz = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * gamma
 // dx = dz * keep * scale (only when dropout is active; else dx aliases dz on the host side)
 template <int VPL>
-__global__ void __launch_bounds__(kLnThreads) ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z,
-                                                            const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
-                                                            const bf16* __restrict__ gamma, bf16* __restrict__ dz,
-                                                            bf16* __restrict__ dx, float* __restrict__ partials, int rows, int H,
-                                                            DropCfg drop) {
+__global__ void __launch_bounds__(kLnThreads, (VPL <= 3 ? 2 : 1)) ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z,
+                                                               const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
+                                                               const bf16* __restrict__ gamma, bf16* __restrict__ dz,
+                                                               bf16* __restrict__ dx, float* __restrict__ partials, int rows, int H,
+                                                               DropCfg drop) {
     resolve_seed(drop);
     __shared__ float red[kWarpsPerBlock][32 * 8 + 1];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nv = H >> 3;
     const float inv_h = 1.f / (float)H;
-    float dgam[VPL][8], dbet[VPL][8], gam[VPL][8];
+    // accumulators in fp32; everything else stays packed (bf16x8 = 4 registers) to keep two
+    // blocks resident per SM
+    float dgam[VPL][8], dbet[VPL][8];
+    uint4 gam[VPL];
 #pragma unroll
     for (int k = 0; k < VPL; ++k) {
         const int c = lane + 32 * k;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) dgam[k][j] = dbet[k][j] = gam[k][j] = 0.f;
-        if (c < nv) bf16x8_to_float(ld_global_v4(gamma + c * 8), gam[k]);
+        for (int j = 0; j < 8; ++j) dgam[k][j] = dbet[k][j] = 0.f;
+        gam[k] = make_uint4(0, 0, 0, 0);
+        if (c < nv) gam[k] = ld_global_v4(gamma + c * 8);
     }
     for (long long row = (long long)blockIdx.x * kWarpsPerBlock + warp; row < rows; row += (long long)gridDim.x * kWarpsPerBlock) {
         const float mean = mean_in[row], rstd = rstd_in[row];
-        float g[VPL][8], xh[VPL][8];
-        float s1 = 0.f, s2 = 0.f;
+        uint4 dyv[VPL], zv[VPL];
 #pragma unroll
         for (int k = 0; k < VPL; ++k) {
             const int c = lane + 32 * k;
             if (c < nv) {
                 const size_t off = (size_t)row * H + c * 8;
-                float d[8], zz[8];
-                bf16x8_to_float(ld_stream_v4(dy + off), d);
-                bf16x8_to_float(ld_stream_v4(z + off), zz);
+                dyv[k] = ld_stream_v4(dy + off);
+                zv[k] = ld_stream_v4(z + off);
+            }
+        }
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < VPL; ++k) {
+            if (lane + 32 * k < nv) {
+                float d[8], zz[8], gm[8];
+                bf16x8_to_float(dyv[k], d);
+                bf16x8_to_float(zv[k], zz);
+                bf16x8_to_float(gam[k], gm);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
-                    xh[k][j] = (zz[j] - mean) * rstd;
-                    g[k][j] = d[j] * gam[k][j];
-                    s1 += g[k][j];
-                    s2 += g[k][j] * xh[k][j];
-                    dgam[k][j] += d[j] * xh[k][j];
+                    const float xh = (zz[j] - mean) * rstd;
+                    const float g = d[j] * gm[j];
+                    s1 += g;
+                    s2 += g * xh;
+                    dgam[k][j] += d[j] * xh;
                     dbet[k][j] += d[j];
                 }
             }
@@ -154,9 +166,12 @@ __global__ void __launch_bounds__(kLnThreads) ln_bwd_kernel(const bf16* __restri
             const int c = lane + 32 * k;
             if (c < nv) {
                 const size_t off = (size_t)row * H + c * 8;
-                float o[8];
+                float d[8], zz[8], gm[8], o[8];
+                bf16x8_to_float(dyv[k], d);
+                bf16x8_to_float(zv[k], zz);
+                bf16x8_to_float(gam[k], gm);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) o[j] = rstd * (g[k][j] - c1 - xh[k][j] * c2);
+                for (int j = 0; j < 8; ++j) o[j] = rstd * (d[j] * gm[j] - c1 - (zz[j] - mean) * rstd * c2);
                 st_global_v4(dz + off, float_to_bf16x8(o));
                 if (dx != nullptr && drop.thr) {
                     apply_dropout8(o, drop, ((size_t)row * nv + c));
@@ -186,12 +201,22 @@ __global__ void __launch_bounds__(kLnThreads) ln_bwd_kernel(const bf16* __restri
     }
 }
 
-__global__ void ln_bwd_finalize_kernel(const float* __restrict__ partials, int nblocks, int H, bf16* __restrict__ dgamma,
-                                       bf16* __restrict__ dbeta, float* __restrict__ dgamma_f32, float* __restrict__ dbeta_f32) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= 2 * H) return;
+// grid = ceil(2H / 32), block = 256: 8 warps fold the per-block partial rows in parallel
+__global__ void __launch_bounds__(256) ln_bwd_finalize_kernel(const float* __restrict__ partials, int nblocks, int H,
+                                                              bf16* __restrict__ dgamma, bf16* __restrict__ dbeta,
+                                                              float* __restrict__ dgamma_f32, float* __restrict__ dbeta_f32) {
+    __shared__ float sh[8][33];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int i = blockIdx.x * 32 + lane;
+    float a = 0.f;
+    if (i < 2 * H)
+        for (int b = w; b < nblocks; b += 8) a += partials[(size_t)b * 2 * H + i];
+    sh[w][lane] = a;
+    __syncthreads();
+    if (w != 0 || i >= 2 * H) return;
     float acc = 0.f;
-    for (int b = 0; b < nblocks; ++b) acc += partials[(size_t)b * 2 * H + i];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc += sh[k][lane];
     if (i < H) {
         if (dgamma) dgamma[i] = __float2bfloat16(acc);
         if (dgamma_f32) dgamma_f32[i] = acc;
@@ -349,7 +374,7 @@ DDL_API int ddl_layernorm_bwd(const void* dy, const void* z, const float* mean, 
                                                                   (bf16*)dx, (float*)scratch, rows, H, d)));
     DDL_LAUNCH_CHECK();
     const bool f32 = param_grad_dtype == DDL_F32;
-    ln_bwd_finalize_kernel<<<ddl_ceil_div(2 * H, 256), 256, 0, s>>>((const float*)scratch, grid, H, f32 ? nullptr : (bf16*)dgamma,
+    ln_bwd_finalize_kernel<<<ddl_ceil_div(2 * H, 32), 256, 0, s>>>((const float*)scratch, grid, H, f32 ? nullptr : (bf16*)dgamma,
                                                                     f32 ? nullptr : (bf16*)dbeta, f32 ? (float*)dgamma : nullptr,
                                                                     f32 ? (float*)dbeta : nullptr);
     DDL_LAUNCH_CHECK();

@@ -1,0 +1,182 @@
+// Pooling on NHWC bf16 activations (K14): the 3x3/stride-2/pad-1 max pool of
+// the ResNet stem (112^2 -> 56^2, reference model at notebooks/cv/onnx_experiments.py:19) and
+// the global average pool before the classifier (7^2 -> 1), forward and backward.
+//
+// Max pool: one thread per output pixel x 8 channels (one 16-byte vector): 9 vector loads,
+// one vector store, plus one byte per element recording which of the 9 taps won.  Backward
+// is a gather: one thread per INPUT pixel x 8 channels looks at the (at most 4) windows that
+// contain it and sums the gradients of those whose recorded tap points here - no atomics,
+// every dx element written exactly once.
+#include "../include/b200ddl.h"
+#include "common.cuh"
+
+namespace {
+
+__global__ void __launch_bounds__(256) maxpool3x3s2_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y,
+                                                                unsigned char* __restrict__ idx, int N, int H, int W, int C, int OH,
+                                                                int OW) {
+    const int vc = C >> 3;
+    const size_t total = (size_t)N * OH * OW * vc;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = (int)(t % vc);
+        size_t r = t / vc;
+        const int ow = (int)(r % OW);
+        r /= OW;
+        const int oh = (int)(r % OH);
+        const int n = (int)(r / OH);
+        float best[8];
+        int arg[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            best[j] = -INFINITY;
+            arg[j] = 0;
+        }
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
+            const int ih = oh * 2 - 1 + kh;
+            if (ih < 0 || ih >= H) continue;
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
+                const int iw = ow * 2 - 1 + kw;
+                if (iw < 0 || iw >= W) continue;
+                float f[8];
+                bf16x8_to_float(ld_global_v4(x + (((size_t)n * H + ih) * W + iw) * C + c8 * 8), f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (f[j] > best[j]) {
+                        best[j] = f[j];
+                        arg[j] = kh * 3 + kw;
+                    }
+            }
+        }
+        const size_t o = (((size_t)n * OH + oh) * OW + ow) * C + c8 * 8;
+        st_global_v4(y + o, float_to_bf16x8(best));
+        uint2 packed;
+        packed.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
+        packed.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+        *reinterpret_cast<uint2*>(idx + o) = packed;
+    }
+}
+
+__global__ void __launch_bounds__(256) maxpool3x3s2_bwd_kernel(const bf16* __restrict__ dy, const unsigned char* __restrict__ idx,
+                                                                bf16* __restrict__ dx, int N, int H, int W, int C, int OH, int OW) {
+    const int vc = C >> 3;
+    const size_t total = (size_t)N * H * W * vc;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = (int)(t % vc);
+        size_t r = t / vc;
+        const int iw = (int)(r % W);
+        r /= W;
+        const int ih = (int)(r % H);
+        const int n = (int)(r / H);
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        // windows (oh, ow) with 2*oh - 1 <= ih <= 2*oh + 1
+        const int oh0 = ih >> 1, oh1 = (ih + 1) >> 1;
+        const int ow0 = iw >> 1, ow1 = (iw + 1) >> 1;
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+            const int oh = a == 0 ? oh0 : oh1;
+            if (a == 1 && oh1 == oh0) continue;
+            if (oh >= OH) continue;
+            const int kh = ih - (oh * 2 - 1);
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+                const int ow = b == 0 ? ow0 : ow1;
+                if (b == 1 && ow1 == ow0) continue;
+                if (ow >= OW) continue;
+                const int kw = iw - (ow * 2 - 1);
+                const int code = kh * 3 + kw;
+                const size_t o = (((size_t)n * OH + oh) * OW + ow) * C + c8 * 8;
+                const uint2 packed = *reinterpret_cast<const uint2*>(idx + o);
+                float g[8];
+                bf16x8_to_float(ld_global_v4(dy + o), g);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int aj = (int)(((j < 4 ? packed.x : packed.y) >> (8 * (j & 3))) & 0xffu);
+                    if (aj == code) acc[j] += g[j];
+                }
+            }
+        }
+        st_global_v4(dx + t * 8, float_to_bf16x8(acc));
+    }
+}
+
+// global average pool: y[n, c] = mean_hw x[n, hw, c]
+__global__ void __launch_bounds__(256) avgpool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int N, int HW, int C) {
+    const int vc = C >> 3;
+    const size_t total = (size_t)N * vc;
+    const float inv = 1.f / (float)HW;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = (int)(t % vc);
+        const int n = (int)(t / vc);
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int p = 0; p < HW; ++p) {
+            float f[8];
+            bf16x8_to_float(ld_stream_v4(x + ((size_t)n * HW + p) * C + c8 * 8), f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += f[j];
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] *= inv;
+        st_global_v4(y + t * 8, float_to_bf16x8(acc));
+    }
+}
+
+__global__ void __launch_bounds__(256) avgpool_bwd_kernel(const bf16* __restrict__ dy, bf16* __restrict__ dx, int N, int HW, int C) {
+    const int vc = C >> 3;
+    const size_t total = (size_t)N * HW * vc;
+    const float inv = 1.f / (float)HW;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = (int)(t % vc);
+        const int n = (int)(t / ((size_t)HW * vc));
+        float f[8];
+        bf16x8_to_float(ld_global_v4(dy + ((size_t)n * vc + c8) * 8), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] *= inv;
+        st_global_v4(dx + t * 8, float_to_bf16x8(f));
+    }
+}
+
+int grid_for(size_t total) {
+    long long b = (long long)((total + 255) / 256);
+    const long long cap = DDL_SM_COUNT * 16;
+    return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+}  // namespace
+
+DDL_API int ddl_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, void* stream_) {
+    DDL_REQUIRE(C % 8 == 0, "maxpool: channels must be a multiple of 8");
+    DDL_REQUIRE(x && y && idx, "maxpool: null pointer");
+    const int OH = (H + 2 - 3) / 2 + 1, OW = (W + 2 - 3) / 2 + 1;
+    const size_t total = (size_t)N * OH * OW * (C / 8);
+    maxpool3x3s2_fwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream_>>>((const bf16*)x, (bf16*)y, (unsigned char*)idx, N, H, W, C,
+                                                                               OH, OW);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+DDL_API int ddl_maxpool3x3s2_bwd(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, void* stream_) {
+    DDL_REQUIRE(C % 8 == 0, "maxpool: channels must be a multiple of 8");
+    DDL_REQUIRE(dy && dx && idx, "maxpool: null pointer");
+    const int OH = (H + 2 - 3) / 2 + 1, OW = (W + 2 - 3) / 2 + 1;
+    const size_t total = (size_t)N * H * W * (C / 8);
+    maxpool3x3s2_bwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream_>>>((const bf16*)dy, (const unsigned char*)idx, (bf16*)dx, N, H,
+                                                                               W, C, OH, OW);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+DDL_API int ddl_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream_) {
+    DDL_REQUIRE(C % 8 == 0, "avgpool: channels must be a multiple of 8");
+    avgpool_fwd_kernel<<<grid_for((size_t)N * (C / 8)), 256, 0, (cudaStream_t)stream_>>>((const bf16*)x, (bf16*)y, N, HW, C);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+DDL_API int ddl_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream_) {
+    DDL_REQUIRE(C % 8 == 0, "avgpool: channels must be a multiple of 8");
+    avgpool_bwd_kernel<<<grid_for((size_t)N * HW * (C / 8)), 256, 0, (cudaStream_t)stream_>>>((const bf16*)dy, (bf16*)dx, N, HW, C);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}

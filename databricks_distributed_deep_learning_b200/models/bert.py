@@ -197,10 +197,43 @@ class BertLayer(nn.Module):
         self.attention = BertAttention(cfg)
         self.intermediate = BertIntermediate(cfg)
         self.output = BertSelfOutput(cfg, in_features=cfg.intermediate_size)
+        self.impl = "torch"
 
     def forward(self, x, attn_mask_bias, seqlens=None):
+        if self.impl == "fused" and x.is_cuda:
+            return self._fused_forward(x, seqlens)
         a = self.attention(x, attn_mask_bias, seqlens)
         return self.output(self.intermediate(a), a)
+
+    def _fused_forward(self, x, seqlens):
+        """The whole encoder layer on native kernels: 4 tcgen05 GEMM launches forward
+        (QKV, attention output, FFN up + GELU, FFN down), attention, 2 LayerNorm launches.
+        With dropout off the residual adds ride in the GEMM epilogues; with dropout on they
+        move into the dropout+residual+LayerNorm kernel (the mask must precede the add)."""
+        from ..ops import functional as OF
+        from ..ops import gemm as G
+
+        B, S, H = x.shape
+        x2 = x.reshape(B * S, H)
+        sa, so = self.attention.self, self.attention.output
+        p_h = so.p_drop if self.training else 0.0
+        p_a = sa.p_drop if self.training else 0.0
+        qkv = G.linear(x2, sa.qkv_weight, sa.qkv_bias)
+        ctx = OF.attention_qkvpacked(qkv.view(B, S, 3, sa.num_heads, sa.head_dim), seqlens, p_a).reshape(B * S, H)
+        ln1, ln2 = so.LayerNorm, self.output.LayerNorm
+        if p_h == 0.0:
+            z = G.linear(ctx, so.dense.weight, so.dense.bias, residual=x2)
+            a = OF.layernorm(z, ln1.weight, ln1.bias, ln1.eps)
+            z2 = G.ffn(a, self.intermediate.dense.weight, self.intermediate.dense.bias, self.output.dense.weight,
+                       self.output.dense.bias, residual=a)
+            out = OF.layernorm(z2, ln2.weight, ln2.bias, ln2.eps)
+        else:
+            y = G.linear(ctx, so.dense.weight, so.dense.bias)
+            a = OF.dropout_add_layernorm(y, x2, ln1.weight, ln1.bias, ln1.eps, p_h)
+            y2 = G.ffn(a, self.intermediate.dense.weight, self.intermediate.dense.bias, self.output.dense.weight,
+                       self.output.dense.bias)
+            out = OF.dropout_add_layernorm(y2, a, ln2.weight, ln2.bias, ln2.eps, p_h)
+        return out.view(B, S, H)
 
 
 class BertEncoder(nn.Module):

@@ -142,14 +142,11 @@ class ResNet(nn.Module):
             x = OF.to_nhwc_bf16(x)
         x = _conv_bn_act(x, self.conv1, self.bn1, True, None, self.impl)
         if not self.small_input:
-            x = F.max_pool2d(x, 3, 2, 1)
+            x = OF.maxpool3x3s2(x) if fused else F.max_pool2d(x, 3, 2, 1)
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
-        x = torch.flatten(F.adaptive_avg_pool2d(x, 1), 1)
         if fused:
-            from ..ops import functional as OF
-
-            return OF.linear(x, self.fc.weight, self.fc.bias)
-        return self.fc(x)
+            return OF.linear(OF.global_avgpool(x), self.fc.weight, self.fc.bias)
+        return self.fc(torch.flatten(F.adaptive_avg_pool2d(x, 1), 1))
 
 
 def resnet18(num_classes: int = 1000, small_input: bool = False, impl: str = "torch") -> ResNet:

@@ -68,6 +68,13 @@ _PROTOS = {
     "ddl_bn_act_fwd_train": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _ll, _i, _f, _f, _i, _vp], _i),
     "ddl_bn_act_fwd_eval": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _f, _i, _vp], _i),
     "ddl_bn_act_bwd": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _ll, _i, _i, _vp], _i),
+    "ddl_attention_fwd": ([_vp, _vp, _vp, _vp, _i, _i, _i, _f, _u64, _vp, _vp], _i),
+    "ddl_attention_bwd_scratch_bytes": ([_i, _i, _i], _sz),
+    "ddl_attention_bwd": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i, _i, _i, _f, _u64, _vp, _vp], _i),
+    "ddl_maxpool3x3s2_fwd": ([_vp, _vp, _vp, _i, _i, _i, _i, _vp], _i),
+    "ddl_maxpool3x3s2_bwd": ([_vp, _vp, _vp, _i, _i, _i, _i, _vp], _i),
+    "ddl_avgpool_fwd": ([_vp, _vp, _i, _i, _i, _vp], _i),
+    "ddl_avgpool_bwd": ([_vp, _vp, _i, _i, _i, _vp], _i),
     "ddl_gemm_bf16": ([_vp, _i, _ll, _vp, _i, _ll, _vp, _ll, _i, _i, _i, _vp, _vp, _vp, _i, _i, _vp, _i, _vp], _i),
     "ddl_f32_to_bf16": ([_vp, _vp, _sz, _i, _vp], _i),
     "ddl_colsum_scratch_bytes": ([_i, _i], _sz),

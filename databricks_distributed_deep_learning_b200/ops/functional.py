@@ -253,6 +253,65 @@ def bn_act(x, bn: nn.BatchNorm2d, relu: bool = True, residual: Optional[torch.Te
                         0.1 if bn.momentum is None else bn.momentum, bn.eps, relu)
 
 
+class _MaxPool3x3s2(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        _req_bf16(x)
+        N, Cc, H, W = x.shape
+        if not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+        y = torch.empty(N, Cc, OH, OW, dtype=x.dtype, device=x.device).contiguous(memory_format=torch.channels_last)
+        idx = torch.empty(N * OH * OW * Cc, dtype=torch.uint8, device=x.device)
+        L.call("ddl_maxpool3x3s2_fwd", x.data_ptr(), y.data_ptr(), idx.data_ptr(), N, H, W, Cc, L.stream_ptr(x.device))
+        ctx.save_for_backward(idx)
+        ctx.shape = (N, Cc, H, W)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        N, Cc, H, W = ctx.shape
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dx = torch.empty(N, Cc, H, W, dtype=dy.dtype, device=dy.device).contiguous(memory_format=torch.channels_last)
+        L.call("ddl_maxpool3x3s2_bwd", dy.data_ptr(), idx.data_ptr(), dx.data_ptr(), N, H, W, Cc, L.stream_ptr(dy.device))
+        return dx
+
+
+def maxpool3x3s2(x: torch.Tensor) -> torch.Tensor:
+    """``F.max_pool2d(x, 3, 2, 1)`` on channels-last bf16 (K14)."""
+    return _MaxPool3x3s2.apply(x)
+
+
+class _GlobalAvgPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        _req_bf16(x)
+        N, Cc, H, W = x.shape
+        if not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        y = torch.empty(N, Cc, dtype=x.dtype, device=x.device)
+        L.call("ddl_avgpool_fwd", x.data_ptr(), y.data_ptr(), N, H * W, Cc, L.stream_ptr(x.device))
+        ctx.shape = (N, Cc, H, W)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        N, Cc, H, W = ctx.shape
+        dy = dy.contiguous()
+        dx = torch.empty(N, Cc, H, W, dtype=dy.dtype, device=dy.device).contiguous(memory_format=torch.channels_last)
+        L.call("ddl_avgpool_bwd", dy.data_ptr(), dx.data_ptr(), N, H * W, Cc, L.stream_ptr(dy.device))
+        return dx
+
+
+def global_avgpool(x: torch.Tensor) -> torch.Tensor:
+    """``torch.flatten(F.adaptive_avg_pool2d(x, 1), 1)`` on channels-last bf16 -> [N, C]."""
+    return _GlobalAvgPool.apply(x)
+
+
 def to_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
     return x.to(dtype=torch.bfloat16, memory_format=torch.channels_last)
 
@@ -271,19 +330,20 @@ def conv2d(x, conv: nn.Conv2d) -> torch.Tensor:
 
 
 # ----------------------------------------------------------------------------- linear / attention
-def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, activation: Optional[str] = None) -> torch.Tensor:
-    """``act(x @ weight.T + bias)``; dispatches to the tcgen05 GEMM (``ops/gemm.py``) for bf16
-    operands whose shapes fit its tiles, otherwise to the library GEMM."""
+def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, activation: Optional[str] = None,
+           residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``act(x @ weight.T + bias) + residual``; runs on the tcgen05 GEMM (``ops/gemm.py``) for bf16
+    CUDA operands whose inner dimensions are multiples of 8, otherwise on the library GEMM."""
     from . import gemm
 
     if gemm.usable(x, weight):
-        return gemm.linear(x, weight, bias, activation)
+        return gemm.linear(x, weight, bias, activation, residual)
     y = F.linear(x, weight, bias)
     if activation == "gelu":
         y = F.gelu(y)
     elif activation == "relu":
         y = F.relu(y)
-    return y
+    return y if residual is None else y + residual
 
 
 def attention_qkvpacked(qkv: torch.Tensor, seqlens: Optional[torch.Tensor], p: float = 0.0) -> torch.Tensor:

@@ -130,6 +130,29 @@ int ddl_bn_act_bwd(const void* dy, const void* y, const void* x, const void* gam
                    void* dres, void* dgamma, void* dbeta, int param_grad_dtype, void* scratch, size_t scratch_bytes, long long M,
                    int C, int relu, void* stream);
 
+/* ---- self-attention on tcgen05 (csrc/attention.cu), K11 ---------------------------------- */
+/* qkv: packed projections [B*S, 3*heads*64] bf16 (q | k | v); seqlens[B] = valid (right-padded)
+ * lengths or NULL; ctx [B*S, heads*64]; lse [B, heads, S] fp32 saved for backward.  head_dim is 64,
+ * S a multiple of 128 up to 512 (the BASELINE.json:9-10 configs: 128 and 512).  Dropout acts on the
+ * attention probabilities; its mask is regenerated in backward from (seed, *seed_dev).
+ * Backward writes the packed gradient dqkv [B*S, 3*heads*64]; scratch from
+ * ddl_attention_bwd_scratch_bytes.  The reference has no attention ("Long-context"). */
+int ddl_attention_fwd(const void* qkv, const int* seqlens, void* ctx, float* lse, int B, int S, int heads, float dropout_p,
+                      unsigned long long seed, const unsigned long long* seed_dev, void* stream);
+size_t ddl_attention_bwd_scratch_bytes(int B, int S, int heads);
+int ddl_attention_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse, const int* seqlens, void* dqkv,
+                      void* scratch, size_t scratch_bytes, int B, int S, int heads, float dropout_p, unsigned long long seed,
+                      const unsigned long long* seed_dev, void* stream);
+
+/* ---- pooling on NHWC bf16 (csrc/pool.cu), K14 -------------------------------------------- */
+/* 3x3 / stride 2 / pad 1 max pool (ResNet stem; model at reference:19).  idx: one byte per output
+ * element (winning tap 0..8), consumed by the gather-style backward. */
+int ddl_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, void* stream);
+int ddl_maxpool3x3s2_bwd(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, void* stream);
+/* global average pool [N, HW, C] -> [N, C] and its backward */
+int ddl_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream);
+int ddl_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);
+
 /* ---- tcgen05 / TMEM / TMA GEMM (csrc/gemm_tcgen05.cu), K8 ------------------------------ */
 /* C[M,N] = epilogue(A . B^T), bf16 operands, fp32 accumulation in tensor memory.
  * A is [M,K] row-major (a_mn = 0) or stored as [K,M] (a_mn = 1); B is [N,K] (b_mn = 0) or stored

@@ -372,3 +372,98 @@ def test_ffn_autograd_matches_torch():
     rel = lambda u, v: ((u.float() - v).abs().max() / v.abs().max()).item()
     errs = [rel(y, yr)] + [rel(t.grad, f.grad) for t, f in zip((x, w1, b1, w2, b2, res), fs)]
     assert max(errs) < 3e-2, errs
+
+
+@pytest.mark.parametrize("N,C,H,W", [(4, 64, 112, 112), (2, 8, 7, 9), (3, 24, 10, 10)])
+def test_maxpool3x3s2_fwd_bwd(N, C, H, W):
+    OF = _OF()
+    x = torch.randn(N, C, H, W, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_()
+    y = OF.maxpool3x3s2(x)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xr = x.detach().float().requires_grad_()
+    yr = F.max_pool2d(xr, 3, 2, 1)
+    yr.backward(dy.float())
+    assert y.shape == yr.shape and torch.equal(y.float(), yr)
+    # ties (equal bf16 values in one window) may route the gradient to a different tap: compare sums and the bulk
+    assert torch.allclose(x.grad.float().sum((2, 3)), xr.grad.sum((2, 3)), rtol=2e-2, atol=2e-1)
+    assert ((x.grad.float() - xr.grad).abs() > 1e-2).float().mean().item() < 5e-3
+
+
+def test_global_avgpool_fwd_bwd():
+    OF = _OF()
+    x = torch.randn(8, 2048, 7, 7, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_()
+    y = OF.global_avgpool(x)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xr = x.detach().float().requires_grad_()
+    yr = torch.flatten(F.adaptive_avg_pool2d(xr, 1), 1)
+    yr.backward(dy.float())
+    assert torch.allclose(y.float(), yr, rtol=1e-2, atol=1e-2)
+    assert torch.allclose(x.grad.float(), xr.grad, rtol=1e-2, atol=1e-3)
+
+
+def test_colsum_matches_torch():
+    g = _gemm()
+    for rows, cols in [(16384, 768), (4096, 3072), (1000, 2304), (77, 8)]:
+        x = torch.randn(rows, cols, device="cuda").to(torch.bfloat16)
+        ref = x.float().sum(0)
+        got = g.colsum(x).float()
+        assert (got - ref).abs().max().item() < 1e-2 * ref.abs().max().item() + 0.5, (rows, cols)
+
+
+# ----------------------------------------------------------------------------- tcgen05 attention
+def _attn_ref_fp32(qkv, seqlens):
+    B, S, _, h, d = qkv.shape
+    q, k, v = qkv.float().permute(2, 0, 3, 1, 4)
+    s = (q @ k.transpose(-1, -2)) * (d ** -0.5)
+    if seqlens is not None:
+        keep = torch.arange(S, device=qkv.device)[None, :] < seqlens[:, None]
+        s = s.masked_fill(~keep[:, None, None, :], float("-inf"))
+    return (torch.softmax(s, -1) @ v).transpose(1, 2).reshape(B, S, h * d)
+
+
+@pytest.mark.parametrize("B,S,h", [(2, 128, 2), (3, 128, 12), (2, 256, 4), (2, 512, 16), (1, 384, 3)])
+@pytest.mark.parametrize("masked", [False, True])
+def test_attention_fwd_bwd_matches_fp32(B, S, h, masked):
+    from databricks_distributed_deep_learning_b200.ops import attention as A
+
+    qkv = (torch.randn(B, S, 3, h, 64, device="cuda") * 1.0).to(torch.bfloat16).requires_grad_()
+    seqlens = None
+    if masked:
+        seqlens = torch.randint(1, S + 1, (B,), device="cuda")
+        seqlens[0] = S // 2 + 3  # a partially filled tile
+    assert A.native_ok(qkv)
+    out = A.attention_qkvpacked(qkv, seqlens, 0.0)
+    dout = torch.randn_like(out)
+    out.backward(dout)
+    ref_in = qkv.detach().clone().requires_grad_()
+    ref = _attn_ref_fp32(ref_in, seqlens)
+    ref.backward(dout.float())
+    assert torch.allclose(out.float(), ref, rtol=2e-2, atol=2e-2), (out.float() - ref).abs().max().item()
+    g, gr = qkv.grad.float(), ref_in.grad.float()
+    rel = lambda a, b: ((a - b).abs().max() / b.abs().max().clamp_min(1e-6)).item()
+    assert rel(g[:, :, 2], gr[:, :, 2]) < 3e-2, ("dV", rel(g[:, :, 2], gr[:, :, 2]))
+    assert rel(g[:, :, 1], gr[:, :, 1]) < 3e-2, ("dK", rel(g[:, :, 1], gr[:, :, 1]))
+    assert rel(g[:, :, 0], gr[:, :, 0]) < 3e-2, ("dQ", rel(g[:, :, 0], gr[:, :, 0]))
+
+
+def test_attention_dropout_statistics_and_determinism():
+    from databricks_distributed_deep_learning_b200.ops import attention as A
+    from databricks_distributed_deep_learning_b200.ops import functional as OF
+
+    B, S, h = 4, 128, 8
+    qkv = (torch.randn(B, S, 3, h, 64, device="cuda") * 0.3).to(torch.bfloat16)
+    qkv[:, :, 2] = 1.0  # V = 1: every output element equals sum_k dropout(P)[q, k] -> mean must stay 1
+    out = A._Attention.apply(qkv, None, 0.1)
+    assert abs(out.float().mean().item() - 1.0) < 0.01
+    assert 0.02 < out.float().std().item() < 0.3  # the mask is really applied
+    x = qkv.clone().requires_grad_()
+    y = A._Attention.apply(x, None, 0.1)
+    y.backward(torch.ones_like(y))
+    assert torch.isfinite(x.grad.float()).all()
+    # dV[k] = sum_q dropout(P)[q, k] * dO[q]: with dO = 1 the total over keys equals the total of the outputs
+    assert abs(x.grad.float()[:, :, 2, :, 0].sum().item() - y.float()[..., 0::64].sum().item()) < 0.02 * y.float()[..., 0::64].sum().abs().item()
+    OF.advance_seed(qkv.device)
+    out2 = A._Attention.apply(qkv, None, 0.1)
+    assert not torch.equal(out, out2)
