@@ -75,13 +75,15 @@ struct SmemLayout {
     static constexpr int kABytes = BM * BK * 2;
     static constexpr int kBBytes = BN * BK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kBarOffset = kStages * kStageBytes;
+    static constexpr int kStageOffset = kStages * kStageBytes;          // 8 epilogue warps x 4 KB staging
+    static constexpr int kBarOffset = kStageOffset + kEpiWarps * 4096;
     static constexpr int kTotal = kBarOffset + 256 + 1024;  // barriers + alignment slack
 };
 
-template <int BN, bool A_MN, bool B_MN, int kStages>
+template <int BN, bool A_MN, bool B_MN, int kStages, int kCluster>
 __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a,
-                                                                const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
+                                                                const __grid_constant__ CUtensorMap tma_b,
+                                                                const __grid_constant__ CUtensorMap tma_b_half, const GemmParams p) {
     using L = SmemLayout<BN, A_MN, B_MN, kStages>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -99,7 +101,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
         tma_prefetch_desc(&tma_b);
         for (int s = 0; s < kStages; ++s) {
             mbar_init(&full_bar[s], 1);
-            mbar_init(&empty_bar[s], 1);
+            mbar_init(&empty_bar[s], kCluster);  // every CTA that receives the multicast B must release the stage
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(&tmem_full[s], 1);
@@ -110,10 +112,17 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
     if (warp == 1) tmem_alloc(tmem_ptr_smem, kTmemCols);
     tc_fence_before();
     __syncthreads();
+    if (kCluster > 1) cluster_sync_all();  // peers' barriers exist before any multicast can land
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
 
-    const int tiles_mn = p.num_m_blocks * p.num_n_blocks;
+    // kCluster == 2: the two CTAs of a cluster take vertically adjacent tiles (m, n) / (m+1, n) and
+    // share the B tile: each loads half of it and multicasts that half to both, which cuts the
+    // L2 -> SM operand traffic per CTA from A + B to A + B/2 (the mainloop is L2-bandwidth bound).
+    const int cta_rank = kCluster > 1 ? (int)cluster_ctarank() : 0;
+    const int sched_id = blockIdx.x / kCluster, sched_n = gridDim.x / kCluster;
+    const int m_groups = (p.num_m_blocks + kCluster - 1) / kCluster;
+    const int tiles_mn = m_groups * p.num_n_blocks;
     const int num_tiles = tiles_mn * p.split_k;
     const int kb_per_split = (p.k_blocks_total + p.split_k - 1) / p.split_k;
 
@@ -122,9 +131,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int tile = sched_id; tile < num_tiles; tile += sched_n) {
                 const int ks = tile / tiles_mn, mn = tile % tiles_mn;
-                const int m_blk = mn / p.num_n_blocks, n_blk = mn % p.num_n_blocks;
+                const int m_blk = (mn / p.num_n_blocks) * kCluster + cta_rank, n_blk = mn % p.num_n_blocks;
                 const int kb0 = ks * kb_per_split;
                 const int kb1 = min(kb0 + kb_per_split, p.k_blocks_total);
                 for (int kb = kb0; kb < kb1; ++kb) {
@@ -138,11 +147,25 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
                     } else {
                         tma_load_2d(sa, &tma_a, &full_bar[stage], kb * BK, m_blk * BM);
                     }
-                    if (B_MN) {
+                    if (kCluster == 1) {
+                        if (B_MN) {
 #pragma unroll
-                        for (int j = 0; j < BN / 64; ++j) tma_load_2d(sb + j * (BK * 128), &tma_b, &full_bar[stage], n_blk * BN + j * 64, kb * BK);
+                            for (int j = 0; j < BN / 64; ++j) tma_load_2d(sb + j * (BK * 128), &tma_b, &full_bar[stage], n_blk * BN + j * 64, kb * BK);
+                        } else {
+                            tma_load_2d(sb, &tma_b, &full_bar[stage], kb * BK, n_blk * BN);
+                        }
                     } else {
-                        tma_load_2d(sb, &tma_b, &full_bar[stage], kb * BK, n_blk * BN);
+                        // my half of B, delivered to both CTAs (same offsets, both full barriers)
+                        constexpr int kHalf = BN / 2;
+                        if (B_MN) {
+#pragma unroll
+                            for (int j = 0; j < kHalf / 64; ++j) {
+                                const int jj = cta_rank * (kHalf / 64) + j;
+                                tma_load_2d_mcast(sb + jj * (BK * 128), &tma_b, &full_bar[stage], n_blk * BN + jj * 64, kb * BK, 0x3);
+                            }
+                        } else {
+                            tma_load_2d_mcast(sb + cta_rank * (kHalf * 128), &tma_b_half, &full_bar[stage], kb * BK, n_blk * BN + cta_rank * kHalf, 0x3);
+                        }
                     }
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
@@ -156,7 +179,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
             uint32_t phase = 0;
             int acc_stage = 0;
             uint32_t acc_phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int tile = sched_id; tile < num_tiles; tile += sched_n) {
                 const int ks = tile / tiles_mn;
                 const int kb0 = ks * kb_per_split;
                 const int kb1 = min(kb0 + kb_per_split, p.k_blocks_total);
@@ -176,7 +199,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
                         const uint64_t db = B_MN ? make_smem_desc(sb + k * 2048, BK * 128, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
                         umma_bf16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
                     }
-                    umma_commit(&empty_bar[stage]);  // frees the smem stage once these MMAs retire
+                    // frees the smem stage once these MMAs retire (in both CTAs when B is shared)
+                    if (kCluster > 1) umma_commit_mcast(&empty_bar[stage], 0x3);
+                    else umma_commit(&empty_bar[stage]);
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
                 umma_commit(&tmem_full[acc_stage]);  // accumulator complete -> epilogue
@@ -185,80 +210,127 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
         }
     } else {
         // ===================== epilogue warps =====================
+        // TMEM gives each thread one ROW of the tile; global memory wants one 128-byte line per
+        // 8 lanes.  Each warp therefore stages its 32 x 64 bf16 chunk in a private 4 KB
+        // swizzled smem buffer and re-reads it transposed: lane l <-> (row it*4 + l/8, 16-byte
+        // chunk l%8), so every global access (output, aux, residual) is 4 full lines per
+        // instruction instead of 32 partial ones.
         const int ew = warp - 2;              // 0..7
         const int quarter = warp & 3;         // TMEM lane quarter this warp may access
         const int half = ew >> 2;             // which half of the tile's columns
         constexpr int kColsPerWarp = BN / 2;
+        uint8_t* stg = smem + L::kStageOffset + ew * 4096;
+        const int t_sr = lane >> 3, t_ch = lane & 7;
+        auto stg_row = [&](int r, int c) -> uint4* { return reinterpret_cast<uint4*>(stg + r * 128 + ((c ^ (r & 7)) << 4)); };
         int acc_stage = 0;
         uint32_t acc_phase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        for (int tile = sched_id; tile < num_tiles; tile += sched_n) {
             const int mn = tile % tiles_mn;
-            const int m_blk = mn / p.num_n_blocks, n_blk = mn % p.num_n_blocks;
+            const int m_blk = (mn / p.num_n_blocks) * kCluster + cta_rank, n_blk = mn % p.num_n_blocks;
             mbar_wait(&tmem_full[acc_stage], acc_phase);
             tc_fence_after();
-            const int row = m_blk * BM + quarter * 32 + lane;
-            const bool row_ok = row < p.M;
+            const int row_base = m_blk * BM + quarter * 32;   // first row of this warp's 32
+            const int row = row_base + lane;
 #pragma unroll 1
-            for (int c = 0; c < kColsPerWarp; c += 32) {
+            for (int c = 0; c < kColsPerWarp; c += 64) {
                 const int col0 = n_blk * BN + half * kColsPerWarp + c;
-                uint32_t r[32];
+                uint32_t r0[32], r1[32];
                 const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc_stage * BN + half * kColsPerWarp + c);
-                tmem_ld_32x32(taddr, r);
+                tmem_ld_32x32(taddr, r0);
+                tmem_ld_32x32(taddr + 32, r1);
                 tmem_ld_wait();
-                if (row_ok && col0 < p.N) {
-                    float v[32];
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                    if (p.split_k > 1) {
+                if (col0 >= p.N) continue;
+                if (p.split_k > 1) {
+                    if (row < p.M) {
                         float* dst = p.acc_f32 + (size_t)row * p.N + col0;
 #pragma unroll
-                        for (int j = 0; j < 32; j += 4)
-                            if (col0 + j < p.N) red_add_f32x4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
-                    } else {
-                        const size_t off = (size_t)row * p.ldc + col0;
+                        for (int j = 0; j < 32; j += 4) {
+                            if (col0 + j < p.N)
+                                red_add_f32x4(dst + j, __uint_as_float(r0[j]), __uint_as_float(r0[j + 1]), __uint_as_float(r0[j + 2]), __uint_as_float(r0[j + 3]));
+                            if (col0 + 32 + j < p.N)
+                                red_add_f32x4(dst + 32 + j, __uint_as_float(r1[j]), __uint_as_float(r1[j + 1]), __uint_as_float(r1[j + 2]), __uint_as_float(r1[j + 3]));
+                        }
+                    }
+                    continue;
+                }
+                // dGELU: bring the saved pre-activation in through the same buffer (coalesced load -> row domain)
+                if (p.epilogue == DDL_EPI_DGELU) {
 #pragma unroll
-                        for (int j = 0; j < 32; j += 8) {
-                            if (col0 + j >= p.N) break;
-                            float* w = &v[j];
-                            if (p.bias) {
-                                float b[8];
-                                bf16x8_to_float(ld_global_v4(p.bias + col0 + j), b);
+                    for (int it = 0; it < 8; ++it) {
+                        const int rr = it * 4 + t_sr;
+                        uint4 v = make_uint4(0, 0, 0, 0);
+                        if (row_base + rr < p.M && col0 + t_ch * 8 < p.N) v = ld_global_v4(p.aux + (size_t)(row_base + rr) * p.ldc + col0 + t_ch * 8);
+                        *stg_row(rr, t_ch) = v;
+                    }
+                    __syncwarp();
+                }
 #pragma unroll
-                                for (int q = 0; q < 8; ++q) w[q] += b[q];
-                            }
-                            if (p.epilogue == DDL_EPI_GELU) {
-                                float pre[8];
+                for (int g = 0; g < 8; ++g) {  // 8 column groups of 8
+                    float w[8];
 #pragma unroll
-                                for (int q = 0; q < 8; ++q) pre[q] = w[q];
-                                if (p.aux) {
-                                    const uint4 pq = float_to_bf16x8(pre);
-                                    st_global_v4(p.aux + off + j, pq);
-                                    bf16x8_to_float(pq, pre);  // backward sees the rounded pre-activation
-                                }
+                    for (int q = 0; q < 8; ++q) w[q] = __uint_as_float(g < 4 ? r0[g * 8 + q] : r1[(g - 4) * 8 + q]);
+                    const bool col_ok = col0 + g * 8 < p.N;
+                    if (p.bias && col_ok) {
+                        float bsv[8];
+                        bf16x8_to_float(ld_global_v4(p.bias + col0 + g * 8), bsv);
 #pragma unroll
-                                for (int q = 0; q < 8; ++q) w[q] = gelu_f(pre[q]);
-                            } else if (p.epilogue == DDL_EPI_DGELU) {
-                                float pre[8];
-                                bf16x8_to_float(ld_global_v4(p.aux + off + j), pre);
+                        for (int q = 0; q < 8; ++q) w[q] += bsv[q];
+                    }
+                    if (p.epilogue == DDL_EPI_DGELU) {
+                        float pre[8];
+                        bf16x8_to_float(*stg_row(lane, g), pre);
 #pragma unroll
-                                for (int q = 0; q < 8; ++q) w[q] *= dgelu_f(pre[q]);
-                            } else if (p.epilogue == DDL_EPI_RELU) {
+                        for (int q = 0; q < 8; ++q) w[q] *= dgelu_f(pre[q]);
+                    } else if (p.epilogue == DDL_EPI_RELU) {
 #pragma unroll
-                                for (int q = 0; q < 8; ++q) w[q] = fmaxf(w[q], 0.f);
-                            }
+                        for (int q = 0; q < 8; ++q) w[q] = fmaxf(w[q], 0.f);
+                    }
+                    // GELU keeps fp32 values in registers for the second pass; first pass stages the pre-activation
+                    *stg_row(lane, g) = float_to_bf16x8(w);
+                }
+                __syncwarp();
+                if (p.epilogue == DDL_EPI_GELU) {
+                    // pass 1: pre-activation -> aux (coalesced); pass 2: gelu(rounded pre) -> C
+#pragma unroll
+                    for (int it = 0; it < 8; ++it) {
+                        const int rr = it * 4 + t_sr;
+                        const uint4 pv = *stg_row(rr, t_ch);
+                        if (row_base + rr < p.M && col0 + t_ch * 8 < p.N) {
+                            const size_t off = (size_t)(row_base + rr) * p.ldc + col0 + t_ch * 8;
+                            if (p.aux) st_global_v4(p.aux + off, pv);
+                            float f[8];
+                            bf16x8_to_float(pv, f);
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) f[q] = gelu_f(f[q]);
                             if (p.residual) {
                                 float rs[8];
-                                bf16x8_to_float(ld_global_v4(p.residual + off + j), rs);
+                                bf16x8_to_float(ld_global_v4(p.residual + off), rs);
 #pragma unroll
-                                for (int q = 0; q < 8; ++q) w[q] += rs[q];
+                                for (int q = 0; q < 8; ++q) f[q] += rs[q];
                             }
-                            float o[8];
+                            st_global_v4(p.C + off, float_to_bf16x8(f));
+                        }
+                    }
+                } else {
 #pragma unroll
-                            for (int q = 0; q < 8; ++q) o[q] = w[q];
-                            st_global_v4(p.C + off + j, float_to_bf16x8(o));
+                    for (int it = 0; it < 8; ++it) {
+                        const int rr = it * 4 + t_sr;
+                        uint4 pv = *stg_row(rr, t_ch);
+                        if (row_base + rr < p.M && col0 + t_ch * 8 < p.N) {
+                            const size_t off = (size_t)(row_base + rr) * p.ldc + col0 + t_ch * 8;
+                            if (p.residual) {
+                                float f[8], rs[8];
+                                bf16x8_to_float(pv, f);
+                                bf16x8_to_float(ld_global_v4(p.residual + off), rs);
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) f[q] += rs[q];
+                                pv = float_to_bf16x8(f);
+                            }
+                            st_global_v4(p.C + off, pv);
                         }
                     }
                 }
+                __syncwarp();  // buffer free for the next chunk
             }
             tc_fence_before();
             __syncwarp();
@@ -268,6 +340,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
     }
     tc_fence_before();
     __syncthreads();
+    if (kCluster > 1) cluster_sync_all();  // nobody leaves while a peer may still multicast into its smem
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, kTmemCols);
@@ -374,22 +447,34 @@ int make_map(CUtensorMap* map, const void* ptr, long long rows, long long cols, 
     return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN>
-int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t stream) {
+template <int BN, bool A_MN, bool B_MN, int kCluster>
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tbh, const GemmParams& p, int grid, cudaStream_t stream) {
     constexpr int kStages = BN == 256 ? 4 : 6;
     using L = SmemLayout<BN, A_MN, B_MN, kStages>;
-    auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, kStages>;
+    auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, kStages, kCluster>;
     static bool attr_set = false;
     if (!attr_set) {
         DDL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
         attr_set = true;
     }
-    kern<<<grid, kThreads, L::kTotal, stream>>>(ta, tb, p);
-    DDL_LAUNCH_CHECK();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = L::kTotal;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kCluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DDL_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, tbh, p));
     return 0;
 }
 
 int g_sm_count = 0;
+int g_force_cluster = 0;  // 0 = auto, 1 or 2 = forced (benchmarks)
 
 }  // namespace
 
@@ -430,10 +515,21 @@ DDL_API int ddl_gemm_bf16(const void* A, int a_mn, long long lda, const void* B,
     // K-major operand [R=M|N, K]: box 64 (K) x BM|BN rows.  MN-major operand stored [K, M|N]: box 64 (MN) x 64 (K) rows.
     if (int e = a_mn ? make_map(&ta, A, K, M, lda, BK) : make_map(&ta, A, M, K, lda, BM)) return e;
     if (int e = b_mn ? make_map(&tb, B, K, N, ldb, BK) : make_map(&tb, B, N, K, ldb, BN)) return e;
-    const int tiles = p.num_m_blocks * p.num_n_blocks * p.split_k;
-    const int grid = tiles < g_sm_count ? tiles : g_sm_count;
+    // B shared by a 2-CTA cluster (multicast) whenever there are at least two row blocks
+    const int cluster = (g_force_cluster ? g_force_cluster : (p.num_m_blocks >= 2 ? 2 : 1));
+    CUtensorMap tbh = tb;
+    if (cluster == 2 && !b_mn) {
+        if (int e = make_map(&tbh, B, N, K, ldb, BN / 2)) return e;  // half-height box for the K-major B tile
+    }
+    const int m_groups = (p.num_m_blocks + cluster - 1) / cluster;
+    const int tiles = m_groups * p.num_n_blocks * p.split_k;  // per cluster
+    int grid = tiles * cluster < g_sm_count ? tiles * cluster : (g_sm_count / cluster) * cluster;
     cudaStream_t s = (cudaStream_t)stream_;
-#define GO(BN_, AM, BMN) return launch<BN_, AM, BMN>(ta, tb, p, grid, s)
+#define GO(BN_, AM, BMN)                                                         \
+    do {                                                                         \
+        if (cluster == 2) return launch<BN_, AM, BMN, 2>(ta, tb, tbh, p, grid, s); \
+        return launch<BN_, AM, BMN, 1>(ta, tb, tbh, p, grid, s);                   \
+    } while (0)
     if (BN == 256) {
         if (!a_mn && !b_mn) GO(256, false, false);
         if (!a_mn && b_mn) GO(256, false, true);
@@ -446,6 +542,12 @@ DDL_API int ddl_gemm_bf16(const void* A, int a_mn, long long lda, const void* B,
         GO(128, true, false);
     }
 #undef GO
+}
+
+DDL_API int ddl_gemm_set_cluster(int cluster) {
+    DDL_REQUIRE(cluster == 0 || cluster == 1 || cluster == 2, "cluster must be 0 (auto), 1 or 2");
+    g_force_cluster = cluster;
+    return 0;
 }
 
 DDL_API int ddl_f32_to_bf16(const float* in, void* out, size_t numel, int accumulate, void* stream_) {
