@@ -35,7 +35,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 KERNELS_PER_CALL = {"ddl_bn_act_fwd_train": 3, "ddl_bn_act_fwd_eval": 2, "ddl_bn_act_bwd": 3, "ddl_layernorm_bwd": 2,
-                    "ddl_cross_entropy": 2}
+                    "ddl_cross_entropy": 2, "ddl_colsum_bf16": 2, "ddl_attention_bwd": 2}
 
 
 def parse():
@@ -206,7 +206,8 @@ class OursRunner:
         model = build_model(wl.model, **kw)
         self.kw = kw
         self.trainer = Trainer(model, lr=wl.optim.lr, weight_decay=wl.optim.weight_decay, device=device, impl="fused",
-                               use_graph=not args.no_graph, comm=args.comm, bucket_cap_mb=args.bucket_mb)
+                               use_graph=not args.no_graph, comm=args.comm, bucket_cap_mb=args.bucket_mb,
+                               parallelism=wl.parallelism)
         self.graphed = not args.no_graph
         self.comm_name = self.trainer.ddp.comm.name
         self._count_calls()
@@ -228,7 +229,11 @@ class OursRunner:
         import databricks_distributed_deep_learning_b200.optim as OPT
         import databricks_distributed_deep_learning_b200.parallel.collectives as COL
 
-        for mod in (OF, OPT, COL):
+        import databricks_distributed_deep_learning_b200.ops.attention as ATT
+        import databricks_distributed_deep_learning_b200.ops.gemm as GEM
+        import databricks_distributed_deep_learning_b200.parallel.fsdp as FS  # noqa: F401
+
+        for mod in (OF, OPT, COL, ATT, GEM):
             mod.L.call = counting
         self._launched = 0
         tr = self.trainer

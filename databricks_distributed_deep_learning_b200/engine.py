@@ -55,7 +55,8 @@ class Trainer:
                  device: Optional[torch.device] = None, dtype: torch.dtype = torch.bfloat16, impl: str = "fused",
                  use_graph: bool = True, graph_warmup: int = 3, comm: str = "auto", bucket_cap_mb: float = 25.0,
                  overlap_optimizer: bool = True, loss_fn: Optional[Callable[[nn.Module, Any], torch.Tensor]] = None,
-                 broadcast_buffers: bool = False, channels_last: bool = True):
+                 broadcast_buffers: bool = False, channels_last: bool = True, parallelism: str = "ddp",
+                 reshard_after_forward: bool = False):
         self.device = device or pg.device()
         self.cuda = self.device.type == "cuda"
         self.fused = impl == "fused" and self.cuda
@@ -72,10 +73,22 @@ class Trainer:
         else:
             model = model.to(self.device)
         self.model = model
-        self.ddp = DistributedDataParallel(model, bucket_cap_mb=bucket_cap_mb, comm=comm, flatten_params=True,
-                                           broadcast_buffers=broadcast_buffers)
-        self.opt = FusedAdamW(self.ddp, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay,
-                              overlap=overlap_optimizer and self.cuda)
+        self.parallelism = parallelism
+        if parallelism == "fsdp":
+            # ZeRO-3: sharded parameters/optimizer state; the AdamW update is fused into the
+            # gradient reduce-scatter, so the wrapper is also the optimizer
+            from .parallel.fsdp import FullyShardedDataParallel
+
+            self.ddp = FullyShardedDataParallel(model, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, comm=comm,
+                                                reshard_after_forward=reshard_after_forward)
+            self.opt = self.ddp
+        elif parallelism == "ddp":
+            self.ddp = DistributedDataParallel(model, bucket_cap_mb=bucket_cap_mb, comm=comm, flatten_params=True,
+                                               broadcast_buffers=broadcast_buffers)
+            self.opt = FusedAdamW(self.ddp, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay,
+                                  overlap=overlap_optimizer and self.cuda)
+        else:
+            raise ValueError(f"parallelism must be 'ddp' or 'fsdp', got {parallelism!r}")
         self.loss_fn = loss_fn
         self.use_graph = use_graph and self.cuda
         self.graph_warmup = graph_warmup

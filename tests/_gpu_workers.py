@@ -182,3 +182,32 @@ def w_trainer_graph_sync(steps):
     same = all(torch.equal(flat, o) for o in pg.all_gather_object(flat))
     finite = all(l == l for l in out["losses"])
     return {"ok": same and finite, "losses": out["losses"], "comm": tr.ddp.comm.name}
+
+
+def w_fsdp_gpu(steps):
+    """FSDP Trainer (peer-memory all-gather + fused reduce-scatter/AdamW) vs the DDP Trainer."""
+    from databricks_distributed_deep_learning_b200.engine import Trainer
+    from databricks_distributed_deep_learning_b200.models import bert_tiny
+    from databricks_distributed_deep_learning_b200.utils.data import SyntheticTokenLoader
+
+    pg = _pg()
+    dev = pg.device()
+    rank, world = pg.rank(), pg.world_size()
+    results = {}
+    for mode, kw in (("ddp", {}), ("fsdp", {}), ("fsdp_reshard", {"reshard_after_forward": True})):
+        torch.manual_seed(3)
+        model = bert_tiny(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0)
+        tr = Trainer(model, lr=1e-3, device=dev, use_graph=(mode != "fsdp_reshard"), parallelism=mode.split("_")[0], bucket_cap_mb=1.0, **kw)
+        loader = SyntheticTokenLoader(8, seq_len=128, vocab_size=512, rank=rank, world_size=world, seed=4, steps=steps, pool=steps)
+        out = tr.fit(loader)
+        sd = tr.ddp.full_state_dict() if mode.startswith("fsdp") else {k: v.detach().cpu() for k, v in tr.model.state_dict().items()}
+        flat = torch.cat([sd[k].reshape(-1).float() for k in sorted(sd)])
+        same = all(torch.equal(flat, o) for o in pg.all_gather_object(flat))
+        results[mode] = {"losses": out["losses"], "flat": flat, "same": same}
+    ok = all(r["same"] for r in results.values())
+    ref = results["ddp"]["flat"]
+    diffs = {m: float((results[m]["flat"] - ref).abs().max()) for m in ("fsdp", "fsdp_reshard")}
+    # bf16 training: identical math, different reduction order/rounding points -> small drift
+    ok = ok and all(d < 2e-2 for d in diffs.values())
+    ok = ok and all(l == l for r in results.values() for l in r["losses"])
+    return {"ok": all(pg.all_gather_object(ok)), "diffs": diffs, "losses": {m: r["losses"] for m, r in results.items()}}

@@ -100,3 +100,54 @@ def single_process_resnet18(steps, per_rank_batch, world):
         F.cross_entropy(model(x), y).backward()
         opt.step()
     return torch.cat([p.detach().reshape(-1) for p in model.parameters()])
+
+
+def w_fsdp_bert_tiny(steps, reshard):
+    """FSDP (ZeRO-3) over gloo, world_size=2: ranks stay consistent and match a 1-process AdamW run."""
+    from databricks_distributed_deep_learning_b200.models import bert_tiny
+    from databricks_distributed_deep_learning_b200.parallel import process_group as pg
+    from databricks_distributed_deep_learning_b200.parallel.fsdp import FullyShardedDataParallel
+    from databricks_distributed_deep_learning_b200.utils.data import SyntheticTokenLoader
+
+    torch.set_num_threads(2)
+    rank, world = pg.rank(), pg.world_size()
+    torch.manual_seed(7)
+    model = bert_tiny(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0)
+    if rank != 0:
+        with torch.no_grad():
+            for p in model.parameters():
+                p.add_(0.5)  # must be repaired by the rank-0 broadcast at wrap time
+    fsdp = FullyShardedDataParallel(model, lr=1e-3, weight_decay=0.01, reshard_after_forward=reshard)
+    loader = SyntheticTokenLoader(4, seq_len=16, vocab_size=512, rank=rank, world_size=world, seed=2, steps=steps, pin_memory=False, pool=steps)
+    losses = []
+    for batch in loader:
+        fsdp.zero_grad()
+        loss, _ = fsdp(**batch)
+        loss.backward()
+        fsdp.step()
+        losses.append(float(loss.detach()))
+    sd = fsdp.full_state_dict()
+    keys = sorted(sd)
+    flat = torch.cat([sd[k].reshape(-1).float() for k in keys])
+    return {"flat": pg.all_gather_object(flat), "keys": keys, "units": len(fsdp.units), "losses": losses}
+
+
+def single_process_bert_tiny(steps, world):
+    from databricks_distributed_deep_learning_b200.models import bert_tiny
+    from databricks_distributed_deep_learning_b200.utils.data import SyntheticTokenLoader
+
+    torch.set_num_threads(2)
+    torch.manual_seed(7)
+    model = bert_tiny(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0)
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-3, weight_decay=0.01)
+    loaders = [iter(SyntheticTokenLoader(4, seq_len=16, vocab_size=512, rank=r, world_size=world, seed=2, steps=steps, pin_memory=False, pool=steps))
+               for r in range(world)]
+    for _ in range(steps):
+        bs = [next(l) for l in loaders]
+        batch = {k: torch.cat([b[k] for b in bs]) for k in bs[0]}
+        opt.zero_grad()
+        loss, _ = model(**batch)
+        loss.backward()
+        opt.step()
+    sd = model.state_dict()
+    return torch.cat([sd[k].reshape(-1).float() for k in sorted(sd)])

@@ -30,3 +30,8 @@ def test_ddp_p2p_matches_stock_ddp_nccl():
 def test_trainer_graph_multi_gpu_ranks_stay_in_sync():
     out = Distributor(num_processes=_world(), use_gpu=True, timeout_s=900).run(GW.w_trainer_graph_sync, 5)
     assert out["ok"], out
+
+
+def test_fsdp_gpu_matches_ddp():
+    out = Distributor(num_processes=_world(), use_gpu=True, timeout_s=900).run(GW.w_fsdp_gpu, 4)
+    assert out["ok"], out
