@@ -71,7 +71,7 @@ template <>
 struct G8<float> {
     static constexpr int kBytes = 32;
     __device__ static void load(const char* base, size_t g, float (&f)[8]) {
-        const uint4 a = ld_relaxed_sys_v4(base + g * 32), b = ld_relaxed_sys_v4(base + g * 32 + 16);
+        const uint4 a = ld_weak_noalloc_v4(base + g * 32), b = ld_weak_noalloc_v4(base + g * 32 + 16);
         f[0] = __uint_as_float(a.x); f[1] = __uint_as_float(a.y); f[2] = __uint_as_float(a.z); f[3] = __uint_as_float(a.w);
         f[4] = __uint_as_float(b.x); f[5] = __uint_as_float(b.y); f[6] = __uint_as_float(b.z); f[7] = __uint_as_float(b.w);
     }
@@ -87,7 +87,7 @@ template <>
 struct G8<bf16> {
     static constexpr int kBytes = 16;
     __device__ static void load(const char* base, size_t g, float (&f)[8]) {
-        bf16x8_to_float(ld_relaxed_sys_v4(base + g * 16), f);
+        bf16x8_to_float(ld_weak_noalloc_v4(base + g * 16), f);
     }
     __device__ static void store(char* base, size_t g, const float (&f)[8]) {
         st_global_v4(base + g * 16, float_to_bf16x8(f));
@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(Ctx c, Peer
 template <typename T>
 __device__ __forceinline__ void g8_load_raw(const char* base, size_t g, uint4 (&raw)[G8<T>::kBytes / 16]) {
 #pragma unroll
-    for (int i = 0; i < G8<T>::kBytes / 16; ++i) raw[i] = ld_relaxed_sys_v4(base + g * G8<T>::kBytes + i * 16);
+    for (int i = 0; i < G8<T>::kBytes / 16; ++i) raw[i] = ld_weak_noalloc_v4(base + g * G8<T>::kBytes + i * 16);
 }
 template <typename T>
 __device__ __forceinline__ void g8_accumulate(const uint4 (&raw)[G8<T>::kBytes / 16], float (&acc)[8]) {
@@ -315,7 +315,7 @@ __global__ void __launch_bounds__(kThreads) allgather_kernel(Ctx c, PeerPtrs sha
             uint4 v[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-                if (g + k * stride < shard16) v[k] = ld_relaxed_sys_v4(src + (g + k * stride) * 16);
+                if (g + k * stride < shard16) v[k] = ld_weak_noalloc_v4(src + (g + k * stride) * 16);
 #pragma unroll
             for (int k = 0; k < 4; ++k)
                 if (g + k * stride < shard16) st_global_v4(dst + (g + k * stride) * 16, v[k]);
@@ -418,7 +418,7 @@ __global__ void __launch_bounds__(kThreads) broadcast_kernel(Ctx c, PeerPtrs buf
         const char* src = buf.p[root];
         char* dst = buf.p[c.rank];
         for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < n16; g += stride)
-            st_global_v4(dst + g * 16, ld_relaxed_sys_v4(src + g * 16));
+            st_global_v4(dst + g * 16, ld_weak_noalloc_v4(src + g * 16));
     }
     block_barrier(c, epoch, false);
     epoch_end(c, epoch);

@@ -51,6 +51,16 @@ __device__ __forceinline__ uint4 ld_stream_v4(const void* p) {
                  : "l"(p));
     return r;
 }
+// weak (coalescing) 16 B load that skips L1 allocation: bulk peer-memory reads.  A warp's 32 x 16 B
+// become 128-byte NVLink requests; the strong .sys form below issues one request per lane.
+__device__ __forceinline__ uint4 ld_weak_noalloc_v4(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p)
+                 : "memory");
+    return r;
+}
 // volatile-ish 16 B load for peer memory written during this kernel's lifetime
 __device__ __forceinline__ uint4 ld_relaxed_sys_v4(const void* p) {
     uint4 r;
