@@ -30,6 +30,12 @@ def main():
         for bn in (128, 256):
             t = time_kernel(lambda: G.gemm_nt(a, b, M, N, K, out=out, block_n=bn), warmup=3, iters=20)
             res[f"ours_bn{bn}_tflops"] = flops / t["median_ms"] / 1e9
+        res["ours_2sm_tflops"] = res["ours_bn256_tflops"]  # mode 0 = CTA pairs (cta_group::2)
+        for mode, key in ((1, "ours_1cta_tflops"), (2, "ours_mcast_tflops")):
+            G.set_cluster_mode(mode)
+            t = time_kernel(lambda: G.gemm_nt(a, b, M, N, K, out=out, block_n=256), warmup=3, iters=20)
+            res[key] = flops / t["median_ms"] / 1e9
+        G.set_cluster_mode(0)
         t = time_kernel(lambda: torch.matmul(a, b.t(), out=out), warmup=3, iters=20)
         res["cublas_tflops"] = flops / t["median_ms"] / 1e9
         # backward-shaped calls
@@ -40,7 +46,7 @@ def main():
         t = time_kernel(lambda: G.gemm_nt(dy, a, N, K, M, a_mn=True, b_mn=True, split_k=sk), warmup=3, iters=10)
         res["ours_wgrad_tflops"] = flops / t["median_ms"] / 1e9
         res["wgrad_split_k"] = sk
-        best = max(res["ours_bn128_tflops"], res["ours_bn256_tflops"])
+        best = max(res["ours_bn128_tflops"], res["ours_bn256_tflops"], res.get("ours_2sm_tflops", 0.0))
         res.update(name=name, M=M, N=N, K=K, frac_of_measured_peak=best / peaks["bf16_tflops"], vs_cublas=best / res["cublas_tflops"])
         rows.append(res)
         print(json.dumps({k: (round(v, 3) if isinstance(v, float) else v) for k, v in res.items()}), flush=True)

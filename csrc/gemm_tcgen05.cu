@@ -70,6 +70,122 @@ struct GemmParams {
     int num_m_blocks, num_n_blocks, k_blocks_total;
 };
 
+// Epilogue of one 128-row x BN-column accumulator tile, executed by one epilogue warp (32 rows x BN/2
+// columns).  TMEM gives each thread one ROW; global memory wants one 128-byte line per 8 lanes.  The
+// warp stages each 32 x 64 bf16 chunk in a private 4 KB swizzled smem buffer and re-reads it
+// transposed: lane l <-> (row it*4 + l/8, 16-byte chunk l%8), so every global access (output, aux,
+// residual) is 4 full lines per instruction instead of 32 partial ones.
+template <int BN>
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint8_t* stg, uint32_t tmem_base, int acc_stage, int m_blk,
+                                              int n_blk, int quarter, int half, int lane) {
+    constexpr int kColsPerWarp = BN / 2;
+    const int t_sr = lane >> 3, t_ch = lane & 7;
+    auto stg_row = [&](int r, int c) -> uint4* { return reinterpret_cast<uint4*>(stg + r * 128 + ((c ^ (r & 7)) << 4)); };
+    const int row_base = m_blk * BM + quarter * 32;   // first row of this warp's 32
+    const int row = row_base + lane;
+#pragma unroll 1
+    for (int c = 0; c < kColsPerWarp; c += 64) {
+        const int col0 = n_blk * BN + half * kColsPerWarp + c;
+        uint32_t r0[32], r1[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc_stage * BN + half * kColsPerWarp + c);
+        tmem_ld_32x32(taddr, r0);
+        tmem_ld_32x32(taddr + 32, r1);
+        tmem_ld_wait();
+        if (col0 >= p.N) continue;
+        if (p.split_k > 1) {
+            if (row < p.M) {
+                float* dst = p.acc_f32 + (size_t)row * p.N + col0;
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    if (col0 + j < p.N)
+                        red_add_f32x4(dst + j, __uint_as_float(r0[j]), __uint_as_float(r0[j + 1]), __uint_as_float(r0[j + 2]), __uint_as_float(r0[j + 3]));
+                    if (col0 + 32 + j < p.N)
+                        red_add_f32x4(dst + 32 + j, __uint_as_float(r1[j]), __uint_as_float(r1[j + 1]), __uint_as_float(r1[j + 2]), __uint_as_float(r1[j + 3]));
+                }
+            }
+            continue;
+        }
+        // dGELU: bring the saved pre-activation in through the same buffer (coalesced load -> row domain)
+        if (p.epilogue == DDL_EPI_DGELU) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const int rr = it * 4 + t_sr;
+                uint4 v = make_uint4(0, 0, 0, 0);
+                if (row_base + rr < p.M && col0 + t_ch * 8 < p.N) v = ld_global_v4(p.aux + (size_t)(row_base + rr) * p.ldc + col0 + t_ch * 8);
+                *stg_row(rr, t_ch) = v;
+            }
+            __syncwarp();
+        }
+#pragma unroll
+        for (int g = 0; g < 8; ++g) {  // 8 column groups of 8
+            float w[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) w[q] = __uint_as_float(g < 4 ? r0[g * 8 + q] : r1[(g - 4) * 8 + q]);
+            const bool col_ok = col0 + g * 8 < p.N;
+            if (p.bias && col_ok) {
+                float bsv[8];
+                bf16x8_to_float(ld_global_v4(p.bias + col0 + g * 8), bsv);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) w[q] += bsv[q];
+            }
+            if (p.epilogue == DDL_EPI_DGELU) {
+                float pre[8];
+                bf16x8_to_float(*stg_row(lane, g), pre);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) w[q] *= dgelu_f(pre[q]);
+            } else if (p.epilogue == DDL_EPI_RELU) {
+#pragma unroll
+                for (int q = 0; q < 8; ++q) w[q] = fmaxf(w[q], 0.f);
+            }
+            // GELU keeps fp32 values in registers for the second pass; first pass stages the pre-activation
+            *stg_row(lane, g) = float_to_bf16x8(w);
+        }
+        __syncwarp();
+        if (p.epilogue == DDL_EPI_GELU) {
+            // pass 1: pre-activation -> aux (coalesced); pass 2: gelu(rounded pre) -> C
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const int rr = it * 4 + t_sr;
+                const uint4 pv = *stg_row(rr, t_ch);
+                if (row_base + rr < p.M && col0 + t_ch * 8 < p.N) {
+                    const size_t off = (size_t)(row_base + rr) * p.ldc + col0 + t_ch * 8;
+                    if (p.aux) st_global_v4(p.aux + off, pv);
+                    float f[8];
+                    bf16x8_to_float(pv, f);
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) f[q] = gelu_f(f[q]);
+                    if (p.residual) {
+                        float rs[8];
+                        bf16x8_to_float(ld_global_v4(p.residual + off), rs);
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) f[q] += rs[q];
+                    }
+                    st_global_v4(p.C + off, float_to_bf16x8(f));
+                }
+            }
+        } else {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const int rr = it * 4 + t_sr;
+                uint4 pv = *stg_row(rr, t_ch);
+                if (row_base + rr < p.M && col0 + t_ch * 8 < p.N) {
+                    const size_t off = (size_t)(row_base + rr) * p.ldc + col0 + t_ch * 8;
+                    if (p.residual) {
+                        float f[8], rs[8];
+                        bf16x8_to_float(pv, f);
+                        bf16x8_to_float(ld_global_v4(p.residual + off), rs);
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) f[q] += rs[q];
+                        pv = float_to_bf16x8(f);
+                    }
+                    st_global_v4(p.C + off, pv);
+                }
+            }
+        }
+        __syncwarp();  // buffer free for the next chunk
+    }
+}
+
 template <int BN, bool A_MN, bool B_MN, int kStages>
 struct SmemLayout {
     static constexpr int kABytes = BM * BK * 2;
@@ -210,18 +326,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
         }
     } else {
         // ===================== epilogue warps =====================
-        // TMEM gives each thread one ROW of the tile; global memory wants one 128-byte line per
-        // 8 lanes.  Each warp therefore stages its 32 x 64 bf16 chunk in a private 4 KB
-        // swizzled smem buffer and re-reads it transposed: lane l <-> (row it*4 + l/8, 16-byte
-        // chunk l%8), so every global access (output, aux, residual) is 4 full lines per
-        // instruction instead of 32 partial ones.
         const int ew = warp - 2;              // 0..7
         const int quarter = warp & 3;         // TMEM lane quarter this warp may access
         const int half = ew >> 2;             // which half of the tile's columns
-        constexpr int kColsPerWarp = BN / 2;
         uint8_t* stg = smem + L::kStageOffset + ew * 4096;
-        const int t_sr = lane >> 3, t_ch = lane & 7;
-        auto stg_row = [&](int r, int c) -> uint4* { return reinterpret_cast<uint4*>(stg + r * 128 + ((c ^ (r & 7)) << 4)); };
         int acc_stage = 0;
         uint32_t acc_phase = 0;
         for (int tile = sched_id; tile < num_tiles; tile += sched_n) {
@@ -229,109 +337,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
             const int m_blk = (mn / p.num_n_blocks) * kCluster + cta_rank, n_blk = mn % p.num_n_blocks;
             mbar_wait(&tmem_full[acc_stage], acc_phase);
             tc_fence_after();
-            const int row_base = m_blk * BM + quarter * 32;   // first row of this warp's 32
-            const int row = row_base + lane;
-#pragma unroll 1
-            for (int c = 0; c < kColsPerWarp; c += 64) {
-                const int col0 = n_blk * BN + half * kColsPerWarp + c;
-                uint32_t r0[32], r1[32];
-                const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc_stage * BN + half * kColsPerWarp + c);
-                tmem_ld_32x32(taddr, r0);
-                tmem_ld_32x32(taddr + 32, r1);
-                tmem_ld_wait();
-                if (col0 >= p.N) continue;
-                if (p.split_k > 1) {
-                    if (row < p.M) {
-                        float* dst = p.acc_f32 + (size_t)row * p.N + col0;
-#pragma unroll
-                        for (int j = 0; j < 32; j += 4) {
-                            if (col0 + j < p.N)
-                                red_add_f32x4(dst + j, __uint_as_float(r0[j]), __uint_as_float(r0[j + 1]), __uint_as_float(r0[j + 2]), __uint_as_float(r0[j + 3]));
-                            if (col0 + 32 + j < p.N)
-                                red_add_f32x4(dst + 32 + j, __uint_as_float(r1[j]), __uint_as_float(r1[j + 1]), __uint_as_float(r1[j + 2]), __uint_as_float(r1[j + 3]));
-                        }
-                    }
-                    continue;
-                }
-                // dGELU: bring the saved pre-activation in through the same buffer (coalesced load -> row domain)
-                if (p.epilogue == DDL_EPI_DGELU) {
-#pragma unroll
-                    for (int it = 0; it < 8; ++it) {
-                        const int rr = it * 4 + t_sr;
-                        uint4 v = make_uint4(0, 0, 0, 0);
-                        if (row_base + rr < p.M && col0 + t_ch * 8 < p.N) v = ld_global_v4(p.aux + (size_t)(row_base + rr) * p.ldc + col0 + t_ch * 8);
-                        *stg_row(rr, t_ch) = v;
-                    }
-                    __syncwarp();
-                }
-#pragma unroll
-                for (int g = 0; g < 8; ++g) {  // 8 column groups of 8
-                    float w[8];
-#pragma unroll
-                    for (int q = 0; q < 8; ++q) w[q] = __uint_as_float(g < 4 ? r0[g * 8 + q] : r1[(g - 4) * 8 + q]);
-                    const bool col_ok = col0 + g * 8 < p.N;
-                    if (p.bias && col_ok) {
-                        float bsv[8];
-                        bf16x8_to_float(ld_global_v4(p.bias + col0 + g * 8), bsv);
-#pragma unroll
-                        for (int q = 0; q < 8; ++q) w[q] += bsv[q];
-                    }
-                    if (p.epilogue == DDL_EPI_DGELU) {
-                        float pre[8];
-                        bf16x8_to_float(*stg_row(lane, g), pre);
-#pragma unroll
-                        for (int q = 0; q < 8; ++q) w[q] *= dgelu_f(pre[q]);
-                    } else if (p.epilogue == DDL_EPI_RELU) {
-#pragma unroll
-                        for (int q = 0; q < 8; ++q) w[q] = fmaxf(w[q], 0.f);
-                    }
-                    // GELU keeps fp32 values in registers for the second pass; first pass stages the pre-activation
-                    *stg_row(lane, g) = float_to_bf16x8(w);
-                }
-                __syncwarp();
-                if (p.epilogue == DDL_EPI_GELU) {
-                    // pass 1: pre-activation -> aux (coalesced); pass 2: gelu(rounded pre) -> C
-#pragma unroll
-                    for (int it = 0; it < 8; ++it) {
-                        const int rr = it * 4 + t_sr;
-                        const uint4 pv = *stg_row(rr, t_ch);
-                        if (row_base + rr < p.M && col0 + t_ch * 8 < p.N) {
-                            const size_t off = (size_t)(row_base + rr) * p.ldc + col0 + t_ch * 8;
-                            if (p.aux) st_global_v4(p.aux + off, pv);
-                            float f[8];
-                            bf16x8_to_float(pv, f);
-#pragma unroll
-                            for (int q = 0; q < 8; ++q) f[q] = gelu_f(f[q]);
-                            if (p.residual) {
-                                float rs[8];
-                                bf16x8_to_float(ld_global_v4(p.residual + off), rs);
-#pragma unroll
-                                for (int q = 0; q < 8; ++q) f[q] += rs[q];
-                            }
-                            st_global_v4(p.C + off, float_to_bf16x8(f));
-                        }
-                    }
-                } else {
-#pragma unroll
-                    for (int it = 0; it < 8; ++it) {
-                        const int rr = it * 4 + t_sr;
-                        uint4 pv = *stg_row(rr, t_ch);
-                        if (row_base + rr < p.M && col0 + t_ch * 8 < p.N) {
-                            const size_t off = (size_t)(row_base + rr) * p.ldc + col0 + t_ch * 8;
-                            if (p.residual) {
-                                float f[8], rs[8];
-                                bf16x8_to_float(pv, f);
-                                bf16x8_to_float(ld_global_v4(p.residual + off), rs);
-#pragma unroll
-                                for (int q = 0; q < 8; ++q) f[q] += rs[q];
-                                pv = float_to_bf16x8(f);
-                            }
-                            st_global_v4(p.C + off, pv);
-                        }
-                    }
-                }
-                __syncwarp();  // buffer free for the next chunk
-            }
+            epilogue_tile<BN>(p, stg, tmem_base, acc_stage, m_blk, n_blk, quarter, half, lane);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);
@@ -344,6 +350,151 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// cta_group::2 variant: a CTA PAIR (cluster of 2 on one TPC) computes one 256 x 256 tile.
+// Each CTA stages its own 128 rows of A and its own half (128 rows) of B per k-block (32 KB per
+// stage instead of 48 KB -> 6 stages, and half the shared-memory read traffic per MMA); the leader
+// issues tcgen05.mma.cta_group::2 (M = 256, N = 256) which reads both CTAs' shared memory and
+// accumulates into both CTAs' tensor memory; each CTA's epilogue drains its own 128 rows.
+//   full barrier   : leader's; its producer arms 64 KB, both CTAs' TMA complete on it
+//   empty barriers : one per CTA, released together by the leader's multicast commit
+//   tmem_full      : one per CTA (multicast commit); tmem_empty: leader's, 16 warp arrivals
+template <bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(kThreads, 1) gemm2sm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a,
+                                                                   const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
+    constexpr int BN = 256, kHalfN = 128, kStages = 6;
+    constexpr int kABytes = BM * BK * 2, kBBytes = kHalfN * BK * 2, kStageBytes = kABytes + kBBytes;  // 32 KB
+    constexpr int kStageOffset = kStages * kStageBytes, kBarOffset = kStageOffset + kEpiWarps * 4096;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kBarOffset);
+    uint64_t* empty_bar = full_bar + kStages;
+    uint64_t* tmem_full = empty_bar + kStages;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int cta_rank = (int)cluster_ctarank();
+    const bool leader = cta_rank == 0;
+    constexpr uint32_t kTmemCols = 512;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full[s], 1);
+            mbar_init(&tmem_empty[s], 2 * kEpiWarps);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc_2sm(tmem_ptr_smem, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    const int sched_id = blockIdx.x >> 1, sched_n = gridDim.x >> 1;
+    const int m_pairs = (p.num_m_blocks + 1) / 2;  // 256-row blocks
+    const int tiles_mn = m_pairs * p.num_n_blocks;
+    const int num_tiles = tiles_mn * p.split_k;
+    const int kb_per_split = (p.k_blocks_total + p.split_k - 1) / p.split_k;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = sched_id; tile < num_tiles; tile += sched_n) {
+                const int ks = tile / tiles_mn, mn = tile % tiles_mn;
+                const int m_blk = (mn / p.num_n_blocks) * 2 + cta_rank, n_blk = mn % p.num_n_blocks;
+                const int kb0 = ks * kb_per_split;
+                const int kb1 = min(kb0 + kb_per_split, p.k_blocks_total);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* sa = smem + stage * kStageBytes;
+                    uint8_t* sb = sa + kABytes;
+                    if (leader) mbar_expect_tx(&full_bar[stage], 2 * kStageBytes);
+                    if (A_MN) {
+#pragma unroll
+                        for (int j = 0; j < BM / 64; ++j) tma_load_2d_2sm(sa + j * (BK * 128), &tma_a, &full_bar[stage], m_blk * BM + j * 64, kb * BK);
+                    } else {
+                        tma_load_2d_2sm(sa, &tma_a, &full_bar[stage], kb * BK, m_blk * BM);
+                    }
+                    const int n0 = n_blk * BN + cta_rank * kHalfN;
+                    if (B_MN) {
+#pragma unroll
+                        for (int j = 0; j < kHalfN / 64; ++j) tma_load_2d_2sm(sb + j * (BK * 128), &tma_b, &full_bar[stage], n0 + j * 64, kb * BK);
+                    } else {
+                        tma_load_2d_2sm(sb, &tma_b, &full_bar[stage], kb * BK, n0);
+                    }
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && leader) {
+            constexpr uint32_t idesc = make_idesc(2 * BM, BN, A_MN, B_MN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc_stage = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = sched_id; tile < num_tiles; tile += sched_n) {
+                const int ks = tile / tiles_mn;
+                const int kb0 = ks * kb_per_split;
+                const int kb1 = min(kb0 + kb_per_split, p.k_blocks_total);
+                mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc_stage * BN;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * kStageBytes);
+                    const uint32_t sb = sa + kABytes;
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) {
+                        const uint64_t da = A_MN ? make_smem_desc(sa + k * 2048, BK * 128, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
+                        const uint64_t db = B_MN ? make_smem_desc(sb + k * 2048, BK * 128, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
+                        umma_bf16_2sm(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit_2sm(&empty_bar[stage]);
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit_2sm(&tmem_full[acc_stage]);
+                if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
+            }
+        }
+    } else {
+        const int ew = warp - 2;
+        const int quarter = warp & 3;
+        const int half = ew >> 2;
+        uint8_t* stg = smem + kStageOffset + ew * 4096;
+        int acc_stage = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = sched_id; tile < num_tiles; tile += sched_n) {
+            const int mn = tile % tiles_mn;
+            const int m_blk = (mn / p.num_n_blocks) * 2 + cta_rank, n_blk = mn % p.num_n_blocks;
+            mbar_wait(&tmem_full[acc_stage], acc_phase);
+            tc_fence_after();
+            epilogue_tile<BN>(p, stg, tmem_base, acc_stage, m_blk, n_blk, quarter, half, lane);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(&tmem_empty[acc_stage]);
+            if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_2sm(tmem_base, kTmemCols);
     }
 }
 
@@ -473,7 +624,33 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tbh,
     return 0;
 }
 
+template <bool A_MN, bool B_MN>
+int launch_2sm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t stream) {
+    constexpr int kSmem = 6 * (BM * BK * 2 + 128 * BK * 2) + kEpiWarps * 4096 + 256 + 1024;
+    auto kern = gemm2sm_bf16_kernel<A_MN, B_MN>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        DDL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = kSmem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DDL_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
+    return 0;
+}
+
 int g_sm_count = 0;
+int g_two_sm = 1;  // use the cta_group::2 kernel for BN = 256 problems with >= 2 row blocks (measured fastest)
 int g_force_cluster = 0;  // 0 = auto, 1 or 2 = forced (benchmarks)
 
 }  // namespace
@@ -515,8 +692,23 @@ DDL_API int ddl_gemm_bf16(const void* A, int a_mn, long long lda, const void* B,
     // K-major operand [R=M|N, K]: box 64 (K) x BM|BN rows.  MN-major operand stored [K, M|N]: box 64 (MN) x 64 (K) rows.
     if (int e = a_mn ? make_map(&ta, A, K, M, lda, BK) : make_map(&ta, A, M, K, lda, BM)) return e;
     if (int e = b_mn ? make_map(&tb, B, K, N, ldb, BK) : make_map(&tb, B, N, K, ldb, BN)) return e;
+    if (g_two_sm && BN == 256 && p.num_m_blocks >= 2) {
+        // CTA pairs: 256 x 256 tiles, half-height B boxes (K-major) / 64 x 64 boxes (MN-major)
+        CUtensorMap tb2 = tb;
+        if (!b_mn) {
+            if (int e = make_map(&tb2, B, N, K, ldb, 128)) return e;
+        }
+        const int m_pairs = (p.num_m_blocks + 1) / 2;
+        const int pair_tiles = m_pairs * p.num_n_blocks * p.split_k;
+        const int grid2 = pair_tiles * 2 < g_sm_count ? pair_tiles * 2 : (g_sm_count / 2) * 2;
+        cudaStream_t s2 = (cudaStream_t)stream_;
+        if (!a_mn && !b_mn) return launch_2sm<false, false>(ta, tb2, p, grid2, s2);
+        if (!a_mn && b_mn) return launch_2sm<false, true>(ta, tb2, p, grid2, s2);
+        if (a_mn && b_mn) return launch_2sm<true, true>(ta, tb2, p, grid2, s2);
+        return launch_2sm<true, false>(ta, tb2, p, grid2, s2);
+    }
     // B shared by a 2-CTA cluster (multicast) whenever there are at least two row blocks
-    const int cluster = (g_force_cluster ? g_force_cluster : (p.num_m_blocks >= 2 ? 2 : 1));
+    const int cluster = (g_force_cluster == 2 && p.num_m_blocks >= 2) ? 2 : 1;  // multicast sharing measured no faster than 1 CTA
     CUtensorMap tbh = tb;
     if (cluster == 2 && !b_mn) {
         if (int e = make_map(&tbh, B, N, K, ldb, BN / 2)) return e;  // half-height box for the K-major B tile
@@ -545,7 +737,11 @@ DDL_API int ddl_gemm_bf16(const void* A, int a_mn, long long lda, const void* B,
 }
 
 DDL_API int ddl_gemm_set_cluster(int cluster) {
-    DDL_REQUIRE(cluster == 0 || cluster == 1 || cluster == 2, "cluster must be 0 (auto), 1 or 2");
+    // 0 = auto (CTA pairs with tcgen05.mma.cta_group::2 on 256 x 256 tiles when the problem has >= 2 row
+    //     blocks and BN = 256, else one CTA per tile), 1 = always one CTA per tile,
+    // 2 = 2-CTA cluster sharing B by TMA multicast (cta_group::1 MMAs), 3 = same as 0
+    DDL_REQUIRE(cluster >= 0 && cluster <= 3, "cluster mode must be 0..3");
+    g_two_sm = (cluster == 0 || cluster == 3);
     g_force_cluster = cluster;
     return 0;
 }

@@ -26,11 +26,28 @@ EPI_NONE, EPI_GELU, EPI_DGELU, EPI_RELU = 0, 1, 2, 3
 _NUM_SMS = 148
 
 
+def set_cluster_mode(mode: int) -> None:
+    """0 = auto, 1 = single CTA, 2 = 2-CTA cluster sharing B by TMA multicast, 3 = CTA pairs with
+    ``tcgen05.mma.cta_group::2`` (256 x 256 tiles)."""
+    L.check(L.lib().ddl_gemm_set_cluster(int(mode)), "ddl_gemm_set_cluster")
+
+
+def _apply_env_mode() -> None:
+    import os
+
+    m = os.environ.get("DDL_GEMM_CLUSTER")
+    if m is not None and available():
+        set_cluster_mode(int(m))
+
+
 def available() -> bool:
     try:
         return hasattr(L.lib(), "ddl_gemm_bf16")
     except L.DdlError:
         return False
+
+
+_env_applied = False
 
 
 def usable(x: torch.Tensor, weight: torch.Tensor) -> bool:
@@ -44,6 +61,10 @@ def gemm_nt(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn: b
             epilogue: int = EPI_NONE, out: Optional[torch.Tensor] = None, split_k: int = 1, block_n: int = 0) -> torch.Tensor:
     """C[M,N] = epilogue(A . B^T).  ``a``/``b`` are 2-D row-major bf16 tensors holding the operand
     as [M,K]/[N,K] (default) or as [K,M]/[K,N] (``a_mn``/``b_mn``)."""
+    global _env_applied
+    if not _env_applied:
+        _env_applied = True
+        _apply_env_mode()
     dev = a.device
     if out is None:
         out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)

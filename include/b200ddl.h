@@ -166,7 +166,8 @@ int ddl_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream
 int ddl_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb, void* C, long long ldc, int M, int N,
                   int K, const void* bias, const void* residual, void* aux, int epilogue, int split_k, float* acc_f32, int block_n,
                   void* stream);
-/* 0 = auto (2-CTA clusters sharing the B tile by TMA multicast when M spans >= 2 row blocks), 1, 2 */
+/* launch mode: 0 = auto (CTA pairs, tcgen05.mma.cta_group::2, 256x256 tiles, when eligible), 1 = one CTA per
+ * tile, 2 = 2-CTA cluster sharing B by TMA multicast, 3 = same as 0 */
 int ddl_gemm_set_cluster(int cluster);
 int ddl_f32_to_bf16(const float* in, void* out, size_t numel, int accumulate, void* stream);
 size_t ddl_colsum_scratch_bytes(int rows, int cols);

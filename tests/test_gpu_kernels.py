@@ -276,10 +276,19 @@ def _gemm():
     return gemm
 
 
+@pytest.fixture(params=[0, 1, 2], ids=["2sm-pair", "1cta", "mcast"])
+def gemm_mode(request):
+    """Run the GEMM tests under each launch mode (cluster multicast, single CTA, cta_group::2 pairs)."""
+    g = _gemm()
+    g.set_cluster_mode(request.param)
+    yield request.param
+    g.set_cluster_mode(0)
+
+
 @pytest.mark.parametrize("M,N,K", [(128, 128, 64), (256, 256, 128), (384, 768, 768), (1000, 2304, 768), (128, 3072, 768),
                                    (4096, 768, 3072), (77, 256, 200), (130, 136, 72)])
 @pytest.mark.parametrize("block_n", [128, 256])
-def test_gemm_tn_matches_fp32(M, N, K, block_n):
+def test_gemm_tn_matches_fp32(M, N, K, block_n, gemm_mode):
     g = _gemm()
     a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
     b = torch.randn(N, K, device="cuda").to(torch.bfloat16)
@@ -292,7 +301,7 @@ def test_gemm_tn_matches_fp32(M, N, K, block_n):
 
 @pytest.mark.parametrize("a_mn,b_mn", [(False, True), (True, True), (True, False)])
 @pytest.mark.parametrize("M,N,K", [(256, 256, 128), (768, 768, 1024), (2304, 768, 640), (128, 136, 64)])
-def test_gemm_mn_major_operands(a_mn, b_mn, M, N, K):
+def test_gemm_mn_major_operands(a_mn, b_mn, M, N, K, gemm_mode):
     g = _gemm()
     a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
     b = torch.randn(N, K, device="cuda").to(torch.bfloat16)
@@ -304,7 +313,7 @@ def test_gemm_mn_major_operands(a_mn, b_mn, M, N, K):
 
 
 @pytest.mark.parametrize("split_k", [2, 5, 8])
-def test_gemm_split_k(split_k):
+def test_gemm_split_k(split_k, gemm_mode):
     g = _gemm()
     M, N, K = 768, 768, 4096
     a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
@@ -314,7 +323,7 @@ def test_gemm_split_k(split_k):
     assert torch.allclose(c.float(), ref, rtol=2e-2, atol=1.0), (c.float() - ref).abs().max().item()
 
 
-def test_gemm_epilogues():
+def test_gemm_epilogues(gemm_mode):
     g = _gemm()
     M, N, K = 512, 768, 256
     a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
