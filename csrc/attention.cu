@@ -55,10 +55,20 @@ struct AttnParams {
     float* dq_acc;             // [B*S, H] fp32, only when S > 128
 };
 
+// 32-bit finaliser (two multiplies): cheap enough to run once per 4 probabilities in forward and once
+// per probability in backward (where a thread owns one key and walks the queries)
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {
+    x ^= x >> 16;
+    x *= 0x7feb352du;
+    x ^= x >> 15;
+    x *= 0x846ca68bu;
+    x ^= x >> 16;
+    return x;
+}
 // 4 dropout decisions (bits) for elements (q, kv4*4 .. kv4*4+3) of head `bh`
 __device__ __forceinline__ uint32_t drop_keep4(uint64_t seed, uint32_t bh, uint32_t q, uint32_t kv4, uint32_t S, uint32_t thr) {
-    const uint64_t idx = ((uint64_t)bh * S + q) * (S >> 2) + kv4;
-    const uint32_t h = hash_u32(seed, idx);
+    const uint32_t idx = (bh * S + q) * (S >> 2) + kv4;
+    const uint32_t h = mix32(idx * 0x9E3779B1u + (uint32_t)seed) ^ mix32((uint32_t)(seed >> 32) + idx);
     uint32_t m = 0;
 #pragma unroll
     for (int i = 0; i < 4; ++i) m |= (((h >> (8 * i)) & 0xffu) >= thr ? 1u : 0u) << i;

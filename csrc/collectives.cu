@@ -360,7 +360,7 @@ __global__ void __launch_bounds__(kThreads) reducescatter_kernel(Ctx c, PeerPtrs
 // touches memory: it is consumed in registers by the optimizer, which updates the fp32
 // master / moments of this rank's shard and writes the bf16 parameter shard.
 // hyper = {lr, beta1, beta2, eps, weight_decay, step} in device memory (graph friendly).
-template <typename Tin>
+template <typename Tin, int W>
 __global__ void __launch_bounds__(kThreads) reducescatter_adamw_kernel(Ctx c, PeerPtrs full, size_t shard8, float scale,
                                                                        float* __restrict__ master, float* __restrict__ m,
                                                                        float* __restrict__ v, bf16* __restrict__ param_out,
@@ -369,26 +369,47 @@ __global__ void __launch_bounds__(kThreads) reducescatter_adamw_kernel(Ctx c, Pe
     const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4], step = hyper[5];
     const float bc1 = 1.f - powf(b1, step), bc2 = 1.f - powf(b2, step);
     const float inv_bc1 = 1.f / bc1, inv_sqrt_bc2 = rsqrtf(bc2);
+    const int world = W > 0 ? W : c.world;
     const size_t base = shard8 * c.rank;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
+    constexpr int kVec = G8<Tin>::kBytes / 16;
     block_barrier(c, epoch, false);
     for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < shard8; g += stride) {
         float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        for (int r = 0; r < c.world; ++r) {
-            int peer = c.rank + r;
-            if (peer >= c.world) peer -= c.world;
-            float f[8];
-            G8<Tin>::load(full.p[peer], base + g, f);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) acc[j] += f[j];
-        }
+        // issue every load of this granule first: W peer gradient vectors + 6 optimizer-state vectors
         float w[8], mm[8], vv[8];
-        *reinterpret_cast<float4*>(&w[0]) = *reinterpret_cast<const float4*>(master + g * 8);
-        *reinterpret_cast<float4*>(&w[4]) = *reinterpret_cast<const float4*>(master + g * 8 + 4);
-        *reinterpret_cast<float4*>(&mm[0]) = *reinterpret_cast<const float4*>(m + g * 8);
-        *reinterpret_cast<float4*>(&mm[4]) = *reinterpret_cast<const float4*>(m + g * 8 + 4);
-        *reinterpret_cast<float4*>(&vv[0]) = *reinterpret_cast<const float4*>(v + g * 8);
-        *reinterpret_cast<float4*>(&vv[4]) = *reinterpret_cast<const float4*>(v + g * 8 + 4);
+        if constexpr (W > 0) {
+            uint4 raw[W][kVec];
+#pragma unroll
+            for (int r = 0; r < W; ++r) {
+                int peer = c.rank + r;
+                if (peer >= W) peer -= W;
+                g8_load_raw<Tin>(full.p[peer], base + g, raw[r]);
+            }
+            *reinterpret_cast<float4*>(&w[0]) = *reinterpret_cast<const float4*>(master + g * 8);
+            *reinterpret_cast<float4*>(&w[4]) = *reinterpret_cast<const float4*>(master + g * 8 + 4);
+            *reinterpret_cast<float4*>(&mm[0]) = *reinterpret_cast<const float4*>(m + g * 8);
+            *reinterpret_cast<float4*>(&mm[4]) = *reinterpret_cast<const float4*>(m + g * 8 + 4);
+            *reinterpret_cast<float4*>(&vv[0]) = *reinterpret_cast<const float4*>(v + g * 8);
+            *reinterpret_cast<float4*>(&vv[4]) = *reinterpret_cast<const float4*>(v + g * 8 + 4);
+#pragma unroll
+            for (int r = 0; r < W; ++r) g8_accumulate<Tin>(raw[r], acc);
+        } else {
+            for (int r = 0; r < world; ++r) {
+                int peer = c.rank + r;
+                if (peer >= world) peer -= world;
+                float f[8];
+                G8<Tin>::load(full.p[peer], base + g, f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] += f[j];
+            }
+            *reinterpret_cast<float4*>(&w[0]) = *reinterpret_cast<const float4*>(master + g * 8);
+            *reinterpret_cast<float4*>(&w[4]) = *reinterpret_cast<const float4*>(master + g * 8 + 4);
+            *reinterpret_cast<float4*>(&mm[0]) = *reinterpret_cast<const float4*>(m + g * 8);
+            *reinterpret_cast<float4*>(&mm[4]) = *reinterpret_cast<const float4*>(m + g * 8 + 4);
+            *reinterpret_cast<float4*>(&vv[0]) = *reinterpret_cast<const float4*>(v + g * 8);
+            *reinterpret_cast<float4*>(&vv[4]) = *reinterpret_cast<const float4*>(v + g * 8 + 4);
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const float gr = acc[j] * scale;
@@ -591,12 +612,20 @@ DDL_API int ddl_reducescatter_adamw(const ddl_comm_t* comm, void* const* full_pt
     const size_t s8 = shard_numel / 8;
     const int nb = clamp_blocks(num_blocks, s8, kThreads);
     cudaStream_t stream = (cudaStream_t)stream_;
-    if (in_dtype == DDL_BF16)
-        reducescatter_adamw_kernel<bf16><<<nb, kThreads, 0, stream>>>(c, fp, s8, scale, master, m, v, (bf16*)param_out_bf16, hyper);
-    else if (in_dtype == DDL_F32)
-        reducescatter_adamw_kernel<float><<<nb, kThreads, 0, stream>>>(c, fp, s8, scale, master, m, v, (bf16*)param_out_bf16, hyper);
-    else
-        DDL_REQUIRE(false, "bad dtype");
+#define RSA(TI, W_) reducescatter_adamw_kernel<TI, W_><<<nb, kThreads, 0, stream>>>(c, fp, s8, scale, master, m, v, (bf16*)param_out_bf16, hyper)
+#define RSA_W(TI)                       \
+    do {                                \
+        if (c.world == 1) RSA(TI, 1);   \
+        else if (c.world == 2) RSA(TI, 2); \
+        else if (c.world == 4) RSA(TI, 4); \
+        else if (c.world == 8) RSA(TI, 8); \
+        else RSA(TI, 0);                \
+    } while (0)
+    if (in_dtype == DDL_BF16) RSA_W(bf16);
+    else if (in_dtype == DDL_F32) RSA_W(float);
+    else DDL_REQUIRE(false, "bad dtype");
+#undef RSA_W
+#undef RSA
     DDL_LAUNCH_CHECK();
     return 0;
 }

@@ -109,6 +109,9 @@ class FullyShardedDataParallel(nn.Module):
         self.defaults = dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=weight_decay)
         self.hyper = torch.tensor([lr, betas[0], betas[1], eps, weight_decay, 1.0, 0.0, 0.0], dtype=torch.float32, device=self.device)
         self._step = 1
+        # bandwidth-bound kernels that also stream the optimizer state: one CTA per SM
+        self.comm_blocks = 148
+        self._blk = {"num_blocks": 148} if hasattr(self.comm, "reduce_scatter_adamw_") else {}
         self._comm_stream = torch.cuda.Stream(self.device) if self.cuda else None
         self.require_backward_grad_sync = True
 
@@ -180,7 +183,7 @@ class FullyShardedDataParallel(nn.Module):
         if self.cuda:
             self._comm_stream.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(self._comm_stream):
-                self.comm.all_gather_into(u.full_param, u.shard_param).wait()
+                self.comm.all_gather_into(u.full_param, u.shard_param, **self._blk).wait()
                 u.gathered_event.record(self._comm_stream)
         else:
             self.comm.all_gather_into(u.full_param, u.shard_param).wait()
@@ -252,7 +255,8 @@ class FullyShardedDataParallel(nn.Module):
 
     def _rs_adamw(self, u: _Unit) -> None:
         if hasattr(self.comm, "reduce_scatter_adamw_") and self.cuda:
-            self.comm.reduce_scatter_adamw_(u.full_grad, u.master, u.exp_avg, u.exp_avg_sq, u.shard_param, self.hyper)
+            self.comm.reduce_scatter_adamw_(u.full_grad, u.master, u.exp_avg, u.exp_avg_sq, u.shard_param, self.hyper,
+                                            num_blocks=self.comm_blocks)
             return
         # plumbing path: unfused reduce-scatter, tensor-op AdamW
         g = torch.empty(u.shard_numel, dtype=u.full_grad.dtype, device=self.device)
