@@ -265,33 +265,48 @@ __device__ __forceinline__ void st_swizzled_chunk(uint8_t* tile, int row, int ch
     *reinterpret_cast<uint4*>(dst) = v;
 }
 
-__global__ void __launch_bounds__(128, 1) attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
-                                                          const __grid_constant__ CUtensorMap tma_do, const AttnParams p) {
+// kSingle (S == 128): one query tile, nothing accumulates across iterations, so the gradient
+// accumulators reuse consumed S^T / dP^T columns (256 TMEM columns, 96 KB smem -> two CTAs per SM).
+// Otherwise: dV / dK accumulate over the query tiles in their own columns, and the Q / dO tiles of
+// the next iteration are prefetched by TMA while this one is in its softmax phase.
+template <bool kSingle>
+__global__ void __launch_bounds__(kSingle ? 128 : 256, kSingle ? 2 : 1) attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
+                                                                        const __grid_constant__ CUtensorMap tma_do, const AttnParams p) {
+    constexpr int kBufs = kSingle ? 1 : 2;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    uint8_t* sK = smem;                      // [128 kv x 64]
+    uint8_t* sK = smem;                          // [128 kv x 64]
     uint8_t* sV = sK + kTileBytes;
-    uint8_t* sQ = sV + kTileBytes;           // [128 q x 64]
-    uint8_t* sdO = sQ + kTileBytes;
-    uint8_t* sPt = sdO + kTileBytes;         // P^T  [128 kv x 128 q], two swizzled 64-column blocks
-    uint8_t* sdSt = sPt + 2 * kTileBytes;    // dS^T
+    uint8_t* sQ = sV + kTileBytes;               // [kBufs][128 q x 64]
+    uint8_t* sdO = sQ + kBufs * kTileBytes;      // [kBufs]
+    uint8_t* sdSt = sdO + kBufs * kTileBytes;    // dS^T [128 kv x 128 q], two swizzled 64-column blocks (A of dQ, read MN-major)
     float* sLse = reinterpret_cast<float*>(sdSt + 2 * kTileBytes);  // [128]
     float* sDv = sLse + TILE;                                       // [128]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sDv + TILE);      // [0] kv load, [1] q load, [2] S/dP ready, [3] grads ready
-    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 4);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sDv + TILE);
+    // bars: [0] K/V  [1],[2] Q/dO buffer 0/1  [3] S^T,dP^T ready  [4] dV done (P^T columns free)  [5] all gradients of the tile ready
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 8);
 
+    // thread -> (key row, column half).  kSingle: 128 threads, one per row.  Otherwise 256 threads: warps w and
+    // w+4 share a TMEM lane quarter and split the query columns, which halves the exp/hash work per thread.
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int quarter = warp & 3, half = warp >> 2;
+    constexpr int kHalves = kSingle ? 1 : 2;
+    constexpr int kChunksPerThread = (TILE / 32) / kHalves;
     const int kv_tile = blockIdx.x, hd = blockIdx.y, b = blockIdx.z;
     const int kv_len = p.seqlens ? min(max(p.seqlens[b], 1), p.S) : p.S;
     const int n_q = p.S / TILE;
-    const bool single = p.S == TILE;
-    // TMEM columns: S^T [0,128) dP^T [128,256) dV [256,320) dK [320,384) dQ [384,448)
-    constexpr uint32_t kTmemCols = 512, cST = 0, cDP = 128, cDV = 256, cDK = 320, cDQ = 384;
+    // TMEM columns.  S^T fp32 [0,128) is overwritten in place by P^T bf16 [0,64); dP^T fp32 [128,256) by dS^T bf16 [128,192).
+    constexpr uint32_t kTmemCols = kSingle ? 256 : 512;
+    // With 512 columns (not kSingle) the bf16 copies get their own columns [384,448) / [448,512): two warps work on
+    // one lane quarter concurrently there, and in-place aliasing would let one overwrite what the other has not read.
+    constexpr uint32_t cST = 0, cDP = 128, cDQ = 0;
+    constexpr uint32_t cDV = kSingle ? 64 : 256, cDK = kSingle ? 192 : 320;
+    constexpr uint32_t cPT = kSingle ? cST : 384, cDST = kSingle ? cDP : 448;
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tma_qkv);
         tma_prefetch_desc(&tma_do);
-        for (int i = 0; i < 4; ++i) mbar_init(&bars[i], 1);
+        for (int i = 0; i < 6; ++i) mbar_init(&bars[i], 1);
         fence_barrier_init();
     }
     if (warp == 0) tmem_alloc(tmem_ptr_smem, kTmemCols);
@@ -299,10 +314,10 @@ __global__ void __launch_bounds__(128, 1) attn_bwd_kernel(const __grid_constant_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
-    const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
 
     const int kv_row0 = b * p.S + kv_tile * TILE;
-    const int r = threadIdx.x;                      // this thread's key row inside the tile
+    const int r = quarter * 32 + lane;              // this thread's key row inside the tile
     const int kv_idx = kv_tile * TILE + r;
     const bool kv_valid = kv_idx < kv_len;
     const bool tile_empty = kv_tile * TILE >= kv_len;  // fully padded key tile: gradients are zero
@@ -315,52 +330,63 @@ __global__ void __launch_bounds__(128, 1) attn_bwd_kernel(const __grid_constant_
             mbar_expect_tx(&bars[0], 2 * kTileBytes);
             tma_load_2d(sK, &tma_qkv, &bars[0], p.H + hd * D, kv_row0);
             tma_load_2d(sV, &tma_qkv, &bars[0], 2 * p.H + hd * D, kv_row0);
+            mbar_expect_tx(&bars[1], 2 * kTileBytes);
+            tma_load_2d(sQ, &tma_qkv, &bars[1], hd * D, b * p.S);
+            tma_load_2d(sdO, &tma_do, &bars[1], hd * D, b * p.S);
         }
-        uint32_t ph = 0;
+        uint32_t ph = 0;            // phase of the once-per-iteration barriers [3], [4], [5]
+        uint32_t qph[2] = {0, 0};   // phase of each Q/dO buffer's barrier
         for (int qi = 0; qi < n_q; ++qi) {
+            const int buf = kSingle ? 0 : (qi & 1);
             const int q_row0 = b * p.S + qi * TILE;
-            if (threadIdx.x == 0) {
-                mbar_expect_tx(&bars[1], 2 * kTileBytes);
-                tma_load_2d(sQ, &tma_qkv, &bars[1], hd * D, q_row0);
-                tma_load_2d(sdO, &tma_do, &bars[1], hd * D, q_row0);
+            uint8_t* cQ = sQ + buf * kTileBytes;
+            uint8_t* cdO = sdO + buf * kTileBytes;
+            if (!kSingle && threadIdx.x == 0 && qi + 1 < n_q) {
+                // the other buffer was last read by iteration qi-1's MMAs, which have completed
+                const int nb = buf ^ 1;
+                mbar_expect_tx(&bars[1 + nb], 2 * kTileBytes);
+                tma_load_2d(sQ + nb * kTileBytes, &tma_qkv, &bars[1 + nb], hd * D, q_row0 + TILE);
+                tma_load_2d(sdO + nb * kTileBytes, &tma_do, &bars[1 + nb], hd * D, q_row0 + TILE);
             }
-            sLse[r] = p.lse[((size_t)b * p.heads + hd) * p.S + qi * TILE + r] * kLog2e;
-            sDv[r] = p.dvec[((size_t)b * p.heads + hd) * p.S + qi * TILE + r];
+            if (half == 0) {
+                sLse[r] = p.lse[((size_t)b * p.heads + hd) * p.S + qi * TILE + r] * kLog2e;
+                sDv[r] = p.dvec[((size_t)b * p.heads + hd) * p.S + qi * TILE + r];
+            }
             __syncthreads();
             if (threadIdx.x == 0) {
                 if (qi == 0) mbar_wait(&bars[0], 0);
-                mbar_wait(&bars[1], ph);
+                mbar_wait(&bars[1 + buf], qph[buf]);
                 tc_fence_after();
                 constexpr uint32_t idesc = make_idesc(TILE, TILE, false, false);
 #pragma unroll
-                for (int k = 0; k < D / 16; ++k) {  // S^T = K Q^T
-                    umma_bf16(tmem_base + cST, make_smem_desc(smem_u32(sK) + k * 32, 16, 1024), make_smem_desc(smem_u32(sQ) + k * 32, 16, 1024),
+                for (int k = 0; k < D / 16; ++k)  // S^T = K Q^T
+                    umma_bf16(tmem_base + cST, make_smem_desc(smem_u32(sK) + k * 32, 16, 1024), make_smem_desc(smem_u32(cQ) + k * 32, 16, 1024),
                               idesc, k > 0 ? 1u : 0u);
-                }
 #pragma unroll
-                for (int k = 0; k < D / 16; ++k) {  // dP^T = V dO^T
-                    umma_bf16(tmem_base + cDP, make_smem_desc(smem_u32(sV) + k * 32, 16, 1024), make_smem_desc(smem_u32(sdO) + k * 32, 16, 1024),
+                for (int k = 0; k < D / 16; ++k)  // dP^T = V dO^T
+                    umma_bf16(tmem_base + cDP, make_smem_desc(smem_u32(sV) + k * 32, 16, 1024), make_smem_desc(smem_u32(cdO) + k * 32, 16, 1024),
                               idesc, k > 0 ? 1u : 0u);
-                }
-                umma_commit(&bars[2]);
+                umma_commit(&bars[3]);
             }
-            mbar_wait(&bars[2], ph);
+            qph[buf] ^= 1;
+            mbar_wait(&bars[3], ph);
             __syncwarp();
             tc_fence_after();
-            // ---- softmax backward on row `r` (a key), columns = queries of this tile
+            // ---- softmax backward on row `r` (a key); columns = the queries of this tile
 #pragma unroll 1
-            for (int c = 0; c < TILE / 32; ++c) {
+            for (int c = half * kChunksPerThread; c < (half + 1) * kChunksPerThread; ++c) {
                 uint32_t s[32], dp[32];
                 tmem_ld_32x32(lane_addr + cST + c * 32, s);
                 tmem_ld_32x32(lane_addr + cDP + c * 32, dp);
                 tmem_ld_wait();
+                uint32_t ppk[16], dpk[16];
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
                     float pt[8], ds[8];
 #pragma unroll
                     for (int t = 0; t < 8; ++t) {
                         const int qc = c * 32 + g * 8 + t;
-                        float pv = kv_valid ? exp2f(__uint_as_float(s[g * 8 + t]) * sl2 - sLse[qc]) : 0.f;
+                        const float pv = kv_valid ? exp2f(__uint_as_float(s[g * 8 + t]) * sl2 - sLse[qc]) : 0.f;
                         float dpv = __uint_as_float(dp[g * 8 + t]);
                         float pdrop = pv;
                         if (p.drop_thr) {
@@ -372,51 +398,61 @@ __global__ void __launch_bounds__(128, 1) attn_bwd_kernel(const __grid_constant_
                         pt[t] = pdrop;
                         ds[t] = pv * (dpv - sDv[qc]) * p.scale;
                     }
-                    st_swizzled_chunk(sPt, r, c * 4 + g, float_to_bf16x8(pt));
-                    st_swizzled_chunk(sdSt, r, c * 4 + g, float_to_bf16x8(ds));
+                    const uint4 dsv = float_to_bf16x8(ds);
+                    const uint4 ptv = float_to_bf16x8(pt);
+                    st_swizzled_chunk(sdSt, r, c * 4 + g, dsv);
+                    ppk[g * 4 + 0] = ptv.x; ppk[g * 4 + 1] = ptv.y; ppk[g * 4 + 2] = ptv.z; ppk[g * 4 + 3] = ptv.w;
+                    dpk[g * 4 + 0] = dsv.x; dpk[g * 4 + 1] = dsv.y; dpk[g * 4 + 2] = dsv.z; dpk[g * 4 + 3] = dsv.w;
                 }
+                // kSingle: bf16 pairs go back over the fp32 columns they came from (16c + 15 < 32c for c >= 1)
+                tmem_st_32x16(lane_addr + cPT + c * 16, ppk);
+                tmem_st_32x16(lane_addr + cDST + c * 16, dpk);
             }
+            tmem_st_wait();
             fence_proxy_async();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
             tc_fence_before();
             __syncthreads();
             if (threadIdx.x == 0) {
                 tc_fence_after();
-                constexpr uint32_t idesc_kmaj_bmn = make_idesc(TILE, D, false, true);
-                constexpr uint32_t idesc_amn_bmn = make_idesc(TILE, D, true, true);
-                // dV += P^T dO ; dK += dS^T Q : A K-major [kv x q] (two 64-column blocks), B MN-major (N = d, K = q rows)
+                constexpr uint32_t idesc_ts = make_idesc(TILE, D, false, true);   // A from TMEM (K-major), B MN-major
+                constexpr uint32_t idesc_mm = make_idesc(TILE, D, true, true);    // A, B both MN-major from smem
+                const uint32_t acc0 = (!kSingle && qi > 0) ? 1u : 0u;
+                // dV += P^T dO : A = P^T in TMEM [kv lanes x q], B = dO tile read MN-major (N = d, K = q rows)
 #pragma unroll
-                for (int k = 0; k < TILE / 16; ++k) {
-                    const uint32_t a_off = (k >> 2) * kTileBytes + (k & 3) * 32;
-                    umma_bf16(tmem_base + cDV, make_smem_desc(smem_u32(sPt) + a_off, 16, 1024),
-                              make_smem_desc(smem_u32(sdO) + k * 2048, 8192, 1024), idesc_kmaj_bmn, (qi > 0 || k > 0) ? 1u : 0u);
+                for (int k = 0; k < TILE / 16; ++k)
+                    umma_bf16_ts(tmem_base + cDV, tmem_base + cPT + k * 8, make_smem_desc(smem_u32(cdO) + k * 2048, 8192, 1024), idesc_ts,
+                                 (k > 0) ? 1u : acc0);
+                umma_commit(&bars[4]);
+                // dK += dS^T Q : A = dS^T in TMEM, B = Q tile read MN-major
+#pragma unroll
+                for (int k = 0; k < TILE / 16; ++k)
+                    umma_bf16_ts(tmem_base + cDK, tmem_base + cDST + k * 8, make_smem_desc(smem_u32(cQ) + k * 2048, 8192, 1024), idesc_ts,
+                                 (k > 0) ? 1u : acc0);
+                // dQ = dS K : accumulates into the columns P^T occupied, so wait until the dV MMAs have consumed them.
+                //   A = dS^T smem tile read MN-major (M = q contiguous, 64-wide blocks kTileBytes apart, K = kv rows)
+                //   B = K tile read MN-major (N = d, K = kv rows)
+                if (kSingle) {
+                    mbar_wait(&bars[4], ph);
+                    tc_fence_after();
                 }
 #pragma unroll
-                for (int k = 0; k < TILE / 16; ++k) {
-                    const uint32_t a_off = (k >> 2) * kTileBytes + (k & 3) * 32;
-                    umma_bf16(tmem_base + cDK, make_smem_desc(smem_u32(sdSt) + a_off, 16, 1024),
-                              make_smem_desc(smem_u32(sQ) + k * 2048, 8192, 1024), idesc_kmaj_bmn, (qi > 0 || k > 0) ? 1u : 0u);
-                }
-                // dQ = dS K : A = dS^T tile read MN-major (M = q contiguous: 64-wide blocks kTileBytes apart, K = kv rows),
-                //             B = K tile read MN-major (N = d, K = kv rows)
-#pragma unroll
-                for (int k = 0; k < TILE / 16; ++k) {
+                for (int k = 0; k < TILE / 16; ++k)
                     umma_bf16(tmem_base + cDQ, make_smem_desc(smem_u32(sdSt) + k * 2048, kTileBytes, 1024),
-                              make_smem_desc(smem_u32(sK) + k * 2048, 8192, 1024), idesc_amn_bmn, k > 0 ? 1u : 0u);
-                }
-                umma_commit(&bars[3]);
+                              make_smem_desc(smem_u32(sK) + k * 2048, 8192, 1024), idesc_mm, k > 0 ? 1u : 0u);
+                umma_commit(&bars[5]);
             }
-            mbar_wait(&bars[3], ph);
+            mbar_wait(&bars[5], ph);
             __syncwarp();
             tc_fence_after();
             // dQ rows = queries (TMEM lane = query index inside the tile)
             {
                 const size_t tok = (size_t)q_row0 + r;
 #pragma unroll
-                for (int c = 0; c < 2; ++c) {
+                for (int c = half * (2 / kHalves); c < (half + 1) * (2 / kHalves); ++c) {
                     uint32_t v[32];
                     tmem_ld_32x32(lane_addr + cDQ + c * 32, v);
                     tmem_ld_wait();
-                    if (single) {
+                    if (kSingle) {
                         bf16* dst = p.dqkv + tok * 3 * p.H + hd * D + c * 32;
 #pragma unroll
                         for (int j = 0; j < 32; j += 8) {
@@ -435,7 +471,7 @@ __global__ void __launch_bounds__(128, 1) attn_bwd_kernel(const __grid_constant_
                 }
             }
             tc_fence_before();
-            __syncthreads();  // TMEM S/dP/dQ columns and the Q/dO/P^T/dS^T tiles are free again
+            __syncthreads();  // S^T / dP^T / dQ columns and the dS^T tile are free again
             ph ^= 1;
         }
     }
@@ -446,15 +482,14 @@ __global__ void __launch_bounds__(128, 1) attn_bwd_kernel(const __grid_constant_
         bf16* dv = p.dqkv + tok * 3 * p.H + 2 * p.H + hd * D;
         if (tile_empty) {
             const uint4 z = make_uint4(0, 0, 0, 0);
-#pragma unroll
-            for (int j = 0; j < D; j += 8) {
+            for (int j = half * (D / kHalves); j < (half + 1) * (D / kHalves); j += 8) {
                 st_global_v4(dk + j, z);
                 st_global_v4(dv + j, z);
             }
         } else {
             tc_fence_after();
 #pragma unroll
-            for (int c = 0; c < 2; ++c) {
+            for (int c = half * (2 / kHalves); c < (half + 1) * (2 / kHalves); ++c) {
                 uint32_t a[32], g[32];
                 tmem_ld_32x32(lane_addr + cDK + c * 32, a);
                 tmem_ld_32x32(lane_addr + cDV + c * 32, g);
@@ -600,14 +635,24 @@ DDL_API int ddl_attention_bwd(const void* qkv, const void* ctx, const void* dctx
     CUtensorMap mq, md;
     if (int e = make_tile_map(&mq, qkv, (long long)B * S, 3LL * p.H)) return e;
     if (int e = make_tile_map(&md, dctx, (long long)B * S, (long long)p.H)) return e;
-    constexpr int smem = 8 * kTileBytes + 2 * TILE * 4 + 64 + 1024;
-    static bool set = false;
-    if (!set) {
-        DDL_CHECK(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        set = true;
-    }
     dim3 grid(S / TILE, heads, B);
-    attn_bwd_kernel<<<grid, 128, smem, s>>>(mq, md, p);
+    if (S == TILE) {
+        constexpr int smem = 6 * kTileBytes + 2 * TILE * 4 + 128 + 1024;
+        static bool set1 = false;
+        if (!set1) {
+            DDL_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            set1 = true;
+        }
+        attn_bwd_kernel<true><<<grid, 128, smem, s>>>(mq, md, p);
+    } else {
+        constexpr int smem = 8 * kTileBytes + 2 * TILE * 4 + 128 + 1024;
+        static bool set2 = false;
+        if (!set2) {
+            DDL_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            set2 = true;
+        }
+        attn_bwd_kernel<false><<<grid, 256, smem, s>>>(mq, md, p);
+    }
     DDL_LAUNCH_CHECK();
     if (dq_acc) {
         const size_t total = (size_t)B * S * (p.H / 8);

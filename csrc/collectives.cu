@@ -37,6 +37,12 @@ struct Ctx {
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ uint32_t ld_relaxed_sys_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void fence_acquire_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
     uint32_t v;
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -52,8 +58,9 @@ __device__ __forceinline__ void block_barrier(const Ctx& c, uint32_t& epoch, boo
         const int peer = threadIdx.x;
         st_release_sys(c.pad[peer] + (size_t)blockIdx.x * DDL_MAX_WORLD + c.rank, epoch);
         const uint32_t* mine = c.pad[c.rank] + (size_t)blockIdx.x * DDL_MAX_WORLD + peer;
-        while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
+        while ((int32_t)(ld_relaxed_sys_u32(mine) - epoch) < 0) {
         }
+        fence_acquire_sys();  // one fence after the flag is seen instead of an acquire per poll
     }
     __syncthreads();
 }
@@ -110,9 +117,9 @@ __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(Ctx c, Peer
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[k][j] = 0.f;
         if (g < n8) {
-            for (int r = 0; r < c.world; ++r) {
-                int peer = c.rank + r;
-                if (peer >= c.world) peer -= c.world;
+            // rank order 0..W-1 on every rank: all replicas get bit-identical sums (a staggered
+            // order would let fp32 rounding differ between ranks and the model replicas drift)
+            for (int peer = 0; peer < c.world; ++peer) {
                 float f[8];
                 G8<Tin>::load(in.p[peer], g, f);
 #pragma unroll

@@ -36,10 +36,13 @@ class VariantSelector:
     ``benchmarks/allreduce_sweep.py`` writes to ``profiles/allreduce_table_w{world}.json``.
     """
 
+    # shape of the measured 2- and 8-GPU tables (profiles/allreduce_table_w{2,8}.json): one-shot while
+    # latency dominates, then the switch reduction where the host exposes it, else two-shot
     DEFAULT = [
-        {"max_bytes": 256 << 10, "algo": "oneshot", "blocks": 16},
-        {"max_bytes": 4 << 20, "algo": "twoshot", "blocks": 32},
-        {"max_bytes": 1 << 62, "algo": "twoshot", "blocks": 64},
+        {"max_bytes": 16 << 10, "algo": "oneshot", "blocks": 4},
+        {"max_bytes": 1 << 20, "algo": "nvls", "blocks": 16},
+        {"max_bytes": 8 << 20, "algo": "nvls", "blocks": 32},
+        {"max_bytes": 1 << 62, "algo": "nvls", "blocks": 8},
     ]
 
     def __init__(self, world: int, nvls: bool, table: Optional[List[dict]] = None):
@@ -62,9 +65,11 @@ class VariantSelector:
         for row in self.table:
             if nbytes <= row["max_bytes"]:
                 algo = row["algo"]
+                blocks = int(row["blocks"])
                 if algo == "nvls" and not (self.nvls and same_dtype):
-                    algo = "twoshot"
-                return _ALGO_NAMES[algo], int(row["blocks"])
+                    # the switch is not doing the reduction: the SMs have to move (W-1)/W of the bytes
+                    algo, blocks = "twoshot", max(blocks, 64 if nbytes >= (4 << 20) else 32)
+                return _ALGO_NAMES[algo], blocks
         return L.ALGO_TWOSHOT, 64
 
 

@@ -10,7 +10,9 @@ offset and can ``ld``/``st`` any peer's copy over NVLink 5 / NVSwitch
 
 Providers
 ---------
-``ipc``    (default) the native path above (``csrc/runtime.cu``).
+``auto``   (default) ``torch`` when world size > 1 (it brings the NVLS multicast mapping),
+           falling back to ``ipc`` if the rendezvous is not available; ``ipc`` for one rank.
+``ipc``    the native path above (``csrc/runtime.cu``).
 ``torch``  allocation + handle exchange through ``torch.distributed._symmetric_memory``;
            used when the NVLS multicast mapping is wanted (K3), because it also binds a
            multicast object where the host exposes one.  Only the *mapping* comes from
@@ -78,16 +80,35 @@ class SymmetricHeap:
         if self.world > 8:
             raise RuntimeError("one NVSwitch domain: world size must be <= 8")
         self.slab_bytes = int(slab_bytes or int(os.environ.get("DDL_SYMM_SLAB_MB", "512")) << 20)
-        self.provider = provider or os.environ.get("DDL_SYMM_PROVIDER", "ipc")
-        if self.provider not in ("ipc", "torch"):
+        self.provider = provider or os.environ.get("DDL_SYMM_PROVIDER", "auto")
+        if self.provider not in ("auto", "ipc", "torch"):
             raise ValueError(self.provider)
+        if self.provider == "auto":
+            # the multicast (NVLS) mapping only comes with the torch provider; a single rank has no use for it
+            self.provider = "torch" if self.world > 1 else "ipc"
+            self._auto = True
+        else:
+            self._auto = False
         self.slabs: List[_Slab] = []
         self.multicast_supported = False
 
     # ---- slab creation (collective: every rank must call in the same order) -------------
     def _new_slab(self, min_bytes: int) -> _Slab:
         size = max(self.slab_bytes, (min_bytes + _ALIGN - 1) // _ALIGN * _ALIGN)
-        slab = self._new_slab_torch(size) if self.provider == "torch" else self._new_slab_ipc(size)
+        if self.provider == "torch":
+            try:
+                slab = self._new_slab_torch(size)
+                failed = False
+            except Exception:  # noqa: BLE001 - symmetric-memory rendezvous not available on this host
+                if not (self._auto and not self.slabs):
+                    raise
+                failed = True
+            # every rank must take the same path: agree before falling back
+            if self._auto and not self.slabs and any(pg.all_gather_object(failed)):
+                self.provider = "ipc"
+                slab = self._new_slab_ipc(size)
+        else:
+            slab = self._new_slab_ipc(size)
         self.slabs.append(slab)
         return slab
 
