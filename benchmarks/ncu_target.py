@@ -1,0 +1,74 @@
+#!/usr/bin/env python
+"""Short single-GPU programs for `ncu --set full` captures (one kernel family per mode).
+
+    python benchmarks/ncu_target.py gemm|attention|bn|ln|adamw
+"""
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    mode = sys.argv[1] if len(sys.argv) > 1 else "gemm"
+    torch.manual_seed(0)
+    bf = torch.bfloat16
+    if mode == "gemm":
+        from databricks_distributed_deep_learning_b200.ops import gemm as G
+
+        M, N, K = 16384, 3072, 768  # BERT-base FFN up-projection
+        a = torch.randn(M, K, device="cuda").to(bf)
+        b = torch.randn(N, K, device="cuda").to(bf)
+        bias = torch.randn(N, device="cuda").to(bf)
+        pre = torch.empty(M, N, device="cuda", dtype=bf)
+        for _ in range(4):
+            G.gemm_nt(a, b, M, N, K, bias=bias, aux=pre, epilogue=G.EPI_GELU)
+    elif mode == "attention":
+        from databricks_distributed_deep_learning_b200.ops import attention as A
+
+        for S, B, h in ((128, 128, 12), (512, 16, 16)):
+            qkv = torch.randn(B, S, 3, h, 64, device="cuda").to(bf).requires_grad_()
+            for _ in range(2):
+                out = A.attention_qkvpacked(qkv, None, 0.1)
+                out.backward(torch.randn_like(out))
+    elif mode == "bn":
+        from databricks_distributed_deep_learning_b200.ops import functional as OF
+
+        bn = torch.nn.BatchNorm2d(256).cuda()
+        bn.weight.data = bn.weight.data.to(bf)
+        bn.bias.data = bn.bias.data.to(bf)
+        x = torch.randn(256, 256, 56, 56, device="cuda").to(bf).contiguous(memory_format=torch.channels_last).requires_grad_()
+        res = torch.randn_like(x).contiguous(memory_format=torch.channels_last).requires_grad_()
+        for _ in range(2):
+            y = OF.bn_act(x, bn, relu=True, residual=res)
+            y.backward(torch.randn_like(y))
+    elif mode == "ln":
+        from databricks_distributed_deep_learning_b200.ops import functional as OF
+
+        H = 768
+        x = torch.randn(16384, H, device="cuda").to(bf).requires_grad_()
+        r = torch.randn(16384, H, device="cuda").to(bf).requires_grad_()
+        g = torch.ones(H, device="cuda", dtype=bf).requires_grad_()
+        b = torch.zeros(H, device="cuda", dtype=bf).requires_grad_()
+        for _ in range(2):
+            y = OF.dropout_add_layernorm(x, r, g, b, 1e-12, 0.1)
+            y.backward(torch.randn_like(y))
+    elif mode == "adamw":
+        from databricks_distributed_deep_learning_b200.ops import _lib as L
+
+        n = 8 * 4_000_000
+        gr = torch.randn(n, device="cuda").to(bf)
+        w, m, v = torch.randn(n, device="cuda"), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+        p = torch.empty(n, device="cuda", dtype=bf)
+        hyper = torch.tensor([1e-3, 0.9, 0.999, 1e-8, 0.01, 1.0, 0, 0], device="cuda")
+        for _ in range(3):
+            L.call("ddl_adamw", gr.data_ptr(), 1, w.data_ptr(), m.data_ptr(), v.data_ptr(), p.data_ptr(), 1, n, hyper.data_ptr(), 1.0, L.stream_ptr())
+    torch.cuda.synchronize()
+    print("ok", mode)
+
+
+if __name__ == "__main__":
+    main()

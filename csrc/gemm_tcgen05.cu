@@ -40,21 +40,31 @@ constexpr int kThreads = (2 + kEpiWarps) * 32;
 using namespace tc;
 
 // ---------------------------------------------------------------------------- epilogue math
-__device__ __forceinline__ float erf_fast(float x) {
-    // Abramowitz-Stegun 7.1.26, |err| < 1.5e-7 (far below bf16 resolution)
+// GELU(x) = x * Phi(x), Phi from Abramowitz-Stegun 7.1.26 (|erf error| < 1.5e-7, far below bf16 resolution).
+// With z = |x|/sqrt2, t = 1/(1 + p z), q = (a1 t + ... + a5 t^5) exp(-z^2):  erf(z) = 1 - q, hence
+//     gelu(x)  = max(x, 0) - 0.5 |x| q          (12 instructions, two of them MUFU)
+//     gelu'(x) = Phi(x) + x phi(x),  Phi(x) = 0.5 + sign(x) (0.5 - 0.5 q),  phi(x) = exp(-x^2/2)/sqrt(2 pi)
+// and exp(-z^2) = exp(-x^2/2) is the same exponential in both.
+__device__ __forceinline__ float gelu_q(float x, float& e) {
     const float ax = fabsf(x);
-    const float t = __fdividef(1.f, fmaf(0.3275911f, ax, 1.f));
-    float p = fmaf(1.061405429f, t, -1.453152027f);
-    p = fmaf(p, t, 1.421413741f);
-    p = fmaf(p, t, -0.284496736f);
-    p = fmaf(p, t, 0.254829592f);
-    const float r = 1.f - p * t * __expf(-ax * ax);
-    return copysignf(r, x);
+    const float t = __fdividef(1.f, fmaf(0.3275911f * 0.70710678f, ax, 1.f));
+    float pl = fmaf(1.061405429f, t, -1.453152027f);
+    pl = fmaf(pl, t, 1.421413741f);
+    pl = fmaf(pl, t, -0.284496736f);
+    pl = fmaf(pl, t, 0.254829592f);
+    e = exp2f(x * x * (-0.5f * 1.4426950408889634f));
+    return pl * t * e;
 }
-__device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.f + erf_fast(x * 0.70710678f)); }
+__device__ __forceinline__ float gelu_f(float x) {
+    float e;
+    const float q = gelu_q(x, e);
+    return fmaf(-0.5f * fabsf(x), q, fmaxf(x, 0.f));
+}
 __device__ __forceinline__ float dgelu_f(float x) {
-    const float cdf = 0.5f * (1.f + erf_fast(x * 0.70710678f));
-    return cdf + x * 0.39894228f * __expf(-0.5f * x * x);
+    float e;
+    const float q = gelu_q(x, e);
+    const float cdf = 0.5f + copysignf(fmaf(-0.5f, q, 0.5f), x);
+    return fmaf(x * 0.39894228f, e, cdf);
 }
 
 struct GemmParams {
@@ -77,15 +87,35 @@ struct GemmParams {
 // residual) is 4 full lines per instruction instead of 32 partial ones.
 template <int BN>
 __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint8_t* stg, uint32_t tmem_base, int acc_stage, int m_blk,
-                                              int n_blk, int quarter, int half, int lane) {
+                                              int n_blk, int quarter, int half, int lane, uint64_t* full_bar, uint32_t full_phase) {
     constexpr int kColsPerWarp = BN / 2;
     const int t_sr = lane >> 3, t_ch = lane & 7;
     auto stg_row = [&](int r, int c) -> uint4* { return reinterpret_cast<uint4*>(stg + r * 128 + ((c ^ (r & 7)) << 4)); };
     const int row_base = m_blk * BM + quarter * 32;   // first row of this warp's 32
     const int row = row_base + lane;
+    // the one tensor this epilogue READS per element (dGELU: saved pre-activation, else: residual)
+    const bf16* ext_ptr = p.epilogue == DDL_EPI_DGELU ? p.aux : p.residual;
+    const bool has_ext = ext_ptr != nullptr && p.split_k == 1;
 #pragma unroll 1
     for (int c = 0; c < kColsPerWarp; c += 64) {
         const int col0 = n_blk * BN + half * kColsPerWarp + c;
+        // Issue every external load of this chunk FIRST, in the coalesced (transposed) mapping, so that the
+        // 8 independent 16-byte requests per lane are in flight while the accumulator is fetched and the
+        // math runs (for the first chunk: while the tile's last MMAs are still executing).
+        uint4 ext[8];
+        if (has_ext) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const int rr = it * 4 + t_sr;
+                ext[it] = make_uint4(0, 0, 0, 0);
+                if (row_base + rr < p.M && col0 + t_ch * 8 < p.N)
+                    ext[it] = ld_stream_v4(ext_ptr + (size_t)(row_base + rr) * p.ldc + col0 + t_ch * 8);
+            }
+        }
+        if (c == 0) {
+            mbar_wait(full_bar, full_phase);
+            tc_fence_after();
+        }
         uint32_t r0[32], r1[32];
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc_stage * BN + half * kColsPerWarp + c);
         tmem_ld_32x32(taddr, r0);
@@ -105,81 +135,61 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint8_t* stg,
             }
             continue;
         }
-        // dGELU: bring the saved pre-activation in through the same buffer (coalesced load -> row domain)
-        if (p.epilogue == DDL_EPI_DGELU) {
-#pragma unroll
-            for (int it = 0; it < 8; ++it) {
-                const int rr = it * 4 + t_sr;
-                uint4 v = make_uint4(0, 0, 0, 0);
-                if (row_base + rr < p.M && col0 + t_ch * 8 < p.N) v = ld_global_v4(p.aux + (size_t)(row_base + rr) * p.ldc + col0 + t_ch * 8);
-                *stg_row(rr, t_ch) = v;
-            }
-            __syncwarp();
-        }
+        // row domain (thread = row): + bias, ReLU; round to bf16 and stage
 #pragma unroll
         for (int g = 0; g < 8; ++g) {  // 8 column groups of 8
             float w[8];
 #pragma unroll
             for (int q = 0; q < 8; ++q) w[q] = __uint_as_float(g < 4 ? r0[g * 8 + q] : r1[(g - 4) * 8 + q]);
-            const bool col_ok = col0 + g * 8 < p.N;
-            if (p.bias && col_ok) {
+            if (p.bias && col0 + g * 8 < p.N) {
                 float bsv[8];
                 bf16x8_to_float(ld_global_v4(p.bias + col0 + g * 8), bsv);
 #pragma unroll
                 for (int q = 0; q < 8; ++q) w[q] += bsv[q];
             }
-            if (p.epilogue == DDL_EPI_DGELU) {
-                float pre[8];
-                bf16x8_to_float(*stg_row(lane, g), pre);
-#pragma unroll
-                for (int q = 0; q < 8; ++q) w[q] *= dgelu_f(pre[q]);
-            } else if (p.epilogue == DDL_EPI_RELU) {
+            if (p.epilogue == DDL_EPI_RELU) {
 #pragma unroll
                 for (int q = 0; q < 8; ++q) w[q] = fmaxf(w[q], 0.f);
             }
-            // GELU keeps fp32 values in registers for the second pass; first pass stages the pre-activation
             *stg_row(lane, g) = float_to_bf16x8(w);
         }
         __syncwarp();
-        if (p.epilogue == DDL_EPI_GELU) {
-            // pass 1: pre-activation -> aux (coalesced); pass 2: gelu(rounded pre) -> C
+        // transposed domain (8 lanes = one 128-byte line): activation / dGELU / residual, coalesced stores
 #pragma unroll
-            for (int it = 0; it < 8; ++it) {
-                const int rr = it * 4 + t_sr;
-                const uint4 pv = *stg_row(rr, t_ch);
-                if (row_base + rr < p.M && col0 + t_ch * 8 < p.N) {
-                    const size_t off = (size_t)(row_base + rr) * p.ldc + col0 + t_ch * 8;
-                    if (p.aux) st_global_v4(p.aux + off, pv);
+        for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + t_sr;
+            uint4 pv = *stg_row(rr, t_ch);
+            if (row_base + rr < p.M && col0 + t_ch * 8 < p.N) {
+                const size_t off = (size_t)(row_base + rr) * p.ldc + col0 + t_ch * 8;
+                if (p.epilogue == DDL_EPI_GELU) {
+                    if (p.aux) st_global_v4(p.aux + off, pv);  // backward sees exactly this rounded pre-activation
                     float f[8];
                     bf16x8_to_float(pv, f);
 #pragma unroll
                     for (int q = 0; q < 8; ++q) f[q] = gelu_f(f[q]);
-                    if (p.residual) {
+                    if (has_ext) {
                         float rs[8];
-                        bf16x8_to_float(ld_global_v4(p.residual + off), rs);
+                        bf16x8_to_float(ext[it], rs);
 #pragma unroll
                         for (int q = 0; q < 8; ++q) f[q] += rs[q];
                     }
-                    st_global_v4(p.C + off, float_to_bf16x8(f));
-                }
-            }
-        } else {
+                    pv = float_to_bf16x8(f);
+                } else if (p.epilogue == DDL_EPI_DGELU) {
+                    float f[8], pre[8];
+                    bf16x8_to_float(pv, f);
+                    bf16x8_to_float(ext[it], pre);
 #pragma unroll
-            for (int it = 0; it < 8; ++it) {
-                const int rr = it * 4 + t_sr;
-                uint4 pv = *stg_row(rr, t_ch);
-                if (row_base + rr < p.M && col0 + t_ch * 8 < p.N) {
-                    const size_t off = (size_t)(row_base + rr) * p.ldc + col0 + t_ch * 8;
-                    if (p.residual) {
-                        float f[8], rs[8];
-                        bf16x8_to_float(pv, f);
-                        bf16x8_to_float(ld_global_v4(p.residual + off), rs);
+                    for (int q = 0; q < 8; ++q) f[q] *= dgelu_f(pre[q]);
+                    pv = float_to_bf16x8(f);
+                } else if (has_ext) {
+                    float f[8], rs[8];
+                    bf16x8_to_float(pv, f);
+                    bf16x8_to_float(ext[it], rs);
 #pragma unroll
-                        for (int q = 0; q < 8; ++q) f[q] += rs[q];
-                        pv = float_to_bf16x8(f);
-                    }
-                    st_global_v4(p.C + off, pv);
+                    for (int q = 0; q < 8; ++q) f[q] += rs[q];
+                    pv = float_to_bf16x8(f);
                 }
+                st_global_v4(p.C + off, pv);
             }
         }
         __syncwarp();  // buffer free for the next chunk
@@ -335,9 +345,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
         for (int tile = sched_id; tile < num_tiles; tile += sched_n) {
             const int mn = tile % tiles_mn;
             const int m_blk = (mn / p.num_n_blocks) * kCluster + cta_rank, n_blk = mn % p.num_n_blocks;
-            mbar_wait(&tmem_full[acc_stage], acc_phase);
-            tc_fence_after();
-            epilogue_tile<BN>(p, stg, tmem_base, acc_stage, m_blk, n_blk, quarter, half, lane);
+            epilogue_tile<BN>(p, stg, tmem_base, acc_stage, m_blk, n_blk, quarter, half, lane, &tmem_full[acc_stage], acc_phase);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);
@@ -480,9 +488,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm2sm_bf16_kernel(const __grid_
         for (int tile = sched_id; tile < num_tiles; tile += sched_n) {
             const int mn = tile % tiles_mn;
             const int m_blk = (mn / p.num_n_blocks) * 2 + cta_rank, n_blk = mn % p.num_n_blocks;
-            mbar_wait(&tmem_full[acc_stage], acc_phase);
-            tc_fence_after();
-            epilogue_tile<BN>(p, stg, tmem_base, acc_stage, m_blk, n_blk, quarter, half, lane);
+            epilogue_tile<BN>(p, stg, tmem_base, acc_stage, m_blk, n_blk, quarter, half, lane, &tmem_full[acc_stage], acc_phase);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_leader(&tmem_empty[acc_stage]);
