@@ -356,6 +356,20 @@ DDL_API int ddl_bn_act_fwd_train(const void* x, const void* residual, const void
     return ddl_bn_apply(x, residual, scale, shift, y, M, C, relu, stream_);
 }
 
+DDL_API int ddl_bn_act_fwd_train_from_sums(const void* x, const void* residual, const void* gamma, const void* beta, float* running_mean,
+                                           float* running_var, void* y, float* mean, float* invstd, float* scale, float* shift,
+                                           const float* sums, long long M, int C, float eps, float momentum, int relu, void* stream_) {
+    BnGeom g;
+    if (int e = make_geom(M, C, &g)) return e;
+    DDL_REQUIRE(x && y && mean && invstd && scale && shift && sums, "bn fwd (from sums): null pointer");
+    cudaStream_t s = (cudaStream_t)stream_;
+    // `sums` has the layout of ONE partial block: [2][C]
+    bn_fwd_finalize_kernel<<<ddl_ceil_div(C, 32), 256, 0, s>>>(sums, 1, M, C, (const bf16*)gamma, (const bf16*)beta, running_mean, running_var,
+                                                              momentum, eps, mean, invstd, scale, shift);
+    DDL_LAUNCH_CHECK();
+    return ddl_bn_apply(x, residual, scale, shift, y, M, C, relu, stream_);
+}
+
 DDL_API int ddl_bn_act_fwd_eval(const void* x, const void* residual, const void* gamma, const void* beta, const float* running_mean,
                                 const float* running_var, void* y, float* scale, float* shift, long long M, int C, float eps, int relu,
                                 void* stream_) {

@@ -75,6 +75,7 @@ struct GemmParams {
     const bf16* residual;  // [M, ldc] or null: added to the result (also used as "accumulate into grad")
     bf16* aux;         // EPI_GELU: pre-activation out [M, ldc];  EPI_DGELU: pre-activation in
     float* acc_f32;    // split-K: fp32 [M, N] accumulation target (caller-zeroed), ld = N
+    float* col_stats;  // optional [2][N] fp32 (caller-zeroed): per-column sum and sum of squares of the stored output
     int epilogue;      // DDL_EPI_*
     int split_k;
     int num_m_blocks, num_n_blocks, k_blocks_total;
@@ -155,6 +156,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint8_t* stg,
         }
         __syncwarp();
         // transposed domain (8 lanes = one 128-byte line): activation / dGELU / residual, coalesced stores
+        float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, cq[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
             const int rr = it * 4 + t_sr;
@@ -190,6 +192,33 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint8_t* stg,
                     pv = float_to_bf16x8(f);
                 }
                 st_global_v4(p.C + off, pv);
+                if (p.col_stats) {
+                    float f[8];
+                    bf16x8_to_float(pv, f);
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        cs[q] += f[q];
+                        cq[q] += f[q] * f[q];
+                    }
+                }
+            }
+        }
+        if (p.col_stats) {
+            // BatchNorm statistics of a 1x1 convolution come out of its GEMM for free: fold the 4 row groups
+            // of the warp, then one red.add per column from lanes 0..7 (K9: conv + BN-statistics epilogue)
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                cs[q] += __shfl_xor_sync(0xffffffffu, cs[q], 8);
+                cs[q] += __shfl_xor_sync(0xffffffffu, cs[q], 16);
+                cq[q] += __shfl_xor_sync(0xffffffffu, cq[q], 8);
+                cq[q] += __shfl_xor_sync(0xffffffffu, cq[q], 16);
+            }
+            if (t_sr == 0 && col0 + t_ch * 8 < p.N) {
+                float* d0 = p.col_stats + col0 + t_ch * 8;
+                red_add_f32x4(d0, cs[0], cs[1], cs[2], cs[3]);
+                red_add_f32x4(d0 + 4, cs[4], cs[5], cs[6], cs[7]);
+                red_add_f32x4(d0 + p.N, cq[0], cq[1], cq[2], cq[3]);
+                red_add_f32x4(d0 + p.N + 4, cq[4], cq[5], cq[6], cq[7]);
             }
         }
         __syncwarp();  // buffer free for the next chunk
@@ -664,7 +693,15 @@ int g_force_cluster = 0;  // 0 = auto, 1 or 2 = forced (benchmarks)
 DDL_API int ddl_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb, void* C, long long ldc, int M,
                           int N, int K, const void* bias, const void* residual, void* aux, int epilogue, int split_k, float* acc_f32,
                           int block_n, void* stream_) {
+    return ddl_gemm_bf16_ex(A, a_mn, lda, B, b_mn, ldb, C, ldc, M, N, K, bias, residual, aux, epilogue, split_k, acc_f32, nullptr, block_n,
+                            stream_);
+}
+
+DDL_API int ddl_gemm_bf16_ex(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb, void* C, long long ldc, int M,
+                             int N, int K, const void* bias, const void* residual, void* aux, int epilogue, int split_k, float* acc_f32,
+                             float* col_stats, int block_n, void* stream_) {
     if (int e = get_encode()) return e;
+    DDL_REQUIRE(col_stats == nullptr || split_k == 1, "gemm: column statistics need split_k == 1");
     DDL_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem");
     DDL_REQUIRE(N % 8 == 0 && K % 8 == 0, "gemm: N (%d) and K (%d) must be multiples of 8", N, K);
     DDL_REQUIRE(!a_mn || M % 8 == 0, "gemm: MN-major A needs M %% 8 == 0");
@@ -685,6 +722,7 @@ DDL_API int ddl_gemm_bf16(const void* A, int a_mn, long long lda, const void* B,
     p.C = (bf16*)C; p.ldc = ldc;
     p.bias = (const bf16*)bias; p.residual = (const bf16*)residual; p.aux = (bf16*)aux;
     p.acc_f32 = acc_f32; p.epilogue = epilogue; p.split_k = split_k;
+    p.col_stats = col_stats;
     p.num_m_blocks = (M + BM - 1) / BM;
     p.num_n_blocks = (N + BN - 1) / BN;
     p.k_blocks_total = (K + BK - 1) / BK;

@@ -76,6 +76,8 @@ _PROTOS = {
     "ddl_avgpool_fwd": ([_vp, _vp, _i, _i, _i, _vp], _i),
     "ddl_avgpool_bwd": ([_vp, _vp, _i, _i, _i, _vp], _i),
     "ddl_gemm_bf16": ([_vp, _i, _ll, _vp, _i, _ll, _vp, _ll, _i, _i, _i, _vp, _vp, _vp, _i, _i, _vp, _i, _vp], _i),
+    "ddl_gemm_bf16_ex": ([_vp, _i, _ll, _vp, _i, _ll, _vp, _ll, _i, _i, _i, _vp, _vp, _vp, _i, _i, _vp, _vp, _i, _vp], _i),
+    "ddl_bn_act_fwd_train_from_sums": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _f, _f, _i, _vp], _i),
     "ddl_gemm_set_cluster": ([_i], _i),
     "ddl_f32_to_bf16": ([_vp, _vp, _sz, _i, _vp], _i),
     "ddl_colsum_scratch_bytes": ([_i, _i], _sz),

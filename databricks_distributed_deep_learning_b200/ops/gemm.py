@@ -58,7 +58,8 @@ def usable(x: torch.Tensor, weight: torch.Tensor) -> bool:
 
 def gemm_nt(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool = False, b_mn: bool = False,
             bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None, aux: Optional[torch.Tensor] = None,
-            epilogue: int = EPI_NONE, out: Optional[torch.Tensor] = None, split_k: int = 1, block_n: int = 0) -> torch.Tensor:
+            epilogue: int = EPI_NONE, out: Optional[torch.Tensor] = None, split_k: int = 1, block_n: int = 0,
+            col_stats: Optional[torch.Tensor] = None) -> torch.Tensor:
     """C[M,N] = epilogue(A . B^T).  ``a``/``b`` are 2-D row-major bf16 tensors holding the operand
     as [M,K]/[N,K] (default) or as [K,M]/[K,N] (``a_mn``/``b_mn``)."""
     global _env_applied
@@ -71,8 +72,8 @@ def gemm_nt(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn: b
     acc = None
     if split_k > 1:
         acc = torch.zeros(M, N, dtype=torch.float32, device=dev)
-    L.call("ddl_gemm_bf16", a.data_ptr(), int(a_mn), a.stride(0), b.data_ptr(), int(b_mn), b.stride(0), out.data_ptr(), out.stride(0),
-           M, N, K, L.ptr(bias), L.ptr(residual), L.ptr(aux), epilogue, split_k, L.ptr(acc), block_n, L.stream_ptr(dev))
+    L.call("ddl_gemm_bf16_ex", a.data_ptr(), int(a_mn), a.stride(0), b.data_ptr(), int(b_mn), b.stride(0), out.data_ptr(), out.stride(0),
+           M, N, K, L.ptr(bias), L.ptr(residual), L.ptr(aux), epilogue, split_k, L.ptr(acc), L.ptr(col_stats), block_n, L.stream_ptr(dev))
     if split_k > 1:
         L.call("ddl_f32_to_bf16", acc.data_ptr(), out.data_ptr(), M * N, 0, L.stream_ptr(dev))
     return out

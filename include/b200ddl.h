@@ -110,6 +110,11 @@ int ddl_bn_act_fwd_train(const void* x, const void* residual, const void* gamma,
 int ddl_bn_act_fwd_eval(const void* x, const void* residual, const void* gamma, const void* beta, const float* running_mean,
                         const float* running_var, void* y, float* scale, float* shift, long long M, int C, float eps, int relu,
                         void* stream);
+/* Training-mode BN + residual + ReLU when the per-channel sum / sum of squares already exist (sums = fp32 [2][C],
+ * e.g. from ddl_gemm_bf16_ex): skips the statistics pass over x. */
+int ddl_bn_act_fwd_train_from_sums(const void* x, const void* residual, const void* gamma, const void* beta, float* running_mean,
+                                   float* running_var, void* y, float* mean, float* invstd, float* scale, float* shift,
+                                   const float* sums, long long M, int C, float eps, float momentum, int relu, void* stream);
 /* Allocation-free variant of ddl_bn_act_fwd_train: same arguments minus the scratch buffer.
  * No counterpart in the reference (it has no native code at all).  It exists for callers
  * that cannot allocate device memory - a process whose own arena already owns the whole
@@ -166,6 +171,11 @@ int ddl_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream
 int ddl_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb, void* C, long long ldc, int M, int N,
                   int K, const void* bias, const void* residual, void* aux, int epilogue, int split_k, float* acc_f32, int block_n,
                   void* stream);
+/* Same, plus col_stats: optional fp32 [2][N] (caller-zeroed) that receives the per-column sum and sum of squares
+ * of the stored output - the BatchNorm statistics of a 1x1 convolution for free (K9, conv + BN epilogue). */
+int ddl_gemm_bf16_ex(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb, void* C, long long ldc, int M, int N,
+                     int K, const void* bias, const void* residual, void* aux, int epilogue, int split_k, float* acc_f32,
+                     float* col_stats, int block_n, void* stream);
 /* launch mode: 0 = auto (CTA pairs, tcgen05.mma.cta_group::2, 256x256 tiles, when eligible), 1 = one CTA per
  * tile, 2 = 2-CTA cluster sharing B by TMA multicast, 3 = same as 0 */
 int ddl_gemm_set_cluster(int cluster);

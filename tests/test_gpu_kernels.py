@@ -497,3 +497,53 @@ def test_fsdp_single_gpu_trainer_runs_and_learns():
     losses = [float(tr.step(batch)) for _ in range(8)]
     assert all(l == l for l in losses) and losses[-1] < losses[0], losses
     assert tr.ddp.comm.name == "p2p"
+
+
+def test_gemm_column_stats_epilogue():
+    g = _gemm()
+    M, N, K = 1000, 256, 64
+    a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+    b = (torch.randn(N, K, device="cuda") * 0.2).to(torch.bfloat16)
+    sums = torch.zeros(2, N, device="cuda")
+    c = g.gemm_nt(a, b, M, N, K, col_stats=sums)
+    cf = c.float()
+    assert torch.allclose(sums[0], cf.sum(0), rtol=1e-3, atol=1e-2)
+    assert torch.allclose(sums[1], (cf * cf).sum(0), rtol=1e-3, atol=1e-2)
+
+
+@pytest.mark.parametrize("Cin,Cout,HW,relu,with_res", [(64, 256, 14, True, True), (256, 64, 28, True, False), (512, 128, 7, False, False)])
+def test_conv1x1_gemm_bn_act_matches_torch(Cin, Cout, HW, relu, with_res):
+    OF = _OF()
+    bf = torch.bfloat16
+    conv = torch.nn.Conv2d(Cin, Cout, 1, bias=False).cuda().to(bf).to(memory_format=torch.channels_last)
+    bn = torch.nn.BatchNorm2d(Cout).cuda()
+    bn.weight.data = (1 + 0.2 * torch.randn(Cout, device="cuda")).to(bf)
+    bn.bias.data = (0.2 * torch.randn(Cout, device="cuda")).to(bf)
+    rconv = torch.nn.Conv2d(Cin, Cout, 1, bias=False).cuda()
+    rconv.weight.data = conv.weight.data.float()
+    rbn = torch.nn.BatchNorm2d(Cout).cuda()
+    rbn.weight.data, rbn.bias.data = bn.weight.data.float(), bn.bias.data.float()
+    x = torch.randn(8, Cin, HW, HW, device="cuda").to(bf).contiguous(memory_format=torch.channels_last).requires_grad_()
+    res = torch.randn(8, Cout, HW, HW, device="cuda").to(bf).contiguous(memory_format=torch.channels_last) if with_res else None
+    OF._CONV1X1_GEMM = True  # opt-in route (default is the library convolution)
+    try:
+        assert OF._is_gemm_conv(x, conv)
+        y = OF.conv_bn_act(x, conv, bn, relu=relu, residual=res)
+    finally:
+        OF._CONV1X1_GEMM = False
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xr = x.detach().float().requires_grad_()
+    yr = rbn(rconv(xr))
+    if with_res:
+        yr = yr + res.float()
+    if relu:
+        yr = F.relu(yr)
+    yr.backward(dy.float())
+    rel = lambda a, b: ((a.float() - b).abs().max() / b.abs().max().clamp_min(1e-6)).item()
+    assert y.is_contiguous(memory_format=torch.channels_last)
+    assert rel(y, yr) < 3e-2, rel(y, yr)
+    assert torch.allclose(bn.running_mean, rbn.running_mean, rtol=1e-2, atol=2e-3)
+    assert torch.allclose(bn.running_var, rbn.running_var, rtol=2e-2, atol=2e-3)
+    assert rel(conv.weight.grad.reshape(Cout, Cin), rconv.weight.grad.reshape(Cout, Cin)) < 8e-2
+    assert ((x.grad.float() - xr.grad).abs().mean() / xr.grad.abs().mean()).item() < 3e-2
