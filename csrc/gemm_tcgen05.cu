@@ -533,6 +533,199 @@ __global__ void __launch_bounds__(kThreads, 1) gemm2sm_bf16_kernel(const __grid_
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// K6: all-gather fused into the consuming GEMM (BASELINE.json:5, FSDP mode).
+// The weight W [N, K] is sharded by rows over the ranks (rank r owns rows [r N/W, (r+1) N/W) in its
+// symmetric heap).  ONE kernel per rank does both jobs:
+//   * two copier warps in every CTA pull the shards out of the peers' memory over NVLink into the local
+//     full-W buffer (own shard first) and publish a per-shard ready counter (red.release.gpu);
+//   * the TMA producer walks the output column blocks shard by shard, starting with the LOCAL shard, and
+//     only waits (ld.acquire.gpu + fence.proxy.async) for a shard the first time it needs it -
+//     so the math on the shards that already arrived overlaps the transfer of the ones still in flight.
+// A cross-rank flag barrier (same protocol as csrc/collectives.cu) brackets the copies: peers' shards are
+// final before anyone reads them and nobody's shard is overwritten while a peer still reads it.
+struct GatherParams {
+    const char* shard[DDL_MAX_WORLD];  // peer-mapped shard bases ([N/W, K] bf16, contiguous)
+    char* full;                         // local [N, K] bf16
+    uint32_t* flags;                    // local [DDL_MAX_WORLD + 1], zero before the first call (self-resetting)
+    uint32_t* pad[DDL_MAX_WORLD];       // signal pads [blocks][DDL_MAX_WORLD]
+    uint32_t* epoch;                    // local per-block barrier epochs
+    int rank, world, blocks_per_shard;
+    size_t shard_bytes;
+};
+
+__device__ __forceinline__ void gather_rank_barrier(const GatherParams& g, uint32_t epoch, int lane) {
+    if (lane < g.world) {
+        uint32_t* dst = g.pad[lane] + (size_t)blockIdx.x * DDL_MAX_WORLD + g.rank;
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dst), "r"(epoch) : "memory");
+        const uint32_t* mine = g.pad[g.rank] + (size_t)blockIdx.x * DDL_MAX_WORLD + lane;
+        uint32_t v;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+        } while ((int32_t)(v - epoch) < 0);
+    }
+    __syncwarp();
+}
+
+constexpr int kGatherThreads = kThreads + 64;
+
+__global__ void __launch_bounds__(kGatherThreads, 1) gemm_allgather_kernel(const __grid_constant__ CUtensorMap tma_a,
+                                                                           const __grid_constant__ CUtensorMap tma_b, const GemmParams p,
+                                                                           const GatherParams g) {
+    constexpr int BN = 128, kStages = 6;
+    using L = SmemLayout<BN, false, false, kStages>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
+    uint64_t* empty_bar = full_bar + kStages;
+    uint64_t* tmem_full = empty_bar + kStages;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    constexpr uint32_t kTmemCols = 2 * BN;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full[s], 1);
+            mbar_init(&tmem_empty[s], kEpiWarps);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_ptr_smem, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+    const uint32_t copiers_total = gridDim.x * 2;  // copier warps in the grid
+    // column blocks in shard order, local shard first; all row blocks of one column block are consecutive
+    auto tile_coords = [&](int tile, int& m_blk, int& n_blk) {
+        const int n_idx = tile / p.num_m_blocks;
+        m_blk = tile % p.num_m_blocks;
+        n_blk = (n_idx + g.rank * g.blocks_per_shard) % p.num_n_blocks;
+    };
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0, ready = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                int m_blk, n_blk;
+                tile_coords(tile, m_blk, n_blk);
+                const int sh = n_blk / g.blocks_per_shard;
+                if (!((ready >> sh) & 1u)) {
+                    uint32_t v;
+                    do {
+                        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(g.flags + sh) : "memory");
+                    } while (v < copiers_total);
+                    fence_proxy_async_all();  // copiers wrote with ordinary stores; TMA reads through the async proxy
+                    ready |= 1u << sh;
+                }
+                for (int kb = 0; kb < p.k_blocks_total; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* sa = smem + stage * L::kStageBytes;
+                    uint8_t* sb = sa + L::kABytes;
+                    mbar_expect_tx(&full_bar[stage], L::kStageBytes);
+                    tma_load_2d(sa, &tma_a, &full_bar[stage], kb * BK, m_blk * BM);
+                    tma_load_2d(sb, &tma_b, &full_bar[stage], kb * BK, n_blk * BN);
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc(BM, BN, false, false);
+            int stage = 0, acc_stage = 0;
+            uint32_t phase = 0, acc_phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                mbar_wait(&tmem_empty[acc_stage], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc_stage * BN;
+                for (int kb = 0; kb < p.k_blocks_total; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
+                    const uint32_t sb = sa + L::kABytes;
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k)
+                        umma_bf16(d_tmem, make_smem_desc(sa + k * 32, 16, 1024), make_smem_desc(sb + k * 32, 16, 1024), idesc,
+                                  (kb > 0 || k > 0) ? 1u : 0u);
+                    umma_commit(&empty_bar[stage]);
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&tmem_full[acc_stage]);
+                if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
+            }
+        }
+    } else if (warp < 2 + kEpiWarps) {
+        const int ew = warp - 2, quarter = warp & 3, half = ew >> 2;
+        uint8_t* stg = smem + L::kStageOffset + ew * 4096;
+        int acc_stage = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            int m_blk, n_blk;
+            tile_coords(tile, m_blk, n_blk);
+            epilogue_tile<BN>(p, stg, tmem_base, acc_stage, m_blk, n_blk, quarter, half, lane, &tmem_full[acc_stage], acc_phase);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[acc_stage]);
+            if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
+        }
+    } else {
+        // ===================== copier warps: the all-gather =====================
+        const int cw = warp - (2 + kEpiWarps);  // 0 or 1
+        uint32_t epoch = g.epoch[blockIdx.x];
+        if (cw == 0) gather_rank_barrier(g, epoch + 1, lane);  // every peer's shard is final
+        asm volatile("bar.sync 1, 64;" ::: "memory");           // the two copier warps
+        const size_t n16 = g.shard_bytes >> 4;
+        const size_t tid = (size_t)blockIdx.x * 64 + cw * 32 + lane, nthreads = (size_t)gridDim.x * 64;
+        for (int r = 0; r < g.world; ++r) {
+            int s = g.rank + r;
+            if (s >= g.world) s -= g.world;
+            const char* src = g.shard[s];
+            char* dst = g.full + (size_t)s * g.shard_bytes;
+            for (size_t v = tid; v < n16; v += nthreads * 4) {
+                uint4 t[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (v + u * nthreads < n16) t[u] = ld_weak_noalloc_v4(src + (v + u * nthreads) * 16);
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (v + u * nthreads < n16) st_global_v4(dst + (v + u * nthreads) * 16, t[u]);
+            }
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(g.flags + s) : "memory");
+        }
+        asm volatile("bar.sync 1, 64;" ::: "memory");
+        if (cw == 0) {
+            gather_rank_barrier(g, epoch + 2, lane);  // peers may now overwrite their shards
+            if (lane == 0) g.epoch[blockIdx.x] = epoch + 2;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        // last CTA out resets the ready counters for the next launch (CUDA-graph replayable)
+        const uint32_t old = atomicAdd(g.flags + DDL_MAX_WORLD, 1u);
+        if (old == gridDim.x - 1) {
+            for (int i = 0; i <= DDL_MAX_WORLD; ++i) g.flags[i] = 0;
+            __threadfence();
+        }
+    }
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
 // fp32 split-K accumulator -> bf16 (+ optional accumulate into existing bf16)
 __global__ void f32_to_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, size_t n8, int accumulate) {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
@@ -778,6 +971,58 @@ DDL_API int ddl_gemm_bf16_ex(const void* A, int a_mn, long long lda, const void*
         GO(128, true, false);
     }
 #undef GO
+}
+
+DDL_API int ddl_allgather_gemm_bf16(const ddl_comm_t* comm, void* const* shard_ptrs, void* full_w, void* flags, const void* A, long long lda,
+                                    void* C, long long ldc, int M, int N, int K, const void* bias, const void* residual, void* aux,
+                                    int epilogue, void* stream_) {
+    if (int e = get_encode()) return e;
+    DDL_REQUIRE(comm && shard_ptrs && full_w && flags && A && C, "allgather_gemm: null pointer");
+    DDL_REQUIRE(comm->world >= 1 && comm->world <= DDL_MAX_WORLD, "allgather_gemm: bad world size");
+    DDL_REQUIRE(N % (comm->world * 128) == 0, "allgather_gemm: N (%d) must be a multiple of world * 128", N);
+    DDL_REQUIRE(K % 8 == 0 && ldc % 8 == 0, "allgather_gemm: K and ldc must be multiples of 8");
+    if (g_sm_count == 0) {
+        int dev = 0;
+        DDL_CHECK(cudaGetDevice(&dev));
+        DDL_CHECK(cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev));
+    }
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K;
+    p.C = (bf16*)C; p.ldc = ldc;
+    p.bias = (const bf16*)bias; p.residual = (const bf16*)residual; p.aux = (bf16*)aux;
+    p.acc_f32 = nullptr; p.col_stats = nullptr; p.epilogue = epilogue; p.split_k = 1;
+    p.num_m_blocks = (M + BM - 1) / BM;
+    p.num_n_blocks = N / 128;
+    p.k_blocks_total = (K + BK - 1) / BK;
+    GatherParams g;
+    for (int i = 0; i < DDL_MAX_WORLD; ++i) { g.shard[i] = nullptr; g.pad[i] = nullptr; }
+    for (int i = 0; i < comm->world; ++i) {
+        DDL_REQUIRE(shard_ptrs[i] && comm->signal_pads[i], "allgather_gemm: peer pointer %d is null", i);
+        g.shard[i] = (const char*)shard_ptrs[i];
+        g.pad[i] = (uint32_t*)comm->signal_pads[i];
+    }
+    g.full = (char*)full_w;
+    g.flags = (uint32_t*)flags;
+    g.epoch = (uint32_t*)comm->epoch;
+    g.rank = comm->rank; g.world = comm->world;
+    g.blocks_per_shard = (N / comm->world) / 128;
+    g.shard_bytes = (size_t)(N / comm->world) * K * 2;
+    CUtensorMap ta, tb;
+    if (int e = make_map(&ta, A, M, K, lda, BM)) return e;
+    if (int e = make_map(&tb, full_w, N, K, K, 128)) return e;
+    using L = SmemLayout<128, false, false, 6>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        DDL_CHECK(cudaFuncSetAttribute(gemm_allgather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+        attr_set = true;
+    }
+    // every CTA carries two copier warps, so the whole grid must be resident: one CTA per SM
+    const int tiles = p.num_m_blocks * p.num_n_blocks;
+    int grid = tiles < g_sm_count ? tiles : g_sm_count;
+    if (grid > DDL_COMM_MAX_BLOCKS) grid = DDL_COMM_MAX_BLOCKS;
+    gemm_allgather_kernel<<<grid, kGatherThreads, L::kTotal, (cudaStream_t)stream_>>>(ta, tb, p, g);
+    DDL_LAUNCH_CHECK();
+    return 0;
 }
 
 DDL_API int ddl_gemm_set_cluster(int cluster) {

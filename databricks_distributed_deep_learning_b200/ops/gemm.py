@@ -192,3 +192,38 @@ class _FFN(torch.autograd.Function):
 
 def ffn(x, w1, b1, w2, b2, residual=None) -> torch.Tensor:
     return _FFN.apply(x, w1, b1, w2, b2, residual)
+
+
+# ----------------------------------------------------------------------------- K6: all-gather fused into the GEMM
+class GatheredLinear:
+    """``y = act(x @ W^T + b)`` where W [N, K] is row-sharded over the ranks in symmetric memory.
+
+    One kernel per rank performs the all-gather AND the GEMM (``ddl_allgather_gemm_bf16``): copier warps pull
+    the peers' shards into ``full_w`` while the tensor cores already work on the shards that have arrived
+    (local shard first).  ``full_w`` afterwards holds the whole weight, so the layer's backward can use
+    the plain kernels.  Forward-only helper (the FSDP wrapper drives backward itself).
+    """
+
+    def __init__(self, comm, w_shard: torch.Tensor, n_total: int):
+        import ctypes as C
+
+        self.comm = comm
+        self.w_shard = w_shard                       # [N / W, K] bf16 in the symmetric heap
+        self.N, self.K = n_total, w_shard.shape[1]
+        if self.N % (comm.world_size * 128) != 0:
+            raise L.DdlError("GatheredLinear: out_features must be a multiple of world_size * 128")
+        self.full_w = torch.empty(self.N, self.K, dtype=torch.bfloat16, device=w_shard.device)
+        self.flags = torch.zeros(16, dtype=torch.int32, device=w_shard.device)
+        sb, off = comm.lookup(w_shard)
+        self._ptrs = sb.ptr_array(off)
+        self._C = C
+
+    def __call__(self, x: torch.Tensor, bias: Optional[torch.Tensor] = None, activation: Optional[str] = None,
+                 residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+        M = x.shape[0]
+        out = torch.empty(M, self.N, dtype=torch.bfloat16, device=x.device)
+        epi = {None: EPI_NONE, "gelu": EPI_GELU, "relu": EPI_RELU}[activation]
+        L.call("ddl_allgather_gemm_bf16", self._C.byref(self.comm._ct), self._ptrs, self.full_w.data_ptr(), self.flags.data_ptr(),
+               x.data_ptr(), x.stride(0), out.data_ptr(), out.stride(0), M, self.N, self.K, L.ptr(bias), L.ptr(residual), None, epi,
+               L.stream_ptr(x.device))
+        return out

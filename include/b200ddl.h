@@ -176,6 +176,15 @@ int ddl_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_m
 int ddl_gemm_bf16_ex(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb, void* C, long long ldc, int M, int N,
                      int K, const void* bias, const void* residual, void* aux, int epilogue, int split_k, float* acc_f32,
                      float* col_stats, int block_n, void* stream);
+/* K6 - all-gather fused into the consuming GEMM (BASELINE.json:5, FSDP): C = epilogue(A . W^T) where W [N, K] is
+ * sharded by rows over the ranks (shard_ptrs[r] = rank r's [N/world, K] shard as mapped into this process).  One
+ * kernel per rank: copier warps pull the shards over NVLink into full_w [N, K] (local scratch) and publish
+ * per-shard ready counters; the TMA producer consumes the column blocks shard by shard, local shard first, so math
+ * on arrived shards overlaps the transfer of the rest.  flags: local uint32[9], zero before the first call.
+ * N must be a multiple of world * 128.  No counterpart in the reference. */
+int ddl_allgather_gemm_bf16(const ddl_comm_t* comm, void* const* shard_ptrs, void* full_w, void* flags, const void* A, long long lda,
+                            void* C, long long ldc, int M, int N, int K, const void* bias, const void* residual, void* aux, int epilogue,
+                            void* stream);
 /* launch mode: 0 = auto (CTA pairs, tcgen05.mma.cta_group::2, 256x256 tiles, when eligible), 1 = one CTA per
  * tile, 2 = 2-CTA cluster sharing B by TMA multicast, 3 = same as 0 */
 int ddl_gemm_set_cluster(int cluster);

@@ -35,3 +35,9 @@ def test_trainer_graph_multi_gpu_ranks_stay_in_sync():
 def test_fsdp_gpu_matches_ddp():
     out = Distributor(num_processes=_world(), use_gpu=True, timeout_s=900).run(GW.w_fsdp_gpu, 4)
     assert out["ok"], out
+
+
+def test_allgather_fused_into_gemm():
+    out = Distributor(num_processes=_world(), use_gpu=True, timeout_s=600).run(GW.w_allgather_gemm)
+    print(out["report"])
+    assert out["ok"], out
