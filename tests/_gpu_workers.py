@@ -265,3 +265,41 @@ def w_allgather_gemm():
         t_f, t_u = timeit(lambda: layer(x, bias=bias)), timeit(unfused)
         report[f"{M}x{N}x{K}"] = {"rel_err": err, "gathered_w_exact": same_w, "fused_us": t_f * 1e3, "unfused_us": t_u * 1e3}
     return {"ok": all(pg.all_gather_object(ok)), "report": report}
+
+
+def w_allreduce_stress(iters):
+    """Flag-protocol stress (SURVEY.md 5 "Race detection"; compute-sanitizer is closed on this pool): random
+    per-rank delays in front of back-to-back collectives of random size / algorithm on ONE buffer, every
+    result checked.  A lost or early flag shows up as a wrong sum."""
+    import random
+
+    from databricks_distributed_deep_learning_b200.parallel.collectives import PeerMemoryComm
+
+    pg = _pg()
+    dev = pg.device()
+    rank, world = pg.rank(), pg.world_size()
+    comm = PeerMemoryComm(dev)
+    nmax = 1 << 21
+    buf = comm.alloc_flat(nmax, torch.float32, dev)
+    rng = random.Random(1234)          # same sequence on every rank
+    delay_rng = random.Random(99 + rank)  # different delays per rank
+    algos = ["oneshot", "twoshot"] + (["nvls"] if comm.heap.multicast_supported else [])
+    bad = 0
+    for it in range(iters):
+        n = rng.choice([8 * world, 1024, 8192, 1 << 16, 1 << 18, nmax]) // (8 * world) * (8 * world)
+        algo = rng.choice(algos)
+        if algo == "oneshot" and n * 4 > (1 << 20):
+            algo = "twoshot"
+        blocks = rng.choice([1, 4, 16, 64])
+        view = buf[:n]
+        view.fill_(float(rank + 1 + it % 3))
+        if delay_rng.random() < 0.5:
+            torch.cuda._sleep(int(delay_rng.random() * 2_000_000))  # up to ~1 ms of skew
+        comm.all_reduce_mean_(view, algo=algo, num_blocks=blocks, scale=1.0)
+        expect = sum(r + 1 + it % 3 for r in range(world))
+        # check on device without a host sync every iteration
+        bad += int((view != float(expect)).any().item()) if it % 8 == 7 or it == iters - 1 else 0
+        if it % 8 == 7:
+            comm.barrier()
+    torch.cuda.synchronize()
+    return {"ok": all(pg.all_gather_object(bad == 0)), "bad": bad, "algos": algos}

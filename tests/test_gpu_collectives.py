@@ -41,3 +41,8 @@ def test_allgather_fused_into_gemm():
     out = Distributor(num_processes=_world(), use_gpu=True, timeout_s=600).run(GW.w_allgather_gemm)
     print(out["report"])
     assert out["ok"], out
+
+
+def test_flag_protocol_stress_with_random_skew():
+    out = Distributor(num_processes=_world(), use_gpu=True, timeout_s=600).run(GW.w_allreduce_stress, 200)
+    assert out["ok"], out
