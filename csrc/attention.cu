@@ -65,10 +65,14 @@ __device__ __forceinline__ uint32_t mix32(uint32_t x) {
     x ^= x >> 16;
     return x;
 }
-// 4 dropout decisions (bits) for elements (q, kv4*4 .. kv4*4+3) of head `bh`
-__device__ __forceinline__ uint32_t drop_keep4(uint64_t seed, uint32_t bh, uint32_t q, uint32_t kv4, uint32_t S, uint32_t thr) {
+// One 32-bit hash covers the 4 probabilities (q, 4*kv4 .. 4*kv4+3) of head `bh`: byte i decides element i.
+// Forward (thread = query, walks keys) uses all four bytes; backward (thread = key, walks queries) one of them.
+__device__ __forceinline__ uint32_t drop_hash(uint32_t seed32, uint32_t bh, uint32_t q, uint32_t kv4, uint32_t S) {
     const uint32_t idx = (bh * S + q) * (S >> 2) + kv4;
-    const uint32_t h = mix32(idx * 0x9E3779B1u + (uint32_t)seed) ^ mix32((uint32_t)(seed >> 32) + idx);
+    return mix32(idx * 0x9E3779B1u + seed32);
+}
+__device__ __forceinline__ uint32_t drop_keep4(uint32_t seed32, uint32_t bh, uint32_t q, uint32_t kv4, uint32_t S, uint32_t thr) {
+    const uint32_t h = drop_hash(seed32, bh, q, kv4, S);
     uint32_t m = 0;
 #pragma unroll
     for (int i = 0; i < 4; ++i) m |= (((h >> (8 * i)) & 0xffu) >= thr ? 1u : 0u) << i;
@@ -143,7 +147,8 @@ __global__ void __launch_bounds__(128, 1) attn_fwd_kernel(const __grid_constant_
     const int r = threadIdx.x;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
     const float sl2 = p.scale * kLog2e;
-    const uint64_t seed = resolve_seed(p.seed, p.seed_dev, p.drop_thr);
+    const uint64_t seed64 = resolve_seed(p.seed, p.seed_dev, p.drop_thr);
+    const uint32_t seed = mix32((uint32_t)seed64) ^ (uint32_t)(seed64 >> 32);
     mbar_wait(&bars[1], 0);
     __syncwarp();
     tc_fence_after();
@@ -322,7 +327,8 @@ __global__ void __launch_bounds__(kSingle ? 128 : 256, kSingle ? 2 : 1) attn_bwd
     const bool kv_valid = kv_idx < kv_len;
     const bool tile_empty = kv_tile * TILE >= kv_len;  // fully padded key tile: gradients are zero
     const float sl2 = p.scale * kLog2e;
-    const uint64_t seed = resolve_seed(p.seed, p.seed_dev, p.drop_thr);
+    const uint64_t seed64 = resolve_seed(p.seed, p.seed_dev, p.drop_thr);
+    const uint32_t seed = mix32((uint32_t)seed64) ^ (uint32_t)(seed64 >> 32);
     const uint32_t bh = (uint32_t)(b * p.heads + hd);
 
     if (!tile_empty) {
@@ -382,21 +388,25 @@ __global__ void __launch_bounds__(kSingle ? 128 : 256, kSingle ? 2 : 1) attn_bwd
                 uint32_t ppk[16], dpk[16];
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
-                    float pt[8], ds[8];
+                    float pt[8], ds[8], lse8[8], dv8[8];
+                    const int qc0 = c * 32 + g * 8;
+                    *reinterpret_cast<float4*>(&lse8[0]) = *reinterpret_cast<const float4*>(&sLse[qc0]);
+                    *reinterpret_cast<float4*>(&lse8[4]) = *reinterpret_cast<const float4*>(&sLse[qc0 + 4]);
+                    *reinterpret_cast<float4*>(&dv8[0]) = *reinterpret_cast<const float4*>(&sDv[qc0]);
+                    *reinterpret_cast<float4*>(&dv8[4]) = *reinterpret_cast<const float4*>(&sDv[qc0 + 4]);
 #pragma unroll
                     for (int t = 0; t < 8; ++t) {
-                        const int qc = c * 32 + g * 8 + t;
-                        const float pv = kv_valid ? exp2f(__uint_as_float(s[g * 8 + t]) * sl2 - sLse[qc]) : 0.f;
+                        const float pv = kv_valid ? exp2f(__uint_as_float(s[g * 8 + t]) * sl2 - lse8[t]) : 0.f;
                         float dpv = __uint_as_float(dp[g * 8 + t]);
                         float pdrop = pv;
                         if (p.drop_thr) {
-                            const uint32_t keep = drop_keep4(seed, bh, (uint32_t)(qi * TILE + qc), (uint32_t)(kv_idx >> 2), (uint32_t)p.S, p.drop_thr);
-                            const bool kept = (keep >> (kv_idx & 3)) & 1u;
+                            const uint32_t h = drop_hash(seed, bh, (uint32_t)(qi * TILE + qc0 + t), (uint32_t)(kv_idx >> 2), (uint32_t)p.S);
+                            const bool kept = ((h >> (8 * (kv_idx & 3))) & 0xffu) >= p.drop_thr;
                             pdrop = kept ? pv * p.drop_scale : 0.f;
                             dpv = kept ? dpv * p.drop_scale : 0.f;
                         }
                         pt[t] = pdrop;
-                        ds[t] = pv * (dpv - sDv[qc]) * p.scale;
+                        ds[t] = pv * (dpv - dv8[t]) * p.scale;
                     }
                     const uint4 dsv = float_to_bf16x8(ds);
                     const uint4 ptv = float_to_bf16x8(pt);
