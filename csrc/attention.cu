@@ -93,7 +93,9 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 // forward
 // ------------------------------------------------------------------------------------------------
 template <int kMaxKvTiles>
-__global__ void __launch_bounds__(128, 1) attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnParams p) {
+__global__ void __launch_bounds__(kMaxKvTiles == 1 ? 128 : 256, 1) attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
+                                                                                  const AttnParams p) {
+    constexpr int kHalves = kMaxKvTiles == 1 ? 1 : 2;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* sQ = smem;
@@ -101,6 +103,7 @@ __global__ void __launch_bounds__(128, 1) attn_fwd_kernel(const __grid_constant_
     uint8_t* sV = sK + kMaxKvTiles * kTileBytes;
     uint64_t* bars = reinterpret_cast<uint64_t*>(sV + kMaxKvTiles * kTileBytes);  // [0] load, [1] S ready, [2] O ready
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 4);
+    float* sRed = reinterpret_cast<float*>(bars + 8);  // [2][128] partner exchange (row max, row sum)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q_tile = blockIdx.x, hd = blockIdx.y, b = blockIdx.z;
@@ -143,18 +146,24 @@ __global__ void __launch_bounds__(128, 1) attn_fwd_kernel(const __grid_constant_
         umma_commit(&bars[1]);
     }
 
-    // ---- softmax: thread = query row, its TMEM lane is (warp*32 + lane)
-    const int r = threadIdx.x;
-    const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+    // ---- softmax: thread = (query row, column half).  One key tile: 128 threads, a thread owns its row.
+    // More key tiles: 256 threads - warps w and w+4 share a TMEM lane quarter and take alternate 32-column
+    // chunks, which halves the exp / hash work per thread; row max and row sum are combined through smem.
+    const int quarter = warp & 3, half = warp >> 2;
+    const int r = quarter * 32 + lane;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
     const float sl2 = p.scale * kLog2e;
     const uint64_t seed64 = resolve_seed(p.seed, p.seed_dev, p.drop_thr);
     const uint32_t seed = mix32((uint32_t)seed64) ^ (uint32_t)(seed64 >> 32);
+    auto pair_sync = [&]() {  // the two warps of one lane quarter
+        if (kHalves == 2) asm volatile("bar.sync %0, 64;" ::"r"(1 + quarter) : "memory");
+    };
     mbar_wait(&bars[1], 0);
     __syncwarp();
     tc_fence_after();
     const int n_chunks = n_kv * (TILE / 32);
     float mx = -INFINITY;
-    for (int c = 0; c < n_chunks; ++c) {
+    for (int c = half; c < n_chunks; c += kHalves) {
         uint32_t v[32];
         tmem_ld_32x32(lane_addr + c * 32, v);
         tmem_ld_wait();
@@ -162,14 +171,24 @@ __global__ void __launch_bounds__(128, 1) attn_fwd_kernel(const __grid_constant_
         for (int j = 0; j < 32; ++j)
             if (c * 32 + j < kv_len) mx = fmaxf(mx, __uint_as_float(v[j]));
     }
+    if (kHalves == 2) {
+        sRed[half * TILE + r] = mx;
+        pair_sync();
+        mx = fmaxf(mx, sRed[(half ^ 1) * TILE + r]);
+        pair_sync();
+    }
     const float mxs = mx * sl2;
     float sum = 0.f;
     const uint32_t bh = (uint32_t)(b * p.heads + hd);
     const uint32_t q_idx = (uint32_t)(q_tile * TILE + r);
-    for (int c = 0; c < n_chunks; ++c) {
+    for (int c = half; c < n_chunks; c += kHalves) {
         uint32_t v[32];
         tmem_ld_32x32(lane_addr + c * 32, v);
         tmem_ld_wait();
+        // P (bf16 pairs) of chunk c overwrites S columns [16c, 16c+16), i.e. part of chunk c/2.  With one thread
+        // per row that chunk was consumed earlier; with two, both partners have loaded this step's chunks before
+        // either stores (and chunk c/2 belongs to an earlier step for c >= 2).
+        pair_sync();
         uint32_t packed[16];
 #pragma unroll
         for (int j4 = 0; j4 < 8; ++j4) {
@@ -188,8 +207,12 @@ __global__ void __launch_bounds__(128, 1) attn_fwd_kernel(const __grid_constant_
             packed[j4 * 2] = pack_bf16x2(e[0], e[1]);
             packed[j4 * 2 + 1] = pack_bf16x2(e[2], e[3]);
         }
-        // P (bf16 pairs) overwrites S columns [16c, 16c+16): already consumed (16c+15 <= 32c+31)
         tmem_st_32x16(lane_addr + c * 16, packed);
+    }
+    if (kHalves == 2) {
+        sRed[half * TILE + r] = sum;
+        pair_sync();
+        sum += sRed[(half ^ 1) * TILE + r];
     }
     tmem_st_wait();
     tc_fence_before();
@@ -215,7 +238,7 @@ __global__ void __launch_bounds__(128, 1) attn_fwd_kernel(const __grid_constant_
         const float inv = (p.drop_thr ? p.drop_scale : 1.f) / sum;
         bf16* out = p.ctx + (size_t)(row0 + r) * p.H + hd * D;
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
+        for (int c = half * (2 / kHalves); c < (half + 1) * (2 / kHalves); ++c) {
             uint32_t v[32];
             tmem_ld_32x32(lane_addr + o_col + c * 32, v);
             tmem_ld_wait();
@@ -227,7 +250,7 @@ __global__ void __launch_bounds__(128, 1) attn_fwd_kernel(const __grid_constant_
                 st_global_v4(out + c * 32 + j, float_to_bf16x8(o));
             }
         }
-        if (p.lse) p.lse[((size_t)b * p.heads + hd) * p.S + q_tile * TILE + r] = mx * p.scale + __logf(sum);
+        if (p.lse && half == 0) p.lse[((size_t)b * p.heads + hd) * p.S + q_tile * TILE + r] = mx * p.scale + __logf(sum);
     }
     tc_fence_before();
     __syncthreads();
@@ -586,14 +609,14 @@ int fill_params(AttnParams* p, int B, int S, int heads, const int* seqlens, floa
 
 template <int KV>
 int launch_fwd(const CUtensorMap& map, const AttnParams& p, cudaStream_t s) {
-    constexpr int smem = (1 + 2 * KV) * kTileBytes + 64 + 1024;
+    constexpr int smem = (1 + 2 * KV) * kTileBytes + 64 + 2 * TILE * 4 + 1024;
     static bool set = false;
     if (!set) {
         DDL_CHECK(cudaFuncSetAttribute(attn_fwd_kernel<KV>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         set = true;
     }
     dim3 grid(p.S / TILE, p.heads, p.B);
-    attn_fwd_kernel<KV><<<grid, 128, smem, s>>>(map, p);
+    attn_fwd_kernel<KV><<<grid, KV == 1 ? 128 : 256, smem, s>>>(map, p);
     DDL_LAUNCH_CHECK();
     return 0;
 }
