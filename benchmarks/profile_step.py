@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--dropout", type=float, default=None)
     ap.add_argument("--top", type=int, default=45)
+    ap.add_argument("--trace", default="", help="kernel-name substring: list the ATen ops (with shapes and callers) that launch it")
     args = ap.parse_args()
     import bench
 
@@ -58,7 +59,29 @@ def main():
     with open(out, "w") as f:
         json.dump({"workload": args.workload, "impl": args.impl, "batch": batch, "total_ms": total / 1e3,
                    "kernels": [{"name": n, "ms": u / 1e3, "count": c} for n, u, c in rows]}, f, indent=1)
+    if args.trace:
+        trace_kernel(runner, b, args.trace)
     pg.destroy_process_group()
+
+
+def trace_kernel(runner, b, needle: str) -> None:
+    """Which ATen op (shapes, parent ops) launches the kernels whose name contains ``needle``."""
+    from torch.profiler import ProfilerActivity, profile
+
+    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_shapes=True) as prof:
+        runner.step_device(b)
+        torch.cuda.synchronize()
+    print(f"# ops launching kernels matching {needle!r}")
+    for e in prof.events():
+        ks = [k for k in (e.kernels or []) if needle in k.name]
+        if not ks:
+            continue
+        chain, par = [], e.cpu_parent
+        while par is not None and len(chain) < 6:
+            chain.append(par.name)
+            par = par.cpu_parent
+        us = sum(k.duration for k in ks)
+        print(f"{us:9.1f} us  {e.name}  shapes={e.input_shapes}  <- {' <- '.join(chain)}")
 
 
 if __name__ == "__main__":

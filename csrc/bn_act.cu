@@ -92,34 +92,48 @@ __global__ void __launch_bounds__(kBnMaxThreads) bn_stats_kernel(const bf16* __r
     fold_to_partials(s, q, vec_cols, C, partials + (size_t)blockIdx.x * 2 * C, sh);
 }
 
-// Fold the per-block partials of 32 channels with 8 warps in parallel (fixed order ->
-// deterministic): warp w sums partial rows w, w+8, ...; shared memory folds the 8 warps.
+// Fold the per-block partials of 32 channels with kFoldWarps warps in parallel (fixed order ->
+// deterministic): warp w sums partial rows w, w+kFoldWarps, ... four at a time with independent
+// accumulators (the loads are L2 hits whose latency is the whole cost of this kernel, so they
+// must all be in flight together); shared memory folds the warps.
+constexpr int kFoldWarps = 32, kFoldThreads = kFoldWarps * 32;
 __device__ __forceinline__ void fold_partials32(const float* __restrict__ partials, int nblocks, int C, int c, bool ok, float& s,
                                                 float& q) {
-    __shared__ float sh[8][2][33];
+    __shared__ float sh[kFoldWarps][2][33];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    float a = 0.f, b = 0.f;
+    float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f};
     if (ok) {
-        for (int i = w; i < nblocks; i += 8) {
-            a += partials[(size_t)i * 2 * C + c];
-            b += partials[(size_t)i * 2 * C + C + c];
+        int i = w;
+        for (; i + 3 * kFoldWarps < nblocks; i += 4 * kFoldWarps) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const float* row = partials + (size_t)(i + u * kFoldWarps) * 2 * C;
+                a[u] += row[c];
+                b[u] += row[C + c];
+            }
+        }
+        for (; i < nblocks; i += kFoldWarps) {
+            a[0] += partials[(size_t)i * 2 * C + c];
+            b[0] += partials[(size_t)i * 2 * C + C + c];
         }
     }
-    sh[w][0][lane] = a;
-    sh[w][1][lane] = b;
+    sh[w][0][lane] = (a[0] + a[1]) + (a[2] + a[3]);
+    sh[w][1][lane] = (b[0] + b[1]) + (b[2] + b[3]);
     __syncthreads();
     s = 0.f;
     q = 0.f;
+    if (w == 0) {
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        s += sh[k][0][lane];
-        q += sh[k][1][lane];
+        for (int k = 0; k < kFoldWarps; ++k) {
+            s += sh[k][0][lane];
+            q += sh[k][1][lane];
+        }
     }
 }
 
 // mean/var from partials; running-stat update (unbiased var, like torch); scale/shift
-// grid = ceil(C / 32), block = 256
-__global__ void __launch_bounds__(256) bn_fwd_finalize_kernel(const float* __restrict__ partials, int nblocks, long long M, int C,
+// grid = ceil(C / 32), block = kFoldThreads
+__global__ void __launch_bounds__(kFoldThreads) bn_fwd_finalize_kernel(const float* __restrict__ partials, int nblocks, long long M, int C,
                                        const bf16* __restrict__ gamma, const bf16* __restrict__ beta,
                                        float* __restrict__ running_mean, float* __restrict__ running_var, float momentum, float eps,
                                        float* __restrict__ mean_out, float* __restrict__ invstd_out, float* __restrict__ scale_out,
@@ -245,8 +259,8 @@ __global__ void __launch_bounds__(kBnMaxThreads) bn_bwd_reduce_kernel(const bf16
 }
 
 // dgamma, dbeta and the coefficients of pass 2:  dx = a * (g - b - (x - mean) * c)
-// grid = ceil(C / 32), block = 256
-__global__ void __launch_bounds__(256) bn_bwd_finalize_kernel(const float* __restrict__ partials, int nblocks, long long M, int C,
+// grid = ceil(C / 32), block = kFoldThreads
+__global__ void __launch_bounds__(kFoldThreads) bn_bwd_finalize_kernel(const float* __restrict__ partials, int nblocks, long long M, int C,
                                        const bf16* __restrict__ gamma, const float* __restrict__ invstd, void* __restrict__ dgamma,
                                        void* __restrict__ dbeta, int grad_dtype, float* __restrict__ coef /*[3][C]*/) {
     const int c = blockIdx.x * 32 + (threadIdx.x & 31);
@@ -350,7 +364,7 @@ DDL_API int ddl_bn_act_fwd_train(const void* x, const void* residual, const void
     float* partials = (float*)scratch;
     bn_stats_kernel<<<g.grid, g.threads, smem_bytes(g), s>>>((const bf16*)x, g.nvec, g.vec_cols, C, partials);
     DDL_LAUNCH_CHECK();
-    bn_fwd_finalize_kernel<<<ddl_ceil_div(C, 32), 256, 0, s>>>(partials, g.grid, M, C, (const bf16*)gamma, (const bf16*)beta, running_mean,
+    bn_fwd_finalize_kernel<<<ddl_ceil_div(C, 32), kFoldThreads, 0, s>>>(partials, g.grid, M, C, (const bf16*)gamma, (const bf16*)beta, running_mean,
                                                                running_var, momentum, eps, mean, invstd, scale, shift);
     DDL_LAUNCH_CHECK();
     return ddl_bn_apply(x, residual, scale, shift, y, M, C, relu, stream_);
@@ -364,7 +378,7 @@ DDL_API int ddl_bn_act_fwd_train_from_sums(const void* x, const void* residual, 
     DDL_REQUIRE(x && y && mean && invstd && scale && shift && sums, "bn fwd (from sums): null pointer");
     cudaStream_t s = (cudaStream_t)stream_;
     // `sums` has the layout of ONE partial block: [2][C]
-    bn_fwd_finalize_kernel<<<ddl_ceil_div(C, 32), 256, 0, s>>>(sums, 1, M, C, (const bf16*)gamma, (const bf16*)beta, running_mean, running_var,
+    bn_fwd_finalize_kernel<<<ddl_ceil_div(C, 32), kFoldThreads, 0, s>>>(sums, 1, M, C, (const bf16*)gamma, (const bf16*)beta, running_mean, running_var,
                                                               momentum, eps, mean, invstd, scale, shift);
     DDL_LAUNCH_CHECK();
     return ddl_bn_apply(x, residual, scale, shift, y, M, C, relu, stream_);
@@ -398,7 +412,7 @@ DDL_API int ddl_bn_act_bwd(const void* dy, const void* y, const void* x, const v
     else if (relu) bn_bwd_reduce_kernel<true, false><<<g.grid, g.threads, smem_bytes(g), s>>>(dyp, yp, xp, mean, nullptr, g.nvec, g.vec_cols, C, partials);
     else bn_bwd_reduce_kernel<false, false><<<g.grid, g.threads, smem_bytes(g), s>>>(dyp, yp, xp, mean, nullptr, g.nvec, g.vec_cols, C, partials);
     DDL_LAUNCH_CHECK();
-    bn_bwd_finalize_kernel<<<ddl_ceil_div(C, 32), 256, 0, s>>>(partials, g.grid, M, C, (const bf16*)gamma, invstd, dgamma, dbeta,
+    bn_bwd_finalize_kernel<<<ddl_ceil_div(C, 32), kFoldThreads, 0, s>>>(partials, g.grid, M, C, (const bf16*)gamma, invstd, dgamma, dbeta,
                                                                param_grad_dtype, coef);
     DDL_LAUNCH_CHECK();
     if (write_g) bn_bwd_apply_kernel<true, true><<<g.grid, g.threads, 0, s>>>((const bf16*)dres, yp, xp, mean, coef, (bf16*)dx, g.nvec, g.vec_cols, C);

@@ -137,6 +137,21 @@ __global__ void __launch_bounds__(256) avgpool_bwd_kernel(const bf16* __restrict
     }
 }
 
+// Network input: [N, C, H*W] planes (fp32 or bf16, C <= 8) -> [N, H*W, 8] bf16 pixels with the channels
+// C..7 zero.  One thread per pixel: C coalesced plane reads, one 16-byte store.  Eight channels make the stem
+// convolution an ordinary tensor-core implicit GEMM for the library (a 3-channel NHWC input is not).
+template <typename T>
+__global__ void __launch_bounds__(256) nchw_to_nhwc8_kernel(const T* __restrict__ x, bf16* __restrict__ y, int N, int C, size_t HW) {
+    const size_t total = (size_t)N * HW;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const size_t n = t / HW, px = t - n * HW;
+        float v[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) v[c] = c < C ? (float)x[(n * C + c) * HW + px] : 0.f;
+        st_global_v4(y + t * 8, float_to_bf16x8(v));
+    }
+}
+
 int grid_for(size_t total) {
     long long b = (long long)((total + 255) / 256);
     const long long cap = DDL_SM_COUNT * 16;
@@ -177,6 +192,17 @@ DDL_API int ddl_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* 
 DDL_API int ddl_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream_) {
     DDL_REQUIRE(C % 8 == 0, "avgpool: channels must be a multiple of 8");
     avgpool_bwd_kernel<<<grid_for((size_t)N * HW * (C / 8)), 256, 0, (cudaStream_t)stream_>>>((const bf16*)dy, (bf16*)dx, N, HW, C);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+DDL_API int ddl_nchw_to_nhwc8_bf16(const void* x, int x_dtype, void* y, int N, int C, long long HW, void* stream_) {
+    DDL_REQUIRE(x && y, "nchw_to_nhwc8: null pointer");
+    DDL_REQUIRE(C >= 1 && C <= 8 && N >= 1 && HW >= 1, "nchw_to_nhwc8: need 1 <= C <= 8 (got %d)", C);
+    DDL_REQUIRE(x_dtype == DDL_F32 || x_dtype == DDL_BF16, "nchw_to_nhwc8: input must be float32 or bfloat16");
+    const int grid = grid_for((size_t)N * HW);
+    if (x_dtype == DDL_F32) nchw_to_nhwc8_kernel<float><<<grid, 256, 0, (cudaStream_t)stream_>>>((const float*)x, (bf16*)y, N, C, (size_t)HW);
+    else nchw_to_nhwc8_kernel<bf16><<<grid, 256, 0, (cudaStream_t)stream_>>>((const bf16*)x, (bf16*)y, N, C, (size_t)HW);
     DDL_LAUNCH_CHECK();
     return 0;
 }

@@ -63,13 +63,9 @@ class Trainer:
         if hasattr(model, "set_impl"):
             model.set_impl("fused" if self.fused else "torch")
         if self.cuda:
-            model = model.to(self.device, dtype)
-            if channels_last and any(isinstance(m, nn.Conv2d) for m in model.modules()):
-                model = model.to(memory_format=torch.channels_last)
-                for m in model.modules():  # running statistics stay fp32
-                    if isinstance(m, nn.modules.batchnorm._BatchNorm) and m.running_mean is not None:
-                        m.running_mean.data = m.running_mean.data.float()
-                        m.running_var.data = m.running_var.data.float()
+            from .models import prepare_for_fused
+
+            model = prepare_for_fused(model, self.device, dtype, channels_last)
         else:
             model = model.to(self.device)
         self.model = model
@@ -103,7 +99,9 @@ class Trainer:
 
     # ---- one optimisation step on device-resident inputs ----------------------------------
     def _step_impl(self, batch) -> torch.Tensor:
-        self.ddp.zero_grad()
+        # no memset: every step is synchronised, so each bucket collects its fresh gradients with one
+        # multi-tensor copy when it is launched (parallel/ddp.py::_gather_grads)
+        self.ddp.zero_grad(set_to_none=True)
         loss = self.loss_fn(self.ddp, batch) if self.loss_fn else _default_loss(self.ddp, batch, self.fused)
         loss.backward()
         self.opt.step()

@@ -17,6 +17,7 @@ Two execution paths share the same parameters:
 """
 from __future__ import annotations
 
+import os
 from typing import List, Optional, Type
 
 import torch
@@ -94,6 +95,10 @@ class ResNet(nn.Module):
         super().__init__()
         self.inplanes = 64
         self.small_input = small_input
+        # fused path, opt-in: zero-pad the 3-channel input (and stem weight) to 8 channels (ops.functional.to_nhwc_bf16).
+        # Measured on B200 (profiles/resnet50_step_r1.md): cuDNN then picks a 256x64 tcgen05 implicit GEMM that takes
+        # 2.8 ms against 1.47 ms for the 3-channel legacy kernel, so the default stays 0.
+        self.stem_pad = int(os.environ.get("DDL_STEM_PAD", "0"))
         if small_input:
             self.conv1 = nn.Conv2d(3, 64, 3, 1, 1, bias=False)
         else:
@@ -139,8 +144,16 @@ class ResNet(nn.Module):
         if fused:
             from ..ops import functional as OF
 
-            x = OF.to_nhwc_bf16(x)
-        x = _conv_bn_act(x, self.conv1, self.bn1, True, None, self.impl)
+            x = OF.to_nhwc_bf16(x, pad_channels=self.stem_pad)
+            if x.shape[1] != self.conv1.in_channels:
+                # input zero-padded to 8 channels: pad the 3-channel stem weight the same way
+                c = self.conv1
+                y = F.conv2d(x, OF.pad_in_channels(c.weight, x.shape[1]), None, c.stride, c.padding)
+                x = OF.bn_act(y, self.bn1, relu=True)
+            else:
+                x = _conv_bn_act(x, self.conv1, self.bn1, True, None, self.impl)
+        else:
+            x = _conv_bn_act(x, self.conv1, self.bn1, True, None, self.impl)
         if not self.small_input:
             x = OF.maxpool3x3s2(x) if fused else F.max_pool2d(x, 3, 2, 1)
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))

@@ -75,6 +75,7 @@ _PROTOS = {
     "ddl_maxpool3x3s2_bwd": ([_vp, _vp, _vp, _i, _i, _i, _i, _vp], _i),
     "ddl_avgpool_fwd": ([_vp, _vp, _i, _i, _i, _vp], _i),
     "ddl_avgpool_bwd": ([_vp, _vp, _i, _i, _i, _vp], _i),
+    "ddl_nchw_to_nhwc8_bf16": ([_vp, _i, _vp, _i, _i, _ll, _vp], _i),
     "ddl_gemm_bf16": ([_vp, _i, _ll, _vp, _i, _ll, _vp, _ll, _i, _i, _i, _vp, _vp, _vp, _i, _i, _vp, _i, _vp], _i),
     "ddl_gemm_bf16_ex": ([_vp, _i, _ll, _vp, _i, _ll, _vp, _ll, _i, _i, _i, _vp, _vp, _vp, _i, _i, _vp, _vp, _i, _vp], _i),
     "ddl_bn_act_fwd_train_from_sums": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _f, _f, _i, _vp], _i),

@@ -254,6 +254,9 @@ def bn_act(x, bn: nn.BatchNorm2d, relu: bool = True, residual: Optional[torch.Te
     """``relu(batch_norm(x) + residual)`` with torch's training/eval semantics (running stats
     updated with the unbiased variance and ``bn.momentum``)."""
     training = bn.training or bn.running_mean is None
+    if bn.running_mean is not None and (bn.running_mean.dtype != torch.float32 or bn.running_var.dtype != torch.float32):
+        raise L.DdlError("fused BatchNorm keeps running_mean / running_var in float32 (got "
+                         f"{bn.running_mean.dtype}); convert the model with models.prepare_for_fused() instead of .to(bfloat16)")
     if training and bn.num_batches_tracked is not None:
         bn.num_batches_tracked.add_(1)
     return _BnAct.apply(x, residual, bn.weight, bn.bias, bn.running_mean, bn.running_var, training,
@@ -268,7 +271,7 @@ class _MaxPool3x3s2(torch.autograd.Function):
         if not x.is_contiguous(memory_format=torch.channels_last):
             x = x.contiguous(memory_format=torch.channels_last)
         OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
-        y = torch.empty(N, Cc, OH, OW, dtype=x.dtype, device=x.device).contiguous(memory_format=torch.channels_last)
+        y = torch.empty((N, Cc, OH, OW), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
         idx = torch.empty(N * OH * OW * Cc, dtype=torch.uint8, device=x.device)
         L.call("ddl_maxpool3x3s2_fwd", x.data_ptr(), y.data_ptr(), idx.data_ptr(), N, H, W, Cc, L.stream_ptr(x.device))
         ctx.save_for_backward(idx)
@@ -282,7 +285,7 @@ class _MaxPool3x3s2(torch.autograd.Function):
         N, Cc, H, W = ctx.shape
         if not dy.is_contiguous(memory_format=torch.channels_last):
             dy = dy.contiguous(memory_format=torch.channels_last)
-        dx = torch.empty(N, Cc, H, W, dtype=dy.dtype, device=dy.device).contiguous(memory_format=torch.channels_last)
+        dx = torch.empty((N, Cc, H, W), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
         L.call("ddl_maxpool3x3s2_bwd", dy.data_ptr(), idx.data_ptr(), dx.data_ptr(), N, H, W, Cc, L.stream_ptr(dy.device))
         return dx
 
@@ -309,7 +312,7 @@ class _GlobalAvgPool(torch.autograd.Function):
     def backward(ctx, dy):
         N, Cc, H, W = ctx.shape
         dy = dy.contiguous()
-        dx = torch.empty(N, Cc, H, W, dtype=dy.dtype, device=dy.device).contiguous(memory_format=torch.channels_last)
+        dx = torch.empty((N, Cc, H, W), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
         L.call("ddl_avgpool_bwd", dy.data_ptr(), dx.data_ptr(), N, H * W, Cc, L.stream_ptr(dy.device))
         return dx
 
@@ -319,8 +322,26 @@ def global_avgpool(x: torch.Tensor) -> torch.Tensor:
     return _GlobalAvgPool.apply(x)
 
 
-def to_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
+def to_nhwc_bf16(x: torch.Tensor, pad_channels: int = 0) -> torch.Tensor:
+    """Network input -> bf16 channels-last.  ``pad_channels=8`` (native kernel, ``csrc/pool.cu``) also
+    zero-pads the channel dimension to 8 so that the stem convolution is a tensor-core implicit GEMM;
+    use it together with :func:`pad_in_channels` on the weight."""
+    if (pad_channels == 8 and x.is_cuda and x.dim() == 4 and x.shape[1] < 8 and not x.requires_grad
+            and x.dtype in (torch.float32, torch.bfloat16) and x.is_contiguous()):
+        N, C, H, W = x.shape
+        y = torch.empty((N, 8, H, W), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
+        L.call("ddl_nchw_to_nhwc8_bf16", x.data_ptr(), L.dtype_code(x.dtype), y.data_ptr(), N, C, H * W, L.stream_ptr(x.device))
+        return y
     return x.to(dtype=torch.bfloat16, memory_format=torch.channels_last)
+
+
+def pad_in_channels(weight: torch.Tensor, cin: int) -> torch.Tensor:
+    """Zero-pad a convolution weight [Cout, Cin, kh, kw] to ``cin`` input channels (differentiable; the
+    gradient of the padding is dropped), keeping the channels-last layout."""
+    if weight.shape[1] >= cin:
+        return weight
+    w = F.pad(weight, (0, 0, 0, 0, 0, cin - weight.shape[1]))
+    return w.contiguous(memory_format=torch.channels_last)
 
 
 class _Conv1x1(torch.autograd.Function):

@@ -17,7 +17,7 @@ from typing import Any, Dict, List
 import torch
 
 from .ops import _lib as L
-from .parallel.ddp import DistributedDataParallel, GradBucket
+from .parallel.ddp import DistributedDataParallel, GradBucket, flat_view
 
 
 class FusedAdamW:
@@ -88,7 +88,7 @@ class FusedAdamW:
             self.hyper[5] += 1
 
     def zero_grad(self, set_to_none: bool = False) -> None:
-        self.ddp.zero_grad()
+        self.ddp.zero_grad(set_to_none=set_to_none)
 
     # ---- checkpoint (per-parameter entries, independent of the bucket layout) ----------
     def state_dict(self) -> Dict[str, Any]:
@@ -98,9 +98,9 @@ class FusedAdamW:
             for p, off in zip(b.params, b.offsets):
                 n = p.numel()
                 state[index[p]] = {
-                    "master": w[off : off + n].view(p.shape).cpu().clone(),
-                    "exp_avg": m[off : off + n].view(p.shape).cpu().clone(),
-                    "exp_avg_sq": v[off : off + n].view(p.shape).cpu().clone(),
+                    "master": flat_view(w, off, p).cpu().contiguous().clone(),
+                    "exp_avg": flat_view(m, off, p).cpu().contiguous().clone(),
+                    "exp_avg_sq": flat_view(v, off, p).cpu().contiguous().clone(),
                 }
         return {"state": state, "step": float(self.hyper[5].item()), "defaults": dict(self.defaults)}
 
@@ -110,9 +110,9 @@ class FusedAdamW:
             for p, off in zip(b.params, b.offsets):
                 n = p.numel()
                 e = sd["state"][index[p]]
-                w[off : off + n].copy_(e["master"].reshape(-1))
-                m[off : off + n].copy_(e["exp_avg"].reshape(-1))
-                v[off : off + n].copy_(e["exp_avg_sq"].reshape(-1))
+                flat_view(w, off, p).copy_(e["master"])
+                flat_view(m, off, p).copy_(e["exp_avg"])
+                flat_view(v, off, p).copy_(e["exp_avg_sq"])
             flat_p.copy_(w)
         self.defaults.update(sd.get("defaults", {}))
         d = self.defaults

@@ -59,6 +59,19 @@ def _align(n: int, a: int) -> int:
     return (n + a - 1) // a * a
 
 
+def flat_view(flat: torch.Tensor, off: int, p: torch.Tensor) -> torch.Tensor:
+    """View of ``flat[off : off + p.numel()]`` with ``p``'s shape AND memory layout.
+
+    A channels-last 4-D parameter (convolution weights of an NHWC model) keeps its channels-last
+    strides inside the flat buffer.  A plain ``.view(p.shape)`` would silently turn it into an NCHW
+    tensor and make cuDNN convert the weight (and its gradient) on every step."""
+    n = p.numel()
+    if p.dim() == 4 and p.is_contiguous(memory_format=torch.channels_last) and not p.is_contiguous():
+        co, ci, kh, kw = p.shape
+        return flat[off : off + n].view(co, kh, kw, ci).permute(0, 3, 1, 2)
+    return flat[off : off + n].view(p.shape)
+
+
 def assign_buckets(
     params: Iterable[nn.Parameter],
     bucket_cap_bytes: int,
@@ -144,6 +157,7 @@ class DistributedDataParallel(nn.Module):
         self.gradient_as_bucket_view = gradient_as_bucket_view
         self.on_bucket_reduced: Optional[Callable[[GradBucket], None]] = None
         self._callback_queued = False
+        self._grads_detached = False  # True after zero_grad(set_to_none=True): buckets are not pre-zeroed
         self._comm_stream = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" else None
 
         self.buckets = assign_buckets(
@@ -161,11 +175,11 @@ class DistributedDataParallel(nn.Module):
                 flat_p = torch.zeros(b.padded_numel, dtype=b.dtype, device=self.device)
             self.param_buffers.append(flat_p)
             for i, (p, off) in enumerate(zip(b.params, b.offsets)):
-                view = b.buffer[off : off + p.numel()].view(p.shape)
+                view = flat_view(b.buffer, off, p)
                 b.views.append(view)
                 self._param_to_bucket[p] = (b, i)
                 if flat_p is not None:
-                    pv = flat_p[off : off + p.numel()].view(p.shape)
+                    pv = flat_view(flat_p, off, p)
                     pv.copy_(p.data)
                     p.data = pv
                 if gradient_as_bucket_view:
@@ -232,15 +246,9 @@ class DistributedDataParallel(nn.Module):
 
     def _grad_ready(self, p: nn.Parameter) -> None:
         b, i = self._param_to_bucket[p]
-        view = b.views[i]
-        g = p.grad
-        if g is not None and g.data_ptr() != view.data_ptr():
-            # grad was (re)allocated by autograd (e.g. after zero_grad(set_to_none=True)):
-            # move it into the bucket and point .grad back at the view
-            view.copy_(g)
-            if self.gradient_as_bucket_view:
-                p.grad = view
         if not self.require_backward_grad_sync:
+            # no_sync(): leave .grad where autograd put it (the bucket view, or its own tensor after
+            # zero_grad(set_to_none=True)); later backward passes accumulate into it
             return
         if not self._callback_queued:
             torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
@@ -249,8 +257,30 @@ class DistributedDataParallel(nn.Module):
         if b.pending == 0 and not b.launched:
             self._launch_bucket(b)
 
+    @torch.no_grad()
+    def _gather_grads(self, b: GradBucket) -> None:
+        """Bring every gradient of the bucket into its slot of the flat buffer.
+
+        After ``zero_grad(set_to_none=True)`` autograd hands each parameter a gradient tensor of its
+        own; they are moved here with ONE multi-tensor copy per bucket (instead of one memset per
+        bucket plus one accumulate kernel per parameter), and ``.grad`` is pointed at the bucket view."""
+        src, dst = [], []
+        for p, v in zip(b.params, b.views):
+            g = p.grad
+            if g is None:
+                if self._grads_detached:
+                    v.zero_()  # unused parameter: contributes zeros, like find_unused_parameters=True
+            elif g.data_ptr() != v.data_ptr():
+                src.append(g)
+                dst.append(v)
+            if self.gradient_as_bucket_view and (g is not None or self._grads_detached):
+                p.grad = v
+        if src:
+            torch._foreach_copy_(dst, src)
+
     def _launch_bucket(self, b: GradBucket) -> None:
         b.launched = True
+        self._gather_grads(b)
         if self._comm_stream is not None:
             # the comm stream must see every gradient write of this bucket
             self._comm_stream.wait_stream(torch.cuda.current_stream(self.device))
@@ -301,15 +331,20 @@ class DistributedDataParallel(nn.Module):
 
     @torch.no_grad()
     def zero_grad(self, set_to_none: bool = False) -> None:  # type: ignore[override]
-        """Zero the flat gradient buckets (one memset per bucket)."""
+        """``set_to_none=False``: zero the flat buckets (one memset per bucket), ``.grad`` stays the
+        bucket view and autograd accumulates into it.  ``set_to_none=True``: no memset at all; autograd
+        produces fresh gradient tensors and each bucket collects them with one multi-tensor copy when
+        it is launched (the cheaper choice when every step is synchronised)."""
+        self._grads_detached = bool(set_to_none)
         for b in self.buckets:
-            b.buffer.zero_()
-            if self.gradient_as_bucket_view:
-                for p, v in zip(b.params, b.views):
-                    p.grad = v
-            elif set_to_none:
+            if set_to_none:
                 for p in b.params:
                     p.grad = None
+            else:
+                b.buffer.zero_()
+                if self.gradient_as_bucket_view:
+                    for p, v in zip(b.params, b.views):
+                        p.grad = v
 
     def flat_grads(self) -> List[torch.Tensor]:
         return [b.buffer for b in self.buckets]

@@ -31,7 +31,7 @@ import torch.nn as nn
 
 from . import process_group as pg
 from .comm import CommBackend, default_comm
-from .ddp import _SingleProcessComm, _align
+from .ddp import _SingleProcessComm, _align, flat_view
 
 
 class _Unit:
@@ -128,7 +128,7 @@ class FullyShardedDataParallel(nn.Module):
         for u in self.units:
             flat = torch.zeros(u.padded, dtype=self.dtype, device=self.device)
             for p, off in zip(u.params, u.offsets):
-                flat[off : off + p.numel()].copy_(p.data.reshape(-1))
+                flat_view(flat, off, p).copy_(p.data)
             # rank 0's values are the truth (same contract as DDP's init broadcast)
             if W > 1:
                 self._broadcast(flat)
@@ -149,8 +149,8 @@ class FullyShardedDataParallel(nn.Module):
                 u.full_param = flat
             u.grad_views, u.param_index = [], {}
             for i, (p, off) in enumerate(zip(u.params, u.offsets)):
-                p.data = u.full_param[off : off + p.numel()].view(p.shape)
-                u.grad_views.append(u.full_grad[off : off + p.numel()].view(p.shape))
+                p.data = flat_view(u.full_param, off, p)
+                u.grad_views.append(flat_view(u.full_grad, off, p))
                 u.param_index[id(p)] = i
                 p.grad = u.grad_views[i]
                 self._param_unit[p] = u
@@ -323,7 +323,7 @@ class FullyShardedDataParallel(nn.Module):
             self.comm.all_gather_into(tmp, u.shard_param).wait()
             for p, off in zip(u.params, u.offsets):
                 saved.append((p, p.data))
-                p.data = tmp[off : off + p.numel()].view(p.shape)
+                p.data = flat_view(tmp, off, p)
         if self.cuda:
             torch.cuda.synchronize(self.device)
         sd = {k: v.detach().cpu().clone() for k, v in self.module.state_dict().items()}

@@ -157,6 +157,9 @@ int ddl_maxpool3x3s2_bwd(const void* dy, const void* idx, void* dx, int N, int H
 /* global average pool [N, HW, C] -> [N, C] and its backward */
 int ddl_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream);
 int ddl_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);
+/* network input [N, C, HW] (x_dtype DDL_F32 / DDL_BF16, C <= 8) -> [N, HW, 8] bf16, channels C..7 zero: the stem
+ * convolution of the reference's ResNet-50 (reference:19) then has 8 input channels and runs on tensor cores */
+int ddl_nchw_to_nhwc8_bf16(const void* x, int x_dtype, void* y, int N, int C, long long HW, void* stream);
 
 /* ---- tcgen05 / TMEM / TMA GEMM (csrc/gemm_tcgen05.cu), K8 ------------------------------ */
 /* C[M,N] = epilogue(A . B^T), bf16 operands, fp32 accumulation in tensor memory.

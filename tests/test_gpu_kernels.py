@@ -547,3 +547,55 @@ def test_conv1x1_gemm_bn_act_matches_torch(Cin, Cout, HW, relu, with_res):
     assert torch.allclose(bn.running_var, rbn.running_var, rtol=2e-2, atol=2e-3)
     assert rel(conv.weight.grad.reshape(Cout, Cin), rconv.weight.grad.reshape(Cout, Cin)) < 8e-2
     assert ((x.grad.float() - xr.grad).abs().mean() / xr.grad.abs().mean()).item() < 3e-2
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_nchw_to_nhwc8_input_conversion(dtype):
+    from databricks_distributed_deep_learning_b200.ops import _lib as L
+
+    OF, bf = _OF(), torch.bfloat16
+    x = torch.randn(5, 3, 17, 23, device="cuda").to(dtype)
+    n0 = L.launch_count
+    y = OF.to_nhwc_bf16(x, pad_channels=8)
+    assert L.launch_count == n0 + 1
+    assert y.shape == (5, 8, 17, 23) and y.dtype == bf and y.is_contiguous(memory_format=torch.channels_last)
+    assert torch.equal(y[:, :3], x.to(bf))
+    assert float(y[:, 3:].abs().sum()) == 0.0
+
+
+def test_padded_stem_matches_plain_stem():
+    """ResNet stem with the input/weight zero-padded to 8 channels == the 3-channel stem (fp32 oracle)."""
+    from databricks_distributed_deep_learning_b200.models import prepare_for_fused, resnet18
+
+    bf = torch.bfloat16
+    m = prepare_for_fused(resnet18(num_classes=10, impl="fused"), "cuda")
+    ref = resnet18(num_classes=10, impl="torch").cuda().float()
+    ref.load_state_dict({k: v.float() for k, v in m.state_dict().items()})
+    x = torch.randn(16, 3, 64, 64, device="cuda")
+    outs = {}
+    for pad in (0, 8):
+        m.stem_pad = pad
+        m.zero_grad(set_to_none=True)
+        y = m(x)
+        y.float().square().mean().backward()
+        outs[pad] = (y.detach().float(), m.conv1.weight.grad.detach().float().clone())
+        assert m.conv1.weight.grad.shape == (64, 3, 7, 7)
+    yr = ref(x)
+    yr.square().mean().backward()
+    rel = lambda a, b: ((a - b).abs().max() / b.abs().max().clamp_min(1e-6)).item()
+    assert rel(outs[0][0], yr.detach()) < 1e-1, "plain fused stem vs fp32 oracle"
+    assert rel(outs[8][0], yr.detach()) < 1e-1
+    assert rel(outs[8][0], outs[0][0]) < 6e-2
+    assert rel(outs[8][1], ref.conv1.weight.grad) < 1.5e-1
+    assert rel(outs[8][1], outs[0][1]) < 1e-1
+
+
+def test_bn_rejects_low_precision_running_stats():
+    """The BN kernels write fp32 running statistics; a bf16 buffer would be overrun, so it is refused."""
+    from databricks_distributed_deep_learning_b200.ops import _lib as L
+
+    OF = _OF()
+    bn = torch.nn.BatchNorm2d(16).cuda().to(torch.bfloat16)
+    x = torch.randn(2, 16, 4, 4, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    with pytest.raises(L.DdlError, match="float32"):
+        OF.bn_act(x, bn)

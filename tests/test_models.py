@@ -71,3 +71,15 @@ def test_bert_loss_and_backward():
     loss, logits = m(ids, torch.ones_like(ids), labels=torch.tensor([0, 1]))
     loss.backward()
     assert logits.shape == (2, 2) and all(p.grad is not None for p in m.parameters())
+
+
+def test_prepare_for_fused_keeps_bn_statistics_fp32():
+    import torch
+
+    from databricks_distributed_deep_learning_b200.models import prepare_for_fused, resnet18
+
+    m = prepare_for_fused(resnet18(num_classes=10, small_input=True))
+    assert m.conv1.weight.dtype == torch.bfloat16
+    assert m.conv1.weight.is_contiguous(memory_format=torch.channels_last)
+    assert m.bn1.running_mean.dtype == torch.float32 and m.bn1.running_var.dtype == torch.float32
+    assert m.bn1.weight.dtype == torch.bfloat16
