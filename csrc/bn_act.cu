@@ -174,7 +174,8 @@ __global__ void bn_eval_coeff_kernel(int C, const bf16* __restrict__ gamma, cons
 template <bool kRelu, bool kRes>
 __global__ void __launch_bounds__(kBnMaxThreads) bn_apply_kernel(const bf16* __restrict__ x, const bf16* __restrict__ res,
                                                                  const float* __restrict__ scale, const float* __restrict__ shift,
-                                                                 bf16* __restrict__ y, size_t nvec, int vec_cols) {
+                                                                 bf16* __restrict__ y, unsigned char* __restrict__ mask, size_t nvec,
+                                                                 int vec_cols) {
     const int vc = (int)(((size_t)blockIdx.x * blockDim.x + threadIdx.x) % vec_cols);
     float sc[8], sf[8];
     *reinterpret_cast<float4*>(&sc[0]) = *reinterpret_cast<const float4*>(scale + vc * 8);
@@ -204,17 +205,27 @@ __global__ void __launch_bounds__(kBnMaxThreads) bn_apply_kernel(const bf16* __r
                     for (int j = 0; j < 8; ++j) f[j] += g[j];
                 }
                 if (kRelu) {
+                    // one byte per vector: bit j = "channel j passed the ReLU"; backward reads this instead of y
+                    unsigned m = 0;
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+                    for (int j = 0; j < 8; ++j) {
+                        m |= (f[j] > 0.f ? 1u : 0u) << j;
+                        f[j] = fmaxf(f[j], 0.f);
+                    }
+                    if (mask) mask[v0 + k * stride] = (unsigned char)m;
                 }
                 st_global_v4(y + (v0 + k * stride) * 8, float_to_bf16x8(f));
             }
     }
 }
 
-// backward pass 1: g = dy * (y > 0); partial sum(g), sum(g * (x - mean)); optionally write g
-template <bool kRelu, bool kWriteG>
-__global__ void __launch_bounds__(kBnMaxThreads) bn_bwd_reduce_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y,
+// backward pass 1: g = (dy [+ dy2]) * relu_mask; partial sum(g), sum(g * (x - mean)); optionally write g.
+// The ReLU mask is the byte-per-vector bitmask written by the forward (kMask) or, for callers that did not
+// keep one, recomputed from the saved output y.  dy2 (nullable) is a second gradient of the same tensor -
+// the other branch of a residual fork - summed here instead of by a separate elementwise kernel.
+template <bool kRelu, bool kWriteG, bool kMask>
+__global__ void __launch_bounds__(kBnMaxThreads) bn_bwd_reduce_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ dy2,
+                                                                      const bf16* __restrict__ y, const unsigned char* __restrict__ mask,
                                                                       const bf16* __restrict__ x, const float* __restrict__ mean,
                                                                       bf16* __restrict__ g_out, size_t nvec, int vec_cols, int C,
                                                                       float* __restrict__ partials) {
@@ -226,13 +237,17 @@ __global__ void __launch_bounds__(kBnMaxThreads) bn_bwd_reduce_kernel(const bf16
 #pragma unroll
     for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const bool add2 = dy2 != nullptr;
     for (size_t v0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v0 < nvec; v0 += stride * kUnroll) {
-        uint4 ud[kUnroll], uy[kUnroll], ux[kUnroll];
+        uint4 ud[kUnroll], ue[kUnroll], uy[kUnroll], ux[kUnroll];
+        unsigned mk[kUnroll];
 #pragma unroll
         for (int k = 0; k < kUnroll; ++k)
             if (v0 + k * stride < nvec) {
                 ud[k] = ld_stream_v4(dy + (v0 + k * stride) * 8);
-                if (kRelu) uy[k] = ld_stream_v4(y + (v0 + k * stride) * 8);
+                if (add2) ue[k] = ld_stream_v4(dy2 + (v0 + k * stride) * 8);
+                if (kRelu && !kMask) uy[k] = ld_stream_v4(y + (v0 + k * stride) * 8);
+                if (kRelu && kMask) mk[k] = mask[v0 + k * stride];
                 ux[k] = ld_stream_v4(x + (v0 + k * stride) * 8);
             }
 #pragma unroll
@@ -241,11 +256,21 @@ __global__ void __launch_bounds__(kBnMaxThreads) bn_bwd_reduce_kernel(const bf16
                 float d[8], xx[8];
                 bf16x8_to_float(ud[k], d);
                 bf16x8_to_float(ux[k], xx);
-                if (kRelu) {
+                if (add2) {
+                    float e[8];
+                    bf16x8_to_float(ue[k], e);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) d[j] += e[j];
+                }
+                if (kRelu && !kMask) {
                     float yy[8];
                     bf16x8_to_float(uy[k], yy);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) d[j] = yy[j] > 0.f ? d[j] : 0.f;
+                }
+                if (kRelu && kMask) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) d[j] = (mk[k] >> j) & 1u ? d[j] : 0.f;
                 }
                 if (kWriteG) st_global_v4(g_out + (v0 + k * stride) * 8, float_to_bf16x8(d));
 #pragma unroll
@@ -282,13 +307,13 @@ __global__ void __launch_bounds__(kFoldThreads) bn_bwd_finalize_kernel(const flo
     coef[2 * C + c] = sgx * inv_m * is * is;
 }
 
-// backward pass 2.  kFromG: g was materialised by pass 1 (residual blocks); else recompute
-// the ReLU mask from y.
-template <bool kRelu, bool kFromG>
+// backward pass 2.  kFromG: g was materialised by pass 1 (residual blocks); else apply the ReLU mask
+// (bitmask when kMask, recomputed from y otherwise) to dy again.
+template <bool kRelu, bool kFromG, bool kMask>
 __global__ void __launch_bounds__(kBnMaxThreads) bn_bwd_apply_kernel(const bf16* __restrict__ dy_or_g, const bf16* __restrict__ y,
-                                                                     const bf16* __restrict__ x, const float* __restrict__ mean,
-                                                                     const float* __restrict__ coef, bf16* __restrict__ dx, size_t nvec,
-                                                                     int vec_cols, int C) {
+                                                                     const unsigned char* __restrict__ mask, const bf16* __restrict__ x,
+                                                                     const float* __restrict__ mean, const float* __restrict__ coef,
+                                                                     bf16* __restrict__ dx, size_t nvec, int vec_cols, int C) {
     const int vc = (int)(((size_t)blockIdx.x * blockDim.x + threadIdx.x) % vec_cols);
     float mu[8], a[8], b[8], cc[8];
 #pragma unroll
@@ -298,14 +323,17 @@ __global__ void __launch_bounds__(kBnMaxThreads) bn_bwd_apply_kernel(const bf16*
         *reinterpret_cast<float4*>(&b[4 * h]) = *reinterpret_cast<const float4*>(coef + C + vc * 8 + 4 * h);
         *reinterpret_cast<float4*>(&cc[4 * h]) = *reinterpret_cast<const float4*>(coef + 2 * C + vc * 8 + 4 * h);
     }
+    constexpr bool kNeedMask = kRelu && !kFromG;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t v0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v0 < nvec; v0 += stride * kUnroll) {
         uint4 ud[kUnroll], uy[kUnroll], ux[kUnroll];
+        unsigned mk[kUnroll];
 #pragma unroll
         for (int k = 0; k < kUnroll; ++k)
             if (v0 + k * stride < nvec) {
                 ud[k] = ld_stream_v4(dy_or_g + (v0 + k * stride) * 8);
-                if (kRelu && !kFromG) uy[k] = ld_stream_v4(y + (v0 + k * stride) * 8);
+                if (kNeedMask && !kMask) uy[k] = ld_stream_v4(y + (v0 + k * stride) * 8);
+                if (kNeedMask && kMask) mk[k] = mask[v0 + k * stride];
                 ux[k] = ld_stream_v4(x + (v0 + k * stride) * 8);
             }
 #pragma unroll
@@ -314,11 +342,15 @@ __global__ void __launch_bounds__(kBnMaxThreads) bn_bwd_apply_kernel(const bf16*
                 float d[8], xx[8], o[8];
                 bf16x8_to_float(ud[k], d);
                 bf16x8_to_float(ux[k], xx);
-                if (kRelu && !kFromG) {
+                if (kNeedMask && !kMask) {
                     float yy[8];
                     bf16x8_to_float(uy[k], yy);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) d[j] = yy[j] > 0.f ? d[j] : 0.f;
+                }
+                if (kNeedMask && kMask) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) d[j] = (mk[k] >> j) & 1u ? d[j] : 0.f;
                 }
 #pragma unroll
                 for (int j = 0; j < 8; ++j) o[j] = a[j] * (d[j] - b[j] - (xx[j] - mu[j]) * cc[j]);
@@ -338,24 +370,31 @@ DDL_API size_t ddl_bn_scratch_bytes(long long M, int C) {
     return ((size_t)g.grid * 2 * C + 3 * (size_t)C) * sizeof(float);
 }
 
-DDL_API int ddl_bn_apply(const void* x, const void* residual, const float* scale, const float* shift, void* y, long long M, int C,
-                         int relu, void* stream_) {
+static int bn_apply_impl(const void* x, const void* residual, const float* scale, const float* shift, void* y, void* relu_mask,
+                         long long M, int C, int relu, void* stream_) {
     BnGeom g;
     if (int e = make_geom(M, C, &g)) return e;
     cudaStream_t s = (cudaStream_t)stream_;
     const bf16 *xp = (const bf16*)x, *rp = (const bf16*)residual;
     bf16* yp = (bf16*)y;
-    if (relu && rp) bn_apply_kernel<true, true><<<g.grid, g.threads, 0, s>>>(xp, rp, scale, shift, yp, g.nvec, g.vec_cols);
-    else if (relu) bn_apply_kernel<true, false><<<g.grid, g.threads, 0, s>>>(xp, rp, scale, shift, yp, g.nvec, g.vec_cols);
-    else if (rp) bn_apply_kernel<false, true><<<g.grid, g.threads, 0, s>>>(xp, rp, scale, shift, yp, g.nvec, g.vec_cols);
-    else bn_apply_kernel<false, false><<<g.grid, g.threads, 0, s>>>(xp, rp, scale, shift, yp, g.nvec, g.vec_cols);
+    unsigned char* mp = (unsigned char*)relu_mask;
+    if (relu && rp) bn_apply_kernel<true, true><<<g.grid, g.threads, 0, s>>>(xp, rp, scale, shift, yp, mp, g.nvec, g.vec_cols);
+    else if (relu) bn_apply_kernel<true, false><<<g.grid, g.threads, 0, s>>>(xp, rp, scale, shift, yp, mp, g.nvec, g.vec_cols);
+    else if (rp) bn_apply_kernel<false, true><<<g.grid, g.threads, 0, s>>>(xp, rp, scale, shift, yp, nullptr, g.nvec, g.vec_cols);
+    else bn_apply_kernel<false, false><<<g.grid, g.threads, 0, s>>>(xp, rp, scale, shift, yp, nullptr, g.nvec, g.vec_cols);
     DDL_LAUNCH_CHECK();
     return 0;
 }
 
-DDL_API int ddl_bn_act_fwd_train(const void* x, const void* residual, const void* gamma, const void* beta, float* running_mean,
-                                 float* running_var, void* y, float* mean, float* invstd, float* scale, float* shift, void* scratch,
-                                 size_t scratch_bytes, long long M, int C, float eps, float momentum, int relu, void* stream_) {
+DDL_API int ddl_bn_apply(const void* x, const void* residual, const float* scale, const float* shift, void* y, long long M, int C,
+                         int relu, void* stream_) {
+    return bn_apply_impl(x, residual, scale, shift, y, nullptr, M, C, relu, stream_);
+}
+
+DDL_API int ddl_bn_act_fwd_train_mask(const void* x, const void* residual, const void* gamma, const void* beta, float* running_mean,
+                                      float* running_var, void* y, void* relu_mask, float* mean, float* invstd, float* scale, float* shift,
+                                      void* scratch, size_t scratch_bytes, long long M, int C, float eps, float momentum, int relu,
+                                      void* stream_) {
     BnGeom g;
     if (int e = make_geom(M, C, &g)) return e;
     DDL_REQUIRE(x && y && mean && invstd && scale && shift && scratch, "bn fwd: null pointer");
@@ -367,7 +406,14 @@ DDL_API int ddl_bn_act_fwd_train(const void* x, const void* residual, const void
     bn_fwd_finalize_kernel<<<ddl_ceil_div(C, 32), kFoldThreads, 0, s>>>(partials, g.grid, M, C, (const bf16*)gamma, (const bf16*)beta, running_mean,
                                                                running_var, momentum, eps, mean, invstd, scale, shift);
     DDL_LAUNCH_CHECK();
-    return ddl_bn_apply(x, residual, scale, shift, y, M, C, relu, stream_);
+    return bn_apply_impl(x, residual, scale, shift, y, relu ? relu_mask : nullptr, M, C, relu, stream_);
+}
+
+DDL_API int ddl_bn_act_fwd_train(const void* x, const void* residual, const void* gamma, const void* beta, float* running_mean,
+                                 float* running_var, void* y, float* mean, float* invstd, float* scale, float* shift, void* scratch,
+                                 size_t scratch_bytes, long long M, int C, float eps, float momentum, int relu, void* stream_) {
+    return ddl_bn_act_fwd_train_mask(x, residual, gamma, beta, running_mean, running_var, y, nullptr, mean, invstd, scale, shift, scratch,
+                                     scratch_bytes, M, C, eps, momentum, relu, stream_);
 }
 
 DDL_API int ddl_bn_act_fwd_train_from_sums(const void* x, const void* residual, const void* gamma, const void* beta, float* running_mean,
@@ -394,32 +440,51 @@ DDL_API int ddl_bn_act_fwd_eval(const void* x, const void* residual, const void*
     return ddl_bn_apply(x, residual, scale, shift, y, M, C, relu, stream_);
 }
 
-DDL_API int ddl_bn_act_bwd(const void* dy, const void* y, const void* x, const void* gamma, const float* mean, const float* invstd,
-                           void* dx, void* dres, void* dgamma, void* dbeta, int param_grad_dtype, void* scratch, size_t scratch_bytes,
-                           long long M, int C, int relu, void* stream_) {
+DDL_API int ddl_bn_act_bwd_ex(const void* dy, const void* dy2, const void* y, const void* relu_mask, const void* x, const void* gamma,
+                              const float* mean, const float* invstd, void* dx, void* dres, void* dgamma, void* dbeta,
+                              int param_grad_dtype, void* scratch, size_t scratch_bytes, long long M, int C, int relu, void* stream_) {
     BnGeom g;
     if (int e = make_geom(M, C, &g)) return e;
     DDL_REQUIRE(dy && x && mean && invstd && dx && scratch, "bn bwd: null pointer");
-    DDL_REQUIRE(!relu || y, "bn bwd: relu needs the saved output");
+    DDL_REQUIRE(!relu || y || relu_mask, "bn bwd: relu needs the saved output or the relu bitmask of the forward");
     DDL_REQUIRE(scratch_bytes >= ddl_bn_scratch_bytes(M, C), "bn bwd: scratch too small");
+    // g must be materialised when it is itself an output (gradient of the residual branch)
+    const bool write_g = dres != nullptr && relu;
+    DDL_REQUIRE(!dy2 || write_g, "bn bwd: a second incoming gradient is only fused for relu + residual layers");
     cudaStream_t s = (cudaStream_t)stream_;
     float* partials = (float*)scratch;
     float* coef = partials + (size_t)g.grid * 2 * C;
-    const bf16 *dyp = (const bf16*)dy, *yp = (const bf16*)y, *xp = (const bf16*)x;
-    // g must be materialised when it is itself an output (gradient of the residual branch)
-    const bool write_g = dres != nullptr && relu;
-    if (relu && write_g) bn_bwd_reduce_kernel<true, true><<<g.grid, g.threads, smem_bytes(g), s>>>(dyp, yp, xp, mean, (bf16*)dres, g.nvec, g.vec_cols, C, partials);
-    else if (relu) bn_bwd_reduce_kernel<true, false><<<g.grid, g.threads, smem_bytes(g), s>>>(dyp, yp, xp, mean, nullptr, g.nvec, g.vec_cols, C, partials);
-    else bn_bwd_reduce_kernel<false, false><<<g.grid, g.threads, smem_bytes(g), s>>>(dyp, yp, xp, mean, nullptr, g.nvec, g.vec_cols, C, partials);
+    const bf16 *dyp = (const bf16*)dy, *dy2p = (const bf16*)dy2, *yp = (const bf16*)y, *xp = (const bf16*)x;
+    const unsigned char* mp = (const unsigned char*)relu_mask;
+    const size_t sm = smem_bytes(g);
+#define BN_REDUCE(R, W, K, GOUT) \
+    bn_bwd_reduce_kernel<R, W, K><<<g.grid, g.threads, sm, s>>>(dyp, dy2p, yp, mp, xp, mean, GOUT, g.nvec, g.vec_cols, C, partials)
+    if (write_g && mp) BN_REDUCE(true, true, true, (bf16*)dres);
+    else if (write_g) BN_REDUCE(true, true, false, (bf16*)dres);
+    else if (relu && mp) BN_REDUCE(true, false, true, nullptr);
+    else if (relu) BN_REDUCE(true, false, false, nullptr);
+    else BN_REDUCE(false, false, false, nullptr);
+#undef BN_REDUCE
     DDL_LAUNCH_CHECK();
     bn_bwd_finalize_kernel<<<ddl_ceil_div(C, 32), kFoldThreads, 0, s>>>(partials, g.grid, M, C, (const bf16*)gamma, invstd, dgamma, dbeta,
                                                                param_grad_dtype, coef);
     DDL_LAUNCH_CHECK();
-    if (write_g) bn_bwd_apply_kernel<true, true><<<g.grid, g.threads, 0, s>>>((const bf16*)dres, yp, xp, mean, coef, (bf16*)dx, g.nvec, g.vec_cols, C);
-    else if (relu) bn_bwd_apply_kernel<true, false><<<g.grid, g.threads, 0, s>>>(dyp, yp, xp, mean, coef, (bf16*)dx, g.nvec, g.vec_cols, C);
-    else bn_bwd_apply_kernel<false, false><<<g.grid, g.threads, 0, s>>>(dyp, yp, xp, mean, coef, (bf16*)dx, g.nvec, g.vec_cols, C);
+#define BN_APPLY(R, F, K, SRC) \
+    bn_bwd_apply_kernel<R, F, K><<<g.grid, g.threads, 0, s>>>(SRC, yp, mp, xp, mean, coef, (bf16*)dx, g.nvec, g.vec_cols, C)
+    if (write_g) BN_APPLY(true, true, false, (const bf16*)dres);
+    else if (relu && mp) BN_APPLY(true, false, true, dyp);
+    else if (relu) BN_APPLY(true, false, false, dyp);
+    else BN_APPLY(false, false, false, dyp);
+#undef BN_APPLY
     DDL_LAUNCH_CHECK();
     return 0;
+}
+
+DDL_API int ddl_bn_act_bwd(const void* dy, const void* y, const void* x, const void* gamma, const float* mean, const float* invstd,
+                           void* dx, void* dres, void* dgamma, void* dbeta, int param_grad_dtype, void* scratch, size_t scratch_bytes,
+                           long long M, int C, int relu, void* stream_) {
+    return ddl_bn_act_bwd_ex(dy, nullptr, y, nullptr, x, gamma, mean, invstd, dx, dres, dgamma, dbeta, param_grad_dtype, scratch,
+                             scratch_bytes, M, C, relu, stream_);
 }
 
 // ---------------------------------------------------------------------------------------

@@ -58,8 +58,10 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_fwd_kernel(const bf16* __res
     }
 }
 
-__global__ void __launch_bounds__(256) maxpool3x3s2_bwd_kernel(const bf16* __restrict__ dy, const unsigned char* __restrict__ idx,
-                                                                bf16* __restrict__ dx, int N, int H, int W, int C, int OH, int OW) {
+// dy2 (nullable): a second gradient of the pooled tensor (the other branch of a residual fork), summed on the fly
+__global__ void __launch_bounds__(256) maxpool3x3s2_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ dy2,
+                                                                const unsigned char* __restrict__ idx, bf16* __restrict__ dx, int N, int H,
+                                                                int W, int C, int OH, int OW) {
     const int vc = C >> 3;
     const size_t total = (size_t)N * H * W * vc;
     for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
@@ -90,6 +92,12 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_bwd_kernel(const bf16* __res
                 const uint2 packed = *reinterpret_cast<const uint2*>(idx + o);
                 float g[8];
                 bf16x8_to_float(ld_global_v4(dy + o), g);
+                if (dy2) {
+                    float g2[8];
+                    bf16x8_to_float(ld_global_v4(dy2 + o), g2);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) g[j] += g2[j];
+                }
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const int aj = (int)(((j < 4 ? packed.x : packed.y) >> (8 * (j & 3))) & 0xffu);
@@ -171,15 +179,20 @@ DDL_API int ddl_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, int H
     return 0;
 }
 
-DDL_API int ddl_maxpool3x3s2_bwd(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, void* stream_) {
+DDL_API int ddl_maxpool3x3s2_bwd_ex(const void* dy, const void* dy2, const void* idx, void* dx, int N, int H, int W, int C,
+                                    void* stream_) {
     DDL_REQUIRE(C % 8 == 0, "maxpool: channels must be a multiple of 8");
     DDL_REQUIRE(dy && dx && idx, "maxpool: null pointer");
     const int OH = (H + 2 - 3) / 2 + 1, OW = (W + 2 - 3) / 2 + 1;
     const size_t total = (size_t)N * H * W * (C / 8);
-    maxpool3x3s2_bwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream_>>>((const bf16*)dy, (const unsigned char*)idx, (bf16*)dx, N, H,
-                                                                               W, C, OH, OW);
+    maxpool3x3s2_bwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream_>>>((const bf16*)dy, (const bf16*)dy2, (const unsigned char*)idx,
+                                                                               (bf16*)dx, N, H, W, C, OH, OW);
     DDL_LAUNCH_CHECK();
     return 0;
+}
+
+DDL_API int ddl_maxpool3x3s2_bwd(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, void* stream_) {
+    return ddl_maxpool3x3s2_bwd_ex(dy, nullptr, idx, dx, N, H, W, C, stream_);
 }
 
 DDL_API int ddl_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream_) {

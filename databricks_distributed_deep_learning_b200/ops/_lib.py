@@ -68,6 +68,9 @@ _PROTOS = {
     "ddl_bn_act_fwd_train": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _ll, _i, _f, _f, _i, _vp], _i),
     "ddl_bn_act_fwd_eval": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _f, _i, _vp], _i),
     "ddl_bn_act_bwd": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _ll, _i, _i, _vp], _i),
+    "ddl_bn_act_fwd_train_mask": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _ll, _i, _f, _f, _i, _vp], _i),
+    "ddl_bn_act_bwd_ex": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _ll, _i, _i, _vp], _i),
+    "ddl_maxpool3x3s2_bwd_ex": ([_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp], _i),
     "ddl_attention_fwd": ([_vp, _vp, _vp, _vp, _i, _i, _i, _f, _u64, _vp, _vp], _i),
     "ddl_attention_bwd_scratch_bytes": ([_i, _i, _i], _sz),
     "ddl_attention_bwd": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i, _i, _i, _f, _u64, _vp, _vp], _i),

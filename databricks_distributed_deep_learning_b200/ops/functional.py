@@ -8,6 +8,7 @@ in ``tests/``) is given in each docstring.
 from __future__ import annotations
 
 import itertools
+import os
 from typing import Optional
 
 import torch
@@ -188,6 +189,64 @@ def embed_layernorm(ids, token_type_ids, word, pos, typ, gamma, beta, eps: float
     return _EmbedLayerNorm.apply(ids, token_type_ids, word, pos, typ, gamma, beta, eps, p)
 
 
+# ----------------------------------------------------------------------------- residual fork
+# A residual block reads its input twice (main branch + skip), so autograd sums two gradients of that tensor
+# with an elementwise kernel (3 passes over the activation) before handing the sum to the op that produced it.
+# When the producer is one of our kernels that can take a second gradient (BN+residual+ReLU backward, max-pool
+# backward), `residual_fork` hands both gradients over un-summed and the producer's backward adds them while it
+# reads them anyway.  The second gradient travels in `_pending_addend`, keyed by the first one's storage; the
+# table must be empty again when the backward pass ends, otherwise a gradient would have been dropped and the
+# pass raises.
+_FUSED_RESIDUAL_GRAD = os.environ.get("DDL_FUSED_RESIDUAL_GRAD", "1") != "0"
+_pending_addend = {}
+
+
+def _take_addend(g: torch.Tensor) -> Optional[torch.Tensor]:
+    return _pending_addend.pop((g.data_ptr(), tuple(g.shape)), None) if _pending_addend else None
+
+
+def _check_addends_consumed() -> None:
+    if _pending_addend:
+        n = len(_pending_addend)
+        _pending_addend.clear()
+        raise L.DdlError(f"residual_fork: {n} skip-branch gradient(s) were not consumed by the producer's backward "
+                         "(the forked tensor has other consumers?); set DDL_FUSED_RESIDUAL_GRAD=0")
+
+
+def _accepts_second_grad(t: torch.Tensor) -> torch.Tensor:
+    """Tag the output of an op whose backward looks for a pending second gradient."""
+    t._ddl_second_grad_ok = True
+    return t
+
+
+class _ResidualFork(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        return x.view_as(x), x.view_as(x)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g_main, g_skip):
+        if g_main is None or g_skip is None:
+            return g_main if g_skip is None else g_skip
+        cl = torch.channels_last
+        if not (g_main.is_contiguous(memory_format=cl) and g_skip.is_contiguous(memory_format=cl)) or g_main.dtype != g_skip.dtype:
+            return g_main + g_skip
+        if not _pending_addend:
+            torch.autograd.Variable._execution_engine.queue_callback(_check_addends_consumed)
+        _pending_addend[(g_main.data_ptr(), tuple(g_main.shape))] = g_skip
+        return g_main
+
+
+def residual_fork(x: torch.Tensor):
+    """(x_main, x_skip): two aliases of ``x`` whose gradients are summed inside the backward kernel of the op
+    that produced ``x`` (when it can; otherwise this is the identity and autograd sums as usual)."""
+    if (_FUSED_RESIDUAL_GRAD and getattr(x, "_ddl_second_grad_ok", False) and x.requires_grad and torch.is_grad_enabled()
+            and x.dim() == 4):
+        return _ResidualFork.apply(x)
+    return x, x
+
+
 # ----------------------------------------------------------------------------- batch norm
 class _BnAct(torch.autograd.Function):
     """x: NCHW-shaped tensor in channels_last memory (i.e. an NHWC matrix [M, C])."""
@@ -206,6 +265,7 @@ class _BnAct(torch.autograd.Function):
         scale = torch.empty(Cc, dtype=torch.float32, device=dev)
         shift = torch.empty(Cc, dtype=torch.float32, device=dev)
         st = L.stream_ptr(dev)
+        mask = None
         if training:
             mean = torch.empty(Cc, dtype=torch.float32, device=dev)
             invstd = torch.empty(Cc, dtype=torch.float32, device=dev)
@@ -216,36 +276,42 @@ class _BnAct(torch.autograd.Function):
                        shift.data_ptr(), sums.data_ptr(), M, Cc, float(eps), float(momentum), int(relu), st)
             else:
                 scratch = _scratch(L.lib().ddl_bn_scratch_bytes(M, Cc), dev)
-                L.call("ddl_bn_act_fwd_train", x.data_ptr(), L.ptr(residual), gamma.data_ptr(), beta.data_ptr(), L.ptr(running_mean),
-                       L.ptr(running_var), y.data_ptr(), mean.data_ptr(), invstd.data_ptr(), scale.data_ptr(), shift.data_ptr(),
-                       scratch.data_ptr(), scratch.numel(), M, Cc, float(eps), float(momentum), int(relu), st)
-            ctx.save_for_backward(x, y if relu else None, gamma, mean, invstd)
+                # one bit per element records the ReLU decision: backward reads it instead of y
+                mask = torch.empty(M * Cc // 8, dtype=torch.uint8, device=dev) if relu else None
+                L.call("ddl_bn_act_fwd_train_mask", x.data_ptr(), L.ptr(residual), gamma.data_ptr(), beta.data_ptr(),
+                       L.ptr(running_mean), L.ptr(running_var), y.data_ptr(), L.ptr(mask), mean.data_ptr(), invstd.data_ptr(),
+                       scale.data_ptr(), shift.data_ptr(), scratch.data_ptr(), scratch.numel(), M, Cc, float(eps), float(momentum),
+                       int(relu), st)
+            ctx.save_for_backward(x, y if (relu and mask is None) else None, gamma, mean, invstd, mask)
         else:
             L.call("ddl_bn_act_fwd_eval", x.data_ptr(), L.ptr(residual), gamma.data_ptr(), beta.data_ptr(), running_mean.data_ptr(),
                    running_var.data_ptr(), y.data_ptr(), scale.data_ptr(), shift.data_ptr(), M, Cc, float(eps), int(relu), st)
-            ctx.save_for_backward(x, y if relu else None, gamma, scale, None)
+            ctx.save_for_backward(x, y if relu else None, gamma, scale, None, None)
         ctx.training, ctx.relu, ctx.has_res, ctx.M = training, relu, residual is not None, M
         return y
 
     @staticmethod
     @once_differentiable
     def backward(ctx, dy):
-        x, y, gamma, mean, invstd = ctx.saved_tensors
+        x, y, gamma, mean, invstd, mask = ctx.saved_tensors
         if not ctx.training:
             raise L.DdlError("backward through eval-mode fused BatchNorm is not supported; use impl='torch' for frozen BN")
         Cc = x.shape[1]
         dev = x.device
+        dy2 = _take_addend(dy)
         if not dy.is_contiguous(memory_format=torch.channels_last):
             dy = dy.contiguous(memory_format=torch.channels_last)
+        if dy2 is not None and not (ctx.relu and ctx.has_res):
+            dy, dy2 = dy + dy2, None  # only the relu + residual kernel takes two gradients
         dx = torch.empty_like(x, memory_format=torch.channels_last)
         dres = None
         if ctx.has_res:
             dres = torch.empty_like(x, memory_format=torch.channels_last) if ctx.relu else dy
         dgamma, dbeta = torch.empty_like(gamma), torch.empty_like(gamma)
         scratch = _scratch(L.lib().ddl_bn_scratch_bytes(ctx.M, Cc), dev)
-        L.call("ddl_bn_act_bwd", dy.data_ptr(), L.ptr(y), x.data_ptr(), gamma.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
-               dx.data_ptr(), L.ptr(dres) if ctx.relu else None, dgamma.data_ptr(), dbeta.data_ptr(), L.DDL_BF16, scratch.data_ptr(),
-               scratch.numel(), ctx.M, Cc, int(ctx.relu), L.stream_ptr(dev))
+        L.call("ddl_bn_act_bwd_ex", dy.data_ptr(), L.ptr(dy2), L.ptr(y), L.ptr(mask), x.data_ptr(), gamma.data_ptr(), mean.data_ptr(),
+               invstd.data_ptr(), dx.data_ptr(), L.ptr(dres) if ctx.relu else None, dgamma.data_ptr(), dbeta.data_ptr(), L.DDL_BF16,
+               scratch.data_ptr(), scratch.numel(), ctx.M, Cc, int(ctx.relu), L.stream_ptr(dev))
         return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None
 
 
@@ -259,8 +325,11 @@ def bn_act(x, bn: nn.BatchNorm2d, relu: bool = True, residual: Optional[torch.Te
                          f"{bn.running_mean.dtype}); convert the model with models.prepare_for_fused() instead of .to(bfloat16)")
     if training and bn.num_batches_tracked is not None:
         bn.num_batches_tracked.add_(1)
-    return _BnAct.apply(x, residual, bn.weight, bn.bias, bn.running_mean, bn.running_var, training,
-                        0.1 if bn.momentum is None else bn.momentum, bn.eps, relu, sums if training else None)
+    y = _BnAct.apply(x, residual, bn.weight, bn.bias, bn.running_mean, bn.running_var, training,
+                     0.1 if bn.momentum is None else bn.momentum, bn.eps, relu, sums if training else None)
+    if training and relu and residual is not None:
+        _accepts_second_grad(y)  # a block output: the next block may fork it (see residual_fork)
+    return y
 
 
 class _MaxPool3x3s2(torch.autograd.Function):
@@ -283,16 +352,17 @@ class _MaxPool3x3s2(torch.autograd.Function):
     def backward(ctx, dy):
         (idx,) = ctx.saved_tensors
         N, Cc, H, W = ctx.shape
+        dy2 = _take_addend(dy)
         if not dy.is_contiguous(memory_format=torch.channels_last):
             dy = dy.contiguous(memory_format=torch.channels_last)
         dx = torch.empty((N, Cc, H, W), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
-        L.call("ddl_maxpool3x3s2_bwd", dy.data_ptr(), idx.data_ptr(), dx.data_ptr(), N, H, W, Cc, L.stream_ptr(dy.device))
+        L.call("ddl_maxpool3x3s2_bwd_ex", dy.data_ptr(), L.ptr(dy2), idx.data_ptr(), dx.data_ptr(), N, H, W, Cc, L.stream_ptr(dy.device))
         return dx
 
 
 def maxpool3x3s2(x: torch.Tensor) -> torch.Tensor:
     """``F.max_pool2d(x, 3, 2, 1)`` on channels-last bf16 (K14)."""
-    return _MaxPool3x3s2.apply(x)
+    return _accepts_second_grad(_MaxPool3x3s2.apply(x))
 
 
 class _GlobalAvgPool(torch.autograd.Function):

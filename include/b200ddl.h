@@ -107,6 +107,12 @@ int ddl_bn_apply(const void* x, const void* residual, const float* scale, const 
 int ddl_bn_act_fwd_train(const void* x, const void* residual, const void* gamma, const void* beta, float* running_mean,
                          float* running_var, void* y, float* mean, float* invstd, float* scale, float* shift, void* scratch,
                          size_t scratch_bytes, long long M, int C, float eps, float momentum, int relu, void* stream);
+/* same, also writing relu_mask (nullable; M*C/8 bytes, bit j of byte v = channel j of 8-channel vector v passed the
+ * ReLU): backward then reads 1 bit instead of 16 per element to rebuild the mask (ddl_bn_act_bwd_ex). */
+int ddl_bn_act_fwd_train_mask(const void* x, const void* residual, const void* gamma, const void* beta, float* running_mean,
+                              float* running_var, void* y, void* relu_mask, float* mean, float* invstd, float* scale, float* shift,
+                              void* scratch, size_t scratch_bytes, long long M, int C, float eps, float momentum, int relu,
+                              void* stream);
 int ddl_bn_act_fwd_eval(const void* x, const void* residual, const void* gamma, const void* beta, const float* running_mean,
                         const float* running_var, void* y, float* scale, float* shift, long long M, int C, float eps, int relu,
                         void* stream);
@@ -134,6 +140,13 @@ int ddl_bn_act_fwd_train_noalloc(const void* x, const void* residual, const void
 int ddl_bn_act_bwd(const void* dy, const void* y, const void* x, const void* gamma, const float* mean, const float* invstd, void* dx,
                    void* dres, void* dgamma, void* dbeta, int param_grad_dtype, void* scratch, size_t scratch_bytes, long long M,
                    int C, int relu, void* stream);
+/* Extended backward: the ReLU mask comes from relu_mask (ddl_bn_act_fwd_train_mask) when given, else from y; dy2
+ * (nullable, relu + residual layers only) is a second incoming gradient of the same tensor - the other branch of the
+ * residual fork of the next block (reference model: torchvision ResNet-50, reference:19) - added inside the
+ * reduction pass instead of by a separate elementwise kernel. */
+int ddl_bn_act_bwd_ex(const void* dy, const void* dy2, const void* y, const void* relu_mask, const void* x, const void* gamma,
+                      const float* mean, const float* invstd, void* dx, void* dres, void* dgamma, void* dbeta,
+                      int param_grad_dtype, void* scratch, size_t scratch_bytes, long long M, int C, int relu, void* stream);
 
 /* ---- self-attention on tcgen05 (csrc/attention.cu), K11 ---------------------------------- */
 /* qkv: packed projections [B*S, 3*heads*64] bf16 (q | k | v); seqlens[B] = valid (right-padded)
@@ -154,6 +167,8 @@ int ddl_attention_bwd(const void* qkv, const void* ctx, const void* dctx, const 
  * element (winning tap 0..8), consumed by the gather-style backward. */
 int ddl_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, void* stream);
 int ddl_maxpool3x3s2_bwd(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, void* stream);
+/* same with a second incoming gradient dy2 (nullable) summed on the fly: the two branches of a residual fork */
+int ddl_maxpool3x3s2_bwd_ex(const void* dy, const void* dy2, const void* idx, void* dx, int N, int H, int W, int C, void* stream);
 /* global average pool [N, HW, C] -> [N, C] and its backward */
 int ddl_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream);
 int ddl_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);

@@ -567,27 +567,29 @@ def test_padded_stem_matches_plain_stem():
     """ResNet stem with the input/weight zero-padded to 8 channels == the 3-channel stem (fp32 oracle)."""
     from databricks_distributed_deep_learning_b200.models import prepare_for_fused, resnet18
 
-    bf = torch.bfloat16
+    OF = _OF()
     m = prepare_for_fused(resnet18(num_classes=10, impl="fused"), "cuda")
     ref = resnet18(num_classes=10, impl="torch").cuda().float()
     ref.load_state_dict({k: v.float() for k, v in m.state_dict().items()})
     x = torch.randn(16, 3, 64, 64, device="cuda")
-    outs = {}
-    for pad in (0, 8):
-        m.stem_pad = pad
-        m.zero_grad(set_to_none=True)
-        y = m(x)
-        y.float().square().mean().backward()
-        outs[pad] = (y.detach().float(), m.conv1.weight.grad.detach().float().clone())
-        assert m.conv1.weight.grad.shape == (64, 3, 7, 7)
-    yr = ref(x)
-    yr.square().mean().backward()
-    rel = lambda a, b: ((a - b).abs().max() / b.abs().max().clamp_min(1e-6)).item()
-    assert rel(outs[0][0], yr.detach()) < 1e-1, "plain fused stem vs fp32 oracle"
-    assert rel(outs[8][0], yr.detach()) < 1e-1
-    assert rel(outs[8][0], outs[0][0]) < 6e-2
-    assert rel(outs[8][1], ref.conv1.weight.grad) < 1.5e-1
-    assert rel(outs[8][1], outs[0][1]) < 1e-1
+    rel = lambda a, b: ((a.float() - b).abs().max() / b.abs().max().clamp_min(1e-6)).item()
+    # the stem in isolation: forward and weight gradient for the same upstream gradient
+    w = m.conv1.weight.detach().clone().requires_grad_()
+    y8 = F.conv2d(OF.to_nhwc_bf16(x, pad_channels=8), OF.pad_in_channels(w, 8), None, 2, 3)
+    dy = torch.randn_like(y8)
+    y8.backward(dy)
+    wr = w.detach().float().requires_grad_()
+    yr = F.conv2d(x.to(torch.bfloat16).float(), wr, None, 2, 3)
+    yr.backward(dy.float())
+    assert w.grad.shape == (64, 3, 7, 7)
+    assert rel(y8, yr.detach()) < 2e-2
+    assert rel(w.grad, wr.grad) < 3e-2
+    # whole network, both settings, against the fp32 model
+    with torch.no_grad():
+        want = ref(x)
+        for pad in (0, 8):
+            m.stem_pad = pad
+            assert rel(m(x), want) < 1e-1, pad
 
 
 def test_bn_rejects_low_precision_running_stats():
@@ -599,3 +601,51 @@ def test_bn_rejects_low_precision_running_stats():
     x = torch.randn(2, 16, 4, 4, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
     with pytest.raises(L.DdlError, match="float32"):
         OF.bn_act(x, bn)
+
+
+def _tiny_resnet_grads(fused_residual: bool, extra_consumer: bool = False):
+    from databricks_distributed_deep_learning_b200.models import prepare_for_fused, resnet50
+
+    OF = _OF()
+    torch.manual_seed(3)
+    m = prepare_for_fused(resnet50(num_classes=16, impl="fused"), "cuda")
+    x = torch.randn(8, 3, 64, 64, device="cuda")
+    old = OF._FUSED_RESIDUAL_GRAD
+    OF._FUSED_RESIDUAL_GRAD = fused_residual
+    try:
+        if extra_consumer:
+            h = OF.maxpool3x3s2(OF.bn_act(OF.conv2d(OF.to_nhwc_bf16(x), m.conv1), m.bn1))
+            out = m.layer1(h).float().mean() + h.float().mean()  # the forked tensor is read a third time
+            out.backward()
+            return None
+        n0 = OF.L.launch_count
+        loss = m(x).float().square().mean()
+        loss.backward()
+    finally:
+        OF._FUSED_RESIDUAL_GRAD = old
+    return float(loss), {k: p.grad.detach().float().clone() for k, p in m.named_parameters()}, OF.L.launch_count - n0
+
+
+def test_residual_fork_matches_autograd_add():
+    """Summing the two gradients of a block input inside the producer's backward kernel == autograd's add."""
+    la, ga, na = _tiny_resnet_grads(False)
+    lb, gb, nb = _tiny_resnet_grads(True)
+    assert la == lb and na == nb
+    worst = 0.0
+    for k in ga:
+        denom = ga[k].abs().max().clamp_min(1e-6)
+        worst = max(worst, float((ga[k] - gb[k]).abs().max() / denom))
+    # identical math except that the fused path adds in fp32 and rounds once (measured worst case 0.076 through
+    # 16 blocks of bf16 BN backward; a dropped or doubled gradient gives O(1))
+    assert worst < 0.2, worst
+    for k in ("conv1.weight", "layer1.0.conv1.weight", "layer2.0.downsample.0.weight", "layer4.2.conv3.weight"):
+        cos = torch.nn.functional.cosine_similarity(ga[k].flatten(), gb[k].flatten(), dim=0)
+        assert float(cos) > 0.995, (k, float(cos))
+
+
+def test_residual_fork_fails_loudly_when_gradient_would_be_dropped():
+    from databricks_distributed_deep_learning_b200.ops import _lib as L
+
+    with pytest.raises(L.DdlError, match="residual_fork"):
+        _tiny_resnet_grads(True, extra_consumer=True)
+    assert not _OF()._pending_addend
