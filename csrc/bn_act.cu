@@ -416,6 +416,21 @@ DDL_API int ddl_bn_act_fwd_train(const void* x, const void* residual, const void
                                      scratch_bytes, M, C, eps, momentum, relu, stream_);
 }
 
+// statistics already available as per-block partials [nblocks][2][C] (e.g. written by the stem convolution's epilogue)
+DDL_API int ddl_bn_act_fwd_train_from_partials(const void* x, const void* residual, const void* gamma, const void* beta,
+                                               float* running_mean, float* running_var, void* y, void* relu_mask, float* mean,
+                                               float* invstd, float* scale, float* shift, const float* partials, int nblocks,
+                                               long long M, int C, float eps, float momentum, int relu, void* stream_) {
+    BnGeom g;
+    if (int e = make_geom(M, C, &g)) return e;
+    DDL_REQUIRE(x && y && mean && invstd && scale && shift && partials && nblocks >= 1, "bn fwd (partials): null pointer");
+    cudaStream_t s = (cudaStream_t)stream_;
+    bn_fwd_finalize_kernel<<<ddl_ceil_div(C, 32), kFoldThreads, 0, s>>>(partials, nblocks, M, C, (const bf16*)gamma, (const bf16*)beta,
+                                                                        running_mean, running_var, momentum, eps, mean, invstd, scale, shift);
+    DDL_LAUNCH_CHECK();
+    return bn_apply_impl(x, residual, scale, shift, y, relu ? relu_mask : nullptr, M, C, relu, stream_);
+}
+
 DDL_API int ddl_bn_act_fwd_train_from_sums(const void* x, const void* residual, const void* gamma, const void* beta, float* running_mean,
                                            float* running_var, void* y, float* mean, float* invstd, float* scale, float* shift,
                                            const float* sums, long long M, int C, float eps, float momentum, int relu, void* stream_) {

@@ -154,6 +154,11 @@ class ResNet(nn.Module):
         if fused:
             from ..ops import functional as OF
 
+            if OF.stem_usable(x, self.conv1):
+                # native stem: space-to-depth + tcgen05 implicit GEMM, BatchNorm statistics from its epilogue
+                y, partials = OF.stem_conv(x, self.conv1.weight)
+                x = OF.bn_act(y, self.bn1, relu=True, partials=partials)
+                return self._trunk(x, fused)
             x = OF.to_nhwc_bf16(x, pad_channels=self.stem_pad)
             if x.shape[1] != self.conv1.in_channels:
                 # input zero-padded to 8 channels: pad the 3-channel stem weight the same way
@@ -164,6 +169,11 @@ class ResNet(nn.Module):
                 x = _conv_bn_act(x, self.conv1, self.bn1, True, None, self.impl)
         else:
             x = _conv_bn_act(x, self.conv1, self.bn1, True, None, self.impl)
+        return self._trunk(x, fused)
+
+    def _trunk(self, x, fused: bool):
+        if fused:
+            from ..ops import functional as OF
         if not self.small_input:
             x = OF.maxpool3x3s2(x) if fused else F.max_pool2d(x, 3, 2, 1)
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))

@@ -71,6 +71,14 @@ _PROTOS = {
     "ddl_bn_act_fwd_train_mask": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _ll, _i, _f, _f, _i, _vp], _i),
     "ddl_bn_act_bwd_ex": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _ll, _i, _i, _vp], _i),
     "ddl_maxpool3x3s2_bwd_ex": ([_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp], _i),
+    "ddl_bn_act_fwd_train_from_partials": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _ll, _i, _f, _f, _i, _vp], _i),
+    "ddl_stem_z_bytes": ([_i, _i, _i], _sz),
+    "ddl_stem_fwd_grid": ([_i, _i, _i], _i),
+    "ddl_stem_wgrad_grid": ([_i, _i, _i], _i),
+    "ddl_stem_wgrad_scratch_bytes": ([_i, _i, _i], _sz),
+    "ddl_stem_s2d": ([_vp, _i, _vp, _i, _i, _i, _vp], _i),
+    "ddl_stem_conv_fwd": ([_vp, _vp, _ll, _ll, _ll, _ll, _vp, _vp, _vp, _i, _i, _i, _vp], _i),
+    "ddl_stem_conv_wgrad": ([_vp, _vp, _vp, _ll, _ll, _ll, _ll, _vp, _sz, _i, _i, _i, _vp], _i),
     "ddl_attention_fwd": ([_vp, _vp, _vp, _vp, _i, _i, _i, _f, _u64, _vp, _vp], _i),
     "ddl_attention_bwd_scratch_bytes": ([_i, _i, _i], _sz),
     "ddl_attention_bwd": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i, _i, _i, _f, _u64, _vp, _vp], _i),

@@ -252,7 +252,7 @@ class _BnAct(torch.autograd.Function):
     """x: NCHW-shaped tensor in channels_last memory (i.e. an NHWC matrix [M, C])."""
 
     @staticmethod
-    def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu, sums=None):
+    def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu, sums=None, partials=None):
         _req_bf16(x, residual, gamma, beta)
         N, Cc, H, W = x.shape
         if not x.is_contiguous(memory_format=torch.channels_last):
@@ -269,7 +269,14 @@ class _BnAct(torch.autograd.Function):
         if training:
             mean = torch.empty(Cc, dtype=torch.float32, device=dev)
             invstd = torch.empty(Cc, dtype=torch.float32, device=dev)
-            if sums is not None:
+            if partials is not None:
+                # per-CTA partial statistics written by the stem convolution's epilogue: no extra pass over x
+                mask = torch.empty(M * Cc // 8, dtype=torch.uint8, device=dev) if relu else None
+                L.call("ddl_bn_act_fwd_train_from_partials", x.data_ptr(), L.ptr(residual), gamma.data_ptr(), beta.data_ptr(),
+                       L.ptr(running_mean), L.ptr(running_var), y.data_ptr(), L.ptr(mask), mean.data_ptr(), invstd.data_ptr(),
+                       scale.data_ptr(), shift.data_ptr(), partials.data_ptr(), partials.numel() // (2 * Cc), M, Cc, float(eps),
+                       float(momentum), int(relu), st)
+            elif sums is not None:
                 # statistics already produced by the convolution's GEMM epilogue: no extra pass over x
                 L.call("ddl_bn_act_fwd_train_from_sums", x.data_ptr(), L.ptr(residual), gamma.data_ptr(), beta.data_ptr(),
                        L.ptr(running_mean), L.ptr(running_var), y.data_ptr(), mean.data_ptr(), invstd.data_ptr(), scale.data_ptr(),
@@ -312,11 +319,11 @@ class _BnAct(torch.autograd.Function):
         L.call("ddl_bn_act_bwd_ex", dy.data_ptr(), L.ptr(dy2), L.ptr(y), L.ptr(mask), x.data_ptr(), gamma.data_ptr(), mean.data_ptr(),
                invstd.data_ptr(), dx.data_ptr(), L.ptr(dres) if ctx.relu else None, dgamma.data_ptr(), dbeta.data_ptr(), L.DDL_BF16,
                scratch.data_ptr(), scratch.numel(), ctx.M, Cc, int(ctx.relu), L.stream_ptr(dev))
-        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None, None
 
 
 def bn_act(x, bn: nn.BatchNorm2d, relu: bool = True, residual: Optional[torch.Tensor] = None,
-           sums: Optional[torch.Tensor] = None) -> torch.Tensor:
+           sums: Optional[torch.Tensor] = None, partials: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``relu(batch_norm(x) + residual)`` with torch's training/eval semantics (running stats
     updated with the unbiased variance and ``bn.momentum``)."""
     training = bn.training or bn.running_mean is None
@@ -326,7 +333,8 @@ def bn_act(x, bn: nn.BatchNorm2d, relu: bool = True, residual: Optional[torch.Te
     if training and bn.num_batches_tracked is not None:
         bn.num_batches_tracked.add_(1)
     y = _BnAct.apply(x, residual, bn.weight, bn.bias, bn.running_mean, bn.running_var, training,
-                     0.1 if bn.momentum is None else bn.momentum, bn.eps, relu, sums if training else None)
+                     0.1 if bn.momentum is None else bn.momentum, bn.eps, relu, sums if training else None,
+                     partials if training else None)
     if training and relu and residual is not None:
         _accepts_second_grad(y)  # a block output: the next block may fork it (see residual_fork)
     return y
@@ -390,6 +398,64 @@ class _GlobalAvgPool(torch.autograd.Function):
 def global_avgpool(x: torch.Tensor) -> torch.Tensor:
     """``torch.flatten(F.adaptive_avg_pool2d(x, 1), 1)`` on channels-last bf16 -> [N, C]."""
     return _GlobalAvgPool.apply(x)
+
+
+# ----------------------------------------------------------------------------- stem convolution (tcgen05)
+_STEM_NATIVE = os.environ.get("DDL_STEM", "tcgen05") == "tcgen05"
+
+
+def stem_usable(x: torch.Tensor, conv: nn.Conv2d) -> bool:
+    """The native stem kernel takes the ResNet stem exactly: 7x7 / stride 2 / pad 3, 3 -> 64 channels, no bias, a
+    contiguous NCHW fp32/bf16 network input that needs no gradient, even H and W, W/2 a multiple of 16."""
+    if not (_STEM_NATIVE and x.is_cuda and x.dim() == 4 and x.shape[1] == 3 and x.is_contiguous() and not x.requires_grad
+            and x.dtype in (torch.float32, torch.bfloat16)):
+        return False
+    H, W = x.shape[2], x.shape[3]
+    return (conv.in_channels == 3 and conv.out_channels == 64 and conv.kernel_size == (7, 7) and conv.stride == (2, 2)
+            and conv.padding == (3, 3) and conv.dilation == (1, 1) and conv.groups == 1 and conv.bias is None
+            and conv.weight.dtype == torch.bfloat16 and H % 2 == 0 and W % 2 == 0 and H >= 8 and (W // 2) % 16 == 0 and W // 2 <= 256)
+
+
+class _StemConv(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight):
+        N, _, H, W = x.shape
+        dev = x.device
+        lib = L.lib()
+        st = L.stream_ptr(dev)
+        z = torch.empty(lib.ddl_stem_z_bytes(N, H, W) // 2, dtype=torch.bfloat16, device=dev)
+        L.call("ddl_stem_s2d", x.data_ptr(), L.dtype_code(x.dtype), z.data_ptr(), N, H, W, st)
+        y = torch.empty((N, 64, H // 2, W // 2), dtype=torch.bfloat16, device=dev, memory_format=torch.channels_last)
+        partials = torch.empty(lib.ddl_stem_fwd_grid(N, H, W) * 2 * 64, dtype=torch.float32, device=dev)
+        w2 = torch.empty(4 * 64 * 64, dtype=torch.bfloat16, device=dev)
+        L.call("ddl_stem_conv_fwd", z.data_ptr(), weight.data_ptr(), *weight.stride(), w2.data_ptr(), y.data_ptr(), partials.data_ptr(),
+               N, H, W, st)
+        ctx.save_for_backward(z)
+        ctx.geom = (N, H, W)
+        ctx.wlike = weight  # only its shape / strides are used
+        ctx.mark_non_differentiable(partials)
+        return y, partials
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy, _unused):
+        (z,) = ctx.saved_tensors
+        N, H, W = ctx.geom
+        dev = z.device
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dw = torch.empty_like(ctx.wlike)
+        scratch = _scratch(L.lib().ddl_stem_wgrad_scratch_bytes(N, H, W), dev)
+        L.call("ddl_stem_conv_wgrad", z.data_ptr(), dy.data_ptr(), dw.data_ptr(), *dw.stride(), scratch.data_ptr(), scratch.numel(),
+               N, H, W, L.stream_ptr(dev))
+        return None, dw
+
+
+def stem_conv(x: torch.Tensor, weight: torch.Tensor):
+    """``F.conv2d(x, weight, stride=2, padding=3)`` for the 3 -> 64 channel 7x7 stem on the tcgen05 kernel
+    (``csrc/stem_conv.cu``).  Returns ``(y, partials)``: y is NHWC bf16 (NCHW-shaped, channels-last), ``partials`` the
+    per-CTA BatchNorm statistics of y for :func:`bn_act` (``partials=``)."""
+    return _StemConv.apply(x, weight)
 
 
 def to_nhwc_bf16(x: torch.Tensor, pad_channels: int = 0) -> torch.Tensor:

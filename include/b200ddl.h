@@ -121,6 +121,11 @@ int ddl_bn_act_fwd_eval(const void* x, const void* residual, const void* gamma, 
 int ddl_bn_act_fwd_train_from_sums(const void* x, const void* residual, const void* gamma, const void* beta, float* running_mean,
                                    float* running_var, void* y, float* mean, float* invstd, float* scale, float* shift,
                                    const float* sums, long long M, int C, float eps, float momentum, int relu, void* stream);
+/* same with per-block partial statistics [nblocks][2][C] (written by ddl_stem_conv_fwd) and the optional relu_mask */
+int ddl_bn_act_fwd_train_from_partials(const void* x, const void* residual, const void* gamma, const void* beta, float* running_mean,
+                                       float* running_var, void* y, void* relu_mask, float* mean, float* invstd, float* scale,
+                                       float* shift, const float* partials, int nblocks, long long M, int C, float eps,
+                                       float momentum, int relu, void* stream);
 /* Allocation-free variant of ddl_bn_act_fwd_train: same arguments minus the scratch buffer.
  * No counterpart in the reference (it has no native code at all).  It exists for callers
  * that cannot allocate device memory - a process whose own arena already owns the whole
@@ -175,6 +180,23 @@ int ddl_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream
 /* network input [N, C, HW] (x_dtype DDL_F32 / DDL_BF16, C <= 8) -> [N, HW, 8] bf16, channels C..7 zero: the stem
  * convolution of the reference's ResNet-50 (reference:19) then has 8 input channels and runs on tensor cores */
 int ddl_nchw_to_nhwc8_bf16(const void* x, int x_dtype, void* y, int N, int C, long long HW, void* stream);
+
+/* ---- ResNet stem convolution on tcgen05 (csrc/stem_conv.cu), K9 ---------------------------
+ * 7x7 / stride 2 / pad 3, 3 -> 64 channels (torchvision resnet50 conv1, reference:19) as a 4x4 convolution over the
+ * space-to-depth input z [N, H/2+3, W/2+3, 16] bf16; the im2col tiles are fetched by TMA through a tensor map with
+ * overlapping rows.  H, W even.  w / dw: bf16 [64, 3, 7, 7] addressed with element strides (sk, sc, sr, ss), so both
+ * contiguous and channels-last weights work.  w2: 32 KB scratch for the packed weights.  y: [N, H/2, W/2, 64] bf16 NHWC.
+ * partials: fp32 [ddl_stem_fwd_grid][2][64] per-CTA BatchNorm statistics of y (feed ddl_bn_act_fwd_train_from_partials). */
+size_t ddl_stem_z_bytes(int N, int H, int W);
+int ddl_stem_fwd_grid(int N, int H, int W);
+int ddl_stem_wgrad_grid(int N, int H, int W);
+size_t ddl_stem_wgrad_scratch_bytes(int N, int H, int W);
+int ddl_stem_s2d(const void* x, int x_dtype, void* z, int N, int H, int W, void* stream);
+int ddl_stem_conv_fwd(const void* z, const void* w, long long sk, long long sc, long long sr, long long ss, void* w2, void* y,
+                      float* partials, int N, int H, int W, void* stream);
+/* weight gradient from z and dy [N, H/2, W/2, 64]; W/2 must be a multiple of 16 (the reduction runs over whole output rows) */
+int ddl_stem_conv_wgrad(const void* z, const void* dy, void* dw, long long sk, long long sc, long long sr, long long ss,
+                        void* scratch, size_t scratch_bytes, int N, int H, int W, void* stream);
 
 /* ---- tcgen05 / TMEM / TMA GEMM (csrc/gemm_tcgen05.cu), K8 ------------------------------ */
 /* C[M,N] = epilogue(A . B^T), bf16 operands, fp32 accumulation in tensor memory.

@@ -649,3 +649,63 @@ def test_residual_fork_fails_loudly_when_gradient_would_be_dropped():
     with pytest.raises(L.DdlError, match="residual_fork"):
         _tiny_resnet_grads(True, extra_consumer=True)
     assert not _OF()._pending_addend
+
+
+@pytest.mark.parametrize("N,H,W", [(4, 64, 64), (2, 224, 224), (3, 40, 96), (1, 8, 32)])
+def test_stem_conv_tcgen05_fwd_stats_wgrad(N, H, W):
+    """7x7/2 stem on the tcgen05 implicit GEMM (space-to-depth + overlapping-row TMA im2col) vs F.conv2d in fp32."""
+    OF = _OF()
+    bf = torch.bfloat16
+    conv = torch.nn.Conv2d(3, 64, 7, 2, 3, bias=False).cuda().to(bf).to(memory_format=torch.channels_last)
+    x = torch.randn(N, 3, H, W, device="cuda")
+    assert OF.stem_usable(x, conv)
+    w = conv.weight.detach().clone().requires_grad_()
+    assert w.is_contiguous(memory_format=torch.channels_last)
+    y, partials = OF.stem_conv(x, w)
+    assert y.shape == (N, 64, H // 2, W // 2) and y.is_contiguous(memory_format=torch.channels_last)
+    wr = w.detach().float().requires_grad_()
+    yr = F.conv2d(x.to(bf).float(), wr, None, 2, 3)
+    rel = lambda a, b: ((a.float() - b).abs().max() / b.abs().max().clamp_min(1e-6)).item()
+    assert rel(y, yr.detach()) < 1e-2, rel(y, yr.detach())
+    # BatchNorm statistics from the epilogue == sums over the (rounded) output
+    st = partials.view(-1, 2, 64).sum(0)
+    yf = y.float()
+    torch.testing.assert_close(st[0], yf.sum((0, 2, 3)), rtol=2e-3, atol=2e-2)
+    torch.testing.assert_close(st[1], yf.square().sum((0, 2, 3)), rtol=2e-3, atol=2e-2)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    yr.backward(dy.float())
+    assert w.grad.shape == (64, 3, 7, 7) and w.grad.stride() == w.stride()
+    assert rel(w.grad, wr.grad) < 1e-2, rel(w.grad, wr.grad)
+    # NCHW-contiguous weights go through the same kernels via their strides
+    w2 = conv.weight.detach().contiguous().clone().requires_grad_()
+    y2, _ = OF.stem_conv(x, w2)
+    assert torch.equal(y2, y)
+    y2.backward(dy)
+    assert torch.equal(w2.grad, w.grad)
+
+
+def test_resnet50_native_stem_matches_library_stem():
+    from databricks_distributed_deep_learning_b200.models import prepare_for_fused, resnet50
+
+    OF = _OF()
+    m = prepare_for_fused(resnet50(num_classes=16, impl="fused"), "cuda")
+    x = torch.randn(8, 3, 64, 64, device="cuda")
+    outs = []
+    for native in (True, False):
+        old = OF._STEM_NATIVE
+        OF._STEM_NATIVE = native
+        try:
+            m.zero_grad(set_to_none=True)
+            m.bn1.reset_running_stats()
+            y = m(x)
+            y.float().square().mean().backward()
+            outs.append((y.detach().float(), m.conv1.weight.grad.detach().float().clone(), m.bn1.running_var.clone()))
+        finally:
+            OF._STEM_NATIVE = old
+    # 50 layers of bf16 with batch statistics over a handful of elements amplify rounding differences of the first
+    # layer; the statistics of that layer itself must agree closely
+    cosf = lambda a, b: float(torch.nn.functional.cosine_similarity(a.flatten(), b.flatten(), dim=0))
+    torch.testing.assert_close(outs[0][2], outs[1][2], rtol=5e-3, atol=1e-4)
+    assert cosf(outs[0][0], outs[1][0]) > 0.98, cosf(outs[0][0], outs[1][0])
+    assert cosf(outs[0][1], outs[1][1]) > 0.98, cosf(outs[0][1], outs[1][1])
