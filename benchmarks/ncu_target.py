@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Short single-GPU programs for `ncu --set full` captures (one kernel family per mode).
 
-    python benchmarks/ncu_target.py gemm|attention|bn|ln|adamw
+    python benchmarks/ncu_target.py gemm|attention|bn|ln|adamw|stem
 """
 import os
 import sys
@@ -66,6 +66,14 @@ def main():
         hyper = torch.tensor([1e-3, 0.9, 0.999, 1e-8, 0.01, 1.0, 0, 0], device="cuda")
         for _ in range(3):
             L.call("ddl_adamw", gr.data_ptr(), 1, w.data_ptr(), m.data_ptr(), v.data_ptr(), p.data_ptr(), 1, n, hyper.data_ptr(), 1.0, L.stream_ptr())
+    elif mode == "stem":
+        from databricks_distributed_deep_learning_b200.ops import functional as OF
+
+        w = torch.randn(64, 3, 7, 7, device="cuda").to(bf).contiguous(memory_format=torch.channels_last).requires_grad_()
+        x = torch.randn(256, 3, 224, 224, device="cuda")
+        for _ in range(2):
+            y, _ = OF.stem_conv(x, w)
+            y.backward(torch.randn_like(y))
     torch.cuda.synchronize()
     print("ok", mode)
 

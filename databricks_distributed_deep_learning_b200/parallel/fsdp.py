@@ -24,6 +24,7 @@ On CPU / gloo (tests, BASELINE.json:7-style plumbing) the same schedule runs wit
 """
 from __future__ import annotations
 
+from contextlib import contextmanager
 from typing import Dict, Iterable, List, Optional, Sequence
 
 import torch
@@ -159,6 +160,7 @@ class FullyShardedDataParallel(nn.Module):
                 u.gathered_event = torch.cuda.Event()
         self._install_hooks(names)
         self._callback_queued = False
+        self._grads_detached = False
 
     # ------------------------------------------------------------------ plumbing
     def _broadcast(self, flat: torch.Tensor) -> None:
@@ -230,13 +232,8 @@ class FullyShardedDataParallel(nn.Module):
 
     def _grad_hook(self, p: nn.Parameter) -> None:
         u = self._param_unit[p]
-        v = u.grad_views[u.param_index[id(p)]]
-        if p.grad is not None and p.grad.data_ptr() != v.data_ptr():
-            # autograd re-allocated the gradient (e.g. after set_to_none): move it into the flat buffer
-            v.copy_(p.grad)
-            p.grad = v
         if not self.require_backward_grad_sync:
-            return
+            return  # no_sync(): .grad stays where autograd put it and keeps accumulating
         if not self._callback_queued:
             torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
             self._callback_queued = True
@@ -244,8 +241,27 @@ class FullyShardedDataParallel(nn.Module):
         if u.pending == 0 and not u.reduced:
             self._reduce_and_update(u)
 
+    @torch.no_grad()
+    def _gather_grads(self, u: _Unit) -> None:
+        """Move gradients that autograd allocated itself (after ``zero_grad(set_to_none=True)``) into the unit's
+        flat buffer with one multi-tensor copy; parameters without a gradient contribute zeros."""
+        src, dst = [], []
+        for p, v in zip(u.params, u.grad_views):
+            g = p.grad
+            if g is None:
+                if self._grads_detached:
+                    v.zero_()
+            elif g.data_ptr() != v.data_ptr():
+                src.append(g)
+                dst.append(v)
+            if g is not None or self._grads_detached:
+                p.grad = v
+        if src:
+            torch._foreach_copy_(dst, src)
+
     def _reduce_and_update(self, u: _Unit) -> None:
         u.reduced = True
+        self._gather_grads(u)
         if self.cuda:
             self._comm_stream.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(self._comm_stream):
@@ -278,13 +294,31 @@ class FullyShardedDataParallel(nn.Module):
         if self.cuda:
             torch.cuda.current_stream(self.device).wait_stream(self._comm_stream)
 
+    @contextmanager
+    def no_sync(self):
+        """Gradient accumulation: backward passes inside the context only accumulate into ``.grad``; the next
+        synchronised backward reduce-scatters the sum and applies the update (same surface as stock FSDP)."""
+        old = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = old
+
     # ------------------------------------------------------------------ optimizer surface
     @torch.no_grad()
     def zero_grad(self, set_to_none: bool = False) -> None:  # type: ignore[override]
+        """``set_to_none=True`` skips the memsets: autograd produces fresh gradients and each unit collects them
+        with one multi-tensor copy right before its reduce-scatter (same contract as the DDP wrapper)."""
+        self._grads_detached = bool(set_to_none)
         for u in self.units:
-            u.full_grad.zero_()
-            for p, v in zip(u.params, u.grad_views):
-                p.grad = v
+            if set_to_none:
+                for p in u.params:
+                    p.grad = None
+            else:
+                u.full_grad.zero_()
+                for p, v in zip(u.params, u.grad_views):
+                    p.grad = v
 
     @torch.no_grad()
     def step(self) -> None:

@@ -112,3 +112,26 @@ def test_fused_adamw_state_roundtrip_channels_last():
     opt2.load_state_dict(sd)
     torch.testing.assert_close(m2.conv.weight, m.conv.weight)
     torch.testing.assert_close(m2.fc.weight, m.fc.weight)
+
+
+def test_fsdp_set_to_none_matches_memset_path():
+    from databricks_distributed_deep_learning_b200.parallel.fsdp import FullyShardedDataParallel
+
+    def run(set_to_none: bool, accumulate: bool):
+        m = _model(False)
+        fsdp = FullyShardedDataParallel(m, lr=1e-2)
+        torch.manual_seed(1)
+        xs = [torch.randn(4, 3, 6, 6) for _ in range(3)]
+        for step in range(2):
+            fsdp.zero_grad(set_to_none=set_to_none)
+            if accumulate:
+                with fsdp.no_sync():
+                    fsdp(xs[0]).square().mean().backward()
+            fsdp(xs[1 + step]).square().mean().backward()
+            fsdp.step()
+        return {k: v.clone() for k, v in fsdp.full_state_dict().items()}
+
+    for acc in (False, True):
+        a, b = run(False, acc), run(True, acc)
+        for k in a:
+            torch.testing.assert_close(a[k], b[k], rtol=1e-5, atol=1e-6, msg=k)
