@@ -1,0 +1,109 @@
+#!/usr/bin/env python
+"""Per-layer timing of the ResNet-50 convolutions at per-GPU batch 256:
+library convolution (cuDNN through ATen, bf16 NHWC, benchmark mode) forward / dgrad / wgrad, against the
+memory and tensor-core floors, and - for the 1x1 / stride-1 layers - the tcgen05 GEMM route of this repo
+(forward with the BatchNorm-statistics epilogue, dgrad, wgrad).
+
+    python benchmarks/conv_bench.py [--batch 256] [--json gpurun_out/conv_bench.json]
+
+CUDA events, 3 warm-up + 10 timed runs per point, L2 flushed between runs by a 256 MB memset.
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+import torch.nn.functional as F
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+# (count, Cin, HW_in, Cout, k, stride)
+LAYERS = [
+    (1, 3, 224, 64, 7, 2), (1, 64, 56, 64, 1, 1), (3, 64, 56, 64, 3, 1), (4, 64, 56, 256, 1, 1), (2, 256, 56, 64, 1, 1),
+    (1, 256, 56, 128, 1, 1), (1, 128, 56, 128, 3, 2), (4, 128, 28, 512, 1, 1), (1, 256, 56, 512, 1, 2), (3, 512, 28, 128, 1, 1),
+    (3, 128, 28, 128, 3, 1), (1, 512, 28, 256, 1, 1), (1, 256, 28, 256, 3, 2), (6, 256, 14, 1024, 1, 1), (1, 512, 28, 1024, 1, 2),
+    (5, 1024, 14, 256, 1, 1), (5, 256, 14, 256, 3, 1), (1, 1024, 14, 512, 1, 1), (1, 512, 14, 512, 3, 2), (3, 512, 7, 2048, 1, 1),
+    (1, 1024, 14, 2048, 1, 2), (2, 2048, 7, 512, 1, 1), (2, 512, 7, 512, 3, 1),
+]
+
+
+def timeit(fn, flush, iters=10, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b) * 1e3)
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--batch", type=int, default=256)
+    ap.add_argument("--json", default=os.path.join(ROOT, "gpurun_out", "conv_bench.json"))
+    args = ap.parse_args()
+    from databricks_distributed_deep_learning_b200.ops import gemm as G
+
+    torch.backends.cudnn.benchmark = True
+    dev = torch.device("cuda")
+    bf = torch.bfloat16
+    peaks = {"hbm_gbs": 6551.4, "bf16_tflops": 1397.3}
+    try:
+        peaks.update({k: v for k, v in json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).items() if k in ("hbm_gbs",)})
+        peaks["bf16_tflops"] = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"]
+    except Exception:
+        pass
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    N = args.batch
+    rows = []
+    tot = {"cudnn_fwd": 0.0, "cudnn_dgrad": 0.0, "cudnn_wgrad": 0.0, "floor": 0.0}
+    print(f"{'layer':32s} {'x':>2s} {'fwd':>8s} {'dgrad':>8s} {'wgrad':>8s} {'floor':>7s} | {'g.fwd':>8s} {'g.dgrad':>8s} {'g.wgrad':>8s}   (us per call)")
+    for cnt, cin, hw, cout, k, s in LAYERS:
+        pad = k // 2
+        x = torch.randn(N, cin, hw, hw, device=dev).to(bf).contiguous(memory_format=torch.channels_last)
+        w = torch.randn(cout, cin, k, k, device=dev).to(bf).contiguous(memory_format=torch.channels_last)
+        y = F.conv2d(x, w, None, s, pad)
+        dy = torch.randn_like(y).contiguous(memory_format=torch.channels_last)
+        ho = y.shape[2]
+        t_f = timeit(lambda: F.conv2d(x, w, None, s, pad), flush)
+        t_d = timeit(lambda: torch.ops.aten.convolution_backward(dy, x, w, None, (s, s), (pad, pad), (1, 1), False, (0, 0), 1, (True, False, False)), flush) if cin > 3 else 0.0
+        t_w = timeit(lambda: torch.ops.aten.convolution_backward(dy, x, w, None, (s, s), (pad, pad), (1, 1), False, (0, 0), 1, (False, True, False)), flush)
+        flops = 2.0 * N * ho * ho * cout * cin * k * k
+        bytes_io = 2.0 * (x.numel() + y.numel())
+        floor = max(flops / (peaks["bf16_tflops"] * 1e12), bytes_io / (peaks["hbm_gbs"] * 1e9)) * 1e6
+        row = {"cin": cin, "hw": hw, "cout": cout, "k": k, "stride": s, "count": cnt, "cudnn_fwd_us": t_f, "cudnn_dgrad_us": t_d,
+               "cudnn_wgrad_us": t_w, "floor_us": floor, "gflop": flops / 1e9, "mbytes": bytes_io / 1e6}
+        g = ["", "", ""]
+        if k == 1 and s == 1:
+            M = N * hw * hw
+            x2, w2, dy2 = x.permute(0, 2, 3, 1).reshape(M, cin), w.reshape(cout, cin), dy.permute(0, 2, 3, 1).reshape(M, cout)
+            sums = torch.zeros(2, cout, dtype=torch.float32, device=dev)
+            row["gemm_fwd_us"] = timeit(lambda: G.gemm_nt(x2, w2, M, cout, cin, col_stats=sums), flush)
+            row["gemm_dgrad_us"] = timeit(lambda: G.gemm_nt(dy2, w2, M, cin, cout, b_mn=True), flush)
+            sk = G.pick_split_k(cout, cin, M)
+            row["gemm_wgrad_us"] = timeit(lambda: G.gemm_nt(dy2, x2, cout, cin, M, a_mn=True, b_mn=True, split_k=sk), flush)
+            g = [f"{row['gemm_fwd_us']:8.1f}", f"{row['gemm_dgrad_us']:8.1f}", f"{row['gemm_wgrad_us']:8.1f}"]
+        rows.append(row)
+        tot["cudnn_fwd"] += cnt * t_f
+        tot["cudnn_dgrad"] += cnt * t_d
+        tot["cudnn_wgrad"] += cnt * t_w
+        tot["floor"] += cnt * floor
+        name = f"{cin}x{hw}^2 -> {cout} k{k}/s{s}"
+        print(f"{name:32s} {cnt:2d} {t_f:8.1f} {t_d:8.1f} {t_w:8.1f} {floor:7.1f} | {g[0]:>8s} {g[1]:>8s} {g[2]:>8s}")
+        del x, w, y, dy
+    print("totals per step (ms):", {k: round(v / 1e3, 3) for k, v in tot.items()})
+    os.makedirs(os.path.dirname(args.json), exist_ok=True)
+    json.dump({"batch": N, "peaks": peaks, "rows": rows, "totals_ms": {k: v / 1e3 for k, v in tot.items()}}, open(args.json, "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()

@@ -93,7 +93,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 // forward
 // ------------------------------------------------------------------------------------------------
 template <int kMaxKvTiles>
-__global__ void __launch_bounds__(kMaxKvTiles == 1 ? 128 : 256, 1) attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
+__global__ void __launch_bounds__(kMaxKvTiles == 1 ? 128 : 256, kMaxKvTiles == 1 ? 4 : 1) attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
                                                                                   const AttnParams p) {
     constexpr int kHalves = kMaxKvTiles == 1 ? 1 : 2;
     extern __shared__ uint8_t smem_raw[];
@@ -109,8 +109,11 @@ __global__ void __launch_bounds__(kMaxKvTiles == 1 ? 128 : 256, 1) attn_fwd_kern
     const int q_tile = blockIdx.x, hd = blockIdx.y, b = blockIdx.z;
     const int kv_len = p.seqlens ? min(max(p.seqlens[b], 1), p.S) : p.S;
     const int n_kv = (kv_len + TILE - 1) / TILE;
-    constexpr uint32_t kTmemCols = kMaxKvTiles == 1 ? 256 : 512;
-    const uint32_t o_col = (kMaxKvTiles * TILE < 512) ? (uint32_t)(kMaxKvTiles * TILE) : 256u;
+    // One key tile: by the time O is produced, S (128 fp32 columns) has been consumed and P (bf16 pairs) sits in
+    // columns [0, 64), so O takes columns [64, 128): 128 TMEM columns per CTA instead of 256 -> four CTAs per SM
+    // (their serial TMA -> MMA -> softmax -> MMA chains overlap each other).
+    constexpr uint32_t kTmemCols = kMaxKvTiles == 1 ? 128 : 512;
+    const uint32_t o_col = kMaxKvTiles == 1 ? 64u : ((kMaxKvTiles * TILE < 512) ? (uint32_t)(kMaxKvTiles * TILE) : 256u);
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tma_qkv);
