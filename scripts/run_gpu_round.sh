@@ -1,4 +1,11 @@
 mkdir -p gpurun_out
-for mb in 0 16 32 64 128; do
-echo "max_mb=$mb"; DDL_CONV_BWD_OVERLAP_MAX_MB=$mb timeout 600 python bench.py --steps 30 --warmup 5 2>/dev/null | tail -1 | cut -c80-190
-done
+N=${NGPU:-8}
+run() { # impl workload
+  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 bench.py --gpus $N --impl $1 --workload $2 --steps 20 --warmup 5 > gpurun_out/t41_bench_$2_$1_${N}gpu.json 2> gpurun_out/t41_bench_$2_$1_${N}gpu.err
+  echo "rc=$? $1 $2"; tail -1 gpurun_out/t41_bench_$2_$1_${N}gpu.json | cut -c1-340
+}
+run ours resnet50
+run ours bert-base
+run ours bert-large
+run stock bert-base
+run stock bert-large
