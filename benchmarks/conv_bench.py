@@ -66,7 +66,7 @@ def main():
     N = args.batch
     rows = []
     tot = {"cudnn_fwd": 0.0, "cudnn_dgrad": 0.0, "cudnn_wgrad": 0.0, "floor": 0.0}
-    print(f"{'layer':32s} {'x':>2s} {'fwd':>8s} {'dgrad':>8s} {'wgrad':>8s} {'floor':>7s} | {'g.fwd':>8s} {'g.dgrad':>8s} {'g.wgrad':>8s}   (us per call)")
+    print(f"{'layer':32s} {'x':>2s} {'fwd':>8s} {'dgrad':>8s} {'wgrad':>8s} {'floor':>7s} | {'g.fwd':>8s} {'g.dgrad':>8s} {'g.wgrad':>8s} {'ws.fwd':>8s}   (us per call; ws.fwd = weight-stationary kernel incl. BN statistics)")
     for cnt, cin, hw, cout, k, s in LAYERS:
         pad = k // 2
         x = torch.randn(N, cin, hw, hw, device=dev).to(bf).contiguous(memory_format=torch.channels_last)
@@ -92,13 +92,21 @@ def main():
             sk = G.pick_split_k(cout, cin, M)
             row["gemm_wgrad_us"] = timeit(lambda: G.gemm_nt(dy2, x2, cout, cin, M, a_mn=True, b_mn=True, split_k=sk), flush)
             g = [f"{row['gemm_fwd_us']:8.1f}", f"{row['gemm_dgrad_us']:8.1f}", f"{row['gemm_wgrad_us']:8.1f}"]
+            from databricks_distributed_deep_learning_b200.ops import _lib as L
+
+            if L.lib().ddl_conv1x1_supported(M, cout, cin):
+                part = torch.empty(L.lib().ddl_conv1x1_grid(M, cout) * 2 * cout, dtype=torch.float32, device=dev)
+                yy = torch.empty(M, cout, dtype=bf, device=dev)
+                row["ws_fwd_stats_us"] = timeit(lambda: L.call("ddl_conv1x1_fwd", x2.data_ptr(), w2.data_ptr(), yy.data_ptr(), part.data_ptr(),
+                                                               M, cout, cin, L.stream_ptr(dev)), flush)
+                g.append(f"{row['ws_fwd_stats_us']:8.1f}")
         rows.append(row)
         tot["cudnn_fwd"] += cnt * t_f
         tot["cudnn_dgrad"] += cnt * t_d
         tot["cudnn_wgrad"] += cnt * t_w
         tot["floor"] += cnt * floor
         name = f"{cin}x{hw}^2 -> {cout} k{k}/s{s}"
-        print(f"{name:32s} {cnt:2d} {t_f:8.1f} {t_d:8.1f} {t_w:8.1f} {floor:7.1f} | {g[0]:>8s} {g[1]:>8s} {g[2]:>8s}")
+        print(f"{name:32s} {cnt:2d} {t_f:8.1f} {t_d:8.1f} {t_w:8.1f} {floor:7.1f} | {g[0]:>8s} {g[1]:>8s} {g[2]:>8s} {(g[3] if len(g) > 3 else ''):>8s}")
         del x, w, y, dy
     print("totals per step (ms):", {k: round(v / 1e3, 3) for k, v in tot.items()})
     os.makedirs(os.path.dirname(args.json), exist_ok=True)

@@ -538,6 +538,53 @@ import os as _os
 _CONV1X1_GEMM = _os.environ.get("DDL_CONV1X1", "cudnn") == "gemm"
 
 
+# Weight-stationary tcgen05 kernel for the skinny 1x1 convolutions (csrc/conv1x1.cu): forward + BatchNorm statistics in
+# one pass; DDL_CONV1X1_WS=0 sends these layers back to the library.
+_CONV1X1_WS = _os.environ.get("DDL_CONV1X1_WS", "1") != "0"
+
+
+def conv1x1_ws_usable(x: torch.Tensor, conv: nn.Conv2d) -> bool:
+    if not (_CONV1X1_WS and x.is_cuda and x.dim() == 4 and x.dtype == torch.bfloat16 and conv.kernel_size == (1, 1)
+            and conv.stride == (1, 1) and conv.padding == (0, 0) and conv.groups == 1 and conv.bias is None
+            and conv.weight.dtype == torch.bfloat16):
+        return False
+    N_, _, H, W = x.shape
+    return bool(L.lib().ddl_conv1x1_supported(N_ * H * W, conv.out_channels, conv.in_channels))
+
+
+class _Conv1x1WS(torch.autograd.Function):
+    """Forward on the weight-stationary kernel (also yields the BN statistics); both gradients from the library,
+    which is within 1.05 - 1.4x of the memory floor on these layers (benchmarks/conv_bench.py)."""
+
+    @staticmethod
+    def forward(ctx, x, weight):
+        Nb, Cin, H, W = x.shape
+        Cout = weight.shape[0]
+        if not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        w2 = weight.reshape(Cout, Cin)  # [Cout, Cin, 1, 1] is [Cout][Cin] in memory in either layout
+        if not w2.is_contiguous():
+            w2 = w2.contiguous()
+        M = Nb * H * W
+        dev = x.device
+        y = torch.empty((Nb, Cout, H, W), dtype=torch.bfloat16, device=dev, memory_format=torch.channels_last)
+        partials = torch.empty(L.lib().ddl_conv1x1_grid(M, Cout) * 2 * Cout, dtype=torch.float32, device=dev)
+        L.call("ddl_conv1x1_fwd", x.data_ptr(), w2.data_ptr(), y.data_ptr(), partials.data_ptr(), M, Cout, Cin, L.stream_ptr(dev))
+        ctx.save_for_backward(x, weight)
+        ctx.mark_non_differentiable(partials)
+        return y, partials
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy, _unused):
+        x, weight = ctx.saved_tensors
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dx, dw, _ = torch.ops.aten.convolution_backward(dy, x, weight, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
+                                                        [ctx.needs_input_grad[0], ctx.needs_input_grad[1], False])
+        return dx, dw
+
+
 def conv_bn_act(x, conv: nn.Conv2d, bn: nn.BatchNorm2d, relu: bool = True, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
     """conv -> BN -> (+residual) -> ReLU on NHWC bf16.  Normalise, residual add and ReLU are the native kernels in
     ``csrc/bn_act.cu``; the convolution is the library call (cuDNN through ATen) unless ``DDL_CONV1X1=gemm``, which
@@ -547,6 +594,9 @@ def conv_bn_act(x, conv: nn.Conv2d, bn: nn.BatchNorm2d, relu: bool = True, resid
         training = bn.training or bn.running_mean is None
         y, sums = _Conv1x1.apply(x, conv.weight, training)
         return bn_act(y, bn, relu=relu, residual=residual, sums=sums)
+    if conv1x1_ws_usable(x, conv):
+        y, partials = _Conv1x1WS.apply(x, conv.weight)
+        return bn_act(y, bn, relu=relu, residual=residual, partials=partials)
     y = conv2d(x, conv)
     return bn_act(y, bn, relu=relu, residual=residual)
 

@@ -198,6 +198,14 @@ int ddl_stem_conv_fwd(const void* z, const void* w, long long sk, long long sc, 
 int ddl_stem_conv_wgrad(const void* z, const void* dy, void* dw, long long sk, long long sc, long long sr, long long ss,
                         void* scratch, size_t scratch_bytes, int N, int H, int W, void* stream);
 
+/* ---- 1x1 / stride-1 convolution forward, weight-stationary (csrc/conv1x1.cu), K9 --------
+ * y[M, N] = x[M, K] . w[N, K]^T on NHWC bf16 (M = batch*H*W; N, K in {64,128,256,512}, N*K <= 65536: the layer1 / layer2
+ * bottleneck convolutions of the reference's ResNet-50, reference:19) with the BatchNorm statistics of y written as
+ * per-CTA partials fp32 [ddl_conv1x1_grid(M, N)][2][N] for ddl_bn_act_fwd_train_from_partials. */
+int ddl_conv1x1_supported(long long M, int N, int K);
+int ddl_conv1x1_grid(long long M, int N);
+int ddl_conv1x1_fwd(const void* x, const void* w, void* y, float* partials, long long M, int N, int K, void* stream);
+
 /* ---- tcgen05 / TMEM / TMA GEMM (csrc/gemm_tcgen05.cu), K8 ------------------------------ */
 /* C[M,N] = epilogue(A . B^T), bf16 operands, fp32 accumulation in tensor memory.
  * A is [M,K] row-major (a_mn = 0) or stored as [K,M] (a_mn = 1); B is [N,K] (b_mn = 0) or stored

@@ -1,11 +1,5 @@
 mkdir -p gpurun_out
-N=${NGPU:-8}
-run() { # impl workload
-  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 bench.py --gpus $N --impl $1 --workload $2 --steps 20 --warmup 5 > gpurun_out/t41_bench_$2_$1_${N}gpu.json 2> gpurun_out/t41_bench_$2_$1_${N}gpu.err
-  echo "rc=$? $1 $2"; tail -1 gpurun_out/t41_bench_$2_$1_${N}gpu.json | cut -c1-340
-}
-run ours resnet50
-run ours bert-base
-run ours bert-large
-run stock bert-base
-run stock bert-large
+timeout 600 python -m pytest tests/test_gpu_kernels.py -m gpu -x -q -k "conv1x1_weight or resnet" > gpurun_out/t44_tests.log 2>&1; echo "tests rc=$?" >> gpurun_out/t44_tests.log
+tail -5 gpurun_out/t44_tests.log | cut -c1-250
+timeout 900 python benchmarks/conv_bench.py > gpurun_out/conv_bench.log 2>&1; grep "ws.fwd\|k1/s1" gpurun_out/conv_bench.log | head -8
+timeout 600 python bench.py --steps 30 --warmup 5 > gpurun_out/t44_bench_resnet.json 2> gpurun_out/t44_bench_resnet.err; tail -1 gpurun_out/t44_bench_resnet.json | cut -c80-200

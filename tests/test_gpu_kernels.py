@@ -711,3 +711,32 @@ def test_resnet50_native_stem_matches_library_stem():
     torch.testing.assert_close(outs[0][2], outs[1][2], rtol=5e-3, atol=1e-4)
     assert cosf(outs[0][0], outs[1][0]) > 0.98, cosf(outs[0][0], outs[1][0])
     assert cosf(outs[0][1], outs[1][1]) > 0.95, cosf(outs[0][1], outs[1][1])
+
+
+@pytest.mark.parametrize("Nb,HW,K,N", [(4, 56, 64, 64), (4, 56, 64, 256), (3, 56, 256, 64), (2, 56, 256, 128), (4, 28, 128, 512),
+                                        (4, 28, 512, 128), (1, 7, 64, 128), (5, 9, 128, 64)])
+def test_conv1x1_weight_stationary_fwd_stats_and_grads(Nb, HW, K, N):
+    """Skinny 1x1 convolution on the weight-stationary tcgen05 kernel vs F.conv2d in fp32, incl. the BN statistics
+    from its epilogue and a ragged last tile (M not a multiple of 128)."""
+    OF = _OF()
+    bf = torch.bfloat16
+    conv = torch.nn.Conv2d(K, N, 1, bias=False).cuda().to(bf).to(memory_format=torch.channels_last)
+    x = torch.randn(Nb, K, HW, HW, device="cuda").to(bf).contiguous(memory_format=torch.channels_last).requires_grad_()
+    assert OF.conv1x1_ws_usable(x, conv)
+    w = conv.weight.detach().clone().requires_grad_()
+    y, partials = OF._Conv1x1WS.apply(x, w)
+    xr = x.detach().float().requires_grad_()
+    wr = w.detach().float().requires_grad_()
+    yr = F.conv2d(xr, wr)
+    rel = lambda a, b: ((a.float() - b).abs().max() / b.abs().max().clamp_min(1e-6)).item()
+    assert y.is_contiguous(memory_format=torch.channels_last)
+    assert rel(y, yr.detach()) < 1e-2, rel(y, yr.detach())
+    st = partials.view(-1, 2, N).sum(0)
+    yf = y.float()
+    torch.testing.assert_close(st[0], yf.sum((0, 2, 3)), rtol=2e-3, atol=5e-2)
+    torch.testing.assert_close(st[1], yf.square().sum((0, 2, 3)), rtol=2e-3, atol=5e-2)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    yr.backward(dy.float())
+    assert rel(x.grad, xr.grad) < 2e-2
+    assert rel(w.grad, wr.grad) < 2e-2
