@@ -1,5 +1,4 @@
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_kernels.py -m gpu -x -q -k "conv1x1_weight or resnet" > gpurun_out/t44_tests.log 2>&1; echo "tests rc=$?" >> gpurun_out/t44_tests.log
-tail -5 gpurun_out/t44_tests.log | cut -c1-250
-timeout 900 python benchmarks/conv_bench.py > gpurun_out/conv_bench.log 2>&1; grep "ws.fwd\|k1/s1" gpurun_out/conv_bench.log | head -8
-timeout 600 python bench.py --steps 30 --warmup 5 > gpurun_out/t44_bench_resnet.json 2> gpurun_out/t44_bench_resnet.err; tail -1 gpurun_out/t44_bench_resnet.json | cut -c80-200
+timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/t46_tests.log 2>&1; echo "tests rc=$?" >> gpurun_out/t46_tests.log
+tail -4 gpurun_out/t46_tests.log | cut -c1-250
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 20 --warmup 5 > gpurun_out/t46_bench_resnet50_2gpu.json 2> gpurun_out/t46_bench_resnet50_2gpu.err; tail -1 gpurun_out/t46_bench_resnet50_2gpu.json | cut -c1-330
