@@ -330,9 +330,12 @@ __global__ void __launch_bounds__(kSingle ? 128 : 256, kSingle ? 2 : 1) attn_bwd
     constexpr uint32_t kTmemCols = kSingle ? 256 : 512;
     // With 512 columns (not kSingle) the bf16 copies get their own columns [384,448) / [448,512): two warps work on
     // one lane quarter concurrently there, and in-place aliasing would let one overwrite what the other has not read.
-    constexpr uint32_t cST = 0, cDP = 128, cDQ = 0;
+    // Multi-tile variant: dS^T is NOT copied to TMEM; dK reads it from the swizzled smem tile (K-major A operand), which
+    // leaves [448,512) for dQ.  S^T / dP^T are then dead as soon as the softmax threads have read them, so the MMAs of the
+    // NEXT query tile are issued right behind this tile's gradient MMAs and run while dQ is being written out.
+    constexpr uint32_t cST = 0, cDP = 128, cDQ = kSingle ? 0 : 448;
     constexpr uint32_t cDV = kSingle ? 64 : 256, cDK = kSingle ? 192 : 320;
-    constexpr uint32_t cPT = kSingle ? cST : 384, cDST = kSingle ? cDP : 448;
+    constexpr uint32_t cPT = kSingle ? cST : 384, cDST = cDP;  // cDST only used by kSingle
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tma_qkv);
@@ -368,6 +371,22 @@ __global__ void __launch_bounds__(kSingle ? 128 : 256, kSingle ? 2 : 1) attn_bwd
         }
         uint32_t ph = 0;            // phase of the once-per-iteration barriers [3], [4], [5]
         uint32_t qph[2] = {0, 0};   // phase of each Q/dO buffer's barrier
+        // S^T = K Q^T and dP^T = V dO^T of the query tile in buffer `bf` (thread 0 only)
+        auto issue_scores = [&](int bf, uint32_t phase) {
+            mbar_wait(&bars[1 + bf], phase);
+            tc_fence_after();
+            constexpr uint32_t idesc = make_idesc(TILE, TILE, false, false);
+            const uint32_t q_s = smem_u32(sQ + bf * kTileBytes), do_s = smem_u32(sdO + bf * kTileBytes);
+#pragma unroll
+            for (int k = 0; k < D / 16; ++k)
+                umma_bf16(tmem_base + cST, make_smem_desc(smem_u32(sK) + k * 32, 16, 1024), make_smem_desc(q_s + k * 32, 16, 1024), idesc,
+                          k > 0 ? 1u : 0u);
+#pragma unroll
+            for (int k = 0; k < D / 16; ++k)
+                umma_bf16(tmem_base + cDP, make_smem_desc(smem_u32(sV) + k * 32, 16, 1024), make_smem_desc(do_s + k * 32, 16, 1024), idesc,
+                          k > 0 ? 1u : 0u);
+            umma_commit(&bars[3]);
+        };
         for (int qi = 0; qi < n_q; ++qi) {
             const int buf = kSingle ? 0 : (qi & 1);
             const int q_row0 = b * p.S + qi * TILE;
@@ -385,20 +404,9 @@ __global__ void __launch_bounds__(kSingle ? 128 : 256, kSingle ? 2 : 1) attn_bwd
                 sDv[r] = p.dvec[((size_t)b * p.heads + hd) * p.S + qi * TILE + r];
             }
             __syncthreads();
-            if (threadIdx.x == 0) {
-                if (qi == 0) mbar_wait(&bars[0], 0);
-                mbar_wait(&bars[1 + buf], qph[buf]);
-                tc_fence_after();
-                constexpr uint32_t idesc = make_idesc(TILE, TILE, false, false);
-#pragma unroll
-                for (int k = 0; k < D / 16; ++k)  // S^T = K Q^T
-                    umma_bf16(tmem_base + cST, make_smem_desc(smem_u32(sK) + k * 32, 16, 1024), make_smem_desc(smem_u32(cQ) + k * 32, 16, 1024),
-                              idesc, k > 0 ? 1u : 0u);
-#pragma unroll
-                for (int k = 0; k < D / 16; ++k)  // dP^T = V dO^T
-                    umma_bf16(tmem_base + cDP, make_smem_desc(smem_u32(sV) + k * 32, 16, 1024), make_smem_desc(smem_u32(cdO) + k * 32, 16, 1024),
-                              idesc, k > 0 ? 1u : 0u);
-                umma_commit(&bars[3]);
+            if (threadIdx.x == 0 && (kSingle || qi == 0)) {
+                mbar_wait(&bars[0], 0);
+                issue_scores(buf, qph[buf]);
             }
             qph[buf] ^= 1;
             mbar_wait(&bars[3], ph);
@@ -442,7 +450,7 @@ __global__ void __launch_bounds__(kSingle ? 128 : 256, kSingle ? 2 : 1) attn_bwd
                 }
                 // kSingle: bf16 pairs go back over the fp32 columns they came from (16c + 15 < 32c for c >= 1)
                 tmem_st_32x16(lane_addr + cPT + c * 16, ppk);
-                tmem_st_32x16(lane_addr + cDST + c * 16, dpk);
+                if (kSingle) tmem_st_32x16(lane_addr + cDST + c * 16, dpk);
             }
             tmem_st_wait();
             fence_proxy_async();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
@@ -459,11 +467,20 @@ __global__ void __launch_bounds__(kSingle ? 128 : 256, kSingle ? 2 : 1) attn_bwd
                     umma_bf16_ts(tmem_base + cDV, tmem_base + cPT + k * 8, make_smem_desc(smem_u32(cdO) + k * 2048, 8192, 1024), idesc_ts,
                                  (k > 0) ? 1u : acc0);
                 umma_commit(&bars[4]);
-                // dK += dS^T Q : A = dS^T in TMEM, B = Q tile read MN-major
+                // dK += dS^T Q : A = dS^T (kSingle: in TMEM; else: the swizzled smem tile read K-major, two 64-query blocks),
+                //                B = Q tile read MN-major
+                if (kSingle) {
 #pragma unroll
-                for (int k = 0; k < TILE / 16; ++k)
-                    umma_bf16_ts(tmem_base + cDK, tmem_base + cDST + k * 8, make_smem_desc(smem_u32(cQ) + k * 2048, 8192, 1024), idesc_ts,
-                                 (k > 0) ? 1u : acc0);
+                    for (int k = 0; k < TILE / 16; ++k)
+                        umma_bf16_ts(tmem_base + cDK, tmem_base + cDST + k * 8, make_smem_desc(smem_u32(cQ) + k * 2048, 8192, 1024), idesc_ts,
+                                     (k > 0) ? 1u : acc0);
+                } else {
+                    constexpr uint32_t idesc_kmn = make_idesc(TILE, D, false, true);  // A K-major smem, B MN-major smem
+#pragma unroll
+                    for (int k = 0; k < TILE / 16; ++k)
+                        umma_bf16(tmem_base + cDK, make_smem_desc(smem_u32(sdSt) + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024),
+                                  make_smem_desc(smem_u32(cQ) + k * 2048, 8192, 1024), idesc_kmn, (k > 0) ? 1u : acc0);
+                }
                 // dQ = dS K : accumulates into the columns P^T occupied, so wait until the dV MMAs have consumed them.
                 //   A = dS^T smem tile read MN-major (M = q contiguous, 64-wide blocks kTileBytes apart, K = kv rows)
                 //   B = K tile read MN-major (N = d, K = kv rows)
@@ -476,6 +493,8 @@ __global__ void __launch_bounds__(kSingle ? 128 : 256, kSingle ? 2 : 1) attn_bwd
                     umma_bf16(tmem_base + cDQ, make_smem_desc(smem_u32(sdSt) + k * 2048, kTileBytes, 1024),
                               make_smem_desc(smem_u32(sK) + k * 2048, 8192, 1024), idesc_mm, k > 0 ? 1u : 0u);
                 umma_commit(&bars[5]);
+                // software pipeline: the next query tile's S^T / dP^T run behind these MMAs while the threads write dQ out
+                if (!kSingle && qi + 1 < n_q) issue_scores(buf ^ 1, qph[buf ^ 1]);
             }
             mbar_wait(&bars[5], ph);
             __syncwarp();
