@@ -420,6 +420,15 @@ __global__ void __launch_bounds__(kSingle ? 128 : 256, kSingle ? 2 : 1) attn_bwd
                 tmem_ld_32x32(lane_addr + cDP + c * 32, dp);
                 tmem_ld_wait();
                 uint32_t ppk[16], dpk[16];
+                // dropout: the 4 lanes that own keys 4k .. 4k+3 need the SAME 32-bit hash per query (one byte each), so each
+                // computes it for 8 of the chunk's 32 queries and the group exchanges them by shuffle (a shuffle costs one
+                // instruction, the hash eleven)
+                uint32_t hq[8];
+                if (p.drop_thr) {
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        hq[u] = drop_hash(seed, bh, (uint32_t)(qi * TILE + c * 32 + u * 4 + (lane & 3)), (uint32_t)(kv_idx >> 2), (uint32_t)p.S);
+                }
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
                     float pt[8], ds[8], lse8[8], dv8[8];
@@ -434,7 +443,7 @@ __global__ void __launch_bounds__(kSingle ? 128 : 256, kSingle ? 2 : 1) attn_bwd
                         float dpv = __uint_as_float(dp[g * 8 + t]);
                         float pdrop = pv;
                         if (p.drop_thr) {
-                            const uint32_t h = drop_hash(seed, bh, (uint32_t)(qi * TILE + qc0 + t), (uint32_t)(kv_idx >> 2), (uint32_t)p.S);
+                            const uint32_t h = __shfl_sync(0xffffffffu, hq[(g * 8 + t) >> 2], (lane & ~3) | (t & 3));
                             const bool kept = ((h >> (8 * (kv_idx & 3))) & 0xffu) >= p.drop_thr;
                             pdrop = kept ? pv * p.drop_scale : 0.f;
                             dpv = kept ? dpv * p.drop_scale : 0.f;
