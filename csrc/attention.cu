@@ -23,6 +23,8 @@
 //   dV += P^T dO, dK += dS^T Q (TMEM accumulators across query tiles), dQ = dS K (per tile;
 //   written straight to dqkv when the sequence has one key tile, else red.add into fp32).
 #include <math.h>
+#include <stdlib.h>
+#include <string.h>
 
 #include <mutex>
 
@@ -254,6 +256,203 @@ __global__ void __launch_bounds__(kMaxKvTiles == 1 ? 128 : 256, kMaxKvTiles == 1
             }
         }
         if (p.lse && half == 0) p.lse[((size_t)b * p.heads + hd) * p.S + q_tile * TILE + r] = mx * p.scale + __logf(sum);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// forward, streaming variant for S > 128: one CTA per (batch, head, 128-query tile), 256 threads, key / value tiles
+// streamed through a two-stage TMA ring with an online softmax, so that a CTA needs 80 KB of shared memory and 256
+// TMEM columns (S [0,128) fp32, P [128,192) bf16 pairs, O [192,256) fp32) and TWO CTAs fit per SM - their serial
+// TMA -> MMA -> softmax -> MMA chains overlap each other (the resident variant above holds all of S in 512 columns
+// and runs one CTA per SM).  The running maximum is only raised when a tile exceeds it by more than 8 in the log2
+// domain (P then stays <= 256, exact in the final O / l), so the O accumulator is rarely read back and rescaled.
+__global__ void __launch_bounds__(256, 2) attn_fwd_stream_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* sQ = smem;
+    uint8_t* sKV = sQ + kTileBytes;  // [2 stages][K tile, V tile]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sKV + 4 * kTileBytes);  // [0] Q  [1],[2] K/V stage  [3] S ready  [4] PV done
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 8);
+    float* sRed = reinterpret_cast<float*>(bars + 10);  // [2][128] partner exchange
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q_tile = blockIdx.x, hd = blockIdx.y, b = blockIdx.z;
+    const int kv_len = p.seqlens ? min(max(p.seqlens[b], 1), p.S) : p.S;
+    const int n_kv = (kv_len + TILE - 1) / TILE;
+    constexpr uint32_t kTmemCols = 256, cS = 0, cP = 128, cO = 192;
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&tma_qkv);
+        for (int i = 0; i < 5; ++i) mbar_init(&bars[i], 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc(tmem_ptr_smem, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    const int row0 = b * p.S + q_tile * TILE;
+    auto load_kv = [&](int j) {  // thread 0
+        uint8_t* st = sKV + (j & 1) * 2 * kTileBytes;
+        mbar_expect_tx(&bars[1 + (j & 1)], 2 * kTileBytes);
+        tma_load_2d(st, &tma_qkv, &bars[1 + (j & 1)], p.H + hd * D, b * p.S + j * TILE);
+        tma_load_2d(st + kTileBytes, &tma_qkv, &bars[1 + (j & 1)], 2 * p.H + hd * D, b * p.S + j * TILE);
+    };
+    auto issue_scores = [&](int j) {  // thread 0: S = Q K_j^T
+        mbar_wait(&bars[1 + (j & 1)], (uint32_t)((j >> 1) & 1));
+        tc_fence_after();
+        constexpr uint32_t idesc_s = make_idesc(TILE, TILE, false, false);
+        const uint32_t k_s = smem_u32(sKV + (j & 1) * 2 * kTileBytes);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k)
+            umma_bf16(tmem_base + cS, make_smem_desc(smem_u32(sQ) + k * 32, 16, 1024), make_smem_desc(k_s + k * 32, 16, 1024), idesc_s,
+                      k > 0 ? 1u : 0u);
+        umma_commit(&bars[3]);
+    };
+    if (threadIdx.x == 0) {
+        mbar_expect_tx(&bars[0], kTileBytes);
+        tma_load_2d(sQ, &tma_qkv, &bars[0], hd * D, row0);
+        load_kv(0);
+        if (n_kv > 1) load_kv(1);
+        mbar_wait(&bars[0], 0);
+        issue_scores(0);
+    }
+
+    const int quarter = warp & 3, half = warp >> 2;
+    const int r = quarter * 32 + lane;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    const float sl2 = p.scale * kLog2e;
+    const uint64_t seed64 = resolve_seed(p.seed, p.seed_dev, p.drop_thr);
+    const uint32_t seed = mix32((uint32_t)seed64) ^ (uint32_t)(seed64 >> 32);
+    const uint32_t bh = (uint32_t)(b * p.heads + hd);
+    const uint32_t q_idx = (uint32_t)(q_tile * TILE + r);
+    auto pair_sync = [&]() { asm volatile("bar.sync %0, 64;" ::"r"(1 + quarter) : "memory"); };
+
+    float m_used = -INFINITY;  // running maximum (log2 domain, i.e. already multiplied by scale * log2 e)
+    float l_part = 0.f;        // this thread's share of the row sum, relative to m_used
+    for (int j = 0; j < n_kv; ++j) {
+        mbar_wait(&bars[3], (uint32_t)(j & 1));
+        __syncwarp();
+        tc_fence_after();
+        // ---- tile maximum over this thread's two 32-column chunks
+        float mt = -INFINITY;
+#pragma unroll
+        for (int ci = 0; ci < 2; ++ci) {
+            const int c = half + 2 * ci;
+            uint32_t v[32];
+            tmem_ld_32x32(lane_addr + cS + c * 32, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int t = 0; t < 32; ++t)
+                if (j * TILE + c * 32 + t < kv_len) mt = fmaxf(mt, __uint_as_float(v[t]));
+        }
+        sRed[half * TILE + r] = mt;
+        pair_sync();
+        mt = fmaxf(mt, sRed[(half ^ 1) * TILE + r]) * sl2;
+        pair_sync();
+        // raise the running maximum only when this tile exceeds it by more than 8 (P stays <= 2^8)
+        const bool raise = mt > m_used + 8.f;
+        const float m_new = raise ? mt : m_used;
+        const float alpha = raise ? exp2f(m_used - m_new) : 1.f;  // exp2f(-inf) = 0 on the first tile
+        m_used = m_new;
+        l_part *= alpha;
+        if (j > 0) {
+            mbar_wait(&bars[4], (uint32_t)((j - 1) & 1));  // P columns free, O complete up to tile j-1
+            __syncwarp();
+            tc_fence_after();
+            if (__any_sync(0xffffffffu, raise)) {
+                uint32_t o[32];
+                tmem_ld_32x32(lane_addr + cO + half * 32, o);
+                tmem_ld_wait();
+#pragma unroll
+                for (int t = 0; t < 32; ++t) o[t] = __float_as_uint(__uint_as_float(o[t]) * alpha);
+                // 32 columns as two 16-column stores
+                uint32_t lo[16], hi[16];
+#pragma unroll
+                for (int t = 0; t < 16; ++t) {
+                    lo[t] = o[t];
+                    hi[t] = o[16 + t];
+                }
+                tmem_st_32x16(lane_addr + cO + half * 32, lo);
+                tmem_st_32x16(lane_addr + cO + half * 32 + 16, hi);
+            }
+        }
+        // ---- P = exp2(s - m), dropout, bf16 pairs into the P columns
+#pragma unroll
+        for (int ci = 0; ci < 2; ++ci) {
+            const int c = half + 2 * ci;
+            uint32_t v[32];
+            tmem_ld_32x32(lane_addr + cS + c * 32, v);
+            tmem_ld_wait();
+            uint32_t packed[16];
+#pragma unroll
+            for (int j4 = 0; j4 < 8; ++j4) {
+                float e[4];
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const int col = j * TILE + c * 32 + j4 * 4 + t;
+                    e[t] = col < kv_len ? exp2f(__uint_as_float(v[j4 * 4 + t]) * sl2 - m_used) : 0.f;
+                    l_part += e[t];
+                }
+                if (p.drop_thr) {
+                    const uint32_t keep = drop_keep4(seed, bh, q_idx, (uint32_t)(j * (TILE / 4) + c * 8 + j4), (uint32_t)p.S, p.drop_thr);
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) e[t] = ((keep >> t) & 1u) ? e[t] : 0.f;
+                }
+                packed[j4 * 2] = pack_bf16x2(e[0], e[1]);
+                packed[j4 * 2 + 1] = pack_bf16x2(e[2], e[3]);
+            }
+            tmem_st_32x16(lane_addr + cP + c * 16, packed);
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        __syncthreads();  // S consumed, P (and the rescaled O) written by everybody
+        if (threadIdx.x == 0) {
+            tc_fence_after();
+            // O (+)= P V_j : A = P from TMEM, B = V tile read MN-major
+            constexpr uint32_t idesc_o = make_idesc(TILE, D, false, true);
+            const uint32_t v_s = smem_u32(sKV + (j & 1) * 2 * kTileBytes + kTileBytes);
+#pragma unroll
+            for (int k = 0; k < TILE / 16; ++k)
+                umma_bf16_ts(tmem_base + cO, tmem_base + cP + k * 8, make_smem_desc(v_s + k * 2048, 8192, 1024), idesc_o,
+                             (j > 0 || k > 0) ? 1u : 0u);
+            umma_commit(&bars[4]);
+            if (j + 1 < n_kv) issue_scores(j + 1);  // runs behind PV_j
+            if (j + 2 < n_kv) {
+                mbar_wait(&bars[4], (uint32_t)(j & 1));  // stage j&1 (K_j, V_j) no longer read
+                load_kv(j + 2);
+            }
+        }
+    }
+    // ---- epilogue
+    sRed[half * TILE + r] = l_part;
+    pair_sync();
+    const float l = l_part + sRed[(half ^ 1) * TILE + r];
+    mbar_wait(&bars[4], (uint32_t)((n_kv - 1) & 1));
+    __syncwarp();
+    tc_fence_after();
+    {
+        const float inv = (p.drop_thr ? p.drop_scale : 1.f) / l;
+        bf16* out = p.ctx + (size_t)(row0 + r) * p.H + hd * D;
+        uint32_t v[32];
+        tmem_ld_32x32(lane_addr + cO + half * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int t0 = 0; t0 < 32; t0 += 8) {
+            float o[8];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) o[t] = __uint_as_float(v[t0 + t]) * inv;
+            st_global_v4(out + half * 32 + t0, float_to_bf16x8(o));
+        }
+        // natural-log LSE: m_used is in the log2 domain of the scaled scores
+        if (p.lse && half == 0) p.lse[((size_t)b * p.heads + hd) * p.S + q_tile * TILE + r] = m_used * (1.f / kLog2e) + __logf(l);
     }
     tc_fence_before();
     __syncthreads();
@@ -638,6 +837,16 @@ int fill_params(AttnParams* p, int B, int S, int heads, const int* seqlens, floa
     return 0;
 }
 
+// S > 128: streaming kernel (two CTAs per SM) unless DDL_ATTN_FWD=resident asks for the all-of-S-in-TMEM variant
+bool attn_fwd_streaming() {
+    static int mode = -1;
+    if (mode < 0) {
+        const char* e = getenv("DDL_ATTN_FWD");
+        mode = (e && strcmp(e, "resident") == 0) ? 0 : 1;
+    }
+    return mode == 1;
+}
+
 template <int KV>
 int launch_fwd(const CUtensorMap& map, const AttnParams& p, cudaStream_t s) {
     constexpr int smem = (1 + 2 * KV) * kTileBytes + 64 + 2 * TILE * 4 + 1024;
@@ -664,6 +873,18 @@ DDL_API int ddl_attention_fwd(const void* qkv, const int* seqlens, void* ctx, fl
     CUtensorMap map;
     if (int e = make_tile_map(&map, qkv, (long long)B * S, 3LL * p.H)) return e;
     cudaStream_t s = (cudaStream_t)stream_;
+    if (S > TILE && attn_fwd_streaming()) {
+        constexpr int smem = 5 * kTileBytes + 128 + 2 * TILE * 4 + 1024;
+        static bool set = false;
+        if (!set) {
+            DDL_CHECK(cudaFuncSetAttribute(attn_fwd_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            set = true;
+        }
+        dim3 grid(p.S / TILE, p.heads, p.B);
+        attn_fwd_stream_kernel<<<grid, 256, smem, s>>>(map, p);
+        DDL_LAUNCH_CHECK();
+        return 0;
+    }
     switch (S / TILE) {
         case 1: return launch_fwd<1>(map, p, s);
         case 2: return launch_fwd<2>(map, p, s);

@@ -740,3 +740,50 @@ def test_conv1x1_weight_stationary_fwd_stats_and_grads(Nb, HW, K, N):
     yr.backward(dy.float())
     assert rel(x.grad, xr.grad) < 2e-2
     assert rel(w.grad, wr.grad) < 2e-2
+
+
+def test_attention_streaming_forward_rescales_running_max():
+    """S = 512: key tiles whose scores grow by far more than 2^8 from tile to tile force the streaming forward
+    kernel to raise its running maximum and rescale the O accumulator in TMEM."""
+    from databricks_distributed_deep_learning_b200.ops import attention as A
+
+    B, S, h = 2, 512, 3
+    qkv = torch.randn(B, S, 3, h, 64, device="cuda")
+    for j in range(4):
+        qkv[:, j * 128:(j + 1) * 128, 1] *= (1.0 + 4.0 * j)  # keys of tile j are (1 + 4j) times larger
+    qkv = qkv.to(torch.bfloat16).requires_grad_()
+    out = A.attention_qkvpacked(qkv, None, 0.0)
+    dout = torch.randn_like(out)
+    out.backward(dout)
+    ref_in = qkv.detach().clone().requires_grad_()
+    ref = _attn_ref_fp32(ref_in, None)
+    ref.backward(dout.float())
+    assert torch.allclose(out.float(), ref, rtol=3e-2, atol=3e-2), (out.float() - ref).abs().max().item()
+    rel = lambda a, b: ((a - b).abs().max() / b.abs().max().clamp_min(1e-6)).item()
+    g, gr = qkv.grad.float(), ref_in.grad.float()
+    for i, name in enumerate(("dQ", "dK", "dV")):
+        assert rel(g[:, :, i], gr[:, :, i]) < 4e-2, (name, rel(g[:, :, i], gr[:, :, i]))
+
+
+def test_attention_dropout_forward_backward_masks_agree_long_sequence():
+    """S = 512 with dropout: the forward (streaming kernel, one hash per 4 keys) and the backward (hashes shared by
+    shuffle inside 4-lane groups) must drop the same probabilities.  With V = 1 and dO = 1:
+    sum_k dV[k] == sum_q out[q] holds only if the two masks are identical."""
+    from databricks_distributed_deep_learning_b200.ops import attention as A
+
+    B, S, h = 2, 512, 4
+    qkv = (torch.randn(B, S, 3, h, 64, device="cuda") * 0.3).to(torch.bfloat16)
+    qkv[:, :, 2] = 1.0
+    x = qkv.clone().requires_grad_()
+    y = A._Attention.apply(x, None, 0.1)
+    assert abs(y.float().mean().item() - 1.0) < 0.01
+    assert 0.005 < y.float().std().item() < 0.3
+    y.backward(torch.ones_like(y))
+    assert torch.isfinite(x.grad.float()).all()
+    tot_out = y.float()[..., 0::64].sum().item()
+    tot_dv = x.grad.float()[:, :, 2, :, 0].sum().item()
+    assert abs(tot_dv - tot_out) < 0.01 * abs(tot_out), (tot_dv, tot_out)
+    # per (batch, head): column sums of dropout(P) seen by backward == row sums seen by forward
+    per_head_out = y.float().view(B, S, h, 64)[..., 0].sum(1)
+    per_head_dv = x.grad.float()[:, :, 2, :, 0].sum(1)
+    torch.testing.assert_close(per_head_dv, per_head_out, rtol=2e-2, atol=0.5)
