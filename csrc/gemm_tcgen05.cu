@@ -726,12 +726,18 @@ __global__ void __launch_bounds__(kGatherThreads, 1) gemm_allgather_kernel(const
     }
 }
 
-// fp32 split-K accumulator -> bf16 (+ optional accumulate into existing bf16)
-__global__ void f32_to_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, size_t n8, int accumulate) {
+// fp32 split-K accumulator -> bf16.  flags bit 0: accumulate into the existing bf16 output; bit 1: write zeros back to the
+// accumulator after reading it, so that a cached accumulator is ready for the next split-K GEMM without a memset kernel
+__global__ void f32_to_bf16_kernel(float* __restrict__ in, bf16* __restrict__ out, size_t n8, int flags) {
+    const bool accumulate = flags & 1, rezero = flags & 2;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
         float f[8];
         *reinterpret_cast<float4*>(&f[0]) = *reinterpret_cast<const float4*>(in + i * 8);
         *reinterpret_cast<float4*>(&f[4]) = *reinterpret_cast<const float4*>(in + i * 8 + 4);
+        if (rezero) {
+            *reinterpret_cast<float4*>(in + i * 8) = make_float4(0.f, 0.f, 0.f, 0.f);
+            *reinterpret_cast<float4*>(in + i * 8 + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         if (accumulate) {
             float g[8];
             bf16x8_to_float(ld_global_v4(out + i * 8), g);
@@ -1035,12 +1041,12 @@ DDL_API int ddl_gemm_set_cluster(int cluster) {
     return 0;
 }
 
-DDL_API int ddl_f32_to_bf16(const float* in, void* out, size_t numel, int accumulate, void* stream_) {
+DDL_API int ddl_f32_to_bf16(const float* in, void* out, size_t numel, int flags, void* stream_) {
     DDL_REQUIRE(numel % 8 == 0, "ddl_f32_to_bf16: numel must be a multiple of 8");
     if (numel == 0) return 0;
     int blocks = ddl_ceil_div((long long)(numel / 8), 256);
     if (blocks > DDL_SM_COUNT * 8) blocks = DDL_SM_COUNT * 8;
-    f32_to_bf16_kernel<<<blocks, 256, 0, (cudaStream_t)stream_>>>(in, (bf16*)out, numel / 8, accumulate);
+    f32_to_bf16_kernel<<<blocks, 256, 0, (cudaStream_t)stream_>>>(const_cast<float*>(in), (bf16*)out, numel / 8, flags);
     DDL_LAUNCH_CHECK();
     return 0;
 }

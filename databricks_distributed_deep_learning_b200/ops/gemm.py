@@ -48,6 +48,7 @@ def available() -> bool:
 
 
 _env_applied = False
+_acc_cache = {}  # (M, N, device index) -> zeroed fp32 split-K accumulator
 
 
 def usable(x: torch.Tensor, weight: torch.Tensor) -> bool:
@@ -70,12 +71,27 @@ def gemm_nt(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn: b
     if out is None:
         out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
     acc = None
+    rezero = 0
     if split_k > 1:
-        acc = torch.zeros(M, N, dtype=torch.float32, device=dev)
-    L.call("ddl_gemm_bf16_ex", a.data_ptr(), int(a_mn), a.stride(0), b.data_ptr(), int(b_mn), b.stride(0), out.data_ptr(), out.stride(0),
-           M, N, K, L.ptr(bias), L.ptr(residual), L.ptr(aux), epilogue, split_k, L.ptr(acc), L.ptr(col_stats), block_n, L.stream_ptr(dev))
-    if split_k > 1:
-        L.call("ddl_f32_to_bf16", acc.data_ptr(), out.data_ptr(), M * N, 0, L.stream_ptr(dev))
+        # fp32 accumulator of the split-K partial products.  Outside graph capture it is cached per shape and handed back
+        # zeroed by the conversion kernel (flag 2), which saves one memset kernel per split-K GEMM (100 per BERT-large step);
+        # buffers first needed during a capture are not cached (they would belong to that graph's memory pool).
+        key = (M, N, dev.index)
+        acc = _acc_cache.get(key)
+        if acc is None:
+            acc = torch.zeros(M, N, dtype=torch.float32, device=dev)
+            if not torch.cuda.is_current_stream_capturing():
+                _acc_cache[key] = acc
+        if key in _acc_cache:
+            rezero = 2
+    try:
+        L.call("ddl_gemm_bf16_ex", a.data_ptr(), int(a_mn), a.stride(0), b.data_ptr(), int(b_mn), b.stride(0), out.data_ptr(), out.stride(0),
+               M, N, K, L.ptr(bias), L.ptr(residual), L.ptr(aux), epilogue, split_k, L.ptr(acc), L.ptr(col_stats), block_n, L.stream_ptr(dev))
+        if split_k > 1:
+            L.call("ddl_f32_to_bf16", acc.data_ptr(), out.data_ptr(), M * N, rezero, L.stream_ptr(dev))
+    except Exception:
+        _acc_cache.pop((M, N, dev.index), None)  # never reuse an accumulator that may not be zero
+        raise
     return out
 
 

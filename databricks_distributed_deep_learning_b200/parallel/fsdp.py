@@ -24,6 +24,7 @@ On CPU / gloo (tests, BASELINE.json:7-style plumbing) the same schedule runs wit
 """
 from __future__ import annotations
 
+import os
 from contextlib import contextmanager
 from typing import Dict, Iterable, List, Optional, Sequence
 
@@ -111,7 +112,9 @@ class FullyShardedDataParallel(nn.Module):
         self.hyper = torch.tensor([lr, betas[0], betas[1], eps, weight_decay, 1.0, 0.0, 0.0], dtype=torch.float32, device=self.device)
         self._step = 1
         # bandwidth-bound kernels that also stream the optimizer state: one CTA per SM
-        self.comm_blocks = 148
+        # one comm CTA per SM; on a single GPU the fused kernel is a plain AdamW over ALL parameters and wants two
+        # CTAs per SM to cover the HBM latency (measured: 2.8 ms -> see BASELINE.md for 335 M parameters)
+        self.comm_blocks = int(os.environ.get("DDL_FSDP_COMM_BLOCKS", "296" if self.world_size == 1 else "148"))
         self._blk = {"num_blocks": 148} if hasattr(self.comm, "reduce_scatter_adamw_") else {}
         self._comm_stream = torch.cuda.Stream(self.device) if self.cuda else None
         self.require_backward_grad_sync = True

@@ -236,7 +236,9 @@ int ddl_allgather_gemm_bf16(const ddl_comm_t* comm, void* const* shard_ptrs, voi
 /* launch mode: 0 = auto (CTA pairs, tcgen05.mma.cta_group::2, 256x256 tiles, when eligible), 1 = one CTA per
  * tile, 2 = 2-CTA cluster sharing B by TMA multicast, 3 = same as 0 */
 int ddl_gemm_set_cluster(int cluster);
-int ddl_f32_to_bf16(const float* in, void* out, size_t numel, int accumulate, void* stream);
+/* flags: bit 0 = add to the existing bf16 output, bit 1 = write zeros back to `in` after reading it (a cached split-K
+ * accumulator is then ready for the next GEMM without a memset) */
+int ddl_f32_to_bf16(const float* in, void* out, size_t numel, int flags, void* stream);
 size_t ddl_colsum_scratch_bytes(int rows, int cols);
 /* out[c] = sum_r x[r,c] (bias gradients), deterministic two-stage fold */
 int ddl_colsum_bf16(const void* x, int rows, int cols, long long ld, void* out, void* scratch, size_t scratch_bytes, void* stream);
