@@ -784,17 +784,27 @@ __global__ void __launch_bounds__(256) colsum_partial_kernel(const bf16* __restr
     const int c = blockIdx.x * 256 + col;
     if (c < cols) partials[(size_t)blockIdx.y * cols + c] = a;
 }
-__global__ void colsum_final_kernel(const float* __restrict__ partials, int nparts, int cols, bf16* __restrict__ out) {
-    // 8 threads per column group fold `nparts` rows in parallel, then a shuffle folds the 8
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    const int c = t >> 3, sub = t & 7;
-    float a = 0.f;
-    if (c < cols)
-        for (int i = sub; i < nparts; i += 8) a += partials[(size_t)i * cols + c];
-    a += __shfl_xor_sync(0xffffffffu, a, 1);
-    a += __shfl_xor_sync(0xffffffffu, a, 2);
-    a += __shfl_xor_sync(0xffffffffu, a, 4);
-    if (c < cols && sub == 0) out[c] = __float2bfloat16(a);
+// grid = ceil(cols / 32), block = 256: lane = column (coalesced 128-byte rows), 8 warps fold `nparts` rows two at a time
+__global__ void __launch_bounds__(256) colsum_final_kernel(const float* __restrict__ partials, int nparts, int cols, bf16* __restrict__ out) {
+    __shared__ float sh[8][33];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + lane;
+    float a0 = 0.f, a1 = 0.f;
+    if (c < cols) {
+        int i = w;
+        for (; i + 8 < nparts; i += 16) {
+            a0 += partials[(size_t)i * cols + c];
+            a1 += partials[(size_t)(i + 8) * cols + c];
+        }
+        if (i < nparts) a0 += partials[(size_t)i * cols + c];
+    }
+    sh[w][lane] = a0 + a1;
+    __syncthreads();
+    if (w != 0 || c >= cols) return;
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc += sh[k][lane];
+    out[c] = __float2bfloat16(acc);
 }
 
 // ---------------------------------------------------------------------------- host side
@@ -1069,7 +1079,7 @@ DDL_API int ddl_colsum_bf16(const void* x, int rows, int cols, long long ld, voi
     cudaStream_t s = (cudaStream_t)stream_;
     colsum_partial_kernel<<<grid, 256, 0, s>>>((const bf16*)x, rows, cols, ld, (float*)scratch);
     DDL_LAUNCH_CHECK();
-    colsum_final_kernel<<<ddl_ceil_div((long long)cols * 8, 256), 256, 0, s>>>((const float*)scratch, parts, cols, (bf16*)out);
+    colsum_final_kernel<<<ddl_ceil_div(cols, 32), 256, 0, s>>>((const float*)scratch, parts, cols, (bf16*)out);
     DDL_LAUNCH_CHECK();
     return 0;
 }

@@ -201,22 +201,30 @@ __global__ void __launch_bounds__(kLnThreads, (VPL <= 3 ? 2 : 1)) ln_bwd_kernel(
     }
 }
 
-// grid = ceil(2H / 32), block = 256: 8 warps fold the per-block partial rows in parallel
-__global__ void __launch_bounds__(256) ln_bwd_finalize_kernel(const float* __restrict__ partials, int nblocks, int H,
-                                                              bf16* __restrict__ dgamma, bf16* __restrict__ dbeta,
-                                                              float* __restrict__ dgamma_f32, float* __restrict__ dbeta_f32) {
-    __shared__ float sh[8][33];
+// grid = ceil(2H / 32), block = 1024: 32 warps fold the per-block partial rows in parallel, four rows at a time with
+// independent accumulators (the loads are L2 hits whose latency is the whole cost of this kernel); fixed order
+constexpr int kLnFoldWarps = 32;
+__global__ void __launch_bounds__(kLnFoldWarps * 32) ln_bwd_finalize_kernel(const float* __restrict__ partials, int nblocks, int H,
+                                                                            bf16* __restrict__ dgamma, bf16* __restrict__ dbeta,
+                                                                            float* __restrict__ dgamma_f32, float* __restrict__ dbeta_f32) {
+    __shared__ float sh[kLnFoldWarps][33];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int i = blockIdx.x * 32 + lane;
-    float a = 0.f;
-    if (i < 2 * H)
-        for (int b = w; b < nblocks; b += 8) a += partials[(size_t)b * 2 * H + i];
-    sh[w][lane] = a;
+    float a[4] = {0.f, 0.f, 0.f, 0.f};
+    if (i < 2 * H) {
+        int b = w;
+        for (; b + 3 * kLnFoldWarps < nblocks; b += 4 * kLnFoldWarps) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) a[u] += partials[(size_t)(b + u * kLnFoldWarps) * 2 * H + i];
+        }
+        for (; b < nblocks; b += kLnFoldWarps) a[0] += partials[(size_t)b * 2 * H + i];
+    }
+    sh[w][lane] = (a[0] + a[1]) + (a[2] + a[3]);
     __syncthreads();
     if (w != 0 || i >= 2 * H) return;
     float acc = 0.f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) acc += sh[k][lane];
+    for (int k = 0; k < kLnFoldWarps; ++k) acc += sh[k][lane];
     if (i < H) {
         if (dgamma) dgamma[i] = __float2bfloat16(acc);
         if (dgamma_f32) dgamma_f32[i] = acc;
@@ -374,7 +382,7 @@ DDL_API int ddl_layernorm_bwd(const void* dy, const void* z, const float* mean, 
                                                                   (bf16*)dx, (float*)scratch, rows, H, d)));
     DDL_LAUNCH_CHECK();
     const bool f32 = param_grad_dtype == DDL_F32;
-    ln_bwd_finalize_kernel<<<ddl_ceil_div(2 * H, 32), 256, 0, s>>>((const float*)scratch, grid, H, f32 ? nullptr : (bf16*)dgamma,
+    ln_bwd_finalize_kernel<<<ddl_ceil_div(2 * H, 32), kLnFoldWarps * 32, 0, s>>>((const float*)scratch, grid, H, f32 ? nullptr : (bf16*)dgamma,
                                                                     f32 ? nullptr : (bf16*)dbeta, f32 ? (float*)dgamma : nullptr,
                                                                     f32 ? (float*)dbeta : nullptr);
     DDL_LAUNCH_CHECK();

@@ -122,11 +122,39 @@ def colsum(x: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def _wgrad(dy: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+# Where a weight's gradient should be written: id(parameter) -> (weak reference to it, 2-D bf16 view of its slot in the
+# flat gradient bucket), registered by the DDP / FSDP wrappers.  The weight-gradient GEMM then writes there directly,
+# autograd adopts that view as .grad, and the wrapper's gradient collection has nothing left to copy for this parameter.
+_grad_dest = {}
+
+
+def register_grad_destination(weight: torch.Tensor, view: torch.Tensor) -> None:
+    import weakref
+
+    if weight.dim() == 2 and view.dtype == torch.bfloat16 and view.shape == weight.shape and view.is_contiguous():
+        _grad_dest[id(weight)] = (weakref.ref(weight), view)
+
+
+def _grad_destination(weight: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    if weight is None or not _grad_dest:
+        return None
+    ent = _grad_dest.get(id(weight))
+    if ent is None or ent[0]() is not weight:
+        return None
+    # only when nothing has been accumulated yet (first backward after zero_grad(set_to_none=True))
+    return ent[1] if weight.grad is None else None
+
+
+def _wgrad(dy: torch.Tensor, x: torch.Tensor, weight: Optional[torch.Tensor] = None) -> torch.Tensor:
     """dW[N, Kin] = dy^T x  with dy [tok, N], x [tok, Kin]."""
     tok, N = dy.shape
     Kin = x.shape[1]
-    return gemm_nt(dy, x, N, Kin, tok, a_mn=True, b_mn=True, split_k=pick_split_k(N, Kin, tok))
+    out = _grad_destination(weight)
+    if out is not None and (out.shape[0] != N or out.shape[1] != Kin or out.device != dy.device):
+        out = None
+    dw = gemm_nt(dy, x, N, Kin, tok, a_mn=True, b_mn=True, split_k=pick_split_k(N, Kin, tok), out=out)
+    # a FRESH view object: autograd adopts a gradient without copying only if nobody else holds a reference to it
+    return dw if out is None else dw.view(N, Kin)
 
 
 class _Linear(torch.autograd.Function):
@@ -156,7 +184,7 @@ class _Linear(torch.autograd.Function):
         elif ctx.act == "relu":
             dy = dy * (saved > 0)
         dx = gemm_nt(dy, weight, M, K, N, b_mn=True) if ctx.needs_input_grad[0] else None
-        dw = _wgrad(dy, x) if ctx.needs_input_grad[1] else None
+        dw = _wgrad(dy, x, weight) if ctx.needs_input_grad[1] else None
         db = colsum(dy) if ctx.has_bias and ctx.needs_input_grad[2] else None
         return dx, dw, db, dres, None
 
@@ -197,10 +225,10 @@ class _FFN(torch.autograd.Function):
         M, H = x.shape
         I = w1.shape[0]
         O = w2.shape[0]
-        dw2 = _wgrad(dy, h)
+        dw2 = _wgrad(dy, h, w2)
         db2 = colsum(dy)
         dpre = gemm_nt(dy, w2, M, I, O, b_mn=True, aux=pre, epilogue=EPI_DGELU)  # (dy W2) * gelu'(pre)
-        dw1 = _wgrad(dpre, x)
+        dw1 = _wgrad(dpre, x, w1)
         db1 = colsum(dpre)
         dx = gemm_nt(dpre, w1, M, H, I, b_mn=True)
         return dx, dw1, db1, dw2, db2, (dy if ctx.has_res else None)

@@ -59,6 +59,15 @@ def _align(n: int, a: int) -> int:
     return (n + a - 1) // a * a
 
 
+def _register_grad_destination(p: torch.Tensor, view: torch.Tensor) -> None:
+    """Tell the linear-layer kernels where this parameter's gradient lives (ops/gemm.py::register_grad_destination)."""
+    try:
+        from ..ops import gemm as G
+    except Exception:  # native library not importable (CPU-only box)
+        return
+    G.register_grad_destination(p, view)
+
+
 def flat_view(flat: torch.Tensor, off: int, p: torch.Tensor) -> torch.Tensor:
     """View of ``flat[off : off + p.numel()]`` with ``p``'s shape AND memory layout.
 
@@ -184,6 +193,8 @@ class DistributedDataParallel(nn.Module):
                     p.data = pv
                 if gradient_as_bucket_view:
                     p.grad = view
+                    if p.is_cuda:
+                        _register_grad_destination(p, view)
                 p.register_post_accumulate_grad_hook(self._make_hook(p))
         if init_sync:
             self.sync_params_and_buffers()

@@ -33,7 +33,7 @@ import torch.nn as nn
 
 from . import process_group as pg
 from .comm import CommBackend, default_comm
-from .ddp import _SingleProcessComm, _align, flat_view
+from .ddp import _SingleProcessComm, _align, _register_grad_destination, flat_view
 
 
 class _Unit:
@@ -157,6 +157,8 @@ class FullyShardedDataParallel(nn.Module):
                 u.grad_views.append(flat_view(u.full_grad, off, p))
                 u.param_index[id(p)] = i
                 p.grad = u.grad_views[i]
+                if self.cuda:
+                    _register_grad_destination(p, u.grad_views[i])
                 self._param_unit[p] = u
                 p.register_post_accumulate_grad_hook(self._grad_hook)
             if self.cuda:

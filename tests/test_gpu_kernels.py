@@ -787,3 +787,39 @@ def test_attention_dropout_forward_backward_masks_agree_long_sequence():
     per_head_out = y.float().view(B, S, h, 64)[..., 0].sum(1)
     per_head_dv = x.grad.float()[:, :, 2, :, 0].sum(1)
     torch.testing.assert_close(per_head_dv, per_head_out, rtol=2e-2, atol=0.5)
+
+
+def test_linear_weight_gradient_is_written_into_the_flat_bucket():
+    """With DDP's flat gradient buckets the weight-gradient GEMM writes straight into the bucket view and autograd adopts
+    that memory as .grad (no copy left for the wrapper to do); results equal the unregistered path."""
+    from databricks_distributed_deep_learning_b200.ops import gemm as G
+    from databricks_distributed_deep_learning_b200.parallel.ddp import DistributedDataParallel
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.fc = torch.nn.Linear(256, 512)
+
+        def forward(self, x):
+            return G.linear(x, self.fc.weight, self.fc.bias)
+
+    torch.manual_seed(0)
+    net = Net().cuda().to(torch.bfloat16)
+    x = torch.randn(1024, 256, device="cuda").to(torch.bfloat16)
+    y = net(x)
+    y.float().square().mean().backward()
+    want = net.fc.weight.grad.detach().clone()
+    ddp = DistributedDataParallel(net, flatten_params=True)
+    ddp.zero_grad(set_to_none=True)
+    seen = {}
+    def _hook(p):
+        seen.setdefault("ptr", p.grad.data_ptr())
+
+    net.fc.weight.register_post_accumulate_grad_hook(_hook)
+    ddp(x).float().square().mean().backward()
+    b, i = ddp._param_to_bucket[net.fc.weight]
+    assert seen["ptr"] == b.views[i].data_ptr(), "autograd copied the gradient instead of adopting the bucket view"
+    torch.testing.assert_close(net.fc.weight.grad, want)
+    # second backward without zeroing: accumulates (the direct path must not overwrite)
+    ddp(x).float().square().mean().backward()
+    torch.testing.assert_close(net.fc.weight.grad.float(), 2 * want.float(), rtol=2e-2, atol=1e-4)
