@@ -35,7 +35,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 KERNELS_PER_CALL = {"ddl_bn_act_fwd_train": 3, "ddl_bn_act_fwd_train_mask": 3, "ddl_bn_act_fwd_eval": 2, "ddl_bn_act_bwd": 3,
-                    "ddl_bn_act_bwd_ex": 3, "ddl_bn_act_fwd_train_from_partials": 2, "ddl_stem_conv_fwd": 2, "ddl_stem_conv_wgrad": 2, "ddl_layernorm_bwd": 2,
+                    "ddl_bn_act_bwd_ex": 3, "ddl_embed_bwd": 4, "ddl_bn_act_fwd_train_from_partials": 2, "ddl_stem_conv_fwd": 2, "ddl_stem_conv_wgrad": 2, "ddl_layernorm_bwd": 2,
                     "ddl_cross_entropy": 2, "ddl_colsum_bf16": 2, "ddl_attention_bwd": 2}
 
 

@@ -82,6 +82,8 @@ _PROTOS = {
     "ddl_conv1x1_supported": ([_ll, _i, _i], _i),
     "ddl_conv1x1_grid": ([_ll, _i], _i),
     "ddl_conv1x1_fwd": ([_vp, _vp, _vp, _vp, _ll, _i, _i, _vp], _i),
+    "ddl_embed_bwd_scratch_bytes": ([_i, _i], _sz),
+    "ddl_embed_bwd": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i, _i, _i, _i, _i, _i, _vp], _i),
     "ddl_attention_fwd": ([_vp, _vp, _vp, _vp, _i, _i, _i, _f, _u64, _vp, _vp], _i),
     "ddl_attention_bwd_scratch_bytes": ([_i, _i, _i], _sz),
     "ddl_attention_bwd": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i, _i, _i, _f, _u64, _vp, _vp], _i),

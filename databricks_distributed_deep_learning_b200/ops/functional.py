@@ -173,15 +173,18 @@ class _EmbedLayerNorm(torch.autograd.Function):
         L.call("ddl_layernorm_bwd", dy.data_ptr(), z.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(), dz.data_ptr(),
                None, dgamma.data_ptr(), dbeta.data_ptr(), L.DDL_BF16, scratch.data_ptr(), scratch.numel(), rows, H, 0.0, 0, None,
                L.stream_ptr(dev))
-        # scatter-adds into the three tables: fp32 accumulation, then one cast (small next to the GEMMs)
-        dzf = dz.float()
-        dword = torch.zeros(V, H, dtype=torch.float32, device=dev).index_add_(0, ids.view(-1), dzf)
-        dpos = dzf.view(B, S, H).sum(0)
-        dpos_full = torch.zeros(P, H, dtype=torch.float32, device=dev)
-        dpos_full[:S] = dpos
-        dtype_ = torch.zeros(T, H, dtype=torch.float32, device=dev).index_add_(0, tts.view(-1), dzf)
+        # table gradients (csrc/embed_bwd.cu): word = fp32 scatter-add + one cast, position / type = deterministic sums
         bf = torch.bfloat16
-        return None, None, dword.to(bf), dpos_full.to(bf), dtype_.to(bf), dgamma, dbeta, None, None
+        dword_f = torch.zeros(V, H, dtype=torch.float32, device=dev)
+        dword = torch.empty(V, H, dtype=bf, device=dev)
+        dpos_full = torch.empty(P, H, dtype=bf, device=dev)
+        dtype_ = torch.empty(T, H, dtype=bf, device=dev)
+        scr = _scratch(L.lib().ddl_embed_bwd_scratch_bytes(H, T), dev)
+        st = L.stream_ptr(dev)
+        L.call("ddl_embed_bwd", dz.data_ptr(), ids.data_ptr(), tts.data_ptr(), dword_f.data_ptr(), dpos_full.data_ptr(), dtype_.data_ptr(),
+               scr.data_ptr(), scr.numel(), B, S, H, V, P, T, st)
+        L.call("ddl_f32_to_bf16", dword_f.data_ptr(), dword.data_ptr(), V * H, 0, st)
+        return None, None, dword, dpos_full, dtype_, dgamma, dbeta, None, None
 
 
 def embed_layernorm(ids, token_type_ids, word, pos, typ, gamma, beta, eps: float, p: float) -> torch.Tensor:

@@ -90,6 +90,11 @@ int ddl_embed_layernorm_fwd(const long long* ids, const long long* token_types, 
                             const void* type, const void* gamma, const void* beta, void* z_out, void* y, float* mean, float* rstd,
                             int rows, int S, int H, float eps, float dropout_p, unsigned long long seed,
                             const unsigned long long* seed_dev, void* stream);
+/* Gradients of the BERT embedding tables from dz [B*S, H] bf16 (csrc/embed_bwd.cu): dword_f32 [V, H] fp32 is accumulated
+ * into (zero it first; convert with ddl_f32_to_bf16), dpos [P, H] and dtype [T, H] bf16 are overwritten (T <= 4). */
+size_t ddl_embed_bwd_scratch_bytes(int H, int T);
+int ddl_embed_bwd(const void* dz, const long long* ids, const long long* token_types, float* dword_f32, void* dpos, void* dtype,
+                  void* scratch, size_t scratch_bytes, int B, int S, int H, int V, int P, int T, void* stream);
 int ddl_dropout(const void* in, void* out, size_t numel, float dropout_p, unsigned long long seed,
                 const unsigned long long* seed_dev, void* stream);
 
