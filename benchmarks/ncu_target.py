@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Short single-GPU programs for `ncu --set full` captures (one kernel family per mode).
 
-    python benchmarks/ncu_target.py gemm|attention|bn|ln|adamw|stem
+    python benchmarks/ncu_target.py gemm|attention|bn|ln|adamw|stem|conv1x1
 """
 import os
 import sys
@@ -74,6 +74,14 @@ def main():
         for _ in range(2):
             y, _ = OF.stem_conv(x, w)
             y.backward(torch.randn_like(y))
+    elif mode == "conv1x1":
+        from databricks_distributed_deep_learning_b200.ops import functional as OF
+
+        for cin, cout, hw in ((64, 256, 56), (256, 64, 56), (128, 512, 28)):
+            conv = torch.nn.Conv2d(cin, cout, 1, bias=False).cuda().to(bf).to(memory_format=torch.channels_last)
+            x = torch.randn(256, cin, hw, hw, device="cuda").to(bf).contiguous(memory_format=torch.channels_last)
+            for _ in range(2):
+                OF._Conv1x1WS.apply(x, conv.weight)
     torch.cuda.synchronize()
     print("ok", mode)
 
