@@ -20,12 +20,17 @@ Execution paths:
 from __future__ import annotations
 
 import math
+import os
 from dataclasses import dataclass
 from typing import Optional
 
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
+
+
+# fused path: sum the two gradients of each residual stream in GEMM epilogues (ops/gemm.py::GradSlot); 0 = autograd adds
+_FUSE_RESIDUAL_GRAD = os.environ.get("DDL_BERT_FUSE_RESIDUAL_GRAD", "1") != "0"
 
 
 @dataclass
@@ -218,21 +223,25 @@ class BertLayer(nn.Module):
         sa, so = self.attention.self, self.attention.output
         p_h = so.p_drop if self.training else 0.0
         p_a = sa.p_drop if self.training else 0.0
-        qkv = G.linear(x2, sa.qkv_weight, sa.qkv_bias)
+        # the two gradients of each residual stream are summed in GEMM epilogues, not by autograd (ops/gemm.py::GradSlot)
+        fuse = _FUSE_RESIDUAL_GRAD and torch.is_grad_enabled() and x2.requires_grad
+        slot1 = G.GradSlot() if fuse else None
+        slot2 = G.GradSlot() if fuse else None
+        qkv = G.linear(x2, sa.qkv_weight, sa.qkv_bias, input_grad_slot=slot1)
         ctx = OF.attention_qkvpacked(qkv.view(B, S, 3, sa.num_heads, sa.head_dim), seqlens, p_a).reshape(B * S, H)
         ln1, ln2 = so.LayerNorm, self.output.LayerNorm
         if p_h == 0.0:
-            z = G.linear(ctx, so.dense.weight, so.dense.bias, residual=x2)
+            z = G.linear(ctx, so.dense.weight, so.dense.bias, residual=x2, residual_grad_slot=slot1)
             a = OF.layernorm(z, ln1.weight, ln1.bias, ln1.eps)
             z2 = G.ffn(a, self.intermediate.dense.weight, self.intermediate.dense.bias, self.output.dense.weight,
                        self.output.dense.bias, residual=a)
             out = OF.layernorm(z2, ln2.weight, ln2.bias, ln2.eps)
         else:
             y = G.linear(ctx, so.dense.weight, so.dense.bias)
-            a = OF.dropout_add_layernorm(y, x2, ln1.weight, ln1.bias, ln1.eps, p_h)
+            a = OF.dropout_add_layernorm(y, x2, ln1.weight, ln1.bias, ln1.eps, p_h, residual_grad_slot=slot1)
             y2 = G.ffn(a, self.intermediate.dense.weight, self.intermediate.dense.bias, self.output.dense.weight,
-                       self.output.dense.bias)
-            out = OF.dropout_add_layernorm(y2, a, ln2.weight, ln2.bias, ln2.eps, p_h)
+                       self.output.dense.bias, input_grad_slot=slot2)
+            out = OF.dropout_add_layernorm(y2, a, ln2.weight, ln2.bias, ln2.eps, p_h, residual_grad_slot=slot2)
         return out.view(B, S, H)
 
 

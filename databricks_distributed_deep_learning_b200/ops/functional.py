@@ -85,7 +85,8 @@ def cross_entropy(logits: torch.Tensor, labels: torch.Tensor, ignore_index: int 
 # ----------------------------------------------------------------------------- layer norm
 class _AddLayerNorm(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, residual, gamma, beta, eps, p):
+    def forward(ctx, x, residual, gamma, beta, eps, p, res_slot=None):
+        ctx.res_slot = res_slot
         _req_bf16(x, residual, gamma, beta)
         x = x.contiguous()
         rows, H = x.shape
@@ -120,12 +121,17 @@ class _AddLayerNorm(torch.autograd.Function):
         L.call("ddl_layernorm_bwd", dy.data_ptr(), z.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(), dz.data_ptr(),
                L.ptr(dx), dgamma.data_ptr(), dbeta.data_ptr(), L.DDL_BF16, scratch.data_ptr(), scratch.numel(), rows, H,
                float(ctx.p), ctx.salt, L.ptr(sw), L.stream_ptr(dev))
-        return (dx if dx is not None else dz), (dz if ctx.has_res else None), dgamma, dbeta, None, None
+        dres = dz if (ctx.has_res and ctx.needs_input_grad[1]) else None
+        if dres is not None and ctx.res_slot is not None:
+            ctx.res_slot.put(dres)  # added in the epilogue of the data-gradient GEMM that owns the slot (ops/gemm.py::GradSlot)
+            dres = None
+        return (dx if dx is not None else dz), dres, dgamma, dbeta, None, None, None
 
 
-def dropout_add_layernorm(x, residual, gamma, beta, eps: float = 1e-12, p: float = 0.0) -> torch.Tensor:
-    """``F.layer_norm(F.dropout(x, p) + residual, (H,), gamma, beta, eps)`` on [rows, H] bf16 (K10)."""
-    return _AddLayerNorm.apply(x, residual, gamma, beta, eps, p)
+def dropout_add_layernorm(x, residual, gamma, beta, eps: float = 1e-12, p: float = 0.0, residual_grad_slot=None) -> torch.Tensor:
+    """``F.layer_norm(F.dropout(x, p) + residual, (H,), gamma, beta, eps)`` on [rows, H] bf16 (K10).
+    ``residual_grad_slot``: the gradient of ``residual`` is handed to that :class:`ops.gemm.GradSlot` instead of autograd."""
+    return _AddLayerNorm.apply(x, residual, gamma, beta, eps, p, residual_grad_slot)
 
 
 def layernorm(x, gamma, beta, eps: float = 1e-12) -> torch.Tensor:

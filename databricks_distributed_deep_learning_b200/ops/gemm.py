@@ -157,9 +157,47 @@ def _wgrad(dy: torch.Tensor, x: torch.Tensor, weight: Optional[torch.Tensor] = N
     return dw if out is None else dw.view(N, Kin)
 
 
+class GradSlot:
+    """Hand-over point for the gradient of a residual connection.
+
+    In ``z = LN(f(x) + x)`` the tensor ``x`` receives two gradients: one through ``f`` (a linear layer's data gradient,
+    a GEMM) and one through the skip.  Instead of letting autograd sum them with an elementwise kernel, the op that
+    produces the skip gradient (LayerNorm backward, or a linear layer whose epilogue added the residual) ``put``s it
+    here and reports "no gradient" for that input; the linear layer at the head of ``f`` - whose backward always runs
+    later - ``take``s it and adds it in the epilogue of its data-gradient GEMM.  A slot still full when the backward
+    pass ends means a gradient was dropped: the pass raises."""
+
+    __slots__ = ("grad",)
+    _pending = set()
+
+    def __init__(self):
+        self.grad = None
+
+    def put(self, g: torch.Tensor) -> None:
+        if not GradSlot._pending:
+            torch.autograd.Variable._execution_engine.queue_callback(GradSlot._check_all_taken)
+        self.grad = g
+        GradSlot._pending.add(self)
+
+    def take(self) -> Optional[torch.Tensor]:
+        g, self.grad = self.grad, None
+        GradSlot._pending.discard(self)
+        return g
+
+    @staticmethod
+    def _check_all_taken() -> None:
+        left = [s for s in GradSlot._pending if s.grad is not None]
+        for s in left:
+            s.grad = None
+        GradSlot._pending.clear()
+        if left:
+            raise L.DdlError(f"GradSlot: {len(left)} residual gradient(s) were never added to a data gradient "
+                             "(the slot's consumer did not run in this backward pass)")
+
+
 class _Linear(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, residual, act):
+    def forward(ctx, x, weight, bias, residual, act, in_slot=None, res_slot=None):
         x = x.contiguous()
         M, K = x.shape
         N = weight.shape[0]
@@ -168,6 +206,7 @@ class _Linear(torch.autograd.Function):
         y = gemm_nt(x, weight, M, N, K, bias=bias, residual=residual, aux=pre, epilogue=epi)
         ctx.save_for_backward(x, weight, pre if act == "gelu" else (y if act == "relu" else None))
         ctx.act, ctx.has_bias, ctx.has_res = act, bias is not None, residual is not None
+        ctx.in_slot, ctx.res_slot = in_slot, res_slot
         return y
 
     @staticmethod
@@ -177,16 +216,22 @@ class _Linear(torch.autograd.Function):
         dy = dy.contiguous()
         M, K = x.shape
         N = weight.shape[0]
-        dres = dy if ctx.has_res else None
+        dres = dy if (ctx.has_res and ctx.needs_input_grad[3]) else None
+        if dres is not None and ctx.res_slot is not None:
+            ctx.res_slot.put(dres)  # summed into the data gradient of the layer that consumes the slot
+            dres = None
         if ctx.act == "gelu":
             # elementwise dGELU on the incoming gradient (the fused form lives in `ffn`)
             dy = _dgelu_mul(dy, saved)
         elif ctx.act == "relu":
             dy = dy * (saved > 0)
-        dx = gemm_nt(dy, weight, M, K, N, b_mn=True) if ctx.needs_input_grad[0] else None
+        addend = ctx.in_slot.take() if ctx.in_slot is not None else None
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm_nt(dy, weight, M, K, N, b_mn=True, residual=addend)  # + skip gradient in the epilogue
         dw = _wgrad(dy, x, weight) if ctx.needs_input_grad[1] else None
         db = colsum(dy) if ctx.has_bias and ctx.needs_input_grad[2] else None
-        return dx, dw, db, dres, None
+        return dx, dw, db, dres, None, None, None
 
 
 def _dgelu_mul(dy: torch.Tensor, pre: torch.Tensor) -> torch.Tensor:
@@ -196,9 +241,12 @@ def _dgelu_mul(dy: torch.Tensor, pre: torch.Tensor) -> torch.Tensor:
 
 
 def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, activation: Optional[str] = None,
-           residual: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """``act(x @ weight.T + bias) + residual`` on [M, K] bf16 rows, all in one kernel."""
-    return _Linear.apply(x, weight, bias, residual, activation)
+           residual: Optional[torch.Tensor] = None, input_grad_slot: Optional[GradSlot] = None,
+           residual_grad_slot: Optional[GradSlot] = None) -> torch.Tensor:
+    """``act(x @ weight.T + bias) + residual`` on [M, K] bf16 rows, all in one kernel.  ``input_grad_slot``: a skip
+    gradient put there during backward is added to d(x) in the GEMM epilogue; ``residual_grad_slot``: the gradient of
+    ``residual`` is put there instead of being returned to autograd (see :class:`GradSlot`)."""
+    return _Linear.apply(x, weight, bias, residual, activation, input_grad_slot, residual_grad_slot)
 
 
 class _FFN(torch.autograd.Function):
@@ -206,7 +254,8 @@ class _FFN(torch.autograd.Function):
     dGELU fused into the epilogue of the dgrad of the second linear."""
 
     @staticmethod
-    def forward(ctx, x, w1, b1, w2, b2, residual):
+    def forward(ctx, x, w1, b1, w2, b2, residual, in_slot=None, res_slot=None):
+        ctx.res_is_input = residual is x  # out = f(x) + x: both gradients of x are summed in the last dgrad epilogue
         x = x.contiguous()
         M, H = x.shape
         I = w1.shape[0]
@@ -215,6 +264,7 @@ class _FFN(torch.autograd.Function):
         y = gemm_nt(h, w2, M, w2.shape[0], I, bias=b2, residual=residual)
         ctx.save_for_backward(x, w1, w2, pre, h)
         ctx.has_res = residual is not None
+        ctx.in_slot, ctx.res_slot = in_slot, res_slot
         return y
 
     @staticmethod
@@ -230,12 +280,21 @@ class _FFN(torch.autograd.Function):
         dpre = gemm_nt(dy, w2, M, I, O, b_mn=True, aux=pre, epilogue=EPI_DGELU)  # (dy W2) * gelu'(pre)
         dw1 = _wgrad(dpre, x, w1)
         db1 = colsum(dpre)
-        dx = gemm_nt(dpre, w1, M, H, I, b_mn=True)
-        return dx, dw1, db1, dw2, db2, (dy if ctx.has_res else None)
+        dres = dy if (ctx.has_res and ctx.needs_input_grad[5]) else None
+        addend = ctx.in_slot.take() if ctx.in_slot is not None else None
+        if dres is not None and ctx.res_is_input and addend is None and ctx.needs_input_grad[0]:
+            addend, dres = dres, None  # the skip gradient of x rides in the epilogue of d(x)
+        elif dres is not None and ctx.res_slot is not None:
+            ctx.res_slot.put(dres)
+            dres = None
+        dx = gemm_nt(dpre, w1, M, H, I, b_mn=True, residual=addend) if ctx.needs_input_grad[0] else None
+        return dx, dw1, db1, dw2, db2, dres, None, None
 
 
-def ffn(x, w1, b1, w2, b2, residual=None) -> torch.Tensor:
-    return _FFN.apply(x, w1, b1, w2, b2, residual)
+def ffn(x, w1, b1, w2, b2, residual=None, input_grad_slot: Optional[GradSlot] = None,
+        residual_grad_slot: Optional[GradSlot] = None) -> torch.Tensor:
+    """``gelu(x W1^T + b1) W2^T + b2 (+ residual)``; the slots work as in :func:`linear`."""
+    return _FFN.apply(x, w1, b1, w2, b2, residual, input_grad_slot, residual_grad_slot)
 
 
 # ----------------------------------------------------------------------------- K6: all-gather fused into the GEMM

@@ -823,3 +823,35 @@ def test_linear_weight_gradient_is_written_into_the_flat_bucket():
     # second backward without zeroing: accumulates (the direct path must not overwrite)
     ddp(x).float().square().mean().backward()
     torch.testing.assert_close(net.fc.weight.grad.float(), 2 * want.float(), rtol=2e-2, atol=1e-4)
+
+
+@pytest.mark.parametrize("dropout", [0.0, 0.1])
+def test_bert_residual_gradients_summed_in_gemm_epilogues(dropout):
+    """GradSlot: the skip-connection gradients ride in the epilogue of the data-gradient GEMMs; same result as autograd's adds."""
+    from databricks_distributed_deep_learning_b200.models import bert as BM
+    from databricks_distributed_deep_learning_b200.models import bert_tiny, prepare_for_fused
+    from databricks_distributed_deep_learning_b200.ops import _lib as L
+    from databricks_distributed_deep_learning_b200.ops import functional as OF
+
+    def run(fuse):
+        torch.manual_seed(5)
+        m = bert_tiny(hidden_dropout_prob=dropout, attention_probs_dropout_prob=dropout)
+        m.set_impl("fused")
+        m = prepare_for_fused(m, "cuda")
+        OF.manual_seed(1234, torch.device("cuda", 0))
+        OF._salt_counter = __import__("itertools").count(1)  # same per-op dropout salts in both runs
+        ids = torch.randint(1, 512, (4, 128), device="cuda")
+        old = BM._FUSE_RESIDUAL_GRAD
+        BM._FUSE_RESIDUAL_GRAD = fuse
+        try:
+            logits = m(input_ids=ids, attention_mask=torch.ones_like(ids), token_type_ids=torch.zeros_like(ids))
+            logits.float().square().mean().backward()
+        finally:
+            BM._FUSE_RESIDUAL_GRAD = old
+        return {k: p.grad.detach().float().clone() for k, p in m.named_parameters() if p.grad is not None}
+
+    a, b = run(False), run(True)
+    assert a.keys() == b.keys()
+    for k in a:
+        denom = a[k].abs().max().clamp_min(1e-6)
+        assert float((a[k] - b[k]).abs().max() / denom) < 5e-2, k
