@@ -26,11 +26,10 @@
 #include <stdlib.h>
 #include <string.h>
 
-#include <mutex>
-
 #include "../include/b200ddl.h"
 #include "common.cuh"
 #include "tcgen05.cuh"
+#include "tma_host.h"
 
 using namespace tc;
 
@@ -794,30 +793,9 @@ __global__ void attn_dq_convert_kernel(const float* __restrict__ acc, bf16* __re
 }
 
 // ---------------------------------------------------------------------------- host
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-EncodeTiledFn g_encode = nullptr;
-std::once_flag g_once;
-
 int make_tile_map(CUtensorMap* map, const void* ptr, long long rows, long long cols) {
-    std::call_once(g_once, [] {
-        void* fn = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-            g_encode = (EncodeTiledFn)fn;
-    });
-    DDL_REQUIRE(g_encode != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
-    DDL_REQUIRE(((uintptr_t)ptr & 15) == 0 && cols % 8 == 0, "attention: operand must be 16-byte aligned with a pitch multiple of 8");
-    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    cuuint64_t gstride[1] = {(cuuint64_t)cols * 2};
-    cuuint32_t box[2] = {64u, 128u};
-    cuuint32_t estr[2] = {1u, 1u};
-    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    DDL_REQUIRE(r == CUDA_SUCCESS, "attention: cuTensorMapEncodeTiled failed (%d)", (int)r);
-    return 0;
+    DDL_REQUIRE(cols % 8 == 0, "attention: operand pitch must be a multiple of 8 elements");
+    return tma_host::encode_2d(map, ptr, rows, cols, cols * 2, 128, "attention");
 }
 
 int fill_params(AttnParams* p, int B, int S, int heads, const int* seqlens, float dropout_p, unsigned long long seed,

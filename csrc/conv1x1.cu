@@ -19,11 +19,10 @@
 // 1.05 - 1.4x of their floors).
 #include <cuda.h>
 
-#include <mutex>
-
 #include "../include/b200ddl.h"
 #include "common.cuh"
 #include "tcgen05.cuh"
+#include "tma_host.h"
 
 namespace {
 using namespace tc;
@@ -222,36 +221,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv1x1_fwd_kernel(const __grid_c
 }
 
 // ------------------------------------------------------------------------------------------------ host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-EncodeTiledFn g_encode = nullptr;
-std::once_flag g_encode_once;
-
-int get_encode() {
-    std::call_once(g_encode_once, [] {
-        void* fn = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-            g_encode = (EncodeTiledFn)fn;
-    });
-    DDL_REQUIRE(g_encode != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
-    return 0;
-}
-
 // row-major bf16 [rows, cols]; box [box_rows x 64 cols], 128B swizzle
 int make_map(CUtensorMap* map, const void* base, long long rows, long long cols, int box_rows) {
-    DDL_REQUIRE(((uintptr_t)base & 15) == 0, "conv1x1: pointer must be 16-byte aligned");
-    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    cuuint64_t gstride[1] = {(cuuint64_t)cols * 2};
-    cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
-    cuuint32_t estr[2] = {1u, 1u};
-    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    DDL_REQUIRE(r == CUDA_SUCCESS, "conv1x1: cuTensorMapEncodeTiled failed with CUresult %d (rows %lld cols %lld box %d)", (int)r, rows,
-                cols, box_rows);
-    return 0;
+    return tma_host::encode_2d(map, base, rows, cols, cols * 2, box_rows, "conv1x1");
 }
 
 bool shape_ok(long long M, int N, int K) {
@@ -275,7 +247,6 @@ DDL_API int ddl_conv1x1_grid(long long M, int N) {
 DDL_API int ddl_conv1x1_fwd(const void* x, const void* w, void* y, float* partials, long long M, int N, int K, void* stream_) {
     DDL_REQUIRE(shape_ok(M, N, K), "conv1x1: unsupported shape M=%lld N=%d K=%d (N, K in {64,128,256,512}, N*K <= 65536)", M, N, K);
     DDL_REQUIRE(x && w && y && partials, "conv1x1: null pointer");
-    if (int e = get_encode()) return e;
     C1Params p;
     p.y = (bf16*)y;
     p.partials = partials;

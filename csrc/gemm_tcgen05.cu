@@ -28,6 +28,7 @@
 #include "../include/b200ddl.h"
 #include "common.cuh"
 #include "tcgen05.cuh"
+#include "tma_host.h"
 
 namespace {
 
@@ -808,38 +809,10 @@ __global__ void __launch_bounds__(256) colsum_final_kernel(const float* __restri
 }
 
 // ---------------------------------------------------------------------------- host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-EncodeTiledFn g_encode = nullptr;
-std::once_flag g_encode_once;
-
-int get_encode() {
-    std::call_once(g_encode_once, [] {
-        void* fn = nullptr;
-        cudaDriverEntryPointQueryResult qres;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
-            qres == cudaDriverEntryPointSuccess)
-            g_encode = (EncodeTiledFn)fn;
-    });
-    DDL_REQUIRE(g_encode != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
-    return 0;
-}
-
 // 2-D bf16 row-major tensor [rows, cols] with pitch `ld` elements; box = [box_rows, 64 cols], 128B swizzle
 int make_map(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld, int box_rows) {
-    DDL_REQUIRE(((uintptr_t)ptr & 15) == 0, "gemm: operand pointer must be 16-byte aligned");
     DDL_REQUIRE((ld * 2) % 16 == 0, "gemm: operand pitch (%lld elements) must be a multiple of 8", ld);
-    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
-    cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
-    cuuint32_t estr[2] = {1u, 1u};
-    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    DDL_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (rows %lld cols %lld ld %lld box %d)", (int)r, rows,
-                cols, ld, box_rows);
-    return 0;
+    return tma_host::encode_2d(map, ptr, rows, cols, ld * 2, box_rows, "gemm");
 }
 
 template <int BN, bool A_MN, bool B_MN, int kCluster>
@@ -909,7 +882,6 @@ DDL_API int ddl_gemm_bf16(const void* A, int a_mn, long long lda, const void* B,
 DDL_API int ddl_gemm_bf16_ex(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb, void* C, long long ldc, int M,
                              int N, int K, const void* bias, const void* residual, void* aux, int epilogue, int split_k, float* acc_f32,
                              float* col_stats, int block_n, void* stream_) {
-    if (int e = get_encode()) return e;
     DDL_REQUIRE(col_stats == nullptr || split_k == 1, "gemm: column statistics need split_k == 1");
     DDL_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem");
     DDL_REQUIRE(N % 8 == 0 && K % 8 == 0, "gemm: N (%d) and K (%d) must be multiples of 8", N, K);
@@ -992,7 +964,6 @@ DDL_API int ddl_gemm_bf16_ex(const void* A, int a_mn, long long lda, const void*
 DDL_API int ddl_allgather_gemm_bf16(const ddl_comm_t* comm, void* const* shard_ptrs, void* full_w, void* flags, const void* A, long long lda,
                                     void* C, long long ldc, int M, int N, int K, const void* bias, const void* residual, void* aux,
                                     int epilogue, void* stream_) {
-    if (int e = get_encode()) return e;
     DDL_REQUIRE(comm && shard_ptrs && full_w && flags && A && C, "allgather_gemm: null pointer");
     DDL_REQUIRE(comm->world >= 1 && comm->world <= DDL_MAX_WORLD, "allgather_gemm: bad world size");
     DDL_REQUIRE(N % (comm->world * 128) == 0, "allgather_gemm: N (%d) must be a multiple of world * 128", N);

@@ -28,11 +28,10 @@
 // partials in fixed order and scatters them to the [64, 3, 7, 7] gradient.
 #include <cuda.h>
 
-#include <mutex>
-
 #include "../include/b200ddl.h"
 #include "common.cuh"
 #include "tcgen05.cuh"
+#include "tma_host.h"
 
 namespace {
 using namespace tc;
@@ -433,37 +432,9 @@ __global__ void stem_wgrad_finalize_kernel(const float* __restrict__ partials, i
 }
 
 // ------------------------------------------------------------------------------------------------ host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-EncodeTiledFn g_encode = nullptr;
-std::once_flag g_encode_once;
-
-int get_encode() {
-    std::call_once(g_encode_once, [] {
-        void* fn = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-            g_encode = (EncodeTiledFn)fn;
-    });
-    DDL_REQUIRE(g_encode != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
-    return 0;
-}
-
 // [rows x 64] bf16 with row pitch `pitch_bytes` (32 for the overlapping im2col rows of z), box [box_rows x 64], 128B swizzle
 int make_rows_map(CUtensorMap* map, const void* base, long long rows, long long pitch_bytes, int box_rows) {
-    DDL_REQUIRE(((uintptr_t)base & 15) == 0, "stem conv: pointer must be 16-byte aligned");
-    DDL_REQUIRE(rows >= 1 && box_rows >= 1 && box_rows <= 256, "stem conv: bad tensor-map geometry (rows %lld, box %d)", rows, box_rows);
-    cuuint64_t gdim[2] = {64u, (cuuint64_t)rows};
-    cuuint64_t gstride[1] = {(cuuint64_t)pitch_bytes};
-    cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
-    cuuint32_t estr[2] = {1u, 1u};
-    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    DDL_REQUIRE(r == CUDA_SUCCESS, "stem conv: cuTensorMapEncodeTiled failed with CUresult %d (rows %lld pitch %lld box %d)", (int)r, rows,
-                pitch_bytes, box_rows);
-    return 0;
+    return tma_host::encode_2d(map, base, rows, 64, pitch_bytes, box_rows, "stem conv");
 }
 
 int check_geom(int N, int H, int W) {
@@ -508,7 +479,6 @@ DDL_API int ddl_stem_s2d(const void* x, int x_dtype, void* z, int N, int H, int 
 DDL_API int ddl_stem_conv_fwd(const void* z, const void* w, long long sk, long long sc, long long sr, long long ss, void* w2, void* y,
                               float* partials, int N, int H, int W, void* stream_) {
     if (int e = check_geom(N, H, W)) return e;
-    if (int e = get_encode()) return e;
     DDL_REQUIRE(z && w && w2 && y && partials, "stem fwd: null pointer");
     cudaStream_t s = (cudaStream_t)stream_;
     stem_pack_w_kernel<<<(kTaps * kCout * 64 + 255) / 256, 256, 0, s>>>((const bf16*)w, sk, sc, sr, ss, (bf16*)w2);
@@ -538,7 +508,6 @@ DDL_API int ddl_stem_conv_fwd(const void* z, const void* w, long long sk, long l
 DDL_API int ddl_stem_conv_wgrad(const void* z, const void* dy, void* dw, long long sk, long long sc, long long sr, long long ss,
                                 void* scratch, size_t scratch_bytes, int N, int H, int W, void* stream_) {
     if (int e = check_geom(N, H, W)) return e;
-    if (int e = get_encode()) return e;
     DDL_REQUIRE(z && dy && dw && scratch, "stem wgrad: null pointer");
     DDL_REQUIRE(scratch_bytes >= ddl_stem_wgrad_scratch_bytes(N, H, W), "stem wgrad: scratch too small");
     StemWgradParams p;
