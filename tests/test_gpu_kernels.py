@@ -855,3 +855,33 @@ def test_bert_residual_gradients_summed_in_gemm_epilogues(dropout):
     for k in a:
         denom = a[k].abs().max().clamp_min(1e-6)
         assert float((a[k] - b[k]).abs().max() / denom) < 5e-2, k
+
+
+def test_b200_inference_runner_matches_eager_fp32():
+    """Export/inference comparison (reference notebook): the B200 runner (bf16, BN folded, CUDA graph)
+    agrees with eager fp32 on the class ranking and on the logits within bf16 accuracy."""
+    from databricks_distributed_deep_learning_b200.models import resnet50
+    from databricks_distributed_deep_learning_b200.utils.export import B200Runner, EagerRunner
+
+    torch.manual_seed(0)
+    model = resnet50().eval()
+    for m in model.modules():  # non-trivial statistics so that the BN folding is really exercised
+        if isinstance(m, torch.nn.BatchNorm2d):
+            m.running_mean.normal_(0, 0.1)
+            m.running_var.uniform_(0.5, 1.5)
+    x = torch.randn(1, 3, 224, 224)
+    eager = EagerRunner(model, "cpu")
+    eager.prepare()
+    want = eager(x)
+    r = B200Runner(model)
+    assert r.available()
+    r.prepare()
+    got = r(x)
+    got2 = r(x)
+    assert got.shape == want.shape == (1, 1000)
+    assert (got == got2).all()  # graph replay is deterministic
+    import numpy as np
+
+    scale = np.abs(want).max()
+    assert np.abs(got - want).max() < 0.08 * scale, (np.abs(got - want).max(), scale)
+    assert np.corrcoef(got.ravel(), want.ravel())[0, 1] > 0.99
