@@ -35,7 +35,7 @@ __device__ __forceinline__ void apply_dropout8(float (&f)[8], const DropCfg& d, 
 
 // z = dropout(x) + residual ; y = LN(z) * gamma + beta
 template <int VPL>
-__global__ void __launch_bounds__(kLnThreads) add_ln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ residual,
+__global__ void __launch_bounds__(kLnThreads, (VPL <= 3 ? 3 : (VPL <= 6 ? 2 : 1))) add_ln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ residual,
                                                                 const bf16* __restrict__ gamma, const bf16* __restrict__ beta,
                                                                 bf16* __restrict__ z_out, bf16* __restrict__ y,
                                                                 float* __restrict__ mean_out, float* __restrict__ rstd_out,
@@ -47,6 +47,17 @@ __global__ void __launch_bounds__(kLnThreads) add_ln_fwd_kernel(const bf16* __re
     for (long long row = (long long)blockIdx.x * kWarpsPerBlock + warp; row < rows; row += (long long)gridDim.x * kWarpsPerBlock) {
         float v[VPL][8];
         float s = 0.f;
+        // every load of the row is issued before any arithmetic (2 * VPL independent 16-byte requests per lane)
+        uint4 xv[VPL], rv[VPL];
+#pragma unroll
+        for (int k = 0; k < VPL; ++k) {
+            const int c = lane + 32 * k;
+            if (c < nv) {
+                const size_t off = (size_t)row * H + c * 8;
+                xv[k] = ld_stream_v4(x + off);
+                if (residual) rv[k] = ld_stream_v4(residual + off);
+            }
+        }
 #pragma unroll
         for (int k = 0; k < VPL; ++k) {
             const int c = lane + 32 * k;
@@ -54,11 +65,11 @@ __global__ void __launch_bounds__(kLnThreads) add_ln_fwd_kernel(const bf16* __re
             for (int j = 0; j < 8; ++j) v[k][j] = 0.f;
             if (c < nv) {
                 const size_t off = (size_t)row * H + c * 8;
-                bf16x8_to_float(ld_stream_v4(x + off), v[k]);
+                bf16x8_to_float(xv[k], v[k]);
                 if (drop.thr) apply_dropout8(v[k], drop, ((size_t)row * nv + c));
                 if (residual) {
                     float r[8];
-                    bf16x8_to_float(ld_stream_v4(residual + off), r);
+                    bf16x8_to_float(rv[k], r);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) v[k][j] += r[j];
                 }
@@ -326,9 +337,9 @@ DropCfg make_drop(float p, unsigned long long seed, const unsigned long long* se
     return d;
 }
 
-int ln_grid(int rows) {
+int ln_grid(int rows, int per_sm = 2) {
     int blocks = ddl_ceil_div(rows, kWarpsPerBlock);
-    const int cap = DDL_SM_COUNT * 2;
+    const int cap = DDL_SM_COUNT * per_sm;
     return blocks > cap ? cap : (blocks < 1 ? 1 : blocks);
 }
 
@@ -357,7 +368,7 @@ DDL_API int ddl_add_layernorm_fwd(const void* x, const void* residual, const voi
     DDL_REQUIRE(x && gamma && beta && y && mean && rstd, "layernorm fwd: null pointer");
     if (rows == 0) return 0;
     const DropCfg d = make_drop(dropout_p, seed, seed_dev);
-    const int grid = ln_grid(rows);
+    const int grid = ln_grid(rows, H <= 768 ? 3 : 2);  // matches the launch bounds (VPL <= 3: three blocks per SM)
     cudaStream_t s = (cudaStream_t)stream_;
     LN_DISPATCH(H, (add_ln_fwd_kernel<VPL><<<grid, kLnThreads, 0, s>>>((const bf16*)x, (const bf16*)residual, (const bf16*)gamma,
                                                                       (const bf16*)beta, (bf16*)z_out, (bf16*)y, mean, rstd, rows, H, eps, d)));
