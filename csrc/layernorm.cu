@@ -35,7 +35,7 @@ __device__ __forceinline__ void apply_dropout8(float (&f)[8], const DropCfg& d, 
 
 // z = dropout(x) + residual ; y = LN(z) * gamma + beta
 template <int VPL>
-__global__ void __launch_bounds__(kLnThreads, (VPL <= 3 ? 3 : (VPL <= 6 ? 2 : 1))) add_ln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ residual,
+__global__ void __launch_bounds__(kLnThreads, (VPL <= 4 ? 2 : 1)) add_ln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ residual,
                                                                 const bf16* __restrict__ gamma, const bf16* __restrict__ beta,
                                                                 bf16* __restrict__ z_out, bf16* __restrict__ y,
                                                                 float* __restrict__ mean_out, float* __restrict__ rstd_out,
@@ -44,20 +44,29 @@ __global__ void __launch_bounds__(kLnThreads, (VPL <= 3 ? 3 : (VPL <= 6 ? 2 : 1)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nv = H >> 3;
     const float inv_h = 1.f / (float)H;
-    for (long long row = (long long)blockIdx.x * kWarpsPerBlock + warp; row < rows; row += (long long)gridDim.x * kWarpsPerBlock) {
-        float v[VPL][8];
-        float s = 0.f;
-        // every load of the row is issued before any arithmetic (2 * VPL independent 16-byte requests per lane)
-        uint4 xv[VPL], rv[VPL];
+    // software pipeline across rows: the loads of the next row are in flight while this one is reduced and stored
+    const long long stride = (long long)gridDim.x * kWarpsPerBlock;
+    long long row = (long long)blockIdx.x * kWarpsPerBlock + warp;
+    uint4 xv[VPL], rv[VPL];
+    auto load_row = [&](long long r, uint4 (&a)[VPL], uint4 (&b)[VPL]) {
+        if (r < rows) {
 #pragma unroll
-        for (int k = 0; k < VPL; ++k) {
-            const int c = lane + 32 * k;
-            if (c < nv) {
-                const size_t off = (size_t)row * H + c * 8;
-                xv[k] = ld_stream_v4(x + off);
-                if (residual) rv[k] = ld_stream_v4(residual + off);
+            for (int k = 0; k < VPL; ++k) {
+                const int c = lane + 32 * k;
+                if (c < nv) {
+                    const size_t off = (size_t)r * H + c * 8;
+                    a[k] = ld_stream_v4(x + off);
+                    if (residual) b[k] = ld_stream_v4(residual + off);
+                }
             }
         }
+    };
+    load_row(row, xv, rv);
+    for (; row < rows; row += stride) {
+        uint4 nxv[VPL], nrv[VPL];
+        load_row(row + stride, nxv, nrv);
+        float v[VPL][8];
+        float s = 0.f;
 #pragma unroll
         for (int k = 0; k < VPL; ++k) {
             const int c = lane + 32 * k;
@@ -112,51 +121,77 @@ __global__ void __launch_bounds__(kLnThreads, (VPL <= 3 ? 3 : (VPL <= 6 ? 2 : 1)
                 st_global_v4(y + (size_t)row * H + c * 8, float_to_bf16x8(o));
             }
         }
+#pragma unroll
+        for (int k = 0; k < VPL; ++k) {
+            xv[k] = nxv[k];
+            rv[k] = nrv[k];
+        }
     }
 }
 
 // dz = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * gamma
 // dx = dz * keep * scale (only when dropout is active; else dx aliases dz on the host side)
+//
+// A warp owns one row at a time, and a row is a chain load -> reduce -> store, so the loads of the NEXT row are issued
+// before the current one is processed (software pipeline across the row loop; without it each row paid a full memory
+// latency: 7 400 cycles per row measured).  To have registers for that, the dgamma / dbeta column sums of a warp live
+// in shared memory ([warp][which][k][half][lane] float4: conflict-free 512-byte rows) instead of 2 * VPL * 8 registers.
 template <int VPL>
-__global__ void __launch_bounds__(kLnThreads, (VPL <= 3 ? 2 : 1)) ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z,
+__global__ void __launch_bounds__(kLnThreads, (VPL <= 4 ? 2 : 1)) ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z,
                                                                const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
                                                                const bf16* __restrict__ gamma, bf16* __restrict__ dz,
                                                                bf16* __restrict__ dx, float* __restrict__ partials, int rows, int H,
                                                                DropCfg drop) {
     resolve_seed(drop);
-    __shared__ float red[kWarpsPerBlock][32 * 8 + 1];
+    extern __shared__ float4 ln_acc[];  // [kWarpsPerBlock][2][VPL][2][32]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nv = H >> 3;
     const float inv_h = 1.f / (float)H;
-    // accumulators in fp32; everything else stays packed (bf16x8 = 4 registers) to keep two
-    // blocks resident per SM
-    float dgam[VPL][8], dbet[VPL][8];
+    float4* acc_g = ln_acc + (size_t)(warp * 2 + 0) * VPL * 64;  // dgamma: [k][half][lane]
+    float4* acc_b = ln_acc + (size_t)(warp * 2 + 1) * VPL * 64;  // dbeta
+#pragma unroll
+    for (int k = 0; k < VPL; ++k)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            acc_g[(k * 2 + h) * 32 + lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+            acc_b[(k * 2 + h) * 32 + lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
     uint4 gam[VPL];
 #pragma unroll
     for (int k = 0; k < VPL; ++k) {
         const int c = lane + 32 * k;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) dgam[k][j] = dbet[k][j] = 0.f;
         gam[k] = make_uint4(0, 0, 0, 0);
         if (c < nv) gam[k] = ld_global_v4(gamma + c * 8);
     }
-    for (long long row = (long long)blockIdx.x * kWarpsPerBlock + warp; row < rows; row += (long long)gridDim.x * kWarpsPerBlock) {
-        const float mean = mean_in[row], rstd = rstd_in[row];
-        uint4 dyv[VPL], zv[VPL];
+    const long long stride = (long long)gridDim.x * kWarpsPerBlock;
+    long long row = (long long)blockIdx.x * kWarpsPerBlock + warp;
+    uint4 dyv[VPL], zv[VPL];
+    float mean = 0.f, rstd = 0.f;
+    auto load_row = [&](long long r, uint4 (&a)[VPL], uint4 (&b)[VPL], float& mu, float& rs) {
+        if (r < rows) {
+            mu = mean_in[r];
+            rs = rstd_in[r];
 #pragma unroll
-        for (int k = 0; k < VPL; ++k) {
-            const int c = lane + 32 * k;
-            if (c < nv) {
-                const size_t off = (size_t)row * H + c * 8;
-                dyv[k] = ld_stream_v4(dy + off);
-                zv[k] = ld_stream_v4(z + off);
+            for (int k = 0; k < VPL; ++k) {
+                const int c = lane + 32 * k;
+                if (c < nv) {
+                    const size_t off = (size_t)r * H + c * 8;
+                    a[k] = ld_stream_v4(dy + off);
+                    b[k] = ld_stream_v4(z + off);
+                }
             }
         }
+    };
+    load_row(row, dyv, zv, mean, rstd);
+    for (; row < rows; row += stride) {
+        uint4 ndy[VPL], nz[VPL];
+        float nmean = 0.f, nrstd = 0.f;
+        load_row(row + stride, ndy, nz, nmean, nrstd);  // in flight while this row is processed
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
         for (int k = 0; k < VPL; ++k) {
             if (lane + 32 * k < nv) {
-                float d[8], zz[8], gm[8];
+                float d[8], zz[8], gm[8], dg[8];
                 bf16x8_to_float(dyv[k], d);
                 bf16x8_to_float(zv[k], zz);
                 bf16x8_to_float(gam[k], gm);
@@ -166,8 +201,16 @@ __global__ void __launch_bounds__(kLnThreads, (VPL <= 3 ? 2 : 1)) ln_bwd_kernel(
                     const float g = d[j] * gm[j];
                     s1 += g;
                     s2 += g * xh;
-                    dgam[k][j] += d[j] * xh;
-                    dbet[k][j] += d[j];
+                    dg[j] = d[j] * xh;
+                }
+                // only this lane touches these four float4 slots: plain read-modify-write
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    float4 a = acc_g[(k * 2 + h) * 32 + lane], b = acc_b[(k * 2 + h) * 32 + lane];
+                    a.x += dg[4 * h + 0]; a.y += dg[4 * h + 1]; a.z += dg[4 * h + 2]; a.w += dg[4 * h + 3];
+                    b.x += d[4 * h + 0];  b.y += d[4 * h + 1];  b.z += d[4 * h + 2];  b.w += d[4 * h + 3];
+                    acc_g[(k * 2 + h) * 32 + lane] = a;
+                    acc_b[(k * 2 + h) * 32 + lane] = b;
                 }
             }
         }
@@ -190,25 +233,27 @@ __global__ void __launch_bounds__(kLnThreads, (VPL <= 3 ? 2 : 1)) ln_bwd_kernel(
                 }
             }
         }
-    }
-    // block reduction of dgamma / dbeta partials: [blocks][2][H]
-    float* out = partials + (size_t)blockIdx.x * 2 * H;
-#pragma unroll
-    for (int which = 0; which < 2; ++which) {
 #pragma unroll
         for (int k = 0; k < VPL; ++k) {
-            __syncthreads();
-#pragma unroll
-            for (int j = 0; j < 8; ++j) red[warp][lane * 8 + j] = which == 0 ? dgam[k][j] : dbet[k][j];
-            __syncthreads();
-            // 256 threads fold 8 warps x 256 columns
-            const int col = threadIdx.x;  // 0..255 -> (lane = col/8, j = col%8)
-            float acc = 0.f;
-#pragma unroll
-            for (int w = 0; w < kWarpsPerBlock; ++w) acc += red[w][col];
-            const int c = (col >> 3) + 32 * k;
-            if (c < nv) out[which * H + c * 8 + (col & 7)] = acc;
+            dyv[k] = ndy[k];
+            zv[k] = nz[k];
         }
+        mean = nmean;
+        rstd = nrstd;
+    }
+    // block fold of the 8 warps' column sums -> this block's partial row [2][H]
+    __syncthreads();
+    float* out = partials + (size_t)blockIdx.x * 2 * H;
+    const float* accf = reinterpret_cast<const float*>(ln_acc);
+    for (int idx = threadIdx.x; idx < 2 * H; idx += blockDim.x) {
+        const int which = idx / H, col = idx - which * H;
+        const int c = col >> 3, e8 = col & 7;       // vector index, element inside the vector
+        const int k = c >> 5, ln = c & 31, h = e8 >> 2, e = e8 & 3;
+        float a = 0.f;
+#pragma unroll
+        for (int w = 0; w < kWarpsPerBlock; ++w)
+            a += accf[((((size_t)(w * 2 + which) * VPL + k) * 2 + h) * 32 + ln) * 4 + e];
+        out[idx] = a;
     }
 }
 
@@ -368,7 +413,7 @@ DDL_API int ddl_add_layernorm_fwd(const void* x, const void* residual, const voi
     DDL_REQUIRE(x && gamma && beta && y && mean && rstd, "layernorm fwd: null pointer");
     if (rows == 0) return 0;
     const DropCfg d = make_drop(dropout_p, seed, seed_dev);
-    const int grid = ln_grid(rows, H <= 768 ? 3 : 2);  // matches the launch bounds (VPL <= 3: three blocks per SM)
+    const int grid = ln_grid(rows);
     cudaStream_t s = (cudaStream_t)stream_;
     LN_DISPATCH(H, (add_ln_fwd_kernel<VPL><<<grid, kLnThreads, 0, s>>>((const bf16*)x, (const bf16*)residual, (const bf16*)gamma,
                                                                       (const bf16*)beta, (bf16*)z_out, (bf16*)y, mean, rstd, rows, H, eps, d)));
@@ -389,8 +434,16 @@ DDL_API int ddl_layernorm_bwd(const void* dy, const void* z, const float* mean, 
     const DropCfg d = make_drop(dropout_p, seed, seed_dev);
     const int grid = ln_grid(rows);
     cudaStream_t s = (cudaStream_t)stream_;
-    LN_DISPATCH(H, (ln_bwd_kernel<VPL><<<grid, kLnThreads, 0, s>>>((const bf16*)dy, (const bf16*)z, mean, rstd, (const bf16*)gamma, (bf16*)dz,
-                                                                  (bf16*)dx, (float*)scratch, rows, H, d)));
+    LN_DISPATCH(H, ({
+                    const int smem = kWarpsPerBlock * 2 * VPL * 64 * (int)sizeof(float4);
+                    static bool attr_set = false;  // one per VPL instantiation
+                    if (!attr_set) {
+                        DDL_CHECK(cudaFuncSetAttribute(ln_bwd_kernel<VPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+                        attr_set = true;
+                    }
+                    ln_bwd_kernel<VPL><<<grid, kLnThreads, smem, s>>>((const bf16*)dy, (const bf16*)z, mean, rstd, (const bf16*)gamma,
+                                                                      (bf16*)dz, (bf16*)dx, (float*)scratch, rows, H, d);
+                }));
     DDL_LAUNCH_CHECK();
     const bool f32 = param_grad_dtype == DDL_F32;
     ln_bwd_finalize_kernel<<<ddl_ceil_div(2 * H, 32), kLnFoldWarps * 32, 0, s>>>((const float*)scratch, grid, H, f32 ? nullptr : (bf16*)dgamma,
