@@ -1,8 +1,8 @@
 #!/usr/bin/env python
 """Per-layer timing of the ResNet-50 convolutions at per-GPU batch 256:
 library convolution (cuDNN through ATen, bf16 NHWC, benchmark mode) forward / dgrad / wgrad, against the
-memory and tensor-core floors, and - for the 1x1 / stride-1 layers - the tcgen05 GEMM route of this repo
-(forward with the BatchNorm-statistics epilogue, dgrad, wgrad).
+memory and tensor-core floors and the implicit-GEMM tcgen05 kernels of this repo (csrc/conv_igemm.cu: forward with
+the BatchNorm-statistics epilogue, dgrad, wgrad; csrc/conv1x1.cu: weight-stationary forward of the skinny 1x1 layers).
 
     python benchmarks/conv_bench.py [--batch 256] [--json gpurun_out/conv_bench.json]
 
@@ -51,8 +51,6 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--json", default=os.path.join(ROOT, "gpurun_out", "conv_bench.json"))
     args = ap.parse_args()
-    from databricks_distributed_deep_learning_b200.ops import gemm as G
-
     torch.backends.cudnn.benchmark = True
     dev = torch.device("cuda")
     bf = torch.bfloat16
@@ -66,7 +64,7 @@ def main():
     N = args.batch
     rows = []
     tot = {"cudnn_fwd": 0.0, "cudnn_dgrad": 0.0, "cudnn_wgrad": 0.0, "floor": 0.0}
-    print(f"{'layer':32s} {'x':>2s} {'fwd':>8s} {'dgrad':>8s} {'wgrad':>8s} {'floor':>7s} | {'g.fwd':>8s} {'g.dgrad':>8s} {'g.wgrad':>8s} {'ws.fwd':>8s}   (us per call; ws.fwd = weight-stationary kernel incl. BN statistics)")
+    print(f"{'layer':32s} {'x':>2s} {'fwd':>8s} {'dgrad':>8s} {'wgrad':>8s} {'floor':>7s} | {'n.fwd':>8s} {'n.dgrad':>8s} {'n.wgrad':>8s} {'ws.fwd':>8s}   (us per call; n.* = csrc/conv_igemm.cu, n.fwd / ws.fwd include the BN statistics)")
     for cnt, cin, hw, cout, k, s in LAYERS:
         pad = k // 2
         x = torch.randn(N, cin, hw, hw, device=dev).to(bf).contiguous(memory_format=torch.channels_last)
@@ -82,24 +80,32 @@ def main():
         floor = max(flops / (peaks["bf16_tflops"] * 1e12), bytes_io / (peaks["hbm_gbs"] * 1e9)) * 1e6
         row = {"cin": cin, "hw": hw, "cout": cout, "k": k, "stride": s, "count": cnt, "cudnn_fwd_us": t_f, "cudnn_dgrad_us": t_d,
                "cudnn_wgrad_us": t_w, "floor_us": floor, "gflop": flops / 1e9, "mbytes": bytes_io / 1e6}
-        g = ["", "", ""]
-        if k == 1 and s == 1:
-            M = N * hw * hw
-            x2, w2, dy2 = x.permute(0, 2, 3, 1).reshape(M, cin), w.reshape(cout, cin), dy.permute(0, 2, 3, 1).reshape(M, cout)
-            sums = torch.zeros(2, cout, dtype=torch.float32, device=dev)
-            row["gemm_fwd_us"] = timeit(lambda: G.gemm_nt(x2, w2, M, cout, cin, col_stats=sums), flush)
-            row["gemm_dgrad_us"] = timeit(lambda: G.gemm_nt(dy2, w2, M, cin, cout, b_mn=True), flush)
-            sk = G.pick_split_k(cout, cin, M)
-            row["gemm_wgrad_us"] = timeit(lambda: G.gemm_nt(dy2, x2, cout, cin, M, a_mn=True, b_mn=True, split_k=sk), flush)
-            g = [f"{row['gemm_fwd_us']:8.1f}", f"{row['gemm_dgrad_us']:8.1f}", f"{row['gemm_wgrad_us']:8.1f}"]
-            from databricks_distributed_deep_learning_b200.ops import _lib as L
+        g = ["", "", "", ""]
+        from databricks_distributed_deep_learning_b200.ops import _lib as L
 
-            if L.lib().ddl_conv1x1_supported(M, cout, cin):
-                part = torch.empty(L.lib().ddl_conv1x1_grid(M, cout) * 2 * cout, dtype=torch.float32, device=dev)
-                yy = torch.empty(M, cout, dtype=bf, device=dev)
-                row["ws_fwd_stats_us"] = timeit(lambda: L.call("ddl_conv1x1_fwd", x2.data_ptr(), w2.data_ptr(), yy.data_ptr(), part.data_ptr(),
-                                                               M, cout, cin, L.stream_ptr(dev)), flush)
-                g.append(f"{row['ws_fwd_stats_us']:8.1f}")
+        lib = L.lib()
+        geom = (N, hw, hw, cin, cout, k, k, s, pad)
+        if lib.ddl_conv_supported(*geom):
+            st = L.stream_ptr(dev)
+            yy = torch.empty_like(y)
+            part = torch.empty(lib.ddl_conv_fwd_groups(*geom) * 2 * cout, dtype=torch.float32, device=dev)
+            dx = torch.empty_like(x)
+            dw = torch.empty_like(w)
+            scr = torch.empty(max(lib.ddl_conv_wgrad_scratch_bytes(*geom), 16), dtype=torch.uint8, device=dev)
+            row["native_fwd_us"] = timeit(lambda: L.call("ddl_conv_fwd", x.data_ptr(), w.data_ptr(), yy.data_ptr(), part.data_ptr(), *geom, st), flush)
+            row["native_dgrad_us"] = timeit(lambda: L.call("ddl_conv_dgrad", dy.data_ptr(), w.data_ptr(), dx.data_ptr(), *geom, st), flush)
+            row["native_wgrad_us"] = timeit(lambda: L.call("ddl_conv_wgrad", x.data_ptr(), dy.data_ptr(), dw.data_ptr(), *dw.stride(), scr.data_ptr(),
+                                                            scr.numel(), *geom, st), flush)
+            g = [f"{row['native_fwd_us']:8.1f}", f"{row['native_dgrad_us']:8.1f}", f"{row['native_wgrad_us']:8.1f}", ""]
+            for key in ("fwd", "dgrad", "wgrad"):
+                tot["native_" + key] = tot.get("native_" + key, 0.0) + cnt * row[f"native_{key}_us"]
+            M = N * hw * hw
+            if k == 1 and s == 1 and lib.ddl_conv1x1_supported(M, cout, cin):
+                p1 = torch.empty(lib.ddl_conv1x1_grid(M, cout) * 2 * cout, dtype=torch.float32, device=dev)
+                row["ws_fwd_stats_us"] = timeit(lambda: L.call("ddl_conv1x1_fwd", x.data_ptr(), w.data_ptr(), yy.data_ptr(), p1.data_ptr(),
+                                                               M, cout, cin, st), flush)
+                g[3] = f"{row['ws_fwd_stats_us']:8.1f}"
+            del yy, dx, dw, scr
         rows.append(row)
         tot["cudnn_fwd"] += cnt * t_f
         tot["cudnn_dgrad"] += cnt * t_d

@@ -1,0 +1,50 @@
+#!/usr/bin/env python
+"""Development check of the implicit-GEMM convolutions: every ResNet-50 shape, all three kernels, errors against fp32
+autograd, no stop at the first failure (the pytest version is tests/test_gpu_conv.py).  --time also times them at the
+training batch against the library convolution.
+
+    python benchmarks/conv_check.py [--batch 3] [--time 256]
+"""
+import argparse
+import os
+import sys
+import traceback
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--batch", type=int, default=3)
+    ap.add_argument("--only", type=int, default=-1)
+    args = ap.parse_args()
+    from test_gpu_conv import RESNET50_CONVS, conv_case
+
+    bad = 0
+    for i, (cin, hw, cout, k, s) in enumerate(RESNET50_CONVS):
+        if args.only >= 0 and i != args.only:
+            continue
+        name = f"{cin}x{hw}^2 -> {cout} k{k}/s{s}"
+        try:
+            e = conv_case(args.batch, cin, hw, cout, k, s)
+            ok = e["fwd"] < 8e-3 and e["dgrad"] < 8e-3 and e["wgrad"] < 8e-3 and e["sum"] < 2e-3 and e["sumsq"] < 2e-3
+            bad += 0 if ok else 1
+            print(f"{i:2d} {name:30s} " + " ".join(f"{k2}={v:.2e}" for k2, v in e.items()) + ("" if ok else "   <-- FAIL"), flush=True)
+        except Exception:
+            bad += 1
+            print(f"{i:2d} {name:30s} EXCEPTION\n{traceback.format_exc()}", flush=True)
+            try:
+                torch.cuda.synchronize()
+            except Exception:
+                print("CUDA context is broken; stopping", flush=True)
+                break
+    print(f"conv_check: {bad} failing shapes")
+    return 1 if bad else 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

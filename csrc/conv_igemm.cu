@@ -1,0 +1,845 @@
+// Convolutions on NHWC bf16 as implicit GEMMs on tcgen05: forward, data gradient and weight gradient for the 1x1 and
+// 3x3 layers (stride 1 and 2) of the reference's ResNet-50 (notebooks/cv/onnx_experiments.py:19; shapes in SURVEY.md
+// section 2.E.2; K9 in section 2.E.3, BASELINE.json:5 "conv-BN-ReLU epilogues ... no cuBLAS/cuDNN on these paths").
+//
+// No im2col buffer exists anywhere.  The activation tensor is described to TMA as a 4-D tensor [C, W, H, N]; the operand
+// tile of a filter tap is ONE box [64 channels, bw, bh, nb] whose start coordinate is shifted by the tap offset.
+// Coordinates outside the image are zero-filled by TMA - that IS the padding.  Stride-2 layers use four "parity" maps
+// (base pointer shifted by (ph, pw), strides doubled), so that a tap again reads a dense box.  1x1 / stride-1 layers
+// are flattened to [C, N*H*W] and tiled 128 pixels at a time.
+//
+//   data kernel   out[pix, n] = sum_taps  A_tap[pix, :] . W_tap[n, :]           (forward and data gradient)
+//       forward : A = x boxes,  W_tap = w[n][tap][:]  (K-major rows of the channels-last weight),  BatchNorm statistics
+//                 (per-channel sum / sum of squares of the stored bf16 output) accumulated by the epilogue warps in
+//                 registers and written as per-CTA partials for ddl_bn_act_fwd_train_from_partials (deterministic).
+//       dgrad s1: A = dy boxes with mirrored tap offsets, W_tap = w[:][tap][n] read MN-major from the same tensor.
+//       dgrad s2: the input pixels split into 4 parity classes; each class is a dense convolution over dy with the
+//                 subset of taps that reaches it, stored with pixel stride 2.
+//   weight kernel dw[(tap, c), k] = sum_pix  x_tap[pix, c] . dy[pix, k]         (reduction over pixels)
+//       both operands MN-major straight from the NHWC tensors, up to 512 TMEM columns of accumulators per CTA alive for
+//       the CTA's whole pixel range, fp32 partials per pixel split, folded in fixed order (and transposed to the weight
+//       layout) by a second kernel.
+//
+// Structure of both kernels as in gemm_tcgen05.cu / conv1x1.cu: warp 0 = TMA producer, warp 1 = MMA issuer (one thread),
+// remaining warps = epilogue; mbarrier ring between producer and MMA, tcgen05.commit releases stages.
+#include <cuda.h>
+
+#include <algorithm>
+
+#include "../include/b200ddl.h"
+#include "common.cuh"
+#include "tcgen05.cuh"
+#include "tma_host.h"
+
+namespace {
+using namespace tc;
+
+struct Tap {
+    int8_t dh, dw;  // offset of the box in (rows, columns) of the tensor map it reads
+    int8_t map;     // which of the (up to 4) input tensor maps
+    int8_t wtap;    // r * S + s: which filter tap's weights
+};
+
+struct alignas(64) ConvMaps {
+    CUtensorMap in[4];
+    CUtensorMap w;  // data kernel: weights; weight kernel: dy
+};
+
+__device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+            smem_u32(smem_dst)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------ data kernel
+constexpr int kTileM = 128;
+constexpr int kEpiWarps = 16;  // 4 TMEM lane quarters x 4 column groups of 64
+constexpr int kThreads = 64 + kEpiWarps * 32;
+constexpr int kStageA = kTileM * 128;  // [128 pixels x 64 channels] bf16
+constexpr int kStgBytes = 2048;        // per epilogue warp: 32 rows x 32 columns bf16
+constexpr int kMaxStages = 8;
+
+struct DataParams {
+    bf16* out;
+    float* partials;  // [m_groups][2][Cn] or null (data gradient)
+    int ncls;         // output parity classes (1, or up to 4 for the stride-2 data gradient)
+    int cls_ntaps[4], cls_oph[4], cls_opw[4];
+    Tap taps[4][9];
+    int N, OHt, OWt;   // grid of output pixels of one class
+    int OHf, OWf, os;  // full output extent and the pixel stride of a class inside it
+    int Cn;            // output channels
+    int bw, bh, nb;    // box: columns, rows, images (bw * bh * nb <= 128)
+    int tiles_w, tiles_h, tiles_per_cls, num_tiles;
+    int num_n_blocks, bn, groups;  // bn output channels per CTA, groups = bn / 64
+    int cblocks;                   // reduction channels / 64
+    int w_tap_stride;              // elements between consecutive taps inside one weight row (= conv input channels)
+    int stages;
+    uint32_t a_bytes;
+};
+
+template <bool B_MN>
+__global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_constant__ ConvMaps maps, const DataParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int stage_b = p.bn * 128;
+    const int stage_bytes = kStageA + stage_b;
+    uint8_t* stg_base = smem + (size_t)p.stages * stage_bytes;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(stg_base + kEpiWarps * kStgBytes);
+    uint64_t* empty_bar = full_bar + kMaxStages;
+    uint64_t* tmem_full = empty_bar + kMaxStages;  // [2]
+    uint64_t* tmem_empty = tmem_full + 2;           // [2]
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    constexpr uint32_t kTmemCols = 512;
+    // a CTA keeps ONE column block for its whole life, so that the BatchNorm sums can stay in registers
+    const int n_blk = blockIdx.x % p.num_n_blocks, m_group = blockIdx.x / p.num_n_blocks;
+    const int m_groups = gridDim.x / p.num_n_blocks;
+    const int tiles_hw = p.tiles_h * p.tiles_w;
+
+    if (warp == 0 && lane == 0) {
+        for (int i = 0; i < 4; ++i) tma_prefetch_desc(&maps.in[i]);
+        tma_prefetch_desc(&maps.w);
+        for (int s = 0; s < kMaxStages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full[s], 1);
+            mbar_init(&tmem_empty[s], 4 * p.groups);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_ptr_smem, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = m_group; tile < p.num_tiles; tile += m_groups) {
+                const int cls = tile / p.tiles_per_cls, t = tile - cls * p.tiles_per_cls;
+                const int ng = t / tiles_hw, rem = t - ng * tiles_hw;
+                const int hb = rem / p.tiles_w, wb = rem - hb * p.tiles_w;
+                const int n0 = ng * p.nb, oh0 = hb * p.bh, ow0 = wb * p.bw;
+                const int ntaps = p.cls_ntaps[cls];
+                for (int ti = 0; ti < ntaps; ++ti) {
+                    const Tap tp = p.taps[cls][ti];
+                    for (int cb = 0; cb < p.cblocks; ++cb) {
+                        mbar_wait(&empty_bar[stage], phase ^ 1);
+                        uint8_t* sa = smem + (size_t)stage * stage_bytes;
+                        uint8_t* sb = sa + kStageA;
+                        mbar_expect_tx(&full_bar[stage], p.a_bytes + (uint32_t)stage_b);
+                        tma_load_4d(sa, &maps.in[tp.map], &full_bar[stage], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
+                        if (!B_MN) {
+                            tma_load_2d(sb, &maps.w, &full_bar[stage], tp.wtap * p.w_tap_stride + cb * 64, n_blk * p.bn);
+                        } else {
+                            for (int j = 0; j < p.groups; ++j)
+                                tma_load_2d(sb + j * 8192, &maps.w, &full_bar[stage], tp.wtap * p.w_tap_stride + n_blk * p.bn + j * 64, cb * 64);
+                        }
+                        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc(kTileM, p.bn, false, B_MN);
+            int stage = 0, acc = 0;
+            uint32_t phase = 0, acc_phase = 0;
+            for (int tile = m_group; tile < p.num_tiles; tile += m_groups) {
+                const int cls = tile / p.tiles_per_cls;
+                const int nkb = p.cls_ntaps[cls] * p.cblocks;
+                mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * p.bn;
+                for (int kb = 0; kb < nkb; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
+                    const uint32_t sb = sa + kStageA;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint64_t da = make_smem_desc(sa + k * 32, 16, 1024);
+                        const uint64_t db = B_MN ? make_smem_desc(sb + k * 2048, 8192, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
+                        umma_bf16(d_tmem, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[stage]);
+                    if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&tmem_full[acc]);
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else {
+        // ===================== epilogue warps =====================
+        const int ew = warp - 2;
+        const int quarter = warp & 3;  // TMEM lanes 32 * quarter .. + 31
+        const int group = ew >> 2;     // 64-column chunk of the accumulator
+        if (group < p.groups) {
+            uint8_t* stg = stg_base + ew * kStgBytes;
+            const bool stats = p.partials != nullptr;
+            float cs[16], cq[16];  // columns col0 + h * 32 + t_ch * 8 + q  at index h * 8 + q
+#pragma unroll
+            for (int i = 0; i < 16; ++i) cs[i] = cq[i] = 0.f;
+            const int col0 = n_blk * p.bn + group * 64;
+            const int t_row = lane >> 2, t_ch = lane & 3;
+            const int rows_img = p.bw * p.bh, rows_box = rows_img * p.nb;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = m_group; tile < p.num_tiles; tile += m_groups) {
+                const int cls = tile / p.tiles_per_cls, t = tile - cls * p.tiles_per_cls;
+                const int ng = t / tiles_hw, rem = t - ng * tiles_hw;
+                const int hb = rem / p.tiles_w, wb = rem - hb * p.tiles_w;
+                const int n0 = ng * p.nb, oh0 = hb * p.bh, ow0 = wb * p.bw;
+                const int oph = p.cls_oph[cls], opw = p.cls_opw[cls];
+                // element offset of the 16-byte piece this lane stores for each of its 4 rows per 32-column half
+                long long off[4];
+#pragma unroll
+                for (int it = 0; it < 4; ++it) {
+                    const int r = quarter * 32 + it * 8 + t_row;
+                    off[it] = -1;
+                    if (r < rows_box) {
+                        const int j = r / rows_img, rr = r - j * rows_img;
+                        const int a = rr / p.bw, b = rr - a * p.bw;
+                        if (n0 + j < p.N && oh0 + a < p.OHt && ow0 + b < p.OWt)
+                            off[it] = (((long long)(n0 + j) * p.OHf + (oh0 + a) * p.os + oph) * p.OWf + (ow0 + b) * p.os + opw) * p.Cn + col0 + t_ch * 8;
+                    }
+                }
+                mbar_wait(&tmem_full[acc], acc_phase);
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + acc * p.bn + group * 64 + ((uint32_t)(quarter * 32) << 16);
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(taddr + h * 32, r);
+                    tmem_ld_wait();
+                    if (h == 1) {  // accumulator chunk fully read: hand it back before the stores
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        float f[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[j * 8 + e]);
+                        *reinterpret_cast<uint4*>(stg + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4)) = float_to_bf16x8(f);
+                    }
+                    __syncwarp();
+#pragma unroll
+                    for (int it = 0; it < 4; ++it) {
+                        const int rr = it * 8 + t_row;
+                        const uint4 v = *reinterpret_cast<const uint4*>(stg + rr * 64 + ((t_ch ^ ((rr >> 1) & 3)) << 4));
+                        if (off[it] >= 0) {
+                            st_global_v4(p.out + off[it] + h * 32, v);
+                            if (stats) {
+                                float f[8];
+                                bf16x8_to_float(v, f);
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) {
+                                    cs[h * 8 + q] += f[q];
+                                    cq[h * 8 + q] = fmaf(f[q], f[q], cq[h * 8 + q]);
+                                }
+                            }
+                        }
+                    }
+                    __syncwarp();
+                }
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+            if (stats) {
+                // fold the 8 row groups of the warp (lanes with equal t_ch), then the 4 lane-quarter warps of this
+                // column group in fixed order -> this CTA's partial statistics
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+#pragma unroll
+                    for (int o = 4; o < 32; o <<= 1) {
+                        cs[i] += __shfl_xor_sync(0xffffffffu, cs[i], o);
+                        cq[i] += __shfl_xor_sync(0xffffffffu, cq[i], o);
+                    }
+                }
+                float* mine = reinterpret_cast<float*>(stg);  // own staging area, free now: [64 columns][2]
+                if (t_row == 0) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const int c = (i >> 3) * 32 + t_ch * 8 + (i & 7);
+                        mine[c * 2] = cs[i];
+                        mine[c * 2 + 1] = cq[i];
+                    }
+                }
+                asm volatile("bar.sync %0, 128;" ::"r"(1 + group) : "memory");  // the four warps of this group
+                if (quarter == 2) {  // ew = 4 * group
+                    float t4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int qw = 0; qw < 4; ++qw) {
+                        const float* src = reinterpret_cast<const float*>(stg_base + (group * 4 + qw) * kStgBytes);
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) t4[e] += src[lane * 4 + e];
+                    }
+                    float* outp = p.partials + (size_t)m_group * 2 * p.Cn;
+                    const int col = col0 + 2 * lane;
+                    outp[col] = t4[0];
+                    outp[p.Cn + col] = t4[1];
+                    outp[col + 1] = t4[2];
+                    outp[p.Cn + col + 1] = t4[3];
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ weight gradient
+// D[m = (tap, c)][n = k] = sum over pixels of x_tap[pix][c] * dy[pix][k].  Both operands are MN-major: a pixel's
+// 64-channel slice is one 128-byte row, the reduction index (pixel) walks the rows.  The (tap, c) axis is cut into
+// 64-channel "units"; an MMA takes two consecutive units as its M = 128 (two 64-wide blocks one slot apart, LBO =
+// slot size) and bn output channels as N.  A CTA owns `G` such unit pairs x one column block (G * bn <= 512 TMEM
+// columns) and one slice of the pixel range; it writes its fp32 accumulators as a partial that the fold kernel sums in
+// fixed order.  Slots hold ceil16(pixels) rows; the rows past the box are zeroed once and never written again, so the
+// K padding multiplies zeros.
+constexpr int kWgThreads = 192;  // TMA, MMA, 4 epilogue warps
+
+struct WgradParams {
+    float* partials;  // [ksplit][Mtot][Cout]
+    int ntaps;
+    Tap taps[9];
+    int N, OHt, OWt, bw, bh, nb, tiles_w, tiles_h, num_chunks;
+    int cblocks, U, G, mgroups;
+    int Cout, bn, nblk;
+    int ksplit, cps;
+    int slot_bytes, ksteps, stages, pix;
+    long long Mtot;
+};
+
+__global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_kernel(const __grid_constant__ ConvMaps maps, const WgradParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int dy_slots = p.bn >> 6;
+    const int nslots = dy_slots + 2 * p.G;
+    const int stage_bytes = nslots * p.slot_bytes;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)p.stages * stage_bytes);
+    uint64_t* empty_bar = full_bar + kMaxStages;
+    uint64_t* done_bar = empty_bar + kMaxStages;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(done_bar + 1);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    constexpr uint32_t kTmemCols = 512;
+
+    // zero every slot once: the rows behind each box (K padding up to a multiple of 16 pixels) must read as zeros
+    {
+        const int n16 = p.stages * stage_bytes / 16;
+        uint4* s4 = reinterpret_cast<uint4*>(smem);
+        for (int i = threadIdx.x; i < n16; i += kWgThreads) s4[i] = make_uint4(0, 0, 0, 0);
+        fence_proxy_async();
+    }
+    if (warp == 0 && lane == 0) {
+        for (int i = 0; i < 4; ++i) tma_prefetch_desc(&maps.in[i]);
+        tma_prefetch_desc(&maps.w);
+        for (int s = 0; s < kMaxStages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(done_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_ptr_smem, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    const int nb_ = blockIdx.x % p.nblk, t_ = blockIdx.x / p.nblk;
+    const int mg = t_ % p.mgroups, ks = t_ / p.mgroups;
+    const int u0 = mg * 2 * p.G;
+    const int nu = min(2 * p.G, p.U - u0);  // 64-channel units of this CTA
+    const int npairs = (nu + 1) >> 1;
+    const int c0 = ks * p.cps, c1 = min(c0 + p.cps, p.num_chunks);
+    const int tiles_hw = p.tiles_h * p.tiles_w;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            const uint32_t tx_bytes = (uint32_t)(dy_slots + nu) * (uint32_t)p.pix * 128u;
+            for (int chunk = c0; chunk < c1; ++chunk) {
+                const int ng = chunk / tiles_hw, rem = chunk - ng * tiles_hw;
+                const int hb = rem / p.tiles_w, wb = rem - hb * p.tiles_w;
+                const int n0 = ng * p.nb, oh0 = hb * p.bh, ow0 = wb * p.bw;
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                uint8_t* st = smem + (size_t)stage * stage_bytes;
+                mbar_expect_tx(&full_bar[stage], tx_bytes);
+                for (int j = 0; j < dy_slots; ++j)
+                    tma_load_4d(st + j * p.slot_bytes, &maps.w, &full_bar[stage], nb_ * p.bn + j * 64, ow0, oh0, n0);
+                for (int i = 0; i < nu; ++i) {
+                    const int u = u0 + i;
+                    const int ti = u / p.cblocks, cb = u - ti * p.cblocks;
+                    const Tap tp = p.taps[ti];
+                    tma_load_4d(st + (dy_slots + i) * p.slot_bytes, &maps.in[tp.map], &full_bar[stage], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
+                }
+                if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc(128, p.bn, true, true);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int chunk = c0; chunk < c1; ++chunk) {
+                mbar_wait(&full_bar[stage], phase);
+                tc_fence_after();
+                const uint32_t sdy = smem_u32(smem + (size_t)stage * stage_bytes);
+                for (int g = 0; g < npairs; ++g) {
+                    const uint32_t sx = sdy + (dy_slots + 2 * g) * p.slot_bytes;
+                    for (int k = 0; k < p.ksteps; ++k) {
+                        const uint64_t da = make_smem_desc(sx + k * 2048, p.slot_bytes, 1024);
+                        const uint64_t db = make_smem_desc(sdy + k * 2048, p.slot_bytes, 1024);
+                        umma_bf16(tmem_base + g * p.bn, da, db, idesc, (chunk > c0 || k > 0) ? 1u : 0u);
+                    }
+                }
+                umma_commit(&empty_bar[stage]);
+                if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+            umma_commit(done_bar);
+        }
+    } else {
+        // epilogue: TMEM lane = row m of the pair (lanes 0..63 first unit, 64..127 second unit) -> fp32 partial rows
+        const int quarter = warp & 3;
+        mbar_wait(done_bar, 0);
+        tc_fence_after();
+        for (int g = 0; g < npairs; ++g) {
+            const int ui = 2 * g + (quarter >> 1);
+            if (ui >= nu) continue;  // warp-uniform
+            const long long m = (long long)(u0 + ui) * 64 + (quarter & 1) * 32 + lane;
+            float* dst = p.partials + ((size_t)ks * p.Mtot + m) * p.Cout + nb_ * p.bn;
+            for (int cc = 0; cc < p.bn; cc += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32(tmem_base + g * p.bn + cc + ((uint32_t)(quarter * 32) << 16), r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int e = 0; e < 32; e += 4)
+                    *reinterpret_cast<float4*>(dst + cc + e) =
+                        make_float4(__uint_as_float(r[e]), __uint_as_float(r[e + 1]), __uint_as_float(r[e + 2]), __uint_as_float(r[e + 3]));
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// dw[k][r][s][c] (element strides sk, sr, ss, sc) = sum over splits of partial[split][(r*S + s) * C + c][k].
+// 32 x 32 tiles through shared memory: reads are contiguous in k, writes contiguous in c (channels-last weights).
+__global__ void __launch_bounds__(256) conv_wgrad_fold_kernel(const float* __restrict__ partials, int ksplit, long long Mtot, int Cout,
+                                                              bf16* __restrict__ dw, int C, int S, long long sk, long long sr, long long ss,
+                                                              long long sc) {
+    __shared__ float tile[32][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const long long m0 = (long long)blockIdx.x * 32;
+    const int k0 = blockIdx.y * 32;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const long long m = m0 + ty + i * 8;
+        const float* src = partials + (size_t)m * Cout + k0 + tx;
+        float a0 = 0.f, a1 = 0.f;
+        int q = 0;
+        for (; q + 1 < ksplit; q += 2) {
+            a0 += src[(size_t)q * Mtot * Cout];
+            a1 += src[(size_t)(q + 1) * Mtot * Cout];
+        }
+        if (q < ksplit) a0 += src[(size_t)q * Mtot * Cout];
+        tile[ty + i * 8][tx] = a0 + a1;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int k = k0 + ty + i * 8;
+        const long long m = m0 + tx;
+        const int tap = (int)(m / C), c = (int)(m - (long long)tap * C);
+        const int r = tap / S, s = tap - r * S;
+        dw[k * sk + r * sr + s * ss + c * sc] = __float2bfloat16(tile[tx][ty + i * 8]);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+int make_map4(CUtensorMap* map, const void* base, const cuuint64_t (&dims)[4], const cuuint64_t (&strides)[3], const cuuint32_t (&box)[4],
+              const char* what) {
+    tma_host::EncodeTiledFn enc = tma_host::encoder();
+    DDL_REQUIRE(enc != nullptr, "%s: cuTensorMapEncodeTiled is not available from the driver", what);
+    DDL_REQUIRE(((uintptr_t)base & 15) == 0, "%s: tensor must be 16-byte aligned", what);
+    cuuint32_t estr[4] = {1u, 1u, 1u, 1u};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DDL_REQUIRE(r == CUDA_SUCCESS, "%s: cuTensorMapEncodeTiled (4-D) failed with CUresult %d (dims %llu %llu %llu %llu, box %u %u %u %u)", what,
+                (int)r, (unsigned long long)dims[0], (unsigned long long)dims[1], (unsigned long long)dims[2], (unsigned long long)dims[3],
+                box[0], box[1], box[2], box[3]);
+    return 0;
+}
+
+// how one operand tile (box) walks the pixel grid [N][GH][GW]
+struct BoxGeo {
+    int N, GH, GW;  // grid the boxes tile (flattened 1x1 layers: N = GH = 1, GW = all pixels)
+    int bw, bh, nb, tiles_w, tiles_h, ngroups;
+    int pix() const { return bw * bh * nb; }
+    int tiles() const { return ngroups * tiles_h * tiles_w; }
+};
+
+BoxGeo choose_box(int N, int GH, int GW, int max_rows) {
+    BoxGeo g;
+    g.N = N; g.GH = GH; g.GW = GW;
+    g.bw = GW < max_rows ? GW : max_rows;
+    g.tiles_w = (GW + g.bw - 1) / g.bw;
+    int bh = max_rows / g.bw;
+    if (bh < 1) bh = 1;
+    if (bh > GH) bh = GH;
+    g.tiles_h = (GH + bh - 1) / bh;
+    g.bh = (GH + g.tiles_h - 1) / g.tiles_h;  // same number of tiles, evenly filled
+    g.nb = 1;
+    if (g.bh == GH && g.bw == GW) {
+        g.nb = max_rows / (g.bw * g.bh);
+        if (g.nb > N) g.nb = N;
+        if (g.nb < 1) g.nb = 1;
+    }
+    g.ngroups = (N + g.nb - 1) / g.nb;
+    return g;
+}
+
+struct ConvShape {
+    int N, H, W, C, Cout, R, S, stride, pad, OH, OW;
+    bool flat;  // 1x1 / stride 1: no spatial structure
+};
+
+bool conv_ok(int N, int H, int W, int C, int Cout, int R, int S, int stride, int pad) {
+    if (!(N >= 1 && H >= 1 && W >= 1 && R == S && ((R == 1 && pad == 0) || (R == 3 && pad == 1)) && (stride == 1 || stride == 2))) return false;
+    if (C % 64 != 0 || Cout % 64 != 0 || C < 64 || Cout < 64) return false;
+    if (!(Cout <= 256 || Cout % 256 == 0) || !(C <= 256 || C % 256 == 0)) return false;
+    if (stride == 2 && (H % 2 != 0 || W % 2 != 0)) return false;
+    if ((long long)N * H * W >= (1ll << 31) - 256) return false;
+    return true;
+}
+
+ConvShape make_shape(int N, int H, int W, int C, int Cout, int R, int S, int stride, int pad) {
+    ConvShape s;
+    s.N = N; s.H = H; s.W = W; s.C = C; s.Cout = Cout; s.R = R; s.S = S; s.stride = stride; s.pad = pad;
+    s.OH = (H + 2 * pad - R) / stride + 1;
+    s.OW = (W + 2 * pad - S) / stride + 1;
+    s.flat = (R == 1 && stride == 1);
+    return s;
+}
+
+inline int floor_div2(int e) { return e >= 0 ? e / 2 : -((-e + 1) / 2); }
+
+// tensor maps of an NHWC activation [N, H, W, C] read with boxes [64, bw, bh, nb]: one map (stride 1), one flattened map
+// (1x1 layers), or four parity maps (stride 2: map ph * 2 + pw sees the pixels (2i + ph, 2j + pw))
+int make_act_maps(CUtensorMap* out4, const void* base, int N, int H, int W, int C, int stride, bool flat, const BoxGeo& g, const char* what) {
+    const cuuint32_t box[4] = {64u, (cuuint32_t)g.bw, (cuuint32_t)g.bh, (cuuint32_t)g.nb};
+    if (flat) {
+        const cuuint64_t P = (cuuint64_t)N * H * W;
+        const cuuint64_t dims[4] = {(cuuint64_t)C, P, 1, 1};
+        const cuuint64_t str[3] = {(cuuint64_t)C * 2, P * C * 2, P * C * 2};
+        if (int e = make_map4(&out4[0], base, dims, str, box, what)) return e;
+        for (int i = 1; i < 4; ++i) out4[i] = out4[0];
+        return 0;
+    }
+    if (stride == 1) {
+        const cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+        const cuuint64_t str[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+        if (int e = make_map4(&out4[0], base, dims, str, box, what)) return e;
+        for (int i = 1; i < 4; ++i) out4[i] = out4[0];
+        return 0;
+    }
+    for (int ph = 0; ph < 2; ++ph)
+        for (int pw = 0; pw < 2; ++pw) {
+            const char* b = (const char*)base + ((size_t)ph * W + pw) * C * 2;
+            const cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)(W / 2), (cuuint64_t)(H / 2), (cuuint64_t)N};
+            const cuuint64_t str[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 2};
+            if (int e = make_map4(&out4[ph * 2 + pw], b, dims, str, box, what)) return e;
+        }
+    return 0;
+}
+
+// taps of the forward convolution (also the x-side taps of the weight gradient): input pixel = stride * o + r - pad
+int forward_taps(const ConvShape& s, Tap* taps) {
+    int n = 0;
+    for (int r = 0; r < s.R; ++r)
+        for (int q = 0; q < s.S; ++q) {
+            Tap t;
+            if (s.stride == 1) {
+                t.dh = (int8_t)(r - s.pad); t.dw = (int8_t)(q - s.pad); t.map = 0;
+            } else {
+                const int eh = r - s.pad, ew = q - s.pad;
+                const int dh = floor_div2(eh), dw = floor_div2(ew);
+                t.dh = (int8_t)dh; t.dw = (int8_t)dw;
+                t.map = (int8_t)((eh - 2 * dh) * 2 + (ew - 2 * dw));
+            }
+            t.wtap = (int8_t)(r * s.S + q);
+            taps[n++] = t;
+        }
+    return n;
+}
+
+int g_wgrad_rows = 0;  // 0 = auto, 64 / 128 = forced pixel-chunk size of the weight gradient (benchmarks)
+
+int launch_data(bool b_mn, const ConvMaps& maps, DataParams& p, cudaStream_t stream) {
+    p.groups = p.bn / 64;
+    const int stage_bytes = kStageA + p.bn * 128;
+    const int fixed = kEpiWarps * kStgBytes + 512 + 1024;
+    p.stages = (227 * 1024 - fixed) / stage_bytes;
+    if (p.stages > kMaxStages) p.stages = kMaxStages;
+    DDL_REQUIRE(p.stages >= 2, "conv: tile does not fit in shared memory");
+    const int smem = fixed + p.stages * stage_bytes;
+    static int attr_smem[2] = {0, 0};
+    if (smem > attr_smem[b_mn ? 1 : 0]) {
+        if (b_mn) DDL_CHECK(cudaFuncSetAttribute(conv_data_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        else DDL_CHECK(cudaFuncSetAttribute(conv_data_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_smem[b_mn ? 1 : 0] = smem;
+    }
+    int m_groups = DDL_SM_COUNT / p.num_n_blocks;
+    if (m_groups > p.num_tiles) m_groups = p.num_tiles;
+    if (m_groups < 1) m_groups = 1;
+    const int grid = m_groups * p.num_n_blocks;
+    if (b_mn) conv_data_kernel<true><<<grid, kThreads, smem, stream>>>(maps, p);
+    else conv_data_kernel<false><<<grid, kThreads, smem, stream>>>(maps, p);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+void fill_geo(DataParams& p, const BoxGeo& g) {
+    p.N = g.N; p.OHt = g.GH; p.OWt = g.GW;
+    p.bw = g.bw; p.bh = g.bh; p.nb = g.nb;
+    p.tiles_w = g.tiles_w; p.tiles_h = g.tiles_h;
+    p.tiles_per_cls = g.tiles();
+    p.a_bytes = (uint32_t)g.pix() * 128u;
+}
+
+int fwd_m_groups(const ConvShape& s) {
+    const BoxGeo g = s.flat ? choose_box(1, 1, s.N * s.OH * s.OW, kTileM) : choose_box(s.N, s.OH, s.OW, kTileM);
+    const int bn = s.Cout <= 256 ? s.Cout : 256;
+    int m_groups = DDL_SM_COUNT / (s.Cout / bn);
+    if (m_groups > g.tiles()) m_groups = g.tiles();
+    return m_groups < 1 ? 1 : m_groups;
+}
+
+// weight-gradient launch plan (shared by the scratch-size query and the launch)
+struct WgradPlan {
+    BoxGeo g;
+    int bn, nblk, U, G, mgroups, ksteps, slot_bytes, stages, ksplit, cps;
+};
+
+bool plan_wgrad(const ConvShape& s, WgradPlan& w) {
+    w.bn = s.Cout <= 256 ? s.Cout : 256;
+    w.nblk = s.Cout / w.bn;
+    w.U = s.R * s.S * (s.C / 64);
+    int G = 512 / w.bn;
+    if (G > (w.U + 1) / 2) G = (w.U + 1) / 2;
+    const int avail = 227 * 1024 - 1024 - 512;
+    for (;; --G) {
+        if (G < 1) return false;
+        const int nslots = w.bn / 64 + 2 * G;
+        int rows_opts[2] = {128, 64};
+        bool found = false;
+        for (int o = 0; o < 2 && !found; ++o) {
+            const int rows = g_wgrad_rows ? g_wgrad_rows : rows_opts[o];
+            const BoxGeo g = s.flat ? choose_box(1, 1, s.N * s.OH * s.OW, rows) : choose_box(s.N, s.OH, s.OW, rows);
+            const int ksteps = (g.pix() + 15) / 16;
+            const int slot = ksteps * 2048;
+            int stages = avail / (nslots * slot);
+            if (stages > 4) stages = 4;
+            const bool last = (o == 1) || g_wgrad_rows != 0;
+            if (stages >= 3 || (last && stages >= 2)) {
+                w.g = g; w.ksteps = ksteps; w.slot_bytes = slot; w.stages = stages;
+                found = true;
+            }
+            if (g_wgrad_rows) break;
+        }
+        if (found) break;
+    }
+    w.G = G;
+    w.mgroups = (w.U + 2 * G - 1) / (2 * G);
+    const int items = w.nblk * w.mgroups;
+    const int chunks = w.g.tiles();
+    int ksplit = DDL_SM_COUNT / items;
+    if (ksplit < 1) ksplit = 1;
+    if (ksplit > chunks) ksplit = chunks;
+    w.cps = (chunks + ksplit - 1) / ksplit;
+    w.ksplit = (chunks + w.cps - 1) / w.cps;
+    return true;
+}
+
+}  // namespace
+
+DDL_API int ddl_conv_supported(int N, int H, int W, int C, int Cout, int R, int S, int stride, int pad) {
+    return conv_ok(N, H, W, C, Cout, R, S, stride, pad) ? 1 : 0;
+}
+
+DDL_API int ddl_conv_fwd_groups(int N, int H, int W, int C, int Cout, int R, int S, int stride, int pad) {
+    if (!conv_ok(N, H, W, C, Cout, R, S, stride, pad)) return 0;
+    return fwd_m_groups(make_shape(N, H, W, C, Cout, R, S, stride, pad));
+}
+
+DDL_API int ddl_conv_set_tuning(int wgrad_rows) {
+    DDL_REQUIRE(wgrad_rows == 0 || wgrad_rows == 64 || wgrad_rows == 128, "conv tuning: wgrad_rows must be 0, 64 or 128");
+    g_wgrad_rows = wgrad_rows;
+    return 0;
+}
+
+DDL_API int ddl_conv_fwd(const void* x, const void* w, void* y, float* partials, int N, int H, int W, int C, int Cout, int R, int S, int stride,
+                         int pad, void* stream_) {
+    DDL_REQUIRE(conv_ok(N, H, W, C, Cout, R, S, stride, pad), "conv fwd: unsupported shape (N %d, %dx%d, C %d -> %d, k %d, stride %d, pad %d)", N,
+                H, W, C, Cout, R, stride, pad);
+    DDL_REQUIRE(x && w && y, "conv fwd: null pointer");
+    const ConvShape s = make_shape(N, H, W, C, Cout, R, S, stride, pad);
+    const BoxGeo g = s.flat ? choose_box(1, 1, N * s.OH * s.OW, kTileM) : choose_box(N, s.OH, s.OW, kTileM);
+    DataParams p = {};
+    p.out = (bf16*)y;
+    p.partials = partials;
+    p.ncls = 1;
+    p.cls_ntaps[0] = forward_taps(s, p.taps[0]);
+    fill_geo(p, g);
+    p.OHf = g.GH; p.OWf = g.GW; p.os = 1;
+    p.Cn = Cout;
+    p.num_tiles = p.tiles_per_cls;
+    p.bn = Cout <= 256 ? Cout : 256;
+    p.num_n_blocks = Cout / p.bn;
+    p.cblocks = C / 64;
+    p.w_tap_stride = C;
+    ConvMaps maps;
+    if (int e = make_act_maps(maps.in, x, N, H, W, C, stride, s.flat, g, "conv fwd")) return e;
+    if (int e = tma_host::encode_2d(&maps.w, w, Cout, (long long)R * S * C, (long long)R * S * C * 2, p.bn, "conv fwd weights")) return e;
+    return launch_data(false, maps, p, (cudaStream_t)stream_);
+}
+
+// dx [N, H, W, C] from dy [N, OH, OW, Cout] and w [Cout][R][S][C]
+DDL_API int ddl_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C, int Cout, int R, int S, int stride, int pad,
+                           void* stream_) {
+    DDL_REQUIRE(conv_ok(N, H, W, C, Cout, R, S, stride, pad), "conv dgrad: unsupported shape (N %d, %dx%d, C %d -> %d, k %d, stride %d, pad %d)",
+                N, H, W, C, Cout, R, stride, pad);
+    DDL_REQUIRE(dy && w && dx, "conv dgrad: null pointer");
+    const ConvShape s = make_shape(N, H, W, C, Cout, R, S, stride, pad);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    // boxes walk the dy grid; a class of the stride-2 case covers H/2 x W/2 = OH x OW input pixels
+    const BoxGeo g = s.flat ? choose_box(1, 1, N * s.OH * s.OW, kTileM) : choose_box(N, s.OH, s.OW, kTileM);
+    DataParams p = {};
+    p.out = (bf16*)dx;
+    p.partials = nullptr;
+    fill_geo(p, g);
+    p.Cn = C;
+    p.bn = C <= 256 ? C : 256;
+    p.num_n_blocks = C / p.bn;
+    p.cblocks = Cout / 64;
+    p.w_tap_stride = C;
+    if (stride == 1) {
+        p.ncls = 1;
+        int n = 0;
+        for (int r = 0; r < R; ++r)
+            for (int q = 0; q < S; ++q) {
+                Tap t;
+                t.dh = (int8_t)(pad - r); t.dw = (int8_t)(pad - q); t.map = 0; t.wtap = (int8_t)(r * S + q);
+                p.taps[0][n++] = t;
+            }
+        p.cls_ntaps[0] = n;
+        p.OHf = g.GH; p.OWf = g.GW; p.os = 1;
+    } else {
+        // input pixel (2a + ph, 2b + pw) receives dy[(2a + ph + pad - r) / 2, ...] for the taps r of matching parity
+        struct Cls { int ph, pw, n; Tap taps[9]; } cls[4];
+        int nc = 0;
+        bool uncovered = false;
+        for (int ph = 0; ph < 2; ++ph)
+            for (int pw = 0; pw < 2; ++pw) {
+                Cls c;
+                c.ph = ph; c.pw = pw; c.n = 0;
+                for (int r = 0; r < R; ++r)
+                    for (int q = 0; q < S; ++q) {
+                        const int eh = ph + pad - r, ew = pw + pad - q;
+                        if ((eh & 1) || (ew & 1)) continue;
+                        Tap t;
+                        t.dh = (int8_t)(eh / 2); t.dw = (int8_t)(ew / 2); t.map = 0; t.wtap = (int8_t)(r * S + q);
+                        c.taps[c.n++] = t;
+                    }
+                if (c.n == 0) uncovered = true;
+                else cls[nc++] = c;
+            }
+        // pixels that no tap reaches (1x1 / stride 2: three of four) get zeros
+        if (uncovered) DDL_CHECK(cudaMemsetAsync(dx, 0, (size_t)N * H * W * C * 2, stream));
+        std::sort(cls, cls + nc, [](const Cls& a, const Cls& b) { return a.n > b.n; });  // heavy classes first
+        p.ncls = nc;
+        for (int i = 0; i < nc; ++i) {
+            p.cls_ntaps[i] = cls[i].n;
+            p.cls_oph[i] = cls[i].ph;
+            p.cls_opw[i] = cls[i].pw;
+            for (int j = 0; j < cls[i].n; ++j) p.taps[i][j] = cls[i].taps[j];
+        }
+        p.OHf = H; p.OWf = W; p.os = 2;
+    }
+    p.num_tiles = p.ncls * p.tiles_per_cls;
+    ConvMaps maps;
+    if (int e = make_act_maps(maps.in, dy, N, s.OH, s.OW, Cout, 1, s.flat, g, "conv dgrad")) return e;
+    if (int e = tma_host::encode_2d(&maps.w, w, Cout, (long long)R * S * C, (long long)R * S * C * 2, 64, "conv dgrad weights")) return e;
+    return launch_data(true, maps, p, stream);
+}
+
+DDL_API size_t ddl_conv_wgrad_scratch_bytes(int N, int H, int W, int C, int Cout, int R, int S, int stride, int pad) {
+    if (!conv_ok(N, H, W, C, Cout, R, S, stride, pad)) return 0;
+    WgradPlan w;
+    if (!plan_wgrad(make_shape(N, H, W, C, Cout, R, S, stride, pad), w)) return 0;
+    return (size_t)w.ksplit * (size_t)w.U * 64 * Cout * sizeof(float);
+}
+
+// dw [Cout, C, R, S] addressed with element strides (sk, sc, sr, ss) from x [N, H, W, C] and dy [N, OH, OW, Cout]
+DDL_API int ddl_conv_wgrad(const void* x, const void* dy, void* dw, long long sk, long long sc, long long sr, long long ss, void* scratch,
+                           size_t scratch_bytes, int N, int H, int W, int C, int Cout, int R, int S, int stride, int pad, void* stream_) {
+    DDL_REQUIRE(conv_ok(N, H, W, C, Cout, R, S, stride, pad), "conv wgrad: unsupported shape (N %d, %dx%d, C %d -> %d, k %d, stride %d, pad %d)",
+                N, H, W, C, Cout, R, stride, pad);
+    DDL_REQUIRE(x && dy && dw && scratch, "conv wgrad: null pointer");
+    const ConvShape s = make_shape(N, H, W, C, Cout, R, S, stride, pad);
+    WgradPlan w;
+    DDL_REQUIRE(plan_wgrad(s, w), "conv wgrad: no launch plan fits in shared memory");
+    DDL_REQUIRE(scratch_bytes >= ddl_conv_wgrad_scratch_bytes(N, H, W, C, Cout, R, S, stride, pad), "conv wgrad: scratch too small");
+    WgradParams p = {};
+    p.partials = (float*)scratch;
+    p.ntaps = forward_taps(s, p.taps);
+    p.N = w.g.N; p.OHt = w.g.GH; p.OWt = w.g.GW;
+    p.bw = w.g.bw; p.bh = w.g.bh; p.nb = w.g.nb;
+    p.tiles_w = w.g.tiles_w; p.tiles_h = w.g.tiles_h;
+    p.num_chunks = w.g.tiles();
+    p.cblocks = C / 64; p.U = w.U; p.G = w.G; p.mgroups = w.mgroups;
+    p.Cout = Cout; p.bn = w.bn; p.nblk = w.nblk;
+    p.ksplit = w.ksplit; p.cps = w.cps;
+    p.slot_bytes = w.slot_bytes; p.ksteps = w.ksteps; p.stages = w.stages; p.pix = w.g.pix();
+    p.Mtot = (long long)w.U * 64;
+    ConvMaps maps;
+    if (int e = make_act_maps(maps.in, x, N, H, W, C, stride, s.flat, w.g, "conv wgrad x")) return e;
+    {
+        CUtensorMap tmp[4];
+        if (int e = make_act_maps(tmp, dy, N, s.OH, s.OW, Cout, 1, s.flat, w.g, "conv wgrad dy")) return e;
+        maps.w = tmp[0];
+    }
+    const int smem = p.stages * (p.bn / 64 + 2 * p.G) * p.slot_bytes + 512 + 1024;
+    static int attr_smem = 0;
+    if (smem > attr_smem) {
+        DDL_CHECK(cudaFuncSetAttribute(conv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_smem = smem;
+    }
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int grid = p.nblk * p.mgroups * p.ksplit;
+    conv_wgrad_kernel<<<grid, kWgThreads, smem, stream>>>(maps, p);
+    DDL_LAUNCH_CHECK();
+    dim3 fgrid((unsigned)(p.Mtot / 32), (unsigned)(Cout / 32));
+    conv_wgrad_fold_kernel<<<fgrid, 256, 0, stream>>>(p.partials, p.ksplit, p.Mtot, Cout, (bf16*)dw, C, S, sk, sr, ss, sc);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}

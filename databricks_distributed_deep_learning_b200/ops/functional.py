@@ -594,11 +594,100 @@ class _Conv1x1WS(torch.autograd.Function):
         return dx, dw
 
 
+# ----------------------------------------------------------------------------- implicit-GEMM convolutions (tcgen05)
+# csrc/conv_igemm.cu: forward (+ BatchNorm statistics), data gradient and weight gradient of the 1x1 / 3x3 layers.
+# DDL_CONV=cudnn sends every convolution except the stem back to the library (comparison runs only).
+_CONV_NATIVE = _os.environ.get("DDL_CONV", "native") == "native"
+
+
+def _conv_geom(x: torch.Tensor, conv: nn.Conv2d):
+    N_, C, H, W = x.shape
+    return (N_, H, W, C, conv.out_channels, conv.kernel_size[0], conv.kernel_size[1], conv.stride[0], conv.padding[0])
+
+
+def conv_native_usable(x: torch.Tensor, conv: nn.Conv2d) -> bool:
+    if not (_CONV_NATIVE and x.is_cuda and x.dim() == 4 and x.dtype == torch.bfloat16 and conv.weight.dtype == torch.bfloat16
+            and conv.groups == 1 and conv.bias is None and conv.dilation == (1, 1) and conv.stride[0] == conv.stride[1]
+            and conv.padding[0] == conv.padding[1] and conv.padding_mode == "zeros"):
+        return False
+    return bool(L.lib().ddl_conv_supported(*_conv_geom(x, conv)))
+
+
+def _weight_krsc(weight: torch.Tensor) -> torch.Tensor:
+    """The weight as [Cout][R][S][C] memory (channels-last); 1x1 weights are that in either layout."""
+    Cout, C, R, S = weight.shape
+    if weight.stride() == (R * S * C, 1, S * C, C) or (R == 1 and S == 1 and weight.stride(0) == C and weight.stride(1) == 1):
+        return weight
+    return weight.contiguous(memory_format=torch.channels_last)
+
+
+class _ConvNative(torch.autograd.Function):
+    """conv2d on NHWC bf16 through the implicit-GEMM kernels; returns (y, partial BatchNorm statistics of y)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, stride, pad, use_ws):
+        Nb, C, H, W = x.shape
+        Cout, _, R, S = weight.shape
+        if not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        w = _weight_krsc(weight)
+        geom = (Nb, H, W, C, Cout, R, S, stride, pad)
+        OH, OW = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
+        dev = x.device
+        lib = L.lib()
+        y = torch.empty((Nb, Cout, OH, OW), dtype=torch.bfloat16, device=dev, memory_format=torch.channels_last)
+        if use_ws:
+            M = Nb * H * W
+            partials = torch.empty(lib.ddl_conv1x1_grid(M, Cout) * 2 * Cout, dtype=torch.float32, device=dev)
+            L.call("ddl_conv1x1_fwd", x.data_ptr(), w.data_ptr(), y.data_ptr(), partials.data_ptr(), M, Cout, C, L.stream_ptr(dev))
+        else:
+            partials = torch.empty(lib.ddl_conv_fwd_groups(*geom) * 2 * Cout, dtype=torch.float32, device=dev)
+            L.call("ddl_conv_fwd", x.data_ptr(), w.data_ptr(), y.data_ptr(), partials.data_ptr(), *geom, L.stream_ptr(dev))
+        ctx.save_for_backward(x, weight)
+        ctx.geom = geom
+        ctx.mark_non_differentiable(partials)
+        return y, partials
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy, _unused):
+        x, weight = ctx.saved_tensors
+        geom = ctx.geom
+        dev = x.device
+        st = L.stream_ptr(dev)
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x, memory_format=torch.channels_last)
+            L.call("ddl_conv_dgrad", dy.data_ptr(), _weight_krsc(weight).data_ptr(), dx.data_ptr(), *geom, st)
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty_like(weight)
+            if not dw.is_non_overlapping_and_dense():
+                dw = torch.empty(weight.shape, dtype=weight.dtype, device=dev, memory_format=torch.channels_last)
+            scratch = _scratch(L.lib().ddl_conv_wgrad_scratch_bytes(*geom), dev)
+            sk, sc, sr, ss = dw.stride()
+            L.call("ddl_conv_wgrad", x.data_ptr(), dy.data_ptr(), dw.data_ptr(), sk, sc, sr, ss, scratch.data_ptr(), scratch.numel(), *geom, st)
+        return dx, dw, None, None, None
+
+
+def conv2d_native(x: torch.Tensor, conv: nn.Conv2d):
+    """``F.conv2d(x, conv.weight, stride, padding)`` on the tcgen05 implicit-GEMM kernels.  Returns ``(y, partials)``;
+    ``partials`` are the per-CTA BatchNorm statistics of y for :func:`bn_act` (``partials=``)."""
+    use_ws = conv1x1_ws_usable(x, conv)
+    return _ConvNative.apply(x, conv.weight, conv.stride[0], conv.padding[0], use_ws)
+
+
 def conv_bn_act(x, conv: nn.Conv2d, bn: nn.BatchNorm2d, relu: bool = True, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """conv -> BN -> (+residual) -> ReLU on NHWC bf16.  Normalise, residual add and ReLU are the native kernels in
-    ``csrc/bn_act.cu``; the convolution is the library call (cuDNN through ATen) unless ``DDL_CONV1X1=gemm``, which
-    runs the 1x1 / stride-1 convolutions (32 of ResNet-50's 53) on the tcgen05 GEMM whose epilogue also produces the
-    BatchNorm statistics (see the measurement note at ``_CONV1X1_GEMM``)."""
+    """conv -> BN -> (+residual) -> ReLU on NHWC bf16.  The convolution (forward, data gradient, weight gradient) runs on
+    the implicit-GEMM tcgen05 kernels of ``csrc/conv_igemm.cu`` (skinny 1x1 forwards on the weight-stationary kernel of
+    ``csrc/conv1x1.cu``); its epilogue leaves the BatchNorm statistics of the output, so normalise + residual + ReLU
+    (``csrc/bn_act.cu``) is one more pass over y.  Shapes the kernels do not take (channel counts that are not multiples
+    of 64, grouped / dilated / biased convolutions) fall back to the library call."""
+    if conv_native_usable(x, conv):
+        y, partials = conv2d_native(x, conv)
+        training = bn.training or bn.running_mean is None
+        return bn_act(y, bn, relu=relu, residual=residual, partials=partials if training else None)
     if _is_gemm_conv(x, conv):
         training = bn.training or bn.running_mean is None
         y, sums = _Conv1x1.apply(x, conv.weight, training)
@@ -611,9 +700,7 @@ def conv_bn_act(x, conv: nn.Conv2d, bn: nn.BatchNorm2d, relu: bool = True, resid
 
 
 def conv2d(x, conv: nn.Conv2d) -> torch.Tensor:
-    # Library convolution.  Running its data-gradient and weight-gradient kernels concurrently on two streams was
-    # measured (B200, ResNet-50 step, thresholds 16 - 128 MB): no gain beyond the +-1 % run-to-run spread, so it is
-    # not done.
+    """Library convolution: only for shapes outside ``ddl_conv_supported`` (e.g. the 3-channel CIFAR stem)."""
     return F.conv2d(x, conv.weight, None, conv.stride, conv.padding, conv.dilation, conv.groups)
 
 

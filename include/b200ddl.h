@@ -211,6 +211,29 @@ int ddl_conv1x1_supported(long long M, int N, int K);
 int ddl_conv1x1_grid(long long M, int N);
 int ddl_conv1x1_fwd(const void* x, const void* w, void* y, float* partials, long long M, int N, int K, void* stream);
 
+/* ---- 1x1 / 3x3 convolutions as implicit GEMMs on tcgen05 (csrc/conv_igemm.cu), K9 -----------------------------
+ * NHWC bf16 activations, channels-last weights [Cout][R][S][C]; R = S in {1 (pad 0), 3 (pad 1)}, stride 1 or 2 (even H, W),
+ * C and Cout multiples of 64 (<= 256 or multiples of 256): every convolution of the reference's ResNet-50 (reference:19,
+ * SURVEY.md 2.E.2) except the 3-channel stem (csrc/stem_conv.cu).  The operand tiles are TMA boxes of the 4-D activation
+ * tensor shifted by the filter tap (zero fill = padding); nothing is unfolded in memory.
+ *   ddl_conv_fwd   : y [N, OH, OW, Cout]; partials (nullable) = fp32 [ddl_conv_fwd_groups(...)][2][Cout] per-CTA BatchNorm
+ *                    statistics of y for ddl_bn_act_fwd_train_from_partials.
+ *   ddl_conv_dgrad : dx [N, H, W, C] from dy [N, OH, OW, Cout] (every element of dx is written).
+ *   ddl_conv_wgrad : dw addressed with element strides (sk, sc, sr, ss) of a [Cout, C, R, S] tensor; scratch of
+ *                    ddl_conv_wgrad_scratch_bytes(...) holds the fp32 partials of the pixel splits (fixed-order fold).
+ * The reference only ever runs these layers forward through library kernels (reference:32, :174). */
+int ddl_conv_supported(int N, int H, int W, int C, int Cout, int R, int S, int stride, int pad);
+int ddl_conv_fwd_groups(int N, int H, int W, int C, int Cout, int R, int S, int stride, int pad);
+int ddl_conv_fwd(const void* x, const void* w, void* y, float* partials, int N, int H, int W, int C, int Cout, int R, int S, int stride,
+                 int pad, void* stream);
+int ddl_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C, int Cout, int R, int S, int stride, int pad,
+                   void* stream);
+size_t ddl_conv_wgrad_scratch_bytes(int N, int H, int W, int C, int Cout, int R, int S, int stride, int pad);
+int ddl_conv_wgrad(const void* x, const void* dy, void* dw, long long sk, long long sc, long long sr, long long ss, void* scratch,
+                   size_t scratch_bytes, int N, int H, int W, int C, int Cout, int R, int S, int stride, int pad, void* stream);
+/* benchmarks: pixel-chunk size of the weight gradient (0 = auto, 64, 128) */
+int ddl_conv_set_tuning(int wgrad_rows);
+
 /* ---- tcgen05 / TMEM / TMA GEMM (csrc/gemm_tcgen05.cu), K8 ------------------------------ */
 /* C[M,N] = epilogue(A . B^T), bf16 operands, fp32 accumulation in tensor memory.
  * A is [M,K] row-major (a_mn = 0) or stored as [K,M] (a_mn = 1); B is [N,K] (b_mn = 0) or stored
