@@ -64,7 +64,7 @@ def main():
     N = args.batch
     rows = []
     tot = {"cudnn_fwd": 0.0, "cudnn_dgrad": 0.0, "cudnn_wgrad": 0.0, "floor": 0.0}
-    print(f"{'layer':32s} {'x':>2s} {'fwd':>8s} {'dgrad':>8s} {'wgrad':>8s} {'floor':>7s} | {'n.fwd':>8s} {'n.dgrad':>8s} {'n.wgrad':>8s} {'ws.fwd':>8s}   (us per call; n.* = csrc/conv_igemm.cu, n.fwd / ws.fwd include the BN statistics)")
+    print(f"{'layer':32s} {'x':>2s} {'fwd':>8s} {'dgrad':>8s} {'wgrad':>8s} {'floor':>7s} | {'n.fwd':>8s} {'n.dgrad':>8s} {'n.wgrad':>8s} {'ws.fwd /dgrad':>16s}   (us per call; n.* = csrc/conv_igemm.cu, n.fwd / ws.fwd include the BN statistics)")
     for cnt, cin, hw, cout, k, s in LAYERS:
         pad = k // 2
         x = torch.randn(N, cin, hw, hw, device=dev).to(bf).contiguous(memory_format=torch.channels_last)
@@ -105,6 +105,9 @@ def main():
                 row["ws_fwd_stats_us"] = timeit(lambda: L.call("ddl_conv1x1_fwd", x.data_ptr(), w.data_ptr(), yy.data_ptr(), p1.data_ptr(),
                                                                M, cout, cin, st), flush)
                 g[3] = f"{row['ws_fwd_stats_us']:8.1f}"
+            if k == 1 and s == 1 and lib.ddl_conv1x1_supported(M, cin, cout):
+                row["ws_dgrad_us"] = timeit(lambda: L.call("ddl_conv1x1_dgrad", dy.data_ptr(), w.data_ptr(), dx.data_ptr(), M, cin, cout, st), flush)
+                g[3] += f" /{row['ws_dgrad_us']:6.1f}"
             del yy, dx, dw, scr
         rows.append(row)
         tot["cudnn_fwd"] += cnt * t_f
@@ -112,7 +115,7 @@ def main():
         tot["cudnn_wgrad"] += cnt * t_w
         tot["floor"] += cnt * floor
         name = f"{cin}x{hw}^2 -> {cout} k{k}/s{s}"
-        print(f"{name:32s} {cnt:2d} {t_f:8.1f} {t_d:8.1f} {t_w:8.1f} {floor:7.1f} | {g[0]:>8s} {g[1]:>8s} {g[2]:>8s} {(g[3] if len(g) > 3 else ''):>8s}")
+        print(f"{name:32s} {cnt:2d} {t_f:8.1f} {t_d:8.1f} {t_w:8.1f} {floor:7.1f} | {g[0]:>8s} {g[1]:>8s} {g[2]:>8s} {(g[3] if len(g) > 3 else ''):>16s}")
         del x, w, y, dy
     print("totals per step (ms):", {k: round(v / 1e3, 3) for k, v in tot.items()})
     os.makedirs(os.path.dirname(args.json), exist_ok=True)

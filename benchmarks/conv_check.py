@@ -31,7 +31,7 @@ def main():
         name = f"{cin}x{hw}^2 -> {cout} k{k}/s{s}"
         try:
             e = conv_case(args.batch, cin, hw, cout, k, s)
-            ok = e["fwd"] < 8e-3 and e["dgrad"] < 8e-3 and e["wgrad"] < 8e-3 and e["sum"] < 2e-3 and e["sumsq"] < 2e-3
+            ok = all(e[q] < 8e-3 for q in ("fwd", "dgrad", "wgrad")) and e["sum"] < 2e-3 and e["sumsq"] < 2e-3 and e.get("ws_dgrad", 0) < 8e-3
             bad += 0 if ok else 1
             print(f"{i:2d} {name:30s} " + " ".join(f"{k2}={v:.2e}" for k2, v in e.items()) + ("" if ok else "   <-- FAIL"), flush=True)
         except Exception:

@@ -82,6 +82,30 @@ def main():
             x = torch.randn(256, cin, hw, hw, device="cuda").to(bf).contiguous(memory_format=torch.channels_last)
             for _ in range(2):
                 OF._Conv1x1WS.apply(x, conv.weight)
+    elif mode == "conv":
+        # implicit-GEMM convolutions: forward (+ statistics), data gradient, weight gradient on three layer shapes
+        from databricks_distributed_deep_learning_b200.ops import _lib as L
+
+        lib = L.lib()
+        shapes = [(256, 14, 1024, 1, 1), (256, 14, 256, 3, 1), (64, 56, 64, 3, 1)]
+        if len(sys.argv) > 2:
+            shapes = [tuple(int(v) for v in sh.split(",")) for sh in sys.argv[2].split(";")]
+        for cin, hw, cout, k, s in shapes:
+            N, pad = 256, k // 2
+            oh = (hw + 2 * pad - k) // s + 1
+            cl = torch.channels_last
+            x = torch.randn(N, cin, hw, hw, device="cuda").to(bf).contiguous(memory_format=cl)
+            w = torch.randn(cout, cin, k, k, device="cuda").to(bf).contiguous(memory_format=cl)
+            dy = torch.randn(N, cout, oh, oh, device="cuda").to(bf).contiguous(memory_format=cl)
+            y, dx, dw = torch.empty_like(dy), torch.empty_like(x), torch.empty_like(w)
+            geom = (N, hw, hw, cin, cout, k, k, s, pad)
+            part = torch.empty(lib.ddl_conv_fwd_groups(*geom) * 2 * cout, dtype=torch.float32, device="cuda")
+            scr = torch.empty(max(lib.ddl_conv_wgrad_scratch_bytes(*geom), 16), dtype=torch.uint8, device="cuda")
+            st = L.stream_ptr()
+            for _ in range(1 if len(sys.argv) > 3 else 2):
+                L.call("ddl_conv_fwd", x.data_ptr(), w.data_ptr(), y.data_ptr(), part.data_ptr(), *geom, st)
+                L.call("ddl_conv_dgrad", dy.data_ptr(), w.data_ptr(), dx.data_ptr(), *geom, st)
+                L.call("ddl_conv_wgrad", x.data_ptr(), dy.data_ptr(), dw.data_ptr(), *dw.stride(), scr.data_ptr(), scr.numel(), *geom, st)
     torch.cuda.synchronize()
     print("ok", mode)
 

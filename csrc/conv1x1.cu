@@ -43,6 +43,9 @@ struct C1Params {
     int groups;       // n_cta / 64 active column groups
 };
 
+// B_MN = false: forward, w is [N][K] (K-major rows).  B_MN = true: data gradient, the same weight tensor is read as
+// [K][N] (MN-major): y = dx, x = dy, N = conv input channels, K = conv output channels; no statistics (partials null).
+template <bool B_MN>
 __global__ void __launch_bounds__(kThreads, 1) conv1x1_fwd_kernel(const __grid_constant__ CUtensorMap tma_x,
                                                                    const __grid_constant__ CUtensorMap tma_w, const C1Params p) {
     extern __shared__ uint8_t smem_raw[];
@@ -86,8 +89,14 @@ __global__ void __launch_bounds__(kThreads, 1) conv1x1_fwd_kernel(const __grid_c
         // ===================== TMA producer =====================
         if (lane == 0) {
             mbar_expect_tx(w_bar, (uint32_t)w_bytes);
-            for (int kb = 0; kb < p.kblocks; ++kb)
-                tma_load_2d(w_smem + (size_t)kb * p.n_cta * 128, &tma_w, w_bar, kb * 64, col_block);
+            for (int kb = 0; kb < p.kblocks; ++kb) {
+                if (!B_MN) {
+                    tma_load_2d(w_smem + (size_t)kb * p.n_cta * 128, &tma_w, w_bar, kb * 64, col_block);
+                } else {
+                    for (int j = 0; j < p.groups; ++j)  // [64 k-rows x 64 n] boxes, 64-wide n blocks 8 KB apart
+                        tma_load_2d(w_smem + (size_t)kb * p.n_cta * 128 + j * 8192, &tma_w, w_bar, col_block + j * 64, kb * 64);
+                }
+            }
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
@@ -102,7 +111,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv1x1_fwd_kernel(const __grid_c
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
-            const uint32_t idesc = make_idesc(kTileM, p.n_cta, false, false);
+            const uint32_t idesc = make_idesc(kTileM, p.n_cta, false, B_MN);
             mbar_wait(w_bar, 0);
             tc_fence_after();
             int stage = 0, acc = 0;
@@ -119,7 +128,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv1x1_fwd_kernel(const __grid_c
                     const uint32_t sb = sw + kb * (p.n_cta * 128);
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        umma_bf16(d_tmem, make_smem_desc(sa + k * 32, 16, 1024), make_smem_desc(sb + k * 32, 16, 1024), idesc,
+                        umma_bf16(d_tmem, make_smem_desc(sa + k * 32, 16, 1024),
+                                  B_MN ? make_smem_desc(sb + k * 2048, 8192, 1024) : make_smem_desc(sb + k * 32, 16, 1024), idesc,
                                   (kb > 0 || k > 0) ? 1u : 0u);
                     umma_commit(&empty_bar[stage]);
                     if (++stage == p.stages) { stage = 0; phase ^= 1; }
@@ -166,6 +176,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv1x1_fwd_kernel(const __grid_c
                 if (++acc == p.nbuf) { acc = 0; acc_phase ^= 1; }
                 __syncwarp();
                 float a_s0 = 0.f, a_s1 = 0.f, a_q0 = 0.f, a_q1 = 0.f;
+                if (!B_MN) {
 #pragma unroll 8
                 for (int r = 0; r < 32; ++r) {
                     const uint32_t wv = *reinterpret_cast<const uint32_t*>(stg + r * 128 + (((lane >> 2) ^ (r & 7)) * 16) + (lane & 3) * 4);
@@ -174,6 +185,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv1x1_fwd_kernel(const __grid_c
                     a_q0 += v0 * v0;
                     a_s1 += v1;
                     a_q1 += v1 * v1;
+                }
                 }
                 s0 += a_s0;
                 s1 += a_s1;
@@ -187,6 +199,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv1x1_fwd_kernel(const __grid_c
                 }
                 __syncwarp();
             }
+            if (B_MN) goto done;  // data gradient: no statistics
             // fold the four lane-quarter warps of this column group in fixed order -> per-CTA partials
             float* mine = reinterpret_cast<float*>(stg);  // own staging area, free now
             __syncwarp();
@@ -212,6 +225,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv1x1_fwd_kernel(const __grid_c
             }
         }
     }
+done:
     tc_fence_before();
     __syncthreads();
     if (warp == 1) {
@@ -244,9 +258,9 @@ DDL_API int ddl_conv1x1_grid(long long M, int N) {
     return (int)(gx < 1 ? 1 : gx);
 }
 
-DDL_API int ddl_conv1x1_fwd(const void* x, const void* w, void* y, float* partials, long long M, int N, int K, void* stream_) {
+static int conv1x1_launch(bool b_mn, const void* x, const void* w, void* y, float* partials, long long M, int N, int K, void* stream_) {
     DDL_REQUIRE(shape_ok(M, N, K), "conv1x1: unsupported shape M=%lld N=%d K=%d (N, K in {64,128,256,512}, N*K <= 65536)", M, N, K);
-    DDL_REQUIRE(x && w && y && partials, "conv1x1: null pointer");
+    DDL_REQUIRE(x && w && y && (partials || b_mn), "conv1x1: null pointer");
     C1Params p;
     p.y = (bf16*)y;
     p.partials = partials;
@@ -267,14 +281,26 @@ DDL_API int ddl_conv1x1_fwd(const void* x, const void* w, void* y, float* partia
     const int smem = fixed + p.stages * kStageBytes;
     CUtensorMap tx, tw;
     if (int e = make_map(&tx, x, M, K, kTileM)) return e;
-    if (int e = make_map(&tw, w, N, K, p.n_cta)) return e;
-    static int attr_smem = 0;
-    if (smem > attr_smem) {
-        DDL_CHECK(cudaFuncSetAttribute(conv1x1_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr_smem = smem;
+    if (int e = b_mn ? make_map(&tw, w, K, N, 64) : make_map(&tw, w, N, K, p.n_cta)) return e;
+    static int attr_smem[2] = {0, 0};
+    if (smem > attr_smem[b_mn]) {
+        if (b_mn) DDL_CHECK(cudaFuncSetAttribute(conv1x1_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        else DDL_CHECK(cudaFuncSetAttribute(conv1x1_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_smem[b_mn] = smem;
     }
     dim3 grid(ddl_conv1x1_grid(M, N), col_blocks);
-    conv1x1_fwd_kernel<<<grid, kThreads, smem, (cudaStream_t)stream_>>>(tx, tw, p);
+    if (b_mn) conv1x1_fwd_kernel<true><<<grid, kThreads, smem, (cudaStream_t)stream_>>>(tx, tw, p);
+    else conv1x1_fwd_kernel<false><<<grid, kThreads, smem, (cudaStream_t)stream_>>>(tx, tw, p);
     DDL_LAUNCH_CHECK();
     return 0;
+}
+
+DDL_API int ddl_conv1x1_fwd(const void* x, const void* w, void* y, float* partials, long long M, int N, int K, void* stream_) {
+    return conv1x1_launch(false, x, w, y, partials, M, N, K, stream_);
+}
+
+// dx [M, Cin] = dy [M, Cout] . w [Cout][Cin]: the same kernel with the weight read MN-major (supported when
+// ddl_conv1x1_supported(M, Cin, Cout))
+DDL_API int ddl_conv1x1_dgrad(const void* dy, const void* w, void* dx, long long M, int Cin, int Cout, void* stream_) {
+    return conv1x1_launch(true, dy, w, dx, nullptr, M, Cin, Cout, stream_);
 }

@@ -442,36 +442,41 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_kernel(const __grid_
     }
 }
 
-// dw[k][r][s][c] (element strides sk, sr, ss, sc) = sum over splits of partial[split][(r*S + s) * C + c][k].
-// 32 x 32 tiles through shared memory: reads are contiguous in k, writes contiguous in c (channels-last weights).
+// dw[k][r][s][c] (element strides sk, sr, ss, sc) = sum over splits of partial[split][(r*S + s) * C + c][k], folded in a
+// fixed order.  A block owns (8 >> lanes_log2) rows m x 32 columns k; the 8 warps are (row, split lane): each thread sums
+// every lanes-th split of one element (4 independent accumulators, 128-byte coalesced reads along k), the lanes are then
+// folded through shared memory.  Few splits (big weight tensors): lanes = 1, 8 rows per block, 16-byte runs along c in
+// the output.  Many splits (small weight tensors, up to 148): lanes = 8, one row per block, so that the grid stays large.
 __global__ void __launch_bounds__(256) conv_wgrad_fold_kernel(const float* __restrict__ partials, int ksplit, long long Mtot, int Cout,
                                                               bf16* __restrict__ dw, int C, int S, long long sk, long long sr, long long ss,
-                                                              long long sc) {
-    __shared__ float tile[32][33];
+                                                              long long sc, int lanes_log2) {
+    __shared__ float sm[8][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const long long m0 = (long long)blockIdx.x * 32;
+    const int lanes = 1 << lanes_log2, rows = 8 >> lanes_log2;
+    const int row = ty >> lanes_log2, lane = ty & (lanes - 1);
+    const long long m = (long long)blockIdx.x * rows + row;
     const int k0 = blockIdx.y * 32;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const long long m = m0 + ty + i * 8;
-        const float* src = partials + (size_t)m * Cout + k0 + tx;
-        float a0 = 0.f, a1 = 0.f;
-        int q = 0;
-        for (; q + 1 < ksplit; q += 2) {
-            a0 += src[(size_t)q * Mtot * Cout];
-            a1 += src[(size_t)(q + 1) * Mtot * Cout];
-        }
-        if (q < ksplit) a0 += src[(size_t)q * Mtot * Cout];
-        tile[ty + i * 8][tx] = a0 + a1;
+    const size_t stride = (size_t)Mtot * Cout;
+    const float* src = partials + (size_t)m * Cout + k0 + tx;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    int q = lane;
+    for (; q + 3 * lanes < ksplit; q += 4 * lanes) {
+        a0 += src[(size_t)q * stride];
+        a1 += src[(size_t)(q + lanes) * stride];
+        a2 += src[(size_t)(q + 2 * lanes) * stride];
+        a3 += src[(size_t)(q + 3 * lanes) * stride];
     }
+    for (; q < ksplit; q += lanes) a0 += src[(size_t)q * stride];
+    sm[ty][tx] = (a0 + a1) + (a2 + a3);
     __syncthreads();
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int k = k0 + ty + i * 8;
-        const long long m = m0 + tx;
-        const int tap = (int)(m / C), c = (int)(m - (long long)tap * C);
-        const int r = tap / S, s = tap - r * S;
-        dw[k * sk + r * sr + s * ss + c * sc] = __float2bfloat16(tile[tx][ty + i * 8]);
+    if ((int)threadIdx.x < rows * 32) {
+        const int r = threadIdx.x % rows, kk = threadIdx.x / rows;  // m fastest: neighbouring threads write neighbouring c
+        float acc = 0.f;
+        for (int l = 0; l < lanes; ++l) acc += sm[r * lanes + l][kk];
+        const long long mm = (long long)blockIdx.x * rows + r;
+        const int tap = (int)(mm / C), c = (int)(mm - (long long)tap * C);
+        const int fr = tap / S, fs = tap - fr * S;
+        dw[(long long)(k0 + kk) * sk + fr * sr + fs * ss + c * sc] = __float2bfloat16(acc);
     }
 }
 
@@ -838,8 +843,10 @@ DDL_API int ddl_conv_wgrad(const void* x, const void* dy, void* dw, long long sk
     const int grid = p.nblk * p.mgroups * p.ksplit;
     conv_wgrad_kernel<<<grid, kWgThreads, smem, stream>>>(maps, p);
     DDL_LAUNCH_CHECK();
-    dim3 fgrid((unsigned)(p.Mtot / 32), (unsigned)(Cout / 32));
-    conv_wgrad_fold_kernel<<<fgrid, 256, 0, stream>>>(p.partials, p.ksplit, p.Mtot, Cout, (bf16*)dw, C, S, sk, sr, ss, sc);
+    int lanes_log2 = 0;
+    while (lanes_log2 < 3 && (4 << lanes_log2) < p.ksplit) ++lanes_log2;  // about 4 splits per lane before adding lanes
+    dim3 fgrid((unsigned)(p.Mtot / (8 >> lanes_log2)), (unsigned)(Cout / 32));
+    conv_wgrad_fold_kernel<<<fgrid, 256, 0, stream>>>(p.partials, p.ksplit, p.Mtot, Cout, (bf16*)dw, C, S, sk, sr, ss, sc, lanes_log2);
     DDL_LAUNCH_CHECK();
     return 0;
 }

@@ -133,13 +133,45 @@ class Trainer:
             self._consumed = [torch.cuda.Event() for _ in range(2)]
             self._loss_ring = torch.zeros(1024, dtype=torch.float32).pin_memory()
 
+    def _training_state(self) -> List[torch.Tensor]:
+        """Every tensor a training step mutates: parameters, optimizer state, step counters, module buffers (BatchNorm
+        statistics) and the dropout seed word."""
+        ts: List[torch.Tensor] = [b for b in self.model.buffers()]
+        if self.parallelism == "fsdp":
+            for u in self.ddp.units:
+                ts += [u.shard_param, u.master, u.exp_avg, u.exp_avg_sq]
+            ts.append(self.ddp.hyper)
+        else:
+            ts += [t for t in self.ddp.param_buffers if t is not None]
+            ts += self.opt.master + self.opt.exp_avg + self.opt.exp_avg_sq + [self.opt.hyper]
+        if self.fused:
+            from .ops import functional as OF
+
+            ts.append(OF.seed_word(self.device))
+        return ts
+
     def _capture(self) -> None:
+        # The warm-up steps before capture (allocator / autotune / lazy-init warm-up) run real optimizer steps on the
+        # first batch; their effect is rolled back so that a graphed run takes exactly the steps an eager run takes.
+        state = self._training_state()
+        snap = [t.detach().clone() for t in state]
+        py_step = getattr(self.opt, "_step", None)
         s = torch.cuda.Stream(self.device)
         s.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(s):
             for _ in range(self.graph_warmup):
                 self._step_impl(self.static_batch)
         torch.cuda.current_stream(self.device).wait_stream(s)
+        torch.cuda.synchronize(self.device)
+        with torch.no_grad():
+            for t, c in zip(state, snap):
+                t.copy_(c)
+        if py_step is not None:
+            self.opt._step = py_step
+        if self.parallelism == "fsdp":
+            for u in self.ddp.units:
+                u.gathered = False
+        del snap
         torch.cuda.synchronize(self.device)
         pg.barrier()
         self.graph = torch.cuda.CUDAGraph()
@@ -178,8 +210,26 @@ class Trainer:
         self.steps_done += 1
         return loss
 
-    def prefetch_hint(self) -> None:
-        """(reserved) hook for loaders that want to start the next copy early."""
+    # ---- checkpoints --------------------------------------------------------------------------
+    def save_checkpoint(self, path: str, extra: Optional[Dict[str, Any]] = None):
+        """Rank-0 ``state_dict`` checkpoint with optimizer state and step (collective under FSDP)."""
+        from .utils.checkpoint import save_checkpoint
+
+        if self.cuda:
+            torch.cuda.synchronize(self.device)
+        return save_checkpoint(path, self.ddp, self.opt, step=self.steps_done, extra=extra)
+
+    def load_checkpoint(self, path: str, strict: bool = True, with_optimizer: bool = True) -> Dict[str, Any]:
+        """Load weights (+ optimizer state and step when present and wanted) into the live trainer.  A weights-only
+        load keeps the moments but re-seeds the fp32 masters from the loaded values."""
+        from .utils.checkpoint import load_checkpoint
+
+        meta = load_checkpoint(path, self.ddp, self.opt if with_optimizer else None, strict=strict)
+        if with_optimizer:
+            self.steps_done = int(meta.get("step", self.steps_done))
+        if self.cuda:
+            torch.cuda.synchronize(self.device)
+        return meta
 
     def loss_history(self, last: int = 1) -> List[float]:
         """Host values of the last ``last`` losses (synchronises)."""

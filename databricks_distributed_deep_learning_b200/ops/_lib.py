@@ -82,6 +82,7 @@ _PROTOS = {
     "ddl_conv1x1_supported": ([_ll, _i, _i], _i),
     "ddl_conv1x1_grid": ([_ll, _i], _i),
     "ddl_conv1x1_fwd": ([_vp, _vp, _vp, _vp, _ll, _i, _i, _vp], _i),
+    "ddl_conv1x1_dgrad": ([_vp, _vp, _vp, _ll, _i, _i, _vp], _i),
     "ddl_conv_supported": ([_i] * 9, _i),
     "ddl_conv_fwd_groups": ([_i] * 9, _i),
     "ddl_conv_fwd": ([_vp, _vp, _vp, _vp] + [_i] * 9 + [_vp], _i),
@@ -89,6 +90,7 @@ _PROTOS = {
     "ddl_conv_wgrad_scratch_bytes": ([_i] * 9, _sz),
     "ddl_conv_wgrad": ([_vp, _vp, _vp, _ll, _ll, _ll, _ll, _vp, _sz] + [_i] * 9 + [_vp], _i),
     "ddl_conv_set_tuning": ([_i], _i),
+    "ddl_probe_umma_shift": ([_vp, _vp, _vp, _i, _i, _i, _vp], _i),
     "ddl_embed_bwd_scratch_bytes": ([_i, _i], _sz),
     "ddl_embed_bwd": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i, _i, _i, _i, _i, _i, _vp], _i),
     "ddl_attention_fwd": ([_vp, _vp, _vp, _vp, _i, _i, _i, _f, _u64, _vp, _vp], _i),

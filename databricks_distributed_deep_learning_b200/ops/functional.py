@@ -660,7 +660,12 @@ class _ConvNative(torch.autograd.Function):
         dx = dw = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty_like(x, memory_format=torch.channels_last)
-            L.call("ddl_conv_dgrad", dy.data_ptr(), _weight_krsc(weight).data_ptr(), dx.data_ptr(), *geom, st)
+            Nb, H, W, C, Cout, R, S, stride, pad = geom
+            if _CONV1X1_WS and R == 1 and stride == 1 and L.lib().ddl_conv1x1_supported(Nb * H * W, C, Cout):
+                # skinny 1x1 layer: weight-stationary kernel with the weight read MN-major
+                L.call("ddl_conv1x1_dgrad", dy.data_ptr(), _weight_krsc(weight).data_ptr(), dx.data_ptr(), Nb * H * W, C, Cout, st)
+            else:
+                L.call("ddl_conv_dgrad", dy.data_ptr(), _weight_krsc(weight).data_ptr(), dx.data_ptr(), *geom, st)
         if ctx.needs_input_grad[1]:
             dw = torch.empty_like(weight)
             if not dw.is_non_overlapping_and_dense():

@@ -12,7 +12,7 @@ BASELINE.json:7) the same update runs as plain tensor ops.
 """
 from __future__ import annotations
 
-from typing import Any, Dict, List
+from typing import Any, Dict, List, Optional
 
 import torch
 
@@ -44,6 +44,22 @@ class FusedAdamW:
         if overlap:
             ddp.on_bucket_reduced = self._step_bucket
         self._cpu_step = 1
+        # weights loaded into the wrapped module later (load_checkpoint / load_safetensors without optimizer state)
+        # must also replace the fp32 masters, otherwise the next step rewrites the parameters from the stale ones
+        ddp.register_param_listener(self.resync_master)
+
+    @torch.no_grad()
+    def resync_master(self, state: Optional[Dict[str, torch.Tensor]] = None) -> None:
+        """Rebuild the fp32 master copy from the current parameters.  ``state`` (name -> tensor, e.g. the fp32 state
+        dict that was just loaded) supplies full-precision values where available; moments and step are kept."""
+        names = {p: n for n, p in self.ddp.module.named_parameters()}
+        for b, w, flat_p in zip(self.ddp.buckets, self.master, self.ddp.param_buffers):
+            w.copy_(flat_p.float())
+            if state:
+                for p, off in zip(b.params, b.offsets):
+                    src = state.get(names.get(p, ""))
+                    if src is not None and src.shape == p.shape and src.dtype == torch.float32:
+                        flat_view(w, off, p).copy_(src)
 
     # ---- hyper-parameters (device resident) -------------------------------------------
     def set_lr(self, lr: float) -> None:

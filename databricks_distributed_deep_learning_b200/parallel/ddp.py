@@ -23,6 +23,7 @@ What is different (B200-first):
 """
 from __future__ import annotations
 
+import weakref
 from contextlib import contextmanager
 from typing import Callable, Dict, Iterable, List, Optional
 
@@ -168,6 +169,11 @@ class DistributedDataParallel(nn.Module):
         self._callback_queued = False
         self._grads_detached = False  # True after zero_grad(set_to_none=True): buckets are not pre-zeroed
         self._comm_stream = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" else None
+        self._next_bucket = 0  # buckets are launched strictly in index order (see _grad_ready)
+        self._param_listeners: List[Callable] = []
+        # lets checkpoint loaders that only see the bare module find the wrapper (utils/checkpoint.py); a plain
+        # attribute on the module object, not a submodule / parameter / buffer, so state_dict() is unaffected
+        object.__setattr__(module, "_ddl_wrapper", weakref.ref(self))
 
         self.buckets = assign_buckets(
             params,
@@ -248,6 +254,16 @@ class DistributedDataParallel(nn.Module):
             b.launched = False
             b.handle = None
         self._callback_queued = False
+        self._next_bucket = 0
+
+    # ------------------------------------------------------------------ weights changed behind the optimizer's back
+    def register_param_listener(self, fn: Callable) -> None:
+        """``fn(state_or_None)`` runs after parameters were overwritten from outside (checkpoint load)."""
+        self._param_listeners.append(fn)
+
+    def notify_params_changed(self, state=None) -> None:
+        for fn in self._param_listeners:
+            fn(state)
 
     def _make_hook(self, p: nn.Parameter):
         def hook(param: nn.Parameter):
@@ -265,8 +281,17 @@ class DistributedDataParallel(nn.Module):
             torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
             self._callback_queued = True
         b.pending -= 1
-        if b.pending == 0 and not b.launched:
-            self._launch_bucket(b)
+        # Launch in index order only, as the stock reducer does.  The peer-memory kernels pair up across ranks by
+        # per-block epoch counters, not by message identity: if two ranks finished buckets in a different order
+        # (rank-dependent control flow, unused parameters) kernels of DIFFERENT buckets would meet.  A bucket that
+        # completes early waits (pending == 0) until every lower index has been launched.
+        while self._next_bucket < len(self.buckets):
+            nb = self.buckets[self._next_bucket]
+            if nb.pending != 0:
+                break
+            if not nb.launched:
+                self._launch_bucket(nb)
+            self._next_bucket += 1
 
     @torch.no_grad()
     def _gather_grads(self, b: GradBucket) -> None:

@@ -165,6 +165,7 @@ class FullyShardedDataParallel(nn.Module):
                 u.gathered_event = torch.cuda.Event()
         self._install_hooks(names)
         self._callback_queued = False
+        self._next_unit = len(self.units) - 1
         self._grads_detached = False
 
     # ------------------------------------------------------------------ plumbing
@@ -201,8 +202,6 @@ class FullyShardedDataParallel(nn.Module):
             torch.cuda.current_stream(self.device).wait_event(u.gathered_event)
 
     def _pre_forward(self, u: _Unit) -> None:
-        if not torch.is_grad_enabled() and not self.training:
-            pass
         self._launch_gather(u)
         self._wait_gather(u)
         if self.prefetch and u.index + 1 < len(self.units):
@@ -225,6 +224,7 @@ class FullyShardedDataParallel(nn.Module):
             u.reduced = False
             u.pending = len(u.params)
         self._callback_queued = False
+        self._next_unit = len(self.units) - 1
         root = self.units[0] if self.units and self.units[0].name == "<root>" else None
         if root is not None:
             self._launch_gather(root)
@@ -243,8 +243,15 @@ class FullyShardedDataParallel(nn.Module):
             torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
             self._callback_queued = True
         u.pending -= 1
-        if u.pending == 0 and not u.reduced:
-            self._reduce_and_update(u)
+        # Reduce units strictly in backward order (highest index first), whatever order their hooks fired in: the
+        # peer-memory kernels of different ranks pair up by launch order, not by unit identity.
+        while self._next_unit >= 0:
+            nu = self.units[self._next_unit]
+            if nu.pending != 0:
+                break
+            if not nu.reduced:
+                self._reduce_and_update(nu)
+            self._next_unit -= 1
 
     @torch.no_grad()
     def _gather_grads(self, u: _Unit) -> None:
@@ -293,7 +300,7 @@ class FullyShardedDataParallel(nn.Module):
 
     def _finalize_backward(self) -> None:
         self._callback_queued = False
-        for u in self.units:
+        for u in reversed(self.units):
             if not u.reduced:
                 self._reduce_and_update(u)
         if self.cuda:
@@ -372,14 +379,83 @@ class FullyShardedDataParallel(nn.Module):
 
     @torch.no_grad()
     def load_full_state_dict(self, state: Dict[str, torch.Tensor], strict: bool = True):
-        """Every rank passes the same full state dict; each keeps its own shard."""
-        self.gather_all()
+        """Every rank passes the same full state dict; each keeps its own shard (compute-dtype shard + fp32 master;
+        the master takes full-precision values from ``state`` where it has them).  Works unit by unit on private
+        temporaries, so it is also correct when the units share their full-parameter storage
+        (``reshard_after_forward``)."""
+        names = {p: n for n, p in self.module.named_parameters()}
+        saved, tmps = [], []
+        for u in self.units:
+            tmp = torch.empty(u.padded, dtype=self.dtype, device=self.device)
+            self.comm.all_gather_into(tmp, u.shard_param).wait()  # current values: what a non-strict load keeps
+            tmps.append(tmp)
+            for p, off in zip(u.params, u.offsets):
+                saved.append((p, p.data))
+                p.data = flat_view(tmp, off, p)
+        if self.cuda:
+            torch.cuda.synchronize(self.device)
         res = self.module.load_state_dict(state, strict=strict)
+        for u, tmp in zip(self.units, tmps):
+            lo = self.rank * u.shard_numel
+            full32 = tmp.float()
+            for p, off in zip(u.params, u.offsets):
+                src = state.get(names.get(p, ""))
+                if src is not None and src.dtype == torch.float32 and src.shape == p.shape:
+                    flat_view(full32, off, p).copy_(src)
+            u.shard_param.copy_(tmp[lo : lo + u.shard_numel])
+            u.master.copy_(full32[lo : lo + u.shard_numel])
+            u.gathered = False
+        for p, d in saved:
+            p.data = d
+        if not self.reshard_after_forward:
+            self.gather_all()  # private full buffers: make them current right away (eval without a forward hook)
+        return res
+
+    # ---- optimizer state (the wrapper is its own optimizer) ------------------------------------
+    def _gather_fp32(self, shard: torch.Tensor, padded: int) -> torch.Tensor:
+        """All ranks' fp32 shards -> one full vector (checkpoint path: control-plane collective, not the peer kernels)."""
+        import torch.distributed as dist
+
+        if self.world_size == 1:
+            return shard.clone()
+        full = torch.empty(padded, dtype=torch.float32, device=shard.device)
+        dist.all_gather_into_tensor(full, shard.contiguous())
+        return full
+
+    @torch.no_grad()
+    def optim_state_dict(self) -> Dict[str, object]:
+        """Collective: every rank calls.  Full (unsharded) AdamW state keyed by parameter NAME - fp32 master weights,
+        both moments - plus the step counter, so a checkpoint moves between world sizes and between FSDP and DDP
+        runs.  (``state_dict()`` of this wrapper is the module's, as for any ``nn.Module``.)"""
+        names = {p: n for n, p in self.module.named_parameters()}
+        state: Dict[str, Dict[str, torch.Tensor]] = {}
+        for u in self.units:
+            fulls = {k: self._gather_fp32(getattr(u, k), u.padded) for k in ("master", "exp_avg", "exp_avg_sq")}
+            for p, off in zip(u.params, u.offsets):
+                state[names[p]] = {k: flat_view(v, off, p).cpu().contiguous().clone() for k, v in fulls.items()}
+        return {"state": state, "step": float(self.hyper[5].item()), "defaults": dict(self.defaults), "format": "fsdp/by-name/v1"}
+
+    @torch.no_grad()
+    def load_optim_state_dict(self, sd: Dict[str, object]) -> None:
+        """Every rank passes the same dict (from :meth:`optim_state_dict`); each keeps its shard.  Also rewrites the
+        compute-dtype parameter shard from the restored master."""
+        names = {p: n for n, p in self.module.named_parameters()}
+        st = sd["state"]
         for u in self.units:
             lo = self.rank * u.shard_numel
-            u.shard_param.copy_(u.full_param[lo : lo + u.shard_numel])
-            u.master.copy_(u.full_param[lo : lo + u.shard_numel].float())
-        return res
+            for key in ("master", "exp_avg", "exp_avg_sq"):
+                full = torch.zeros(u.padded, dtype=torch.float32, device=self.device)
+                for p, off in zip(u.params, u.offsets):
+                    flat_view(full, off, p).copy_(st[names[p]][key])
+                getattr(u, key).copy_(full[lo : lo + u.shard_numel])
+            u.shard_param.copy_(u.master)
+            u.gathered = False
+        self.defaults.update(sd.get("defaults", {}))
+        d = self.defaults
+        self.hyper.copy_(torch.tensor([d["lr"], d["betas"][0], d["betas"][1], d["eps"], d["weight_decay"], sd["step"], 0.0, 0.0]))
+        self._step = int(sd["step"])
+        if not self.reshard_after_forward:
+            self.gather_all()
 
     def extra_repr(self) -> str:
         return f"world_size={self.world_size}, units={len(self.units)}, comm={self.comm.name}, reshard_after_forward={self.reshard_after_forward}"

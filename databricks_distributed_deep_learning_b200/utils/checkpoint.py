@@ -29,6 +29,26 @@ from ..parallel import process_group as pg
 _PREFIX = "module."
 
 
+def _optimizer_state(optimizer: Any):
+    """FSDP wrappers are their own optimizer (and an nn.Module): their optimizer state has its own method."""
+    if hasattr(optimizer, "optim_state_dict"):
+        return optimizer.optim_state_dict()  # collective
+    return optimizer.state_dict()
+
+
+def _notify_weights_loaded(model: nn.Module, state: Dict[str, torch.Tensor]) -> None:
+    """Weights were written into a module that a DDP wrapper + FusedAdamW may already own: refresh the fp32 masters."""
+    seen = set()
+    for m in (model, unwrap(model)):
+        w = m if hasattr(m, "notify_params_changed") else None
+        if w is None:
+            ref = getattr(m, "_ddl_wrapper", None)
+            w = ref() if ref is not None else None
+        if w is not None and id(w) not in seen:
+            seen.add(id(w))
+            w.notify_params_changed(state)
+
+
 def unwrap(model: nn.Module) -> nn.Module:
     """Return the user's module from under DDP/FSDP wrappers."""
     seen = 0
@@ -72,11 +92,12 @@ def save_checkpoint(
 ) -> Optional[str]:
     """Write a torch ``state_dict`` checkpoint from rank 0; all ranks synchronise after."""
     state = model_state_dict(model)  # collective for FSDP: every rank must call
+    opt_state = _optimizer_state(optimizer) if optimizer is not None else None  # collective for FSDP as well
     wrote = None
     if not rank0_only or pg.rank() == 0:
         blob = {
             "model": {k: v.detach().to("cpu") for k, v in state.items()},
-            "optimizer": optimizer.state_dict() if optimizer is not None else None,
+            "optimizer": opt_state,
             "step": int(step),
             "extra": extra or {},
             "format": "b200-ddl/state_dict/v1",
@@ -108,7 +129,13 @@ def load_checkpoint(
     else:
         target.load_state_dict(state, strict=strict)
     if optimizer is not None and isinstance(blob, dict) and blob.get("optimizer") is not None:
-        optimizer.load_state_dict(blob["optimizer"])
+        if hasattr(optimizer, "load_optim_state_dict"):
+            optimizer.load_optim_state_dict(blob["optimizer"])
+        else:
+            optimizer.load_state_dict(blob["optimizer"])
+    else:
+        # weights only: a live optimizer keeps its moments but must take the loaded values as its masters
+        _notify_weights_loaded(model, state)
     meta = {"step": 0, "extra": {}}
     if isinstance(blob, dict):
         meta["step"] = int(blob.get("step", 0))
@@ -139,8 +166,10 @@ def load_safetensors(path: str, model: nn.Module, strict: bool = True, device: s
 
     state = strip_prefix(load_file(path, device=device))
     if hasattr(model, "load_full_state_dict"):
-        return model.load_full_state_dict(state, strict=strict)
-    return unwrap(model).load_state_dict(state, strict=strict)
+        return model.load_full_state_dict(state, strict=strict)  # refreshes its own master shards
+    res = unwrap(model).load_state_dict(state, strict=strict)
+    _notify_weights_loaded(model, state)
+    return res
 
 
 def save_pretrained(directory: str, model: nn.Module, config: Optional[Dict[str, Any]] = None) -> None:

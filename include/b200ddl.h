@@ -210,6 +210,9 @@ int ddl_stem_conv_wgrad(const void* z, const void* dy, void* dw, long long sk, l
 int ddl_conv1x1_supported(long long M, int N, int K);
 int ddl_conv1x1_grid(long long M, int N);
 int ddl_conv1x1_fwd(const void* x, const void* w, void* y, float* partials, long long M, int N, int K, void* stream);
+/* data gradient of the same layers, same kernel with w [Cout][Cin] read MN-major: dx [M, Cin] = dy [M, Cout] . w
+ * (supported when ddl_conv1x1_supported(M, Cin, Cout)) */
+int ddl_conv1x1_dgrad(const void* dy, const void* w, void* dx, long long M, int Cin, int Cout, void* stream);
 
 /* ---- 1x1 / 3x3 convolutions as implicit GEMMs on tcgen05 (csrc/conv_igemm.cu), K9 -----------------------------
  * NHWC bf16 activations, channels-last weights [Cout][R][S][C]; R = S in {1 (pad 0), 3 (pad 1)}, stride 1 or 2 (even H, W),

@@ -151,3 +151,49 @@ def single_process_bert_tiny(steps, world):
         opt.step()
     sd = model.state_dict()
     return torch.cat([sd[k].reshape(-1).float() for k in sorted(sd)])
+
+
+def w_fsdp_resume(reshard):
+    """FSDP over gloo, world 2: (a) save after 2 steps, load into a fresh wrapper, 2 more steps == 4 uninterrupted steps;
+    (b) load_full_state_dict reproduces the loaded weights on every unit, also with shared full-parameter buffers."""
+    import os
+    import tempfile
+
+    from databricks_distributed_deep_learning_b200.models import bert_tiny
+    from databricks_distributed_deep_learning_b200.parallel import process_group as pg
+    from databricks_distributed_deep_learning_b200.parallel.fsdp import FullyShardedDataParallel
+    from databricks_distributed_deep_learning_b200.utils import checkpoint as ck
+    from databricks_distributed_deep_learning_b200.utils.data import SyntheticTokenLoader
+
+    torch.set_num_threads(2)
+    rank, world = pg.rank(), pg.world_size()
+
+    def make(seed):
+        torch.manual_seed(seed)
+        return FullyShardedDataParallel(bert_tiny(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0), lr=1e-3,
+                                        weight_decay=0.01, reshard_after_forward=reshard)
+
+    def run(f, batches):
+        for batch in batches:
+            f.zero_grad()
+            f(**batch)[0].backward()
+            f.step()
+
+    batches = list(SyntheticTokenLoader(4, seq_len=16, vocab_size=512, rank=rank, world_size=world, seed=2, steps=4, pin_memory=False, pool=4))
+    ref = make(7)
+    run(ref, batches)
+    a = make(7)
+    run(a, batches[:2])
+    path = pg.broadcast_object(os.path.join(tempfile.mkdtemp(), "fsdp.pt") if rank == 0 else None)
+    ck.save_checkpoint(path, a, a, step=2)
+    b = make(11)
+    ck.load_checkpoint(path, b, b)
+    run(b, batches[2:])
+    sr, sb = ref.full_state_dict(), b.full_state_dict()
+    resume_err = max(float((sr[k].float() - sb[k].float()).abs().max()) for k in sr)
+    c = make(13)
+    c.load_full_state_dict(sr)
+    sc = c.full_state_dict()
+    load_err = max(float((sr[k].float() - sc[k].float()).abs().max()) for k in sr)
+    errs = pg.all_gather_object((resume_err, load_err))
+    return {"resume_err": max(e[0] for e in errs), "load_err": max(e[1] for e in errs)}

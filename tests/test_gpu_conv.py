@@ -50,6 +50,15 @@ def conv_case(N, cin, hw, cout, k, stride, seed=0):
     def rel(a, b):
         return ((a.float() - b).abs().max() / b.abs().max().clamp_min(1e-6)).item()
 
+    extra = {}
+    M = N * hw * hw
+    if k == 1 and stride == 1 and lib.ddl_conv1x1_supported(M, cin, cout):
+        # weight-stationary kernel (csrc/conv1x1.cu) in its data-gradient mode
+        dx2 = torch.full((N, cin, hw, hw), float("nan"), dtype=bf, device="cuda").contiguous(memory_format=cl)
+        L.call("ddl_conv1x1_dgrad", dy.data_ptr(), w.data_ptr(), dx2.data_ptr(), M, cin, cout, st)
+        torch.cuda.synchronize()
+        extra["ws_dgrad"] = rel(dx2, xr.grad)
+
     sums = part.view(-1, 2, cout).sum(0)
     yf = y.float()
     return {
@@ -58,6 +67,7 @@ def conv_case(N, cin, hw, cout, k, stride, seed=0):
         "wgrad": rel(dw, wr.grad),
         "sum": ((sums[0] - yf.sum((0, 2, 3))).abs().max() / yf.sum((0, 2, 3)).abs().max().clamp_min(1.0)).item(),
         "sumsq": ((sums[1] - yf.square().sum((0, 2, 3))).abs().max() / yf.square().sum((0, 2, 3)).abs().max()).item(),
+        **extra,
     }
 
 
@@ -67,6 +77,7 @@ def _check(errs):
     assert errs["dgrad"] < 8e-3, errs
     assert errs["wgrad"] < 8e-3, errs
     assert errs["sum"] < 2e-3 and errs["sumsq"] < 2e-3, errs
+    assert errs.get("ws_dgrad", 0.0) < 8e-3, errs
 
 
 @pytest.mark.parametrize("cin,hw,cout,k,stride", RESNET50_CONVS)
