@@ -866,6 +866,21 @@ int launch_2sm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p
     return 0;
 }
 
+// TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory
+// hung the GPU.  The CTA-pair kernel (cp.async.bulk.tensor ... cta_group::2) and the cluster kernel (multicast::cluster)
+// are therefore only chosen when both operands are allocations of the current device; anything else (a peer mapping, an
+// IPC import, host memory) takes the one-CTA kernel, whose loads are plain unicast TMA.
+bool operand_is_local(const void* ptr) {
+    cudaPointerAttributes attr;
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) return false;
+    if (cudaPointerGetAttributes(&attr, ptr) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return false;
+    }
+    return attr.type == cudaMemoryTypeDevice && attr.device == dev;
+}
+
 int g_sm_count = 0;
 int g_two_sm = 1;  // use the cta_group::2 kernel for BN = 256 problems with >= 2 row blocks (measured fastest)
 int g_force_cluster = 0;  // 0 = auto, 1 or 2 = forced (benchmarks)
@@ -917,7 +932,8 @@ DDL_API int ddl_gemm_bf16_ex(const void* A, int a_mn, long long lda, const void*
     // K-major operand [R=M|N, K]: box 64 (K) x BM|BN rows.  MN-major operand stored [K, M|N]: box 64 (MN) x 64 (K) rows.
     if (int e = a_mn ? make_map(&ta, A, K, M, lda, BK) : make_map(&ta, A, M, K, lda, BM)) return e;
     if (int e = b_mn ? make_map(&tb, B, K, N, ldb, BK) : make_map(&tb, B, N, K, ldb, BN)) return e;
-    if (g_two_sm && BN == 256 && p.num_m_blocks >= 2) {
+    const bool local_ops = operand_is_local(A) && operand_is_local(B);
+    if (g_two_sm && BN == 256 && p.num_m_blocks >= 2 && local_ops) {
         // CTA pairs: 256 x 256 tiles, half-height B boxes (K-major) / 64 x 64 boxes (MN-major)
         CUtensorMap tb2 = tb;
         if (!b_mn) {
@@ -933,7 +949,7 @@ DDL_API int ddl_gemm_bf16_ex(const void* A, int a_mn, long long lda, const void*
         return launch_2sm<true, false>(ta, tb2, p, grid2, s2);
     }
     // B shared by a 2-CTA cluster (multicast) whenever there are at least two row blocks
-    const int cluster = (g_force_cluster == 2 && p.num_m_blocks >= 2) ? 2 : 1;  // multicast sharing measured no faster than 1 CTA
+    const int cluster = (g_force_cluster == 2 && p.num_m_blocks >= 2 && local_ops) ? 2 : 1;  // multicast sharing measured no faster than 1 CTA
     CUtensorMap tbh = tb;
     if (cluster == 2 && !b_mn) {
         if (int e = make_map(&tbh, B, N, K, ldb, BN / 2)) return e;  // half-height box for the K-major B tile
