@@ -5,38 +5,49 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
         --master-port P bench.py --gpus N --steps K --warmup W
 
-Arms (``--impl``):
-  ours       this framework: Trainer -> DDP wrapper with peer-memory all-reduce, native
-             BN/LN/CE/AdamW (+GEMM/attention) kernels, whole-step CUDA graph.
-  stock      stock PyTorch: torchvision/HF-shaped model, torch DDP + NCCL, autocast bf16,
-             torch.optim.AdamW(fused=True) - the baseline BASELINE.md section 4 asks us to measure.
-  reference  the unmodified upstream repository from baseline/_ref.  It is a single
-             CPU-inference notebook that needs network downloads and onnxruntime/openvino
-             and has no setup.py, so this arm reports "unavailable" (see DESIGN.md).
+One invocation measures the WHOLE metric of BASELINE.json:2 ("ResNet-50 img/s & BERT seq/s"): every workload
+(``--workload all``: resnet50 BASELINE.json:8, bert-base :9, bert-large/FSDP :10) on every arm (``--impl all``):
 
-Workloads (``--workload``): resnet50 (default, BASELINE.json:8), bert-base (BASELINE.json:9),
-bert-large (BASELINE.json:10, FSDP).  Synthetic data, random-init weights.
+  ours           this framework: Trainer -> DDP / FSDP wrapper with peer-memory collectives, native convolution /
+                 BN / LN / CE / AdamW / GEMM / attention kernels, whole-step CUDA graph.
+  stock          stock PyTorch on the same box: torchvision / HF-shaped model, torch DDP (FSDP2 for bert-large) +
+                 NCCL, cuBLAS / cuDNN, autocast bf16, torch.optim.AdamW(fused=True), eager - the baseline
+                 BASELINE.md section 4 asks for.
+  stock-graphed  the same stock model with the whole step (forward, backward, AdamW) captured in one CUDA graph, so that
+                 the launch-overhead share of ours/stock is visible separately from the kernel share.  One GPU only
+                 (capturing NCCL inside stock DDP is not attempted: a failed capture on one rank would hang the others).
+  reference      the unmodified upstream repository from baseline/_ref.  It is a single CPU-inference notebook that
+                 needs network downloads and onnxruntime/openvino and has no setup.py, so this arm reports
+                 "unavailable" (see DESIGN.md section 3).
 
-Timing: W >= 3 untimed warm-up steps, then exactly K steps between barrier +
-``torch.cuda.synchronize()`` on both sides, CUDA events on the launching stream, max over
-ranks.  ``value`` is the device-resident number (inputs already on the GPU); ``e2e`` repeats
-the measurement through ``Trainer.step`` with a pinned-host -> device copy of every batch and
-a device -> host copy of every loss inside the timed region.
+stdout carries exactly ONE JSON line: the headline (ResNet-50, ours) with ``vs_baseline`` = ours / stock end-to-end
+throughput measured in this same run (BASELINE.json has no published number) and an ``extra`` block with every other
+(workload, arm) result, its end-to-end number, ratio, clocks and peak memory.  One JSON line per (workload, arm) also
+goes to stderr as it is measured.
+
+Timing: W >= 3 untimed warm-up steps, then exactly K steps between barrier + ``torch.cuda.synchronize()`` on both
+sides, CUDA events on the launching stream, max over ranks.  ``value`` is the device-resident number (inputs already on
+the GPU); ``e2e`` repeats the measurement through the public API (``Trainer.step``) with a pinned-host -> device copy of
+every batch and a device -> host copy of every loss inside the timed region.
 """
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
 import sys
 import time
+import traceback
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 KERNELS_PER_CALL = {"ddl_bn_act_fwd_train": 3, "ddl_bn_act_fwd_train_mask": 3, "ddl_bn_act_fwd_eval": 2, "ddl_bn_act_bwd": 3,
                     "ddl_bn_act_bwd_ex": 3, "ddl_embed_bwd": 4, "ddl_bn_act_fwd_train_from_partials": 2, "ddl_stem_conv_fwd": 2, "ddl_stem_conv_wgrad": 2, "ddl_layernorm_bwd": 2,
-                    "ddl_cross_entropy": 2, "ddl_colsum_bf16": 2, "ddl_attention_bwd": 2}
+                    "ddl_cross_entropy": 2, "ddl_colsum_bf16": 2, "ddl_attention_bwd": 2, "ddl_conv_wgrad": 2}
+ALL_WORKLOADS = ["resnet50", "bert-base", "bert-large"]
+ALL_IMPLS = ["ours", "stock", "stock-graphed"]
 
 
 def parse():
@@ -44,13 +55,14 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="ours", choices=["ours", "stock", "reference"])
-    ap.add_argument("--workload", default="resnet50", choices=["resnet50", "bert-base", "bert-large"])
+    ap.add_argument("--impl", default="all", choices=["all", "ours", "stock", "stock-graphed", "reference"])
+    ap.add_argument("--workload", default="all", choices=["all"] + ALL_WORKLOADS)
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (0 = workload default)")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--comm", default="auto")
     ap.add_argument("--bucket-mb", type=float, default=25.0)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--reshard", action="store_true", help="FSDP: share the full-parameter buffers (reshard after forward)")
     ap.add_argument("--dropout", type=float, default=None, help="override BERT dropout (default: HF's 0.1)")
     return ap.parse_args()
 
@@ -81,47 +93,36 @@ def to_device(batch, device):
     return tuple(v.to(device, non_blocking=True) for v in batch)
 
 
-def main():
-    args = parse()
-    if args.impl == "reference":
-        return reference_arm(args)
+def heap_bytes(device):
+    """Bytes handed out by the symmetric heap (invisible to torch's allocator statistics with the IPC provider)."""
+    try:
+        from databricks_distributed_deep_learning_b200.parallel import symm
 
+        h = symm._HEAPS.get((device.type, device.index))
+        return int(sum(s.used for s in h.slabs)) if h is not None else 0
+    except Exception:
+        return 0
+
+
+def measure(args, workload, impl, device, rank, world):
+    """One (workload, arm): device-resident and end-to-end throughput.  Returns the result dict (same on every rank)."""
     import torch
 
     from databricks_distributed_deep_learning_b200.config import get_workload
     from databricks_distributed_deep_learning_b200.parallel import process_group as pg
     from databricks_distributed_deep_learning_b200.utils.timing import ClockSampler
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:
-            # convenience: re-launch ourselves under torchrun
-            import subprocess
-
-            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
-                   "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 1000), os.path.abspath(__file__)] + sys.argv[1:]
-            return subprocess.call(cmd)
-        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device (run it through gpurun)")
-    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-    os.environ.setdefault("MASTER_PORT", "29533")
-    device = pg.init_process_group(use_gpu=True)
-    rank = pg.rank()
-    torch.backends.cudnn.benchmark = True
-    torch.backends.cuda.matmul.allow_tf32 = True
-    torch.backends.cudnn.allow_tf32 = True
-
-    wl = get_workload(args.workload)
+    wl = get_workload(workload)
     batch = args.batch or wl.per_gpu_batch
-    loader = build_batches(args.workload, batch, rank, world)
+    loader = build_batches(workload, batch, rank, world)
     host_batches = list(b for _, b in zip(range(loader.pool), loader))
     K, W = args.steps, max(3, args.warmup)
-
-    if args.impl == "ours":
-        runner = OursRunner(args, wl, device)
+    torch.cuda.reset_peak_memory_stats(device)
+    heap0 = heap_bytes(device)
+    if impl == "ours":
+        runner = OursRunner(args, wl, workload, device)
     else:
-        runner = StockRunner(args, wl, device)
+        runner = StockRunner(args, wl, workload, device, graphed=(impl == "stock-graphed"))
 
     def timed(fn, n):
         pg.barrier()
@@ -164,90 +165,177 @@ def main():
             "h2d_bytes_per_step": int(loader.bytes_per_batch),
             "d2h_bytes_per_step": 4,
         }
+    peak = torch.cuda.max_memory_allocated(device) + (heap_bytes(device) - heap0)
+    value = batch * world * K / (ms / 1e3)
+    out = {
+        "metric": f"{workload} training throughput ({wl.unit}), device-timed, max over ranks",
+        "value": round(value, 2), "unit": wl.unit, "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": round(ms / K, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic (random-init weights, synthetic in-memory batches)",
+        "impl": impl,
+        "config": {"model": workload, "global_batch": batch * world, "per_gpu_batch": batch,
+                   "seq_len": wl.seq_len, "image_size": wl.image_size,
+                   "parallelism": f"{'fsdp' if wl.parallelism == 'fsdp' else 'dp'}{world}",
+                   "optimizer": "AdamW", "cuda_graph": runner.graphed,
+                   "l2_policy": "per-step activations and inputs exceed the 126 MB L2 (no explicit flush)",
+                   "comm": runner.comm_name, "bucket_cap_mb": args.bucket_mb, **runner.extra_config()},
+        "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"),
+                   "reasons": clocks.get("reasons", [])},
+        "e2e": e2e, "gpu_launches": int(launches), "final_loss": final_loss,
+        "peak_mem_gb": round(peak / 2**30, 2),
+        "wall_s_timed_region": round(wall, 3),
+    }
+    runner.close()
+    del runner, dev_batches
+    gc.collect()
+    torch.cuda.empty_cache()
+    return out
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import torch
+
+    from databricks_distributed_deep_learning_b200.parallel import process_group as pg
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            # convenience: re-launch ourselves under torchrun
+            import subprocess
+
+            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+                   "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 1000), os.path.abspath(__file__)] + sys.argv[1:]
+            return subprocess.call(cmd)
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (run it through gpurun)")
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29533")
+    device = pg.init_process_group(use_gpu=True)
+    rank = pg.rank()
+    torch.backends.cudnn.benchmark = True
+    torch.backends.cuda.matmul.allow_tf32 = True
+    torch.backends.cudnn.allow_tf32 = True
+
+    workloads = ALL_WORKLOADS if args.workload == "all" else [args.workload]
+    impls = ALL_IMPLS if args.impl == "all" else [args.impl]
+    results = {}
+    for wl in workloads:
+        for impl in impls:
+            key = f"{wl}/{impl}"
+            if impl == "stock-graphed" and world > 1:
+                results[key] = {"skipped": "stock-graphed is a one-GPU arm (see the module docstring)"}
+                continue
+            try:
+                results[key] = measure(args, wl, impl, device, rank, world)
+            except Exception as e:  # noqa: BLE001 - an arm that cannot run is reported, the others still count
+                if impl == "ours":
+                    raise  # the product arm must never fail silently
+                results[key] = {"error": f"{type(e).__name__}: {e}", "trace": traceback.format_exc(limit=3)}
+                gc.collect()
+                torch.cuda.empty_cache()
+            if rank == 0:
+                print(json.dumps({"kind": "detail", "key": key, **results[key]}), file=sys.stderr, flush=True)
 
     if rank == 0:
-        value = batch * world * K / (ms / 1e3)
-        out = {
-            "metric": f"{args.workload} training throughput ({wl.unit}), device-timed, max over ranks",
-            "value": round(value, 2), "unit": wl.unit, "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": round(ms / K, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16", "data": "synthetic (random-init weights, synthetic in-memory batches)",
-            "impl": args.impl,
-            "config": {"model": args.workload, "global_batch": batch * world, "per_gpu_batch": batch,
-                       "seq_len": wl.seq_len, "image_size": wl.image_size,
-                       "parallelism": f"{'fsdp' if wl.parallelism == 'fsdp' else 'dp'}{world}",
-                       "optimizer": "AdamW", "cuda_graph": runner.graphed,
-                       "l2_policy": "per-step activations and inputs exceed the 126 MB L2 (no explicit flush)",
-                       "comm": runner.comm_name, "bucket_cap_mb": args.bucket_mb, **runner.extra_config()},
-            "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"),
-                       "reasons": clocks.get("reasons", [])},
-            "e2e": e2e, "gpu_launches": int(launches), "final_loss": final_loss,
-            "wall_s_timed_region": round(wall, 3),
-        }
+        head_wl = workloads[0]
+        head_impl = "ours" if "ours" in impls else impls[0]
+        out = dict(results[f"{head_wl}/{head_impl}"])
+
+        def e2e_of(k):
+            r = results.get(k) or {}
+            return (r.get("e2e") or {}).get("value")
+
+        def ratio(a, b):
+            return round(a / b, 4) if a and b else None
+
+        extra = {}
+        for wl in workloads:
+            o, st, sg = results.get(f"{wl}/ours"), results.get(f"{wl}/stock"), results.get(f"{wl}/stock-graphed")
+            extra[wl] = {
+                "ours": o, "stock": st, "stock_graphed": sg,
+                "ours_over_stock_e2e": ratio(e2e_of(f"{wl}/ours"), e2e_of(f"{wl}/stock")),
+                "ours_over_stock_graphed_e2e": ratio(e2e_of(f"{wl}/ours"), e2e_of(f"{wl}/stock-graphed")),
+                "ours_over_stock_device": ratio((o or {}).get("value"), (st or {}).get("value")),
+            }
+        if head_impl == "ours":
+            out["vs_baseline"] = extra[head_wl]["ours_over_stock_e2e"]
+            out["vs_baseline_source"] = ("ours e2e / stock (torch DDP|FSDP + NCCL + cuBLAS/cuDNN, eager) e2e, both measured in this run on "
+                                         "this box; BASELINE.json publishes no number")
+        out["extra"] = extra
         print(json.dumps(out), flush=True)
     pg.barrier()
     pg.destroy_process_group()
     return 0
 
 
+_COUNTER = {"installed": False, "recording": False, "kernels": 0}
+
+
+def install_launch_counter():
+    """Wrap ``_lib.call`` once so that native launches are counted in kernels (also what a graph replay re-issues)."""
+    if _COUNTER["installed"]:
+        return
+    import databricks_distributed_deep_learning_b200.ops.attention as ATT
+    import databricks_distributed_deep_learning_b200.ops.functional as OF
+    import databricks_distributed_deep_learning_b200.ops.gemm as GEM
+    import databricks_distributed_deep_learning_b200.optim as OPT
+    import databricks_distributed_deep_learning_b200.parallel.collectives as COL
+    import databricks_distributed_deep_learning_b200.parallel.fsdp as FS  # noqa: F401
+    from databricks_distributed_deep_learning_b200.ops import _lib as L
+
+    orig = L.call
+
+    def counting(name, *a):
+        if _COUNTER["recording"]:
+            _COUNTER["kernels"] += KERNELS_PER_CALL.get(name, 1)
+        return orig(name, *a)
+
+    L.call = counting
+    for mod in (OF, OPT, COL, ATT, GEM):
+        mod.L.call = counting
+    _COUNTER["installed"] = True
+
+
 class OursRunner:
-    def __init__(self, args, wl, device):
+    def __init__(self, args, wl, workload, device):
         import torch
 
         from databricks_distributed_deep_learning_b200.engine import Trainer
         from databricks_distributed_deep_learning_b200.models import build_model
-        from databricks_distributed_deep_learning_b200.ops import _lib as L
 
-        self.L = L
         self.torch = torch
         torch.manual_seed(0)
         kw = {}
-        if args.workload.startswith("bert") and args.dropout is not None:
+        if workload.startswith("bert") and args.dropout is not None:
             kw = dict(hidden_dropout_prob=args.dropout, attention_probs_dropout_prob=args.dropout)
         model = build_model(wl.model, **kw)
         self.kw = kw
         self.trainer = Trainer(model, lr=wl.optim.lr, weight_decay=wl.optim.weight_decay, device=device, impl="fused",
                                use_graph=not args.no_graph, comm=args.comm, bucket_cap_mb=args.bucket_mb,
-                               parallelism=wl.parallelism)
+                               parallelism=wl.parallelism, reshard_after_forward=args.reshard)
         self.graphed = not args.no_graph
         self.comm_name = self.trainer.ddp.comm.name
-        self._count_calls()
-
-    def _count_calls(self):
-        """Wrap L.call so that launches are counted in kernels, also under graph replay."""
-        L = self.L
+        self.fsdp = wl.parallelism == "fsdp"
+        install_launch_counter()
         self.kernels_per_step = 0
-        self._recording = False
-        orig = L.call
-
-        def counting(name, *a):
-            if self._recording:
-                self.kernels_per_step += KERNELS_PER_CALL.get(name, 1)
-            return orig(name, *a)
-
-        L.call = counting
-        import databricks_distributed_deep_learning_b200.ops.functional as OF
-        import databricks_distributed_deep_learning_b200.optim as OPT
-        import databricks_distributed_deep_learning_b200.parallel.collectives as COL
-
-        import databricks_distributed_deep_learning_b200.ops.attention as ATT
-        import databricks_distributed_deep_learning_b200.ops.gemm as GEM
-        import databricks_distributed_deep_learning_b200.parallel.fsdp as FS  # noqa: F401
-
-        for mod in (OF, OPT, COL, ATT, GEM):
-            mod.L.call = counting
         self._launched = 0
         tr = self.trainer
         inner = tr._step_impl
 
         def step_impl(batch):
             # every execution of the step body (eager, warm-up or capture) records its kernel count
-            self.kernels_per_step = 0
-            self._recording = True
+            _COUNTER["kernels"] = 0
+            _COUNTER["recording"] = True
             try:
                 return inner(batch)
             finally:
-                self._recording = False
+                _COUNTER["recording"] = False
+                self.kernels_per_step = _COUNTER["kernels"]
 
         tr._step_impl = step_impl
 
@@ -275,20 +363,28 @@ class OursRunner:
         return float(self._loss.float().item())
 
     def extra_config(self):
-        return {"dropout": self.kw.get("hidden_dropout_prob", "model default")}
+        cfg = {"dropout": self.kw.get("hidden_dropout_prob", "model default")}
+        if self.fsdp:
+            cfg["reshard_after_forward"] = bool(self.trainer.ddp.reshard_after_forward)
+        return cfg
+
+    def close(self):
+        self.trainer.graph = None
+        self.trainer = None
 
 
 class StockRunner:
-    """Stock PyTorch DDP + NCCL + cuBLAS/cuDNN, eager, autocast bf16 (the measured baseline)."""
+    """Stock PyTorch DDP / FSDP + NCCL + cuBLAS/cuDNN, autocast bf16 (the measured baseline); eager, or - one GPU,
+    ``graphed=True`` - with the whole step captured in one CUDA graph."""
 
-    def __init__(self, args, wl, device):
+    def __init__(self, args, wl, workload, device, graphed=False):
         import torch
         import torch.distributed as dist
 
         self.torch = torch
         self.device = device
         torch.manual_seed(0)
-        if args.workload == "resnet50":
+        if workload == "resnet50":
             import torchvision
 
             model = torchvision.models.resnet50().to(device).to(memory_format=torch.channels_last)
@@ -296,7 +392,7 @@ class StockRunner:
         else:
             import transformers
 
-            cfg = transformers.BertConfig() if args.workload == "bert-base" else transformers.BertConfig(
+            cfg = transformers.BertConfig() if workload == "bert-base" else transformers.BertConfig(
                 hidden_size=1024, num_hidden_layers=24, num_attention_heads=16, intermediate_size=4096)
             if args.dropout is not None:
                 cfg.hidden_dropout_prob = args.dropout
@@ -319,8 +415,14 @@ class StockRunner:
                                                                        gradient_as_bucket_view=True)
         else:
             self.model = model
-        self.opt = torch.optim.AdamW(self.model.parameters(), lr=wl.optim.lr, weight_decay=wl.optim.weight_decay, fused=True)
-        self.graphed = False
+        self.want_graph = bool(graphed)
+        if self.want_graph and self.world > 1:
+            raise RuntimeError("stock-graphed is a one-GPU arm")
+        self.opt = torch.optim.AdamW(self.model.parameters(), lr=wl.optim.lr, weight_decay=wl.optim.weight_decay,
+                                     **({"capturable": True} if self.want_graph else {"fused": True}))
+        self.graphed = self.want_graph
+        self.graph = None
+        self.static = None
         self.comm_name = "nccl" if self.world > 1 else "none"
         self._loss = None
         self._loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
@@ -328,9 +430,9 @@ class StockRunner:
     def native_launches(self):
         return 0
 
-    def step_device(self, batch):
+    def _eager_step(self, batch):
         torch = self.torch
-        self.opt.zero_grad(set_to_none=True)
+        self.opt.zero_grad(set_to_none=not self.want_graph)
         with torch.autocast("cuda", dtype=torch.bfloat16):
             if self.is_image:
                 x, y = batch
@@ -339,7 +441,37 @@ class StockRunner:
                 loss = self.model(**batch).loss
         loss.backward()
         self.opt.step()
-        self._loss = loss.detach()
+        return loss.detach()
+
+    def _capture(self, batch):
+        torch = self.torch
+        self.static = {k: v.clone() for k, v in batch.items()} if isinstance(batch, dict) else tuple(v.clone() for v in batch)
+        s = torch.cuda.Stream(self.device)
+        s.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(s):
+            for _ in range(3):
+                self._eager_step(self.static)
+        torch.cuda.current_stream(self.device).wait_stream(s)
+        torch.cuda.synchronize(self.device)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._static_loss = self._eager_step(self.static)
+        torch.cuda.synchronize(self.device)
+
+    def step_device(self, batch):
+        if not self.want_graph:
+            self._loss = self._eager_step(batch)
+            return
+        if self.graph is None:
+            self._capture(batch)
+        if isinstance(batch, dict):
+            for k, v in batch.items():
+                self.static[k].copy_(v, non_blocking=True)
+        else:
+            for d, v in zip(self.static, batch):
+                d.copy_(v, non_blocking=True)
+        self.graph.replay()
+        self._loss = self._static_loss
 
     def step_host(self, batch):
         dev = {k: v.to(self.device, non_blocking=True) for k, v in batch.items()} if isinstance(batch, dict) else tuple(
@@ -352,6 +484,11 @@ class StockRunner:
 
     def extra_config(self):
         return {}
+
+    def close(self):
+        self.graph = None
+        self.model = None
+        self.opt = None
 
 
 if __name__ == "__main__":
