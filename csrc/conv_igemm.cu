@@ -302,6 +302,313 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
     }
 }
 
+// ------------------------------------------------------------------------------------------------ pair data kernel
+// Same contraction as conv_data_kernel, for layers with >= 128 output channels, restructured around what the profile of
+// that kernel showed (profiles/ncu_prof_conv_v1.md: tensor pipe busy but fed at ~60 % - shared memory is shared between
+// the MMA operand reads and the TMA writes of operands that are re-loaded far too often):
+//   * a CTA PAIR (cluster of 2, tcgen05.mma.cta_group::2) owns two pixel tiles x bn channels: M = 256, each CTA stages
+//     its own pixel tile and only HALF of the weight tile per k-block (half the weight traffic and half the B reads per SM);
+//   * 3x3 / stride-1 layers (forward and data gradient): the activation tile is loaded ONCE per 64-channel block as a
+//     halo box [64, W + 1, th + 2, nb] and the nine taps are the same shared-memory tile read through descriptors shifted
+//     by (dh + 1) * (W + 1) + (dw + 1) rows (the UMMA swizzle is a function of the absolute address: csrc/probe_umma.cu).
+//     The box starts at column -1, so with a row pitch of W + 1 the zero column of row h + 1 doubles as the right-hand
+//     padding of row h.  MMA row m = a * (W + 1) + b; the rows with b = W are computed and dropped.
+//   * A and B move through separate rings (A slots are reused by nine k-blocks in halo mode).
+// The tensor maps of this kernel cover activations and weights of the launching GPU only (its TMA loads are the
+// cta_group::2 form; ddl_conv_fwd / ddl_conv_dgrad check the pointers and otherwise use conv_data_kernel).
+constexpr int kPairMaxStages = 8;
+
+struct PairParams {
+    bf16* out;
+    float* partials;  // [2 * pair groups][2][Cn] or null
+    int ncls;
+    int cls_ntaps[4], cls_oph[4], cls_opw[4];
+    Tap taps[4][9];
+    int N, OHt, OWt, OHf, OWf, os, Cn;
+    int bw, bh, nb;      // the TMA box (halo mode: including the halo)
+    int tiles_w, tiles_h, tiles_per_cls, pair_tiles_per_cls, num_pair_tiles;
+    int th;              // output rows per tile (halo mode: bh - 2, direct: bh)
+    int pitch, rows_img; // row-index geometry of the accumulator: m = j * rows_img + a * pitch + b
+    int num_n_blocks, bn, groups;
+    int cblocks, w_tap_stride;
+    int halo;
+    int a_slot_bytes, a_stages, b_stages;
+    uint32_t a_bytes;
+};
+
+__device__ __forceinline__ void tma_load_4d_2sm(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+            smem_u32(smem_dst)),
+        "l"(map), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+
+template <bool B_MN>
+__global__ void __launch_bounds__(kThreads, 1) conv_pair_kernel(const __grid_constant__ ConvMaps maps, const PairParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int b_half = p.bn >> 1;
+    const int b_slot = b_half * 128;
+    uint8_t* a_ring = smem;
+    uint8_t* b_ring = a_ring + (size_t)p.a_stages * p.a_slot_bytes;
+    uint8_t* stg_base = b_ring + (size_t)p.b_stages * b_slot;
+    uint64_t* a_full = reinterpret_cast<uint64_t*>(stg_base + kEpiWarps * kStgBytes);
+    uint64_t* a_empty = a_full + kPairMaxStages;
+    uint64_t* b_full = a_empty + kPairMaxStages;
+    uint64_t* b_empty = b_full + kPairMaxStages;
+    uint64_t* tmem_full = b_empty + kPairMaxStages;  // [2]
+    uint64_t* tmem_empty = tmem_full + 2;             // [2]
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int cta_rank = (int)cluster_ctarank();
+    const bool leader = cta_rank == 0;
+    constexpr uint32_t kTmemCols = 512;
+    const int cluster_id = blockIdx.x >> 1;
+    const int n_blk = cluster_id % p.num_n_blocks, pgroup = cluster_id / p.num_n_blocks;
+    const int pgroups = (gridDim.x >> 1) / p.num_n_blocks;
+    const int tiles_hw = p.tiles_h * p.tiles_w;
+
+    if (p.halo) {
+        // the row right behind each halo box is read by the last valid pixel's (+1, +1) tap: it must be zero
+        const int box_rows = p.bw * p.bh * p.nb;
+        for (int s = warp; s < p.a_stages; s += kThreads / 32)
+            if (lane < 8) reinterpret_cast<uint4*>(a_ring + (size_t)s * p.a_slot_bytes + (size_t)box_rows * 128)[lane] = make_uint4(0, 0, 0, 0);
+        fence_proxy_async();
+    }
+    if (warp == 0 && lane == 0) {
+        for (int i = 0; i < 4; ++i) tma_prefetch_desc(&maps.in[i]);
+        tma_prefetch_desc(&maps.w);
+        for (int s = 0; s < kPairMaxStages; ++s) {
+            mbar_init(&a_full[s], 1);
+            mbar_init(&a_empty[s], 1);
+            mbar_init(&b_full[s], 1);
+            mbar_init(&b_empty[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full[s], 1);
+            mbar_init(&tmem_empty[s], 2 * 4 * p.groups);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc_2sm(tmem_ptr_smem, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    // pair tile q -> class and this CTA's tile inside the class; a tile index past the end decodes to an image index
+    // >= N: its loads are zero-filled and nothing is stored
+    auto decode = [&](int q, int& cls, int& n0, int& oh0, int& ow0) {
+        cls = q / p.pair_tiles_per_cls;
+        const int t = (q - cls * p.pair_tiles_per_cls) * 2 + cta_rank;
+        const int ng = t / tiles_hw, rem = t - ng * tiles_hw;
+        const int hb = rem / p.tiles_w, wb = rem - hb * p.tiles_w;
+        n0 = ng * p.nb;
+        oh0 = hb * p.th;
+        ow0 = wb * (p.bw - p.halo);
+    };
+
+    if (warp == 0) {
+        // ===================== TMA producer (both CTAs; all bytes complete on the leader's barriers) =====================
+        if (lane == 0) {
+            int as = 0, bs = 0;
+            uint32_t aph = 0, bph = 0;
+            for (int q = pgroup; q < p.num_pair_tiles; q += pgroups) {
+                int cls, n0, oh0, ow0;
+                decode(q, cls, n0, oh0, ow0);
+                const int ntaps = p.cls_ntaps[cls];
+                for (int cb = 0; cb < p.cblocks; ++cb) {
+                    for (int ti = 0; ti < ntaps; ++ti) {
+                        const Tap tp = p.taps[cls][ti];
+                        if (!p.halo || ti == 0) {
+                            mbar_wait(&a_empty[as], aph ^ 1);
+                            if (leader) mbar_expect_tx(&a_full[as], 2 * p.a_bytes);
+                            uint8_t* sa = a_ring + (size_t)as * p.a_slot_bytes;
+                            if (p.halo) tma_load_4d_2sm(sa, &maps.in[0], &a_full[as], cb * 64, ow0 - 1, oh0 - 1, n0);
+                            else tma_load_4d_2sm(sa, &maps.in[tp.map], &a_full[as], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
+                            if (++as == p.a_stages) { as = 0; aph ^= 1; }
+                        }
+                        mbar_wait(&b_empty[bs], bph ^ 1);
+                        if (leader) mbar_expect_tx(&b_full[bs], 2 * (uint32_t)b_slot);
+                        uint8_t* sb = b_ring + (size_t)bs * b_slot;
+                        const int nb0 = n_blk * p.bn + cta_rank * b_half;
+                        if (!B_MN) {
+                            tma_load_2d_2sm(sb, &maps.w, &b_full[bs], tp.wtap * p.w_tap_stride + cb * 64, nb0);
+                        } else {
+                            for (int j = 0; j < (b_half >> 6); ++j)
+                                tma_load_2d_2sm(sb + j * 8192, &maps.w, &b_full[bs], tp.wtap * p.w_tap_stride + nb0 + j * 64, cb * 64);
+                        }
+                        if (++bs == p.b_stages) { bs = 0; bph ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (leader only) =====================
+        if (lane == 0 && leader) {
+            const uint32_t idesc = make_idesc(256, p.bn, false, B_MN);
+            int as = 0, bs = 0, acc = 0;
+            uint32_t aph = 0, bph = 0, acc_phase = 0;
+            for (int q = pgroup; q < p.num_pair_tiles; q += pgroups) {
+                const int cls = q / p.pair_tiles_per_cls;
+                const int ntaps = p.cls_ntaps[cls];
+                mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * p.bn;
+                bool first = true;
+                for (int cb = 0; cb < p.cblocks; ++cb) {
+                    for (int ti = 0; ti < ntaps; ++ti) {
+                        if (!p.halo || ti == 0) {
+                            mbar_wait(&a_full[as], aph);
+                            tc_fence_after();
+                        }
+                        mbar_wait(&b_full[bs], bph);
+                        tc_fence_after();
+                        uint32_t sa = smem_u32(a_ring + (size_t)as * p.a_slot_bytes);
+                        if (p.halo) {
+                            const Tap tp = p.taps[cls][ti];
+                            sa += (uint32_t)(((int)tp.dh + 1) * p.pitch + (int)tp.dw + 1) * 128u;
+                        }
+                        const uint32_t sb = smem_u32(b_ring + (size_t)bs * b_slot);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const uint64_t da = make_smem_desc(sa + k * 32, 16, 1024);
+                            const uint64_t db = B_MN ? make_smem_desc(sb + k * 2048, 8192, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
+                            umma_bf16_2sm(d_tmem, da, db, idesc, (!first || k > 0) ? 1u : 0u);
+                        }
+                        first = false;
+                        umma_commit_2sm(&b_empty[bs]);
+                        if (++bs == p.b_stages) { bs = 0; bph ^= 1; }
+                        if (!p.halo || ti == ntaps - 1) {
+                            umma_commit_2sm(&a_empty[as]);
+                            if (++as == p.a_stages) { as = 0; aph ^= 1; }
+                        }
+                    }
+                }
+                umma_commit_2sm(&tmem_full[acc]);
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else {
+        // ===================== epilogue warps (each CTA drains its own 128 rows) =====================
+        const int ew = warp - 2;
+        const int quarter = warp & 3;
+        const int group = ew >> 2;
+        if (group < p.groups) {
+            uint8_t* stg = stg_base + ew * kStgBytes;
+            const bool stats = p.partials != nullptr;
+            float cs[16], cq[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) cs[i] = cq[i] = 0.f;
+            const int col0 = n_blk * p.bn + group * 64;
+            const int t_row = lane >> 2, t_ch = lane & 3;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int q = pgroup; q < p.num_pair_tiles; q += pgroups) {
+                int cls, n0, oh0, ow0;
+                decode(q, cls, n0, oh0, ow0);
+                const int oph = p.cls_oph[cls], opw = p.cls_opw[cls];
+                long long off[4];
+#pragma unroll
+                for (int it = 0; it < 4; ++it) {
+                    const int r = quarter * 32 + it * 8 + t_row;
+                    off[it] = -1;
+                    const int j = r / p.rows_img, rr = r - j * p.rows_img;
+                    const int a = rr / p.pitch, b = rr - a * p.pitch;
+                    if (j < p.nb && a < p.th && b < p.bw - p.halo && n0 + j < p.N && oh0 + a < p.OHt && ow0 + b < p.OWt)
+                        off[it] = (((long long)(n0 + j) * p.OHf + (oh0 + a) * p.os + oph) * p.OWf + (ow0 + b) * p.os + opw) * p.Cn + col0 + t_ch * 8;
+                }
+                mbar_wait(&tmem_full[acc], acc_phase);
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + acc * p.bn + group * 64 + ((uint32_t)(quarter * 32) << 16);
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(taddr + h * 32, r);
+                    tmem_ld_wait();
+                    if (h == 1) {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive_leader(&tmem_empty[acc]);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        float f[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[j * 8 + e]);
+                        *reinterpret_cast<uint4*>(stg + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4)) = float_to_bf16x8(f);
+                    }
+                    __syncwarp();
+#pragma unroll
+                    for (int it = 0; it < 4; ++it) {
+                        const int rr = it * 8 + t_row;
+                        const uint4 v = *reinterpret_cast<const uint4*>(stg + rr * 64 + ((t_ch ^ ((rr >> 1) & 3)) << 4));
+                        if (off[it] >= 0) {
+                            st_global_v4(p.out + off[it] + h * 32, v);
+                            if (stats) {
+                                float f[8];
+                                bf16x8_to_float(v, f);
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) {
+                                    cs[h * 8 + e] += f[e];
+                                    cq[h * 8 + e] = fmaf(f[e], f[e], cq[h * 8 + e]);
+                                }
+                            }
+                        }
+                    }
+                    __syncwarp();
+                }
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+            if (stats) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+#pragma unroll
+                    for (int o = 4; o < 32; o <<= 1) {
+                        cs[i] += __shfl_xor_sync(0xffffffffu, cs[i], o);
+                        cq[i] += __shfl_xor_sync(0xffffffffu, cq[i], o);
+                    }
+                }
+                float* mine = reinterpret_cast<float*>(stg);
+                if (t_row == 0) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const int c = (i >> 3) * 32 + t_ch * 8 + (i & 7);
+                        mine[c * 2] = cs[i];
+                        mine[c * 2 + 1] = cq[i];
+                    }
+                }
+                asm volatile("bar.sync %0, 128;" ::"r"(1 + group) : "memory");
+                if (quarter == 2) {
+                    float t4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int qw = 0; qw < 4; ++qw) {
+                        const float* src = reinterpret_cast<const float*>(stg_base + (group * 4 + qw) * kStgBytes);
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) t4[e] += src[lane * 4 + e];
+                    }
+                    float* outp = p.partials + (size_t)(pgroup * 2 + cta_rank) * 2 * p.Cn;
+                    const int col = col0 + 2 * lane;
+                    outp[col] = t4[0];
+                    outp[p.Cn + col] = t4[1];
+                    outp[col + 1] = t4[2];
+                    outp[p.Cn + col + 1] = t4[3];
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_2sm(tmem_base, kTmemCols);
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ weight gradient
 // D[m = (tap, c)][n = k] = sum over pixels of x_tap[pix][c] * dy[pix][k].  Both operands are MN-major: a pixel's
 // 64-channel slice is one 128-byte row, the reduction index (pixel) walks the rows.  The (tap, c) axis is cut into
@@ -639,6 +946,153 @@ int fwd_m_groups(const ConvShape& s) {
     return m_groups < 1 ? 1 : m_groups;
 }
 
+// ---- pair kernel launch plan -----------------------------------------------------------------------------
+int g_pair_mode = 1;  // 0 = never use the CTA-pair kernel, 1 = pair kernel (halo tiles where possible), 2 = pair kernel, no halo
+
+bool ptr_is_local(const void* ptr) {
+    cudaPointerAttributes attr;
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) return false;
+    if (cudaPointerGetAttributes(&attr, ptr) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return false;
+    }
+    return attr.type == cudaMemoryTypeDevice && attr.device == dev;
+}
+
+struct PairPlan {
+    bool halo;
+    BoxGeo g;       // the TMA box and how it tiles the grid (halo mode: box includes the halo; g.tiles() counts output tiles)
+    int th, pitch, rows_img;
+    int a_slot, a_stages, b_stages;
+    int pair_tiles_per_cls, pgroups;
+};
+
+// d: classes / taps / grid / bn already filled in.  halo_ok: 3x3 stride-1 geometry (all taps are shifts of one box).
+bool plan_pair(const DataParams& d, bool halo_ok, PairPlan& pl) {
+    if (g_pair_mode == 0 || d.bn % 128 != 0) return false;
+    const int b_slot = (d.bn / 2) * 128;
+    const int avail = 227 * 1024 - kEpiWarps * kStgBytes - 1024 - 1024;
+    pl.halo = false;
+    if (halo_ok && g_pair_mode == 1 && d.ncls == 1 && d.OWt + 1 <= 128) {
+        const int pitch = d.OWt + 1;
+        int th = 128 / pitch;
+        if (th > d.OHt) th = d.OHt;
+        const int tiles_h = (d.OHt + th - 1) / th;
+        th = (d.OHt + tiles_h - 1) / tiles_h;
+        const int rows_img = (th + 2) * pitch;
+        int nb = 1;
+        if (th == d.OHt) {
+            nb = (128 - th * pitch) / rows_img + 1;
+            if (nb > d.N) nb = d.N;
+            if (nb < 1) nb = 1;
+        }
+        BoxGeo g;
+        g.N = d.N; g.GH = d.OHt; g.GW = d.OWt;
+        g.bw = pitch; g.bh = th + 2; g.nb = nb;
+        g.tiles_w = 1; g.tiles_h = tiles_h; g.ngroups = (d.N + nb - 1) / nb;
+        const int box_rows = g.pix();
+        int slot_rows = box_rows + 1;
+        if (slot_rows < 2 * pitch + 2 + 128) slot_rows = 2 * pitch + 2 + 128;
+        const int a_slot = (slot_rows * 128 + 1023) / 1024 * 1024;
+        int b_stages = (avail - 2 * a_slot) / b_slot;
+        if (b_stages > kPairMaxStages) b_stages = kPairMaxStages;
+        if (b_stages >= 3 && g.bh <= 256 && g.nb <= 256) {
+            pl.halo = true;
+            pl.g = g; pl.th = th; pl.pitch = pitch; pl.rows_img = rows_img;
+            pl.a_slot = a_slot; pl.a_stages = 2; pl.b_stages = b_stages;
+        }
+    }
+    if (!pl.halo) {
+        pl.g = choose_box(d.N, d.OHt, d.OWt, kTileM);
+        pl.th = pl.g.bh; pl.pitch = pl.g.bw; pl.rows_img = pl.g.bw * pl.g.bh;
+        pl.a_slot = kStageA;
+        int st = avail / (kStageA + b_slot);
+        if (st > kPairMaxStages) st = kPairMaxStages;
+        if (st < 2) return false;
+        pl.a_stages = pl.b_stages = st;
+    }
+    const int tiles_per_cls = pl.g.tiles();
+    pl.pair_tiles_per_cls = (tiles_per_cls + 1) / 2;
+    int pgroups = (DDL_SM_COUNT / 2) / d.num_n_blocks;
+    if (pgroups > pl.pair_tiles_per_cls * d.ncls) pgroups = pl.pair_tiles_per_cls * d.ncls;
+    pl.pgroups = pgroups < 1 ? 1 : pgroups;
+    return true;
+}
+
+// act: the activation tensor the boxes read ([aN, aH, aW, aC] NHWC, map stride act_stride); w: [w_rows][w_inner] weights
+int launch_pair(bool b_mn, const DataParams& d, const PairPlan& pl, const void* act, int aN, int aH, int aW, int aC, int act_stride, bool flat,
+                const void* w, long long w_rows, long long w_inner, cudaStream_t stream) {
+    PairParams p = {};
+    p.out = d.out; p.partials = d.partials;
+    p.ncls = d.ncls;
+    for (int i = 0; i < 4; ++i) {
+        p.cls_ntaps[i] = d.cls_ntaps[i]; p.cls_oph[i] = d.cls_oph[i]; p.cls_opw[i] = d.cls_opw[i];
+        for (int j = 0; j < 9; ++j) p.taps[i][j] = d.taps[i][j];
+    }
+    p.N = d.N; p.OHt = d.OHt; p.OWt = d.OWt; p.OHf = d.OHf; p.OWf = d.OWf; p.os = d.os; p.Cn = d.Cn;
+    p.bw = pl.g.bw; p.bh = pl.g.bh; p.nb = pl.g.nb;
+    p.tiles_w = pl.g.tiles_w; p.tiles_h = pl.g.tiles_h;
+    p.tiles_per_cls = pl.g.tiles();
+    p.pair_tiles_per_cls = pl.pair_tiles_per_cls;
+    p.num_pair_tiles = pl.pair_tiles_per_cls * d.ncls;
+    p.th = pl.th; p.pitch = pl.pitch; p.rows_img = pl.rows_img;
+    p.num_n_blocks = d.num_n_blocks; p.bn = d.bn; p.groups = d.bn / 64;
+    p.cblocks = d.cblocks; p.w_tap_stride = d.w_tap_stride;
+    p.halo = pl.halo ? 1 : 0;
+    p.a_slot_bytes = pl.a_slot; p.a_stages = pl.a_stages; p.b_stages = pl.b_stages;
+    p.a_bytes = (uint32_t)pl.g.pix() * 128u;
+    ConvMaps maps;
+    if (int e = make_act_maps(maps.in, act, aN, aH, aW, aC, act_stride, flat, pl.g, "conv (pair) activations")) return e;
+    if (int e = tma_host::encode_2d(&maps.w, w, w_rows, w_inner, w_inner * 2, b_mn ? 64 : d.bn / 2, "conv (pair) weights")) return e;
+    const int smem = pl.a_stages * pl.a_slot + pl.b_stages * (d.bn / 2) * 128 + kEpiWarps * kStgBytes + 1024 + 1024;
+    static int attr_smem[2] = {0, 0};
+    if (smem > attr_smem[b_mn ? 1 : 0]) {
+        if (b_mn) DDL_CHECK(cudaFuncSetAttribute(conv_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        else DDL_CHECK(cudaFuncSetAttribute(conv_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_smem[b_mn ? 1 : 0] = smem;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * pl.pgroups * d.num_n_blocks);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (b_mn) DDL_CHECK(cudaLaunchKernelEx(&cfg, conv_pair_kernel<true>, maps, p));
+    else DDL_CHECK(cudaLaunchKernelEx(&cfg, conv_pair_kernel<false>, maps, p));
+    return 0;
+}
+
+// classes / taps / grid of the forward convolution (shared by the launch and the partial-row query)
+void fill_fwd(DataParams& p, const ConvShape& s, const BoxGeo& g) {
+    p.ncls = 1;
+    p.cls_ntaps[0] = forward_taps(s, p.taps[0]);
+    fill_geo(p, g);
+    p.OHf = g.GH; p.OWf = g.GW; p.os = 1;
+    p.Cn = s.Cout;
+    p.num_tiles = p.tiles_per_cls;
+    p.bn = s.Cout <= 256 ? s.Cout : 256;
+    p.num_n_blocks = s.Cout / p.bn;
+    p.cblocks = s.C / 64;
+    p.w_tap_stride = s.C;
+}
+
+// rows of BatchNorm partials the forward writes (the pair kernel when the shape allows it, else the one-CTA kernel)
+int fwd_partial_rows(const ConvShape& s) {
+    const BoxGeo g = s.flat ? choose_box(1, 1, s.N * s.OH * s.OW, kTileM) : choose_box(s.N, s.OH, s.OW, kTileM);
+    DataParams p = {};
+    fill_fwd(p, s, g);
+    PairPlan pl;
+    if (plan_pair(p, s.R == 3 && s.stride == 1, pl)) return 2 * pl.pgroups;
+    return fwd_m_groups(s);
+}
+
 // weight-gradient launch plan (shared by the scratch-size query and the launch)
 struct WgradPlan {
     BoxGeo g;
@@ -693,12 +1147,14 @@ DDL_API int ddl_conv_supported(int N, int H, int W, int C, int Cout, int R, int 
 
 DDL_API int ddl_conv_fwd_groups(int N, int H, int W, int C, int Cout, int R, int S, int stride, int pad) {
     if (!conv_ok(N, H, W, C, Cout, R, S, stride, pad)) return 0;
-    return fwd_m_groups(make_shape(N, H, W, C, Cout, R, S, stride, pad));
+    return fwd_partial_rows(make_shape(N, H, W, C, Cout, R, S, stride, pad));
 }
 
-DDL_API int ddl_conv_set_tuning(int wgrad_rows) {
+DDL_API int ddl_conv_set_tuning(int wgrad_rows, int pair_mode) {
     DDL_REQUIRE(wgrad_rows == 0 || wgrad_rows == 64 || wgrad_rows == 128, "conv tuning: wgrad_rows must be 0, 64 or 128");
+    DDL_REQUIRE(pair_mode >= 0 && pair_mode <= 2, "conv tuning: pair_mode must be 0 (one-CTA kernel), 1 (CTA pairs + halo tiles) or 2 (CTA pairs)");
     g_wgrad_rows = wgrad_rows;
+    g_pair_mode = pair_mode;
     return 0;
 }
 
@@ -712,20 +1168,22 @@ DDL_API int ddl_conv_fwd(const void* x, const void* w, void* y, float* partials,
     DataParams p = {};
     p.out = (bf16*)y;
     p.partials = partials;
-    p.ncls = 1;
-    p.cls_ntaps[0] = forward_taps(s, p.taps[0]);
-    fill_geo(p, g);
-    p.OHf = g.GH; p.OWf = g.GW; p.os = 1;
-    p.Cn = Cout;
-    p.num_tiles = p.tiles_per_cls;
-    p.bn = Cout <= 256 ? Cout : 256;
-    p.num_n_blocks = Cout / p.bn;
-    p.cblocks = C / 64;
-    p.w_tap_stride = C;
+    fill_fwd(p, s, g);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    PairPlan pl;
+    const bool pair_shape = plan_pair(p, R == 3 && stride == 1, pl);
+    if (pair_shape && ptr_is_local(x) && ptr_is_local(w))
+        return launch_pair(false, p, pl, x, N, H, W, C, stride, s.flat, w, Cout, (long long)R * S * C, stream);
     ConvMaps maps;
     if (int e = make_act_maps(maps.in, x, N, H, W, C, stride, s.flat, g, "conv fwd")) return e;
     if (int e = tma_host::encode_2d(&maps.w, w, Cout, (long long)R * S * C, (long long)R * S * C * 2, p.bn, "conv fwd weights")) return e;
-    return launch_data(false, maps, p, (cudaStream_t)stream_);
+    if (int e = launch_data(false, maps, p, stream)) return e;
+    if (pair_shape && partials) {
+        // the caller sized the partials for the pair kernel (ddl_conv_fwd_groups): the rows this kernel does not write are zeros
+        const int rows = fwd_m_groups(s), want = 2 * pl.pgroups;
+        if (want > rows) DDL_CHECK(cudaMemsetAsync(partials + (size_t)rows * 2 * Cout, 0, (size_t)(want - rows) * 2 * Cout * sizeof(float), stream));
+    }
+    return 0;
 }
 
 // dx [N, H, W, C] from dy [N, OH, OW, Cout] and w [Cout][R][S][C]
@@ -791,6 +1249,9 @@ DDL_API int ddl_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H
         p.OHf = H; p.OWf = W; p.os = 2;
     }
     p.num_tiles = p.ncls * p.tiles_per_cls;
+    PairPlan pl;
+    if (plan_pair(p, R == 3 && stride == 1, pl) && ptr_is_local(dy) && ptr_is_local(w))
+        return launch_pair(true, p, pl, dy, N, s.OH, s.OW, Cout, 1, s.flat, w, Cout, (long long)R * S * C, stream);
     ConvMaps maps;
     if (int e = make_act_maps(maps.in, dy, N, s.OH, s.OW, Cout, 1, s.flat, g, "conv dgrad")) return e;
     if (int e = tma_host::encode_2d(&maps.w, w, Cout, (long long)R * S * C, (long long)R * S * C * 2, 64, "conv dgrad weights")) return e;

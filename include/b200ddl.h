@@ -141,7 +141,9 @@ int ddl_bn_act_fwd_train_from_partials(const void* x, const void* residual, cons
  * ask ddl_bn_scratch_bytes) are rejected.  The first call on a device looks up the array's
  * address: make that call with the device current and before any stream capture.  All
  * calls share the array; calls that overlap on the GPU race - serialise them.  Nothing in
- * it needs zeroing between calls. */
+ * it needs zeroing between calls.  The looked-up address is cached per device for the life
+ * of the process: a host program that calls cudaDeviceReset() invalidates it (and every
+ * other handle of this library) and must not call the entry point on that device again. */
 #define DDL_BN_NOALLOC_MAX_BYTES (2u << 20)
 int ddl_bn_act_fwd_train_noalloc(const void* x, const void* residual, const void* gamma, const void* beta, float* running_mean,
                                  float* running_var, void* y, float* mean, float* invstd, float* scale, float* shift, long long M,
@@ -234,8 +236,10 @@ int ddl_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W,
 size_t ddl_conv_wgrad_scratch_bytes(int N, int H, int W, int C, int Cout, int R, int S, int stride, int pad);
 int ddl_conv_wgrad(const void* x, const void* dy, void* dw, long long sk, long long sc, long long sr, long long ss, void* scratch,
                    size_t scratch_bytes, int N, int H, int W, int C, int Cout, int R, int S, int stride, int pad, void* stream);
-/* benchmarks: pixel-chunk size of the weight gradient (0 = auto, 64, 128) */
-int ddl_conv_set_tuning(int wgrad_rows);
+/* benchmarks: pixel-chunk size of the weight gradient (0 = auto, 64, 128); forward / data-gradient kernel for layers with
+ * >= 128 output channels: 0 = one CTA per tile, 1 = CTA pairs (cta_group::2) with halo tiles for 3x3 / stride 1 (default),
+ * 2 = CTA pairs without halo tiles */
+int ddl_conv_set_tuning(int wgrad_rows, int pair_mode);
 
 /* ---- tcgen05 / TMEM / TMA GEMM (csrc/gemm_tcgen05.cu), K8 ------------------------------ */
 /* C[M,N] = epilogue(A . B^T), bf16 operands, fp32 accumulation in tensor memory.
