@@ -21,6 +21,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--batch", type=int, default=3)
     ap.add_argument("--only", type=int, default=-1)
+    ap.add_argument("--im2col", type=int, default=1)
     ap.add_argument("--pair", type=int, default=1, help="0 = one-CTA data kernel, 1 = CTA pairs + halo tiles, 2 = CTA pairs")
     args = ap.parse_args()
     from test_gpu_conv import RESNET50_CONVS, conv_case
@@ -28,6 +29,7 @@ def main():
     from databricks_distributed_deep_learning_b200.ops import _lib as L
 
     L.call("ddl_conv_set_tuning", 0, args.pair)
+    L.call("ddl_conv_set_im2col", args.im2col)
     print(f"pair mode {args.pair}", flush=True)
     bad = 0
     for i, (cin, hw, cout, k, s) in enumerate(RESNET50_CONVS):

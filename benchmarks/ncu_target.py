@@ -87,6 +87,8 @@ def main():
         from databricks_distributed_deep_learning_b200.ops import _lib as L
 
         lib = L.lib()
+        if os.environ.get("DDL_CONV_PAIR"):
+            L.call("ddl_conv_set_tuning", 0, int(os.environ["DDL_CONV_PAIR"]))
         shapes = [(256, 14, 1024, 1, 1), (256, 14, 256, 3, 1), (64, 56, 64, 3, 1)]
         if len(sys.argv) > 2:
             shapes = [tuple(int(v) for v in sh.split(",")) for sh in sys.argv[2].split(";")]

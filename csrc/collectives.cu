@@ -288,6 +288,9 @@ __global__ void __launch_bounds__(kThreads) allreduce_nvls_kernel(Ctx c, char* m
             const size_t g = g0 + k * stride;
             if (g < slice) {
                 if (kBf16) {
+                    // The switch returns the fp32 sum rounded to bf16 (multimem.ld_reduce ... .acc::f32.bf16x2); the scale
+                    // below is 1 / world = a power of two for 2, 4 and 8 ranks, so this second rounding is exact there
+                    // (one rounding in total, like the peer-load kernels); other world sizes pay one extra bf16 rounding.
                     float f[8];
                     bf16x8_to_float(v[k], f);
 #pragma unroll

@@ -53,6 +53,19 @@ __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* m
         : "memory");
 }
 
+// im2col-mode TMA load: `pixels` (fixed in the tensor map) consecutive output positions starting at the base pixel
+// (w, h, n) - walking along W, then H, then N inside the map's bounding box - each displaced by the filter-tap offset
+// (off_w, off_h); positions outside the image are zero-filled.  One instruction delivers a dense [pixels x 64 channels]
+// operand tile that may span image rows and images.
+__device__ __forceinline__ void tma_load_im2col(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c, int w, int h, int n, int off_w,
+                                                int off_h) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(
+            smem_u32(smem_dst)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)off_w), "h"((uint16_t)off_h)
+        : "memory");
+}
+
 // ------------------------------------------------------------------------------------------------ data kernel
 constexpr int kTileM = 128;
 constexpr int kEpiWarps = 16;  // 4 TMEM lane quarters x 4 column groups of 64
@@ -76,7 +89,12 @@ struct DataParams {
     int cblocks;                   // reduction channels / 64
     int w_tap_stride;              // elements between consecutive taps inside one weight row (= conv input channels)
     int stages;
+    int group;  // ring slots are released `group` at a time (one tcgen05.commit per group, see PairParams::bgroup)
     uint32_t a_bytes;
+    // im2col mode: tiles are 128 consecutive positions of the class grid [N][OHt][OWt] (dense, spanning rows and images);
+    // taps[].dw / dh are offsets in input pixels, the base pixel of output (a, b) is (b * cstride + low_w, a * cstride + low_h)
+    int im2col, cstride, low_w, low_h;
+    long long cls_pix;  // N * OHt * OWt
 };
 
 template <bool B_MN>
@@ -132,11 +150,20 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
                 for (int ti = 0; ti < ntaps; ++ti) {
                     const Tap tp = p.taps[cls][ti];
                     for (int cb = 0; cb < p.cblocks; ++cb) {
-                        mbar_wait(&empty_bar[stage], phase ^ 1);
+                        if (stage % p.group == 0) mbar_wait(&empty_bar[stage / p.group], phase ^ 1);
                         uint8_t* sa = smem + (size_t)stage * stage_bytes;
                         uint8_t* sb = sa + kStageA;
                         mbar_expect_tx(&full_bar[stage], p.a_bytes + (uint32_t)stage_b);
-                        tma_load_4d(sa, &maps.in[tp.map], &full_bar[stage], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
+                        if (p.im2col) {
+                            const long long m0 = (long long)t * kTileM;
+                            const int b0 = (int)(m0 % p.OWt);
+                            const long long t2 = m0 / p.OWt;
+                            const int a0 = (int)(t2 % p.OHt), nn = (int)(t2 / p.OHt);
+                            tma_load_im2col(sa, &maps.in[0], &full_bar[stage], cb * 64, b0 * p.cstride + p.low_w, a0 * p.cstride + p.low_h, nn,
+                                            tp.dw - p.low_w, tp.dh - p.low_h);
+                        } else {
+                            tma_load_4d(sa, &maps.in[tp.map], &full_bar[stage], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
+                        }
                         if (!B_MN) {
                             tma_load_2d(sb, &maps.w, &full_bar[stage], tp.wtap * p.w_tap_stride + cb * 64, n_blk * p.bn);
                         } else {
@@ -171,7 +198,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
                         const uint64_t db = B_MN ? make_smem_desc(sb + k * 2048, 8192, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
                         umma_bf16(d_tmem, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
                     }
-                    umma_commit(&empty_bar[stage]);
+                    if (stage % p.group == p.group - 1) umma_commit(&empty_bar[stage / p.group]);
                     if (++stage == p.stages) { stage = 0; phase ^= 1; }
                 }
                 umma_commit(&tmem_full[acc]);
@@ -206,7 +233,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
                 for (int it = 0; it < 4; ++it) {
                     const int r = quarter * 32 + it * 8 + t_row;
                     off[it] = -1;
-                    if (r < rows_box) {
+                    if (p.im2col) {
+                        const long long m = (long long)t * kTileM + r;
+                        if (m < p.cls_pix) {
+                            const int b = (int)(m % p.OWt);
+                            const long long t2 = m / p.OWt;
+                            const int a = (int)(t2 % p.OHt), nn = (int)(t2 / p.OHt);
+                            off[it] = (((long long)nn * p.OHf + a * p.os + oph) * p.OWf + b * p.os + opw) * p.Cn + col0 + t_ch * 8;
+                        }
+                    } else if (r < rows_box) {
                         const int j = r / rows_img, rr = r - j * rows_img;
                         const int a = rr / p.bw, b = rr - a * p.bw;
                         if (n0 + j < p.N && oh0 + a < p.OHt && ow0 + b < p.OWt)
@@ -333,8 +368,24 @@ struct PairParams {
     int cblocks, w_tap_stride;
     int halo;
     int a_slot_bytes, a_stages, b_stages;
+    int bgroup;          // B (and, in direct mode, A) slots are handed back to the producer `bgroup` at a time: a
+                         // tcgen05.commit costs ~450 cycles of tensor-pipe time (csrc/probe_umma.cu), four MMAs of a
+                         // 64-deep k-block take 256 - 512, so one commit per k-block would halve the MMA rate
     uint32_t a_bytes;
+    long long* dbg;  // optional [gridDim.x][8] cycle counters (ddl_conv_set_debug): where each role of a CTA waits
+    int ablate;      // development only: bit 0 = epilogue drops its staging / stores, bit 1 = producer issues no TMA loads
 };
+
+// mbarrier wait that adds the cycles spent waiting to *acc when timing is on
+__device__ __forceinline__ void mbar_wait_timed(uint64_t* bar, uint32_t parity, bool timing, long long& acc) {
+    if (!timing) {
+        mbar_wait(bar, parity);
+        return;
+    }
+    const long long t0 = clock64();
+    mbar_wait(bar, parity);
+    acc += clock64() - t0;
+}
 
 __device__ __forceinline__ void tma_load_4d_2sm(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
     asm volatile(
@@ -416,6 +467,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_pair_kernel(const __grid_con
         if (lane == 0) {
             int as = 0, bs = 0;
             uint32_t aph = 0, bph = 0;
+            const bool timing = p.dbg != nullptr;
+            long long w_ae = 0, w_be = 0;
+            const long long t_start = timing ? clock64() : 0;
             for (int q = pgroup; q < p.num_pair_tiles; q += pgroups) {
                 int cls, n0, oh0, ow0;
                 decode(q, cls, n0, oh0, ow0);
@@ -424,18 +478,29 @@ __global__ void __launch_bounds__(kThreads, 1) conv_pair_kernel(const __grid_con
                     for (int ti = 0; ti < ntaps; ++ti) {
                         const Tap tp = p.taps[cls][ti];
                         if (!p.halo || ti == 0) {
-                            mbar_wait(&a_empty[as], aph ^ 1);
-                            if (leader) mbar_expect_tx(&a_full[as], 2 * p.a_bytes);
+                            // direct mode: A slot i and B slot i are released together (b_empty), no separate wait
+                            if (p.halo) mbar_wait_timed(&a_empty[as], aph ^ 1, timing, w_ae);
+                            else if (bs % p.bgroup == 0) mbar_wait_timed(&b_empty[bs / p.bgroup], bph ^ 1, timing, w_be);
                             uint8_t* sa = a_ring + (size_t)as * p.a_slot_bytes;
-                            if (p.halo) tma_load_4d_2sm(sa, &maps.in[0], &a_full[as], cb * 64, ow0 - 1, oh0 - 1, n0);
-                            else tma_load_4d_2sm(sa, &maps.in[tp.map], &a_full[as], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
+                            if (p.ablate & 2) {
+                                if (leader) mbar_arrive(&a_full[as]);
+                            } else {
+                                if (leader) mbar_expect_tx(&a_full[as], 2 * p.a_bytes);
+                                if (p.halo) tma_load_4d_2sm(sa, &maps.in[0], &a_full[as], cb * 64, ow0 - 1, oh0 - 1, n0);
+                                else tma_load_4d_2sm(sa, &maps.in[tp.map], &a_full[as], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
+                            }
                             if (++as == p.a_stages) { as = 0; aph ^= 1; }
                         }
-                        mbar_wait(&b_empty[bs], bph ^ 1);
-                        if (leader) mbar_expect_tx(&b_full[bs], 2 * (uint32_t)b_slot);
+                        if (p.halo && bs % p.bgroup == 0) mbar_wait_timed(&b_empty[bs / p.bgroup], bph ^ 1, timing, w_be);
                         uint8_t* sb = b_ring + (size_t)bs * b_slot;
                         const int nb0 = n_blk * p.bn + cta_rank * b_half;
-                        if (!B_MN) {
+                        if (p.ablate & 2) {
+                            if (leader) mbar_arrive(&b_full[bs]);
+                        } else if (leader) {
+                            mbar_expect_tx(&b_full[bs], 2 * (uint32_t)b_slot);
+                        }
+                        if (p.ablate & 2) {
+                        } else if (!B_MN) {
                             tma_load_2d_2sm(sb, &maps.w, &b_full[bs], tp.wtap * p.w_tap_stride + cb * 64, nb0);
                         } else {
                             for (int j = 0; j < (b_half >> 6); ++j)
@@ -445,6 +510,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_pair_kernel(const __grid_con
                     }
                 }
             }
+            if (timing) {
+                long long* d = p.dbg + (size_t)blockIdx.x * 8;
+                d[0] = clock64() - t_start;  // producer: total, waiting for a free A slot, waiting for a free B slot
+                d[1] = w_ae;
+                d[2] = w_be;
+            }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer (leader only) =====================
@@ -452,20 +523,23 @@ __global__ void __launch_bounds__(kThreads, 1) conv_pair_kernel(const __grid_con
             const uint32_t idesc = make_idesc(256, p.bn, false, B_MN);
             int as = 0, bs = 0, acc = 0;
             uint32_t aph = 0, bph = 0, acc_phase = 0;
+            const bool timing = p.dbg != nullptr;
+            long long w_af = 0, w_bf = 0, w_te = 0, w_issue = 0, w_commit = 0;
+            const long long t_start = timing ? clock64() : 0;
             for (int q = pgroup; q < p.num_pair_tiles; q += pgroups) {
                 const int cls = q / p.pair_tiles_per_cls;
                 const int ntaps = p.cls_ntaps[cls];
-                mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+                mbar_wait_timed(&tmem_empty[acc], acc_phase ^ 1, timing, w_te);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * p.bn;
                 bool first = true;
                 for (int cb = 0; cb < p.cblocks; ++cb) {
                     for (int ti = 0; ti < ntaps; ++ti) {
                         if (!p.halo || ti == 0) {
-                            mbar_wait(&a_full[as], aph);
+                            mbar_wait_timed(&a_full[as], aph, timing, w_af);
                             tc_fence_after();
                         }
-                        mbar_wait(&b_full[bs], bph);
+                        mbar_wait_timed(&b_full[bs], bph, timing, w_bf);
                         tc_fence_after();
                         uint32_t sa = smem_u32(a_ring + (size_t)as * p.a_slot_bytes);
                         if (p.halo) {
@@ -473,23 +547,38 @@ __global__ void __launch_bounds__(kThreads, 1) conv_pair_kernel(const __grid_con
                             sa += (uint32_t)(((int)tp.dh + 1) * p.pitch + (int)tp.dw + 1) * 128u;
                         }
                         const uint32_t sb = smem_u32(b_ring + (size_t)bs * b_slot);
+                        const long long ti0 = timing ? clock64() : 0;
 #pragma unroll
                         for (int k = 0; k < 4; ++k) {
                             const uint64_t da = make_smem_desc(sa + k * 32, 16, 1024);
                             const uint64_t db = B_MN ? make_smem_desc(sb + k * 2048, 8192, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
                             umma_bf16_2sm(d_tmem, da, db, idesc, (!first || k > 0) ? 1u : 0u);
                         }
+                        const long long ti1 = timing ? clock64() : 0;
                         first = false;
-                        umma_commit_2sm(&b_empty[bs]);
+                        if (bs % p.bgroup == p.bgroup - 1) umma_commit_2sm(&b_empty[bs / p.bgroup]);
+                        if (timing) {
+                            w_issue += ti1 - ti0;
+                            w_commit += clock64() - ti1;
+                        }
                         if (++bs == p.b_stages) { bs = 0; bph ^= 1; }
                         if (!p.halo || ti == ntaps - 1) {
-                            umma_commit_2sm(&a_empty[as]);
+                            if (p.halo) umma_commit_2sm(&a_empty[as]);
                             if (++as == p.a_stages) { as = 0; aph ^= 1; }
                         }
                     }
                 }
                 umma_commit_2sm(&tmem_full[acc]);
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+            if (timing) {
+                long long* d = p.dbg + (size_t)blockIdx.x * 8;
+                d[3] = clock64() - t_start;  // MMA issuer: total, waiting for A data, for B data, for a free accumulator
+                d[4] = w_af;
+                d[5] = w_bf;
+                d[6] = w_te;
+                d[7] = w_issue;
+                d[0] = w_commit;  // (overwrites the leader's producer total)
             }
         }
     } else {
@@ -534,6 +623,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_pair_kernel(const __grid_con
                         __syncwarp();
                         if (lane == 0) mbar_arrive_leader(&tmem_empty[acc]);
                     }
+                    if (p.ablate & 1) continue;
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         float f[8];
@@ -802,6 +892,42 @@ int make_map4(CUtensorMap* map, const void* base, const cuuint64_t (&dims)[4], c
     return 0;
 }
 
+// im2col-mode tensor map of an NHWC activation [N, H, W, C]: `pixels` positions x 64 channels per load; base positions run
+// over [low, dim + up) in steps of `stride` in W and H (see tma_load_im2col)
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const int*,
+                                   const int*, cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeIm2colFn im2col_encoder() {
+    static EncodeIm2colFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        void* q = nullptr;
+        cudaDriverEntryPointQueryResult r;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &q, cudaEnableDefault, &r) == cudaSuccess && r == cudaDriverEntryPointSuccess)
+            fn = (EncodeIm2colFn)q;
+        tried = true;
+    }
+    return fn;
+}
+
+int make_im2col_map(CUtensorMap* map, const void* base, int N, int H, int W, int C, int low_w, int low_h, int up_w, int up_h, int stride,
+                    int pixels, const char* what) {
+    EncodeIm2colFn enc = im2col_encoder();
+    DDL_REQUIRE(enc != nullptr, "%s: cuTensorMapEncodeIm2col is not available from the driver", what);
+    DDL_REQUIRE(((uintptr_t)base & 15) == 0, "%s: tensor must be 16-byte aligned", what);
+    const cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+    const cuuint64_t str[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+    const int lower[2] = {low_w, low_h}, upper[2] = {up_w, up_h};
+    const cuuint32_t estr[4] = {1u, (cuuint32_t)stride, (cuuint32_t)stride, 1u};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, str, lower, upper, 64u, (cuuint32_t)pixels, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DDL_REQUIRE(r == CUDA_SUCCESS, "%s: cuTensorMapEncodeIm2col failed with CUresult %d (N %d H %d W %d C %d, corners [%d %d] [%d %d], stride %d)",
+                what, (int)r, N, H, W, C, low_w, low_h, up_w, up_h, stride);
+    return 0;
+}
+
 // how one operand tile (box) walks the pixel grid [N][GH][GW]
 struct BoxGeo {
     int N, GH, GW;  // grid the boxes tile (flattened 1x1 layers: N = GH = 1, GW = all pixels)
@@ -904,6 +1030,8 @@ int forward_taps(const ConvShape& s, Tap* taps) {
     return n;
 }
 
+int g_im2col = 1;  // activation tiles through im2col-mode TMA (dense 128-pixel tiles) instead of tiled boxes
+int g_ring_group = 1;  // ring slots released per tcgen05.commit (1 = every k-block; larger values measured slower)
 int g_wgrad_rows = 0;  // 0 = auto, 64 / 128 = forced pixel-chunk size of the weight gradient (benchmarks)
 
 int launch_data(bool b_mn, const ConvMaps& maps, DataParams& p, cudaStream_t stream) {
@@ -912,6 +1040,8 @@ int launch_data(bool b_mn, const ConvMaps& maps, DataParams& p, cudaStream_t str
     const int fixed = kEpiWarps * kStgBytes + 512 + 1024;
     p.stages = (227 * 1024 - fixed) / stage_bytes;
     if (p.stages > kMaxStages) p.stages = kMaxStages;
+    p.group = g_ring_group;
+    p.stages = p.stages / p.group * p.group;
     DDL_REQUIRE(p.stages >= 2, "conv: tile does not fit in shared memory");
     const int smem = fixed + p.stages * stage_bytes;
     static int attr_smem[2] = {0, 0};
@@ -942,11 +1072,26 @@ int fwd_m_groups(const ConvShape& s) {
     const BoxGeo g = s.flat ? choose_box(1, 1, s.N * s.OH * s.OW, kTileM) : choose_box(s.N, s.OH, s.OW, kTileM);
     const int bn = s.Cout <= 256 ? s.Cout : 256;
     int m_groups = DDL_SM_COUNT / (s.Cout / bn);
-    if (m_groups > g.tiles()) m_groups = g.tiles();
+    const long long tiles = (g_im2col && !s.flat) ? ((long long)s.N * s.OH * s.OW + kTileM - 1) / kTileM : g.tiles();
+    if (m_groups > tiles) m_groups = (int)tiles;
     return m_groups < 1 ? 1 : m_groups;
 }
 
+// forward taps as offsets in input pixels (im2col mode): input pixel = stride * o + (r - pad)
+int im2col_fwd_taps(const ConvShape& s, Tap* taps) {
+    int n = 0;
+    for (int r = 0; r < s.R; ++r)
+        for (int q = 0; q < s.S; ++q) {
+            Tap t;
+            t.dh = (int8_t)(r - s.pad); t.dw = (int8_t)(q - s.pad); t.map = 0; t.wtap = (int8_t)(r * s.S + q);
+            taps[n++] = t;
+        }
+    return n;
+}
+
 // ---- pair kernel launch plan -----------------------------------------------------------------------------
+long long* g_conv_dbg = nullptr;  // ddl_conv_set_debug
+int g_conv_ablate = 0;
 int g_pair_mode = 1;  // 0 = never use the CTA-pair kernel, 1 = pair kernel (halo tiles where possible), 2 = pair kernel, no halo
 
 bool ptr_is_local(const void* ptr) {
@@ -964,7 +1109,7 @@ struct PairPlan {
     bool halo;
     BoxGeo g;       // the TMA box and how it tiles the grid (halo mode: box includes the halo; g.tiles() counts output tiles)
     int th, pitch, rows_img;
-    int a_slot, a_stages, b_stages;
+    int a_slot, a_stages, b_stages, bgroup;
     int pair_tiles_per_cls, pgroups;
 };
 
@@ -997,10 +1142,12 @@ bool plan_pair(const DataParams& d, bool halo_ok, PairPlan& pl) {
         const int a_slot = (slot_rows * 128 + 1023) / 1024 * 1024;
         int b_stages = (avail - 2 * a_slot) / b_slot;
         if (b_stages > kPairMaxStages) b_stages = kPairMaxStages;
+        const int grp = g_ring_group;
+        b_stages = b_stages / grp * grp;
         if (b_stages >= 3 && g.bh <= 256 && g.nb <= 256) {
             pl.halo = true;
             pl.g = g; pl.th = th; pl.pitch = pitch; pl.rows_img = rows_img;
-            pl.a_slot = a_slot; pl.a_stages = 2; pl.b_stages = b_stages;
+            pl.a_slot = a_slot; pl.a_stages = 2; pl.b_stages = b_stages; pl.bgroup = grp;
         }
     }
     if (!pl.halo) {
@@ -1009,8 +1156,11 @@ bool plan_pair(const DataParams& d, bool halo_ok, PairPlan& pl) {
         pl.a_slot = kStageA;
         int st = avail / (kStageA + b_slot);
         if (st > kPairMaxStages) st = kPairMaxStages;
+        const int grp = g_ring_group;
+        st = st / grp * grp;
         if (st < 2) return false;
         pl.a_stages = pl.b_stages = st;
+        pl.bgroup = grp;
     }
     const int tiles_per_cls = pl.g.tiles();
     pl.pair_tiles_per_cls = (tiles_per_cls + 1) / 2;
@@ -1041,7 +1191,10 @@ int launch_pair(bool b_mn, const DataParams& d, const PairPlan& pl, const void* 
     p.cblocks = d.cblocks; p.w_tap_stride = d.w_tap_stride;
     p.halo = pl.halo ? 1 : 0;
     p.a_slot_bytes = pl.a_slot; p.a_stages = pl.a_stages; p.b_stages = pl.b_stages;
+    p.bgroup = pl.bgroup;
     p.a_bytes = (uint32_t)pl.g.pix() * 128u;
+    p.dbg = g_conv_dbg;
+    p.ablate = g_conv_ablate;
     ConvMaps maps;
     if (int e = make_act_maps(maps.in, act, aN, aH, aW, aC, act_stride, flat, pl.g, "conv (pair) activations")) return e;
     if (int e = tma_host::encode_2d(&maps.w, w, w_rows, w_inner, w_inner * 2, b_mn ? 64 : d.bn / 2, "conv (pair) weights")) return e;
@@ -1067,6 +1220,28 @@ int launch_pair(bool b_mn, const DataParams& d, const PairPlan& pl, const void* 
     if (b_mn) DDL_CHECK(cudaLaunchKernelEx(&cfg, conv_pair_kernel<true>, maps, p));
     else DDL_CHECK(cudaLaunchKernelEx(&cfg, conv_pair_kernel<false>, maps, p));
     return 0;
+}
+
+// Turn a filled DataParams (classes, taps in INPUT-pixel offsets, class grid N x OHt x OWt) into im2col mode over the
+// activation [aN, aH, aW, aC] read with traversal stride `cstride`, and build its tensor map.
+int use_im2col(DataParams& p, CUtensorMap* map, const void* act, int aN, int aH, int aW, int aC, int cstride, int pixels, const char* what) {
+    int low_w = 127, low_h = 127;
+    for (int c = 0; c < p.ncls; ++c)
+        for (int i = 0; i < p.cls_ntaps[c]; ++i) {
+            low_w = p.taps[c][i].dw < low_w ? p.taps[c][i].dw : low_w;
+            low_h = p.taps[c][i].dh < low_h ? p.taps[c][i].dh : low_h;
+        }
+    p.im2col = 1;
+    p.cstride = cstride;
+    p.low_w = low_w; p.low_h = low_h;
+    p.cls_pix = (long long)p.N * p.OHt * p.OWt;
+    p.tiles_per_cls = (int)((p.cls_pix + pixels - 1) / pixels);
+    p.tiles_w = p.tiles_per_cls; p.tiles_h = 1;  // (unused by the im2col decode; kept non-zero)
+    p.num_tiles = p.ncls * p.tiles_per_cls;
+    p.a_bytes = (uint32_t)pixels * 128u;
+    // the base positions must number exactly OWt x OHt per image
+    const int up_w = (p.OWt - 1) * cstride + 1 + low_w - aW, up_h = (p.OHt - 1) * cstride + 1 + low_h - aH;
+    return make_im2col_map(map, act, aN, aH, aW, aC, low_w, low_h, up_w, up_h, cstride, pixels, what);
 }
 
 // classes / taps / grid of the forward convolution (shared by the launch and the partial-row query)
@@ -1150,11 +1325,24 @@ DDL_API int ddl_conv_fwd_groups(int N, int H, int W, int C, int Cout, int R, int
     return fwd_partial_rows(make_shape(N, H, W, C, Cout, R, S, stride, pad));
 }
 
+DDL_API int ddl_conv_set_im2col(int on) {
+    g_im2col = on ? 1 : 0;
+    return 0;
+}
+
 DDL_API int ddl_conv_set_tuning(int wgrad_rows, int pair_mode) {
     DDL_REQUIRE(wgrad_rows == 0 || wgrad_rows == 64 || wgrad_rows == 128, "conv tuning: wgrad_rows must be 0, 64 or 128");
     DDL_REQUIRE(pair_mode >= 0 && pair_mode <= 2, "conv tuning: pair_mode must be 0 (one-CTA kernel), 1 (CTA pairs + halo tiles) or 2 (CTA pairs)");
     g_wgrad_rows = wgrad_rows;
     g_pair_mode = pair_mode;
+    return 0;
+}
+
+// development aid: device buffer of [296][8] int64 that the next pair-kernel launches fill with per-CTA wait-cycle counters
+// (producer: total, wait A slot, wait B slot; MMA issuer: total, wait A data, wait B data, wait accumulator); null = off
+DDL_API int ddl_conv_set_debug(void* buf, int ablate) {
+    g_conv_dbg = (long long*)buf;
+    g_conv_ablate = ablate;  // bit 0: epilogue drops staging / stores, bit 1: no TMA loads (results are garbage: timing only)
     return 0;
 }
 
@@ -1175,7 +1363,13 @@ DDL_API int ddl_conv_fwd(const void* x, const void* w, void* y, float* partials,
     if (pair_shape && ptr_is_local(x) && ptr_is_local(w))
         return launch_pair(false, p, pl, x, N, H, W, C, stride, s.flat, w, Cout, (long long)R * S * C, stream);
     ConvMaps maps;
-    if (int e = make_act_maps(maps.in, x, N, H, W, C, stride, s.flat, g, "conv fwd")) return e;
+    if (g_im2col && !s.flat) {
+        p.cls_ntaps[0] = im2col_fwd_taps(s, p.taps[0]);
+        if (int e = use_im2col(p, &maps.in[0], x, N, H, W, C, stride, kTileM, "conv fwd (im2col)")) return e;
+        for (int i = 1; i < 4; ++i) maps.in[i] = maps.in[0];
+    } else {
+        if (int e = make_act_maps(maps.in, x, N, H, W, C, stride, s.flat, g, "conv fwd")) return e;
+    }
     if (int e = tma_host::encode_2d(&maps.w, w, Cout, (long long)R * S * C, (long long)R * S * C * 2, p.bn, "conv fwd weights")) return e;
     if (int e = launch_data(false, maps, p, stream)) return e;
     if (pair_shape && partials) {
@@ -1253,7 +1447,11 @@ DDL_API int ddl_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H
     if (plan_pair(p, R == 3 && stride == 1, pl) && ptr_is_local(dy) && ptr_is_local(w))
         return launch_pair(true, p, pl, dy, N, s.OH, s.OW, Cout, 1, s.flat, w, Cout, (long long)R * S * C, stream);
     ConvMaps maps;
-    if (int e = make_act_maps(maps.in, dy, N, s.OH, s.OW, Cout, 1, s.flat, g, "conv dgrad")) return e;
+    if (g_im2col && !s.flat) {
+        // the taps are already offsets in dy pixels; every class reads the same map
+        if (int e = use_im2col(p, &maps.in[0], dy, N, s.OH, s.OW, Cout, 1, kTileM, "conv dgrad (im2col)")) return e;
+        for (int i = 1; i < 4; ++i) maps.in[i] = maps.in[0];
+    } else if (int e = make_act_maps(maps.in, dy, N, s.OH, s.OW, Cout, 1, s.flat, g, "conv dgrad")) return e;
     if (int e = tma_host::encode_2d(&maps.w, w, Cout, (long long)R * S * C, (long long)R * S * C * 2, 64, "conv dgrad weights")) return e;
     return launch_data(true, maps, p, stream);
 }

@@ -73,7 +73,122 @@ __global__ void __launch_bounds__(128, 1) probe_umma_kernel(const __grid_constan
         tmem_dealloc(tmem, 64);
     }
 }
+// Issue rate of tcgen05.mma (cta_group::1, M = 128, K = 16, both operands in shared memory) as a function of N: one CTA
+// issues `iters` back-to-back MMAs on resident tiles and reports the SM cycles until the last one has retired.
+__global__ void __launch_bounds__(128, 1) probe_umma_rate_kernel(long long* __restrict__ out, int n, int iters, int kmaj_steps, int mode, int nacc) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* done = reinterpret_cast<uint64_t*>(smem + 128 * 128 + 256 * 128);
+    uint32_t* tptr = reinterpret_cast<uint32_t*>(done + 1);
+    const int warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < (128 * 128 + 256 * 128) / 16; i += 128) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+    fence_proxy_async();
+    if (threadIdx.x == 0) {
+        mbar_init(done, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tptr, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tptr;
+    if (mode == 0) {
+        // issue from one thread inside a divergent region (how the kernels of this library did it at first)
+        if (threadIdx.x == 0) {
+            const uint32_t a0 = smem_u32(smem), b0 = a0 + 128 * 128;
+            const uint32_t idesc = make_idesc(128, n, false, false);
+            const long long t0 = clock64();
+            for (int i = 0; i < iters; i += 4) {
+                const uint32_t d = tmem + ((i >> 2) & (nacc - 1)) * n;  // nacc is a power of two
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    umma_bf16(d, make_smem_desc(a0 + k * 32, 16, 1024), make_smem_desc(b0 + k * 32, 16, 1024), idesc, 1u);
+            }
+            const long long t1 = clock64();
+            umma_commit(done);
+            mbar_wait(done, 0);
+            const long long t2 = clock64();
+            out[blockIdx.x * 2] = t1 - t0;
+            out[blockIdx.x * 2 + 1] = t2 - t0;
+        }
+    } else if (mode == 1) {
+      if (warp == 0) {
+        // the whole warp runs the loop (operands stay warp-uniform); one elected lane issues each instruction
+        const uint32_t a0 = smem_u32(smem), b0 = a0 + 128 * 128;
+        const uint32_t idesc = make_idesc(128, n, false, false);
+        const long long t0 = clock64();
+        for (int i = 0; i < iters; i += 4) {
+            const uint32_t d = tmem + ((i >> 2) & (nacc - 1)) * n;
+            if (elect_one()) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    umma_bf16(d, make_smem_desc(a0 + k * 32, 16, 1024), make_smem_desc(b0 + k * 32, 16, 1024), idesc, 1u);
+            }
+            __syncwarp();
+        }
+        const long long t1 = clock64();
+        if (elect_one()) umma_commit(done);
+        __syncwarp();
+        mbar_wait(done, 0);
+        const long long t2 = clock64();
+        if (threadIdx.x == 0) {
+            out[blockIdx.x * 2] = t1 - t0;
+            out[blockIdx.x * 2 + 1] = t2 - t0;
+        }
+      }
+    } else if (threadIdx.x == 0) {
+        // the k-block loop of the GEMM / convolution kernels, piece by piece (one thread, groups of 4 MMAs):
+        //   mode 3: + tcgen05.commit to a ring of 8 barriers after every group
+        //   mode 4: + tcgen05.fence::after_thread_sync in front of every group
+        //   mode 5: + wait (in front of every group) for the commit issued 6 groups earlier (stage reuse)
+        //   mode 6: like 5, but the wait is for the commit of the PREVIOUS group (no MMA overlap across groups)
+        uint64_t* ring = done + 2;
+        for (int r = 0; r < 8; ++r) mbar_init(&ring[r], 1);
+        fence_barrier_init();
+        const uint32_t a0 = smem_u32(smem), b0 = a0 + 128 * 128;
+        const uint32_t idesc = make_idesc(128, n, false, false);
+        const int lag = mode == 6 ? 1 : 6;
+        const long long t0 = clock64();
+        int g = 0;
+        for (int i = 0; i < iters; i += 4, ++g) {
+            if (mode >= 5 && g >= lag) mbar_wait(&ring[(g - lag) & 7], (uint32_t)(((g - lag) >> 3) & 1));
+            if (mode >= 4) tc_fence_after();
+            const uint32_t d = tmem + (g & (nacc - 1)) * n;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                umma_bf16(d, make_smem_desc(a0 + k * 32, 16, 1024), make_smem_desc(b0 + k * 32, 16, 1024), idesc, 1u);
+            umma_commit(&ring[g & 7]);
+        }
+        const long long t1 = clock64();
+        umma_commit(done);
+        mbar_wait(done, 0);
+        const long long t2 = clock64();
+        out[blockIdx.x * 2] = t1 - t0;
+        out[blockIdx.x * 2 + 1] = t2 - t0;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem, 512);
+    }
+}
 }  // namespace
+
+// out: int64 [grid][2] = {issue cycles, completion cycles} of `iters` MMAs 128 x n x 16 per CTA
+DDL_API int ddl_probe_umma_rate(long long* out, int n, int iters, int grid, int mode, int nacc, void* stream_) {
+    DDL_REQUIRE(nacc >= 1 && nacc * n <= 512, "probe rate: nacc * n must fit in 512 TMEM columns");
+    DDL_REQUIRE(out && n >= 16 && n <= 256 && n % 16 == 0 && iters >= 1 && grid >= 1, "probe rate: bad arguments");
+    const int smem = 128 * 128 + 256 * 128 + 256 + 1024;
+    static bool attr = false;
+    if (!attr) {
+        DDL_CHECK(cudaFuncSetAttribute(probe_umma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr = true;
+    }
+    probe_umma_rate_kernel<<<grid, 128, smem, (cudaStream_t)stream_>>>(out, n, iters, 4, mode, nacc);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
 
 // X: bf16 [256][64]; B: bf16 [64][64]; D: fp32 [128][64].
 // mn = 0: D[i][j] = sum_k X[shift + i][k] B[j][k];  mn = 1: D[m][n] = sum_k X[shift + k][m] B[k][n] (rows m >= 64 repeat).

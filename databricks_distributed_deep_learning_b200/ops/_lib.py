@@ -90,7 +90,10 @@ _PROTOS = {
     "ddl_conv_wgrad_scratch_bytes": ([_i] * 9, _sz),
     "ddl_conv_wgrad": ([_vp, _vp, _vp, _ll, _ll, _ll, _ll, _vp, _sz] + [_i] * 9 + [_vp], _i),
     "ddl_conv_set_tuning": ([_i, _i], _i),
+    "ddl_conv_set_debug": ([_vp, _i], _i),
+    "ddl_conv_set_im2col": ([_i], _i),
     "ddl_probe_umma_shift": ([_vp, _vp, _vp, _i, _i, _i, _vp], _i),
+    "ddl_probe_umma_rate": ([_vp, _i, _i, _i, _i, _i, _vp], _i),
     "ddl_embed_bwd_scratch_bytes": ([_i, _i], _sz),
     "ddl_embed_bwd": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i, _i, _i, _i, _i, _i, _vp], _i),
     "ddl_attention_fwd": ([_vp, _vp, _vp, _vp, _i, _i, _i, _f, _u64, _vp, _vp], _i),

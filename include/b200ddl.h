@@ -240,6 +240,12 @@ int ddl_conv_wgrad(const void* x, const void* dy, void* dw, long long sk, long l
  * >= 128 output channels: 0 = one CTA per tile, 1 = CTA pairs (cta_group::2) with halo tiles for 3x3 / stride 1 (default),
  * 2 = CTA pairs without halo tiles */
 int ddl_conv_set_tuning(int wgrad_rows, int pair_mode);
+/* activation tiles through im2col-mode TMA (1, default: dense 128-pixel tiles) or through tiled boxes (0; comparison runs) */
+int ddl_conv_set_im2col(int on);
+/* development aid: device buffer [296][8] int64 that following forward / data-gradient launches of the CTA-pair kernel fill
+ * with per-CTA wait-cycle counters (which barrier each role waits on); NULL switches it off.  ablate (timing experiments
+ * only, results are garbage): bit 0 = epilogue drops its staging and stores, bit 1 = no TMA loads are issued */
+int ddl_conv_set_debug(void* buf, int ablate);
 
 /* ---- tcgen05 / TMEM / TMA GEMM (csrc/gemm_tcgen05.cu), K8 ------------------------------ */
 /* C[M,N] = epilogue(A . B^T), bf16 operands, fp32 accumulation in tensor memory.

@@ -32,6 +32,13 @@ def test_trainer_graph_multi_gpu_ranks_stay_in_sync():
     assert out["ok"], out
 
 
+@pytest.mark.parametrize("workload", ["resnet50", "bert-base"])
+def test_trainer_20_steps_tracks_stock_ddp_nccl(workload):
+    out = Distributor(num_processes=_world(), use_gpu=True, timeout_s=1200).run(GW.w_trainer_vs_stock, workload, 20)
+    print({k: out[k] for k in ("mean_rel", "max_rel", "ranks_identical", "comm")})
+    assert out["ok"], out
+
+
 def test_fsdp_gpu_matches_ddp():
     out = Distributor(num_processes=_world(), use_gpu=True, timeout_s=900).run(GW.w_fsdp_gpu, 4)
     assert out["ok"], out
