@@ -51,7 +51,7 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--json", default=os.path.join(ROOT, "gpurun_out", "conv_bench.json"))
     ap.add_argument("--im2col", type=int, default=1)
-    ap.add_argument("--pair", type=int, default=1, help="forward / data-gradient kernel: 0 one CTA, 1 CTA pairs + halo tiles, 2 CTA pairs")
+    ap.add_argument("--pair", type=int, default=0, help="forward / data-gradient kernel: 0 one CTA, 1 CTA pairs + halo tiles, 2 CTA pairs")
     ap.add_argument("--wgrad-rows", type=int, default=0)
     args = ap.parse_args()
     from databricks_distributed_deep_learning_b200.ops import _lib as L0

@@ -22,7 +22,7 @@ def main():
     ap.add_argument("--batch", type=int, default=3)
     ap.add_argument("--only", type=int, default=-1)
     ap.add_argument("--im2col", type=int, default=1)
-    ap.add_argument("--pair", type=int, default=1, help="0 = one-CTA data kernel, 1 = CTA pairs + halo tiles, 2 = CTA pairs")
+    ap.add_argument("--pair", type=int, default=0, help="0 = one-CTA data kernel, 1 = CTA pairs + halo tiles, 2 = CTA pairs")
     args = ap.parse_args()
     from test_gpu_conv import RESNET50_CONVS, conv_case
 

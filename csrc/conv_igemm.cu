@@ -147,23 +147,23 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
                 const int hb = rem / p.tiles_w, wb = rem - hb * p.tiles_w;
                 const int n0 = ng * p.nb, oh0 = hb * p.bh, ow0 = wb * p.bw;
                 const int ntaps = p.cls_ntaps[cls];
+                int iw = 0, ih = 0, in_ = 0;  // im2col mode: base pixel of the tile's first position
+                if (p.im2col) {
+                    const int m0 = t * kTileM;  // < 2^31 (checked on the host)
+                    const int b0 = m0 % p.OWt, t2 = m0 / p.OWt;
+                    iw = b0 * p.cstride + p.low_w;
+                    ih = (t2 % p.OHt) * p.cstride + p.low_h;
+                    in_ = t2 / p.OHt;
+                }
                 for (int ti = 0; ti < ntaps; ++ti) {
                     const Tap tp = p.taps[cls][ti];
                     for (int cb = 0; cb < p.cblocks; ++cb) {
-                        if (stage % p.group == 0) mbar_wait(&empty_bar[stage / p.group], phase ^ 1);
+                        mbar_wait(&empty_bar[stage], phase ^ 1);
                         uint8_t* sa = smem + (size_t)stage * stage_bytes;
                         uint8_t* sb = sa + kStageA;
                         mbar_expect_tx(&full_bar[stage], p.a_bytes + (uint32_t)stage_b);
-                        if (p.im2col) {
-                            const long long m0 = (long long)t * kTileM;
-                            const int b0 = (int)(m0 % p.OWt);
-                            const long long t2 = m0 / p.OWt;
-                            const int a0 = (int)(t2 % p.OHt), nn = (int)(t2 / p.OHt);
-                            tma_load_im2col(sa, &maps.in[0], &full_bar[stage], cb * 64, b0 * p.cstride + p.low_w, a0 * p.cstride + p.low_h, nn,
-                                            tp.dw - p.low_w, tp.dh - p.low_h);
-                        } else {
-                            tma_load_4d(sa, &maps.in[tp.map], &full_bar[stage], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
-                        }
+                        if (p.im2col) tma_load_im2col(sa, &maps.in[0], &full_bar[stage], cb * 64, iw, ih, in_, tp.dw - p.low_w, tp.dh - p.low_h);
+                        else tma_load_4d(sa, &maps.in[tp.map], &full_bar[stage], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
                         if (!B_MN) {
                             tma_load_2d(sb, &maps.w, &full_bar[stage], tp.wtap * p.w_tap_stride + cb * 64, n_blk * p.bn);
                         } else {
@@ -177,8 +177,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        // The whole warp runs the loop so that stage addresses and descriptors stay warp-uniform (uniform registers feed
+        // UTCHMMA directly); one elected lane issues.  The descriptors of a stage differ from a per-kernel constant only in
+        // the 14-bit address field, and a k-step only adds to it: +32 B (K-major) or +2048 B (MN-major B).
+        {
             const uint32_t idesc = make_idesc(kTileM, p.bn, false, B_MN);
+            const uint64_t da_const = make_smem_desc(0, 16, 1024);
+            const uint64_t db_const = B_MN ? make_smem_desc(0, 8192, 1024) : make_smem_desc(0, 16, 1024);
+            constexpr uint32_t kStepA = 32 >> 4, kStepB = (B_MN ? 2048 : 32) >> 4;
+            const uint32_t smem_base = smem_u32(smem);
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
             for (int tile = m_group; tile < p.num_tiles; tile += m_groups) {
@@ -190,18 +197,19 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
                 for (int kb = 0; kb < nkb; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
-                    const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
-                    const uint32_t sb = sa + kStageA;
+                    const uint32_t sa = smem_base + (uint32_t)stage * (uint32_t)stage_bytes;
+                    const uint64_t da = da_const | (uint64_t)(sa >> 4), db = db_const | (uint64_t)((sa + kStageA) >> 4);
+                    if (elect_one()) {
+                        umma_bf16(d_tmem, da, db, idesc, kb > 0 ? 1u : 0u);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const uint64_t da = make_smem_desc(sa + k * 32, 16, 1024);
-                        const uint64_t db = B_MN ? make_smem_desc(sb + k * 2048, 8192, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
-                        umma_bf16(d_tmem, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                        for (int k = 1; k < 4; ++k) umma_bf16(d_tmem, da + k * kStepA, db + k * kStepB, idesc, 1u);
+                        umma_commit(&empty_bar[stage]);
                     }
-                    if (stage % p.group == p.group - 1) umma_commit(&empty_bar[stage / p.group]);
+                    __syncwarp();
                     if (++stage == p.stages) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(&tmem_full[acc]);
+                if (elect_one()) umma_commit(&tmem_full[acc]);
+                __syncwarp();
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }
@@ -234,12 +242,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
                     const int r = quarter * 32 + it * 8 + t_row;
                     off[it] = -1;
                     if (p.im2col) {
-                        const long long m = (long long)t * kTileM + r;
-                        if (m < p.cls_pix) {
-                            const int b = (int)(m % p.OWt);
-                            const long long t2 = m / p.OWt;
-                            const int a = (int)(t2 % p.OHt), nn = (int)(t2 / p.OHt);
-                            off[it] = (((long long)nn * p.OHf + a * p.os + oph) * p.OWf + b * p.os + opw) * p.Cn + col0 + t_ch * 8;
+                        const int m = t * kTileM + r;
+                        if (m < (int)p.cls_pix) {
+                            if (p.os == 1) {  // dense output: position m IS the pixel index
+                                off[it] = (long long)m * p.Cn + col0 + t_ch * 8;
+                            } else {
+                                const int b = m % p.OWt, t2 = m / p.OWt;
+                                const int a = t2 % p.OHt, nn = t2 / p.OHt;
+                                off[it] = (((long long)nn * p.OHf + a * p.os + oph) * p.OWf + b * p.os + opw) * p.Cn + col0 + t_ch * 8;
+                            }
                         }
                     } else if (r < rows_box) {
                         const int j = r / rows_img, rr = r - j * rows_img;
@@ -372,6 +383,8 @@ struct PairParams {
                          // tcgen05.commit costs ~450 cycles of tensor-pipe time (csrc/probe_umma.cu), four MMAs of a
                          // 64-deep k-block take 256 - 512, so one commit per k-block would halve the MMA rate
     uint32_t a_bytes;
+    int im2col, cstride, low_w, low_h;  // im2col mode (direct mode only), as in DataParams
+    long long cls_pix;
     long long* dbg;  // optional [gridDim.x][8] cycle counters (ddl_conv_set_debug): where each role of a CTA waits
     int ablate;      // development only: bit 0 = epilogue drops its staging / stores, bit 1 = producer issues no TMA loads
 };
@@ -385,6 +398,15 @@ __device__ __forceinline__ void mbar_wait_timed(uint64_t* bar, uint32_t parity, 
     const long long t0 = clock64();
     mbar_wait(bar, parity);
     acc += clock64() - t0;
+}
+
+__device__ __forceinline__ void tma_load_im2col_2sm(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c, int w, int h, int n, int off_w,
+                                                    int off_h) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(
+            smem_u32(smem_dst)),
+        "l"(map), "r"(smem_u32(bar) & kPeerBitMask), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)off_w), "h"((uint16_t)off_h)
+        : "memory");
 }
 
 __device__ __forceinline__ void tma_load_4d_2sm(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
@@ -455,6 +477,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_pair_kernel(const __grid_con
     auto decode = [&](int q, int& cls, int& n0, int& oh0, int& ow0) {
         cls = q / p.pair_tiles_per_cls;
         const int t = (q - cls * p.pair_tiles_per_cls) * 2 + cta_rank;
+        if (p.im2col) {  // tile t = positions [128 t, 128 t + 128) of the class grid; n0 / oh0 / ow0 = its first position
+            const int m0 = t * kTileM, t2 = m0 / p.OWt;
+            ow0 = m0 % p.OWt;
+            oh0 = t2 % p.OHt;
+            n0 = t2 / p.OHt;
+            return;
+        }
         const int ng = t / tiles_hw, rem = t - ng * tiles_hw;
         const int hb = rem / p.tiles_w, wb = rem - hb * p.tiles_w;
         n0 = ng * p.nb;
@@ -487,6 +516,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_pair_kernel(const __grid_con
                             } else {
                                 if (leader) mbar_expect_tx(&a_full[as], 2 * p.a_bytes);
                                 if (p.halo) tma_load_4d_2sm(sa, &maps.in[0], &a_full[as], cb * 64, ow0 - 1, oh0 - 1, n0);
+                                else if (p.im2col)
+                                    tma_load_im2col_2sm(sa, &maps.in[0], &a_full[as], cb * 64, ow0 * p.cstride + p.low_w, oh0 * p.cstride + p.low_h, n0,
+                                                        tp.dw - p.low_w, tp.dh - p.low_h);
                                 else tma_load_4d_2sm(sa, &maps.in[tp.map], &a_full[as], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
                             }
                             if (++as == p.a_stages) { as = 0; aph ^= 1; }
@@ -605,6 +637,19 @@ __global__ void __launch_bounds__(kThreads, 1) conv_pair_kernel(const __grid_con
                 for (int it = 0; it < 4; ++it) {
                     const int r = quarter * 32 + it * 8 + t_row;
                     off[it] = -1;
+                    if (p.im2col) {
+                        const int m = (n0 * p.OHt + oh0) * p.OWt + ow0 + r;
+                        if (m < (int)p.cls_pix) {
+                            if (p.os == 1) {
+                                off[it] = (long long)m * p.Cn + col0 + t_ch * 8;
+                            } else {
+                                const int b = m % p.OWt, t2 = m / p.OWt;
+                                const int a = t2 % p.OHt, nn = t2 / p.OHt;
+                                off[it] = (((long long)nn * p.OHf + a * p.os + oph) * p.OWf + b * p.os + opw) * p.Cn + col0 + t_ch * 8;
+                            }
+                        }
+                        continue;
+                    }
                     const int j = r / p.rows_img, rr = r - j * p.rows_img;
                     const int a = rr / p.pitch, b = rr - a * p.pitch;
                     if (j < p.nb && a < p.th && b < p.bw - p.halo && n0 + j < p.N && oh0 + a < p.OHt && ow0 + b < p.OWt)
@@ -719,6 +764,9 @@ struct WgradParams {
     int ksplit, cps;
     int slot_bytes, ksteps, stages, pix;
     long long Mtot;
+    // im2col mode: chunk = `pix` consecutive output positions (dense, spanning rows and images); x taps through the im2col
+    // map maps.in[0], dy through the flattened map maps.w; nothing needs zero-filling (TMA fills what lies past the end)
+    int im2col, cstride, low_w, low_h;
 };
 
 __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_kernel(const __grid_constant__ ConvMaps maps, const WgradParams p) {
@@ -735,7 +783,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_kernel(const __grid_
     constexpr uint32_t kTmemCols = 512;
 
     // zero every slot once: the rows behind each box (K padding up to a multiple of 16 pixels) must read as zeros
-    {
+    if (!p.im2col) {
         const int n16 = p.stages * stage_bytes / 16;
         uint4* s4 = reinterpret_cast<uint4*>(smem);
         for (int i = threadIdx.x; i < n16; i += kWgThreads) s4[i] = make_uint4(0, 0, 0, 0);
@@ -777,39 +825,57 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_kernel(const __grid_
                 mbar_wait(&empty_bar[stage], phase ^ 1);
                 uint8_t* st = smem + (size_t)stage * stage_bytes;
                 mbar_expect_tx(&full_bar[stage], tx_bytes);
-                for (int j = 0; j < dy_slots; ++j)
-                    tma_load_4d(st + j * p.slot_bytes, &maps.w, &full_bar[stage], nb_ * p.bn + j * 64, ow0, oh0, n0);
-                for (int i = 0; i < nu; ++i) {
-                    const int u = u0 + i;
-                    const int ti = u / p.cblocks, cb = u - ti * p.cblocks;
-                    const Tap tp = p.taps[ti];
-                    tma_load_4d(st + (dy_slots + i) * p.slot_bytes, &maps.in[tp.map], &full_bar[stage], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
+                if (p.im2col) {
+                    const int m0 = chunk * p.pix, t2 = m0 / p.OWt;
+                    const int iw = (m0 % p.OWt) * p.cstride + p.low_w, ih = (t2 % p.OHt) * p.cstride + p.low_h, in_ = t2 / p.OHt;
+                    for (int j = 0; j < dy_slots; ++j)
+                        tma_load_4d(st + j * p.slot_bytes, &maps.w, &full_bar[stage], nb_ * p.bn + j * 64, m0, 0, 0);
+                    for (int i = 0; i < nu; ++i) {
+                        const int u = u0 + i;
+                        const int ti = u / p.cblocks, cb = u - ti * p.cblocks;
+                        const Tap tp = p.taps[ti];
+                        tma_load_im2col(st + (dy_slots + i) * p.slot_bytes, &maps.in[0], &full_bar[stage], cb * 64, iw, ih, in_, tp.dw - p.low_w,
+                                        tp.dh - p.low_h);
+                    }
+                } else {
+                    for (int j = 0; j < dy_slots; ++j)
+                        tma_load_4d(st + j * p.slot_bytes, &maps.w, &full_bar[stage], nb_ * p.bn + j * 64, ow0, oh0, n0);
+                    for (int i = 0; i < nu; ++i) {
+                        const int u = u0 + i;
+                        const int ti = u / p.cblocks, cb = u - ti * p.cblocks;
+                        const Tap tp = p.taps[ti];
+                        tma_load_4d(st + (dy_slots + i) * p.slot_bytes, &maps.in[tp.map], &full_bar[stage], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
+                    }
                 }
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            const uint32_t idesc = make_idesc(128, p.bn, true, true);
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int chunk = c0; chunk < c1; ++chunk) {
-                mbar_wait(&full_bar[stage], phase);
-                tc_fence_after();
-                const uint32_t sdy = smem_u32(smem + (size_t)stage * stage_bytes);
+        // whole warp runs the loop (uniform addresses / descriptors), one elected lane issues; a k-step of 16 pixels is
+        // +2048 B in both MN-major operands, the second 64-wide block of either operand lies one slot further (LBO)
+        const uint32_t idesc = make_idesc(128, p.bn, true, true);
+        const uint64_t d_const = make_smem_desc(0, (uint32_t)p.slot_bytes, 1024);
+        const uint32_t smem_base = smem_u32(smem);
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int chunk = c0; chunk < c1; ++chunk) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            const uint32_t sdy = smem_base + (uint32_t)stage * (uint32_t)stage_bytes;
+            const uint64_t db0 = d_const | (uint64_t)(sdy >> 4);
+            if (elect_one()) {
                 for (int g = 0; g < npairs; ++g) {
-                    const uint32_t sx = sdy + (dy_slots + 2 * g) * p.slot_bytes;
-                    for (int k = 0; k < p.ksteps; ++k) {
-                        const uint64_t da = make_smem_desc(sx + k * 2048, p.slot_bytes, 1024);
-                        const uint64_t db = make_smem_desc(sdy + k * 2048, p.slot_bytes, 1024);
-                        umma_bf16(tmem_base + g * p.bn, da, db, idesc, (chunk > c0 || k > 0) ? 1u : 0u);
-                    }
+                    const uint64_t da0 = d_const | (uint64_t)((sdy + (uint32_t)(dy_slots + 2 * g) * (uint32_t)p.slot_bytes) >> 4);
+                    const uint32_t d_tmem = tmem_base + g * p.bn;
+                    for (int k = 0; k < p.ksteps; ++k) umma_bf16(d_tmem, da0 + k * 128, db0 + k * 128, idesc, (chunk > c0 || k > 0) ? 1u : 0u);
                 }
                 umma_commit(&empty_bar[stage]);
-                if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
-            umma_commit(done_bar);
+            __syncwarp();
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
+        if (elect_one()) umma_commit(done_bar);
+        __syncwarp();
     } else {
         // epilogue: TMEM lane = row m of the pair (lanes 0..63 first unit, 64..127 second unit) -> fp32 partial rows
         const int quarter = warp & 3;
@@ -1040,8 +1106,7 @@ int launch_data(bool b_mn, const ConvMaps& maps, DataParams& p, cudaStream_t str
     const int fixed = kEpiWarps * kStgBytes + 512 + 1024;
     p.stages = (227 * 1024 - fixed) / stage_bytes;
     if (p.stages > kMaxStages) p.stages = kMaxStages;
-    p.group = g_ring_group;
-    p.stages = p.stages / p.group * p.group;
+    p.group = 1;
     DDL_REQUIRE(p.stages >= 2, "conv: tile does not fit in shared memory");
     const int smem = fixed + p.stages * stage_bytes;
     static int attr_smem[2] = {0, 0};
@@ -1089,10 +1154,32 @@ int im2col_fwd_taps(const ConvShape& s, Tap* taps) {
     return n;
 }
 
+// Turn a filled DataParams (classes, taps in INPUT-pixel offsets, class grid N x OHt x OWt) into im2col mode over the
+// activation [aN, aH, aW, aC] read with traversal stride `cstride`, and build its tensor map.
+int use_im2col(DataParams& p, CUtensorMap* map, const void* act, int aN, int aH, int aW, int aC, int cstride, int pixels, const char* what) {
+    int low_w = 127, low_h = 127;
+    for (int c = 0; c < p.ncls; ++c)
+        for (int i = 0; i < p.cls_ntaps[c]; ++i) {
+            low_w = p.taps[c][i].dw < low_w ? p.taps[c][i].dw : low_w;
+            low_h = p.taps[c][i].dh < low_h ? p.taps[c][i].dh : low_h;
+        }
+    p.im2col = 1;
+    p.cstride = cstride;
+    p.low_w = low_w; p.low_h = low_h;
+    p.cls_pix = (long long)p.N * p.OHt * p.OWt;
+    p.tiles_per_cls = (int)((p.cls_pix + pixels - 1) / pixels);
+    p.tiles_w = p.tiles_per_cls; p.tiles_h = 1;  // (unused by the im2col decode; kept non-zero)
+    p.num_tiles = p.ncls * p.tiles_per_cls;
+    p.a_bytes = (uint32_t)pixels * 128u;
+    // the base positions must number exactly OWt x OHt per image
+    const int up_w = (p.OWt - 1) * cstride + 1 + low_w - aW, up_h = (p.OHt - 1) * cstride + 1 + low_h - aH;
+    return make_im2col_map(map, act, aN, aH, aW, aC, low_w, low_h, up_w, up_h, cstride, pixels, what);
+}
+
 // ---- pair kernel launch plan -----------------------------------------------------------------------------
 long long* g_conv_dbg = nullptr;  // ddl_conv_set_debug
 int g_conv_ablate = 0;
-int g_pair_mode = 1;  // 0 = never use the CTA-pair kernel, 1 = pair kernel (halo tiles where possible), 2 = pair kernel, no halo
+int g_pair_mode = 0;  // 0 = never use the CTA-pair kernel, 1 = pair kernel (halo tiles where possible), 2 = pair kernel, no halo
 
 bool ptr_is_local(const void* ptr) {
     cudaPointerAttributes attr;
@@ -1106,7 +1193,7 @@ bool ptr_is_local(const void* ptr) {
 }
 
 struct PairPlan {
-    bool halo;
+    bool halo, im2col;
     BoxGeo g;       // the TMA box and how it tiles the grid (halo mode: box includes the halo; g.tiles() counts output tiles)
     int th, pitch, rows_img;
     int a_slot, a_stages, b_stages, bgroup;
@@ -1114,8 +1201,9 @@ struct PairPlan {
 };
 
 // d: classes / taps / grid / bn already filled in.  halo_ok: 3x3 stride-1 geometry (all taps are shifts of one box).
-bool plan_pair(const DataParams& d, bool halo_ok, PairPlan& pl) {
+bool plan_pair(const DataParams& d, bool halo_ok, bool flat, PairPlan& pl) {
     if (g_pair_mode == 0 || d.bn % 128 != 0) return false;
+    pl.im2col = false;
     const int b_slot = (d.bn / 2) * 128;
     const int avail = 227 * 1024 - kEpiWarps * kStgBytes - 1024 - 1024;
     pl.halo = false;
@@ -1162,7 +1250,11 @@ bool plan_pair(const DataParams& d, bool halo_ok, PairPlan& pl) {
         pl.a_stages = pl.b_stages = st;
         pl.bgroup = grp;
     }
-    const int tiles_per_cls = pl.g.tiles();
+    int tiles_per_cls = pl.g.tiles();
+    if (!pl.halo && g_im2col && !flat) {
+        pl.im2col = true;  // dense 128-position tiles of the class grid
+        tiles_per_cls = (int)(((long long)d.N * d.OHt * d.OWt + kTileM - 1) / kTileM);
+    }
     pl.pair_tiles_per_cls = (tiles_per_cls + 1) / 2;
     int pgroups = (DDL_SM_COUNT / 2) / d.num_n_blocks;
     if (pgroups > pl.pair_tiles_per_cls * d.ncls) pgroups = pl.pair_tiles_per_cls * d.ncls;
@@ -1171,8 +1263,14 @@ bool plan_pair(const DataParams& d, bool halo_ok, PairPlan& pl) {
 }
 
 // act: the activation tensor the boxes read ([aN, aH, aW, aC] NHWC, map stride act_stride); w: [w_rows][w_inner] weights
-int launch_pair(bool b_mn, const DataParams& d, const PairPlan& pl, const void* act, int aN, int aH, int aW, int aC, int act_stride, bool flat,
+int launch_pair(bool b_mn, const DataParams& d0, const PairPlan& pl, const void* act, int aN, int aH, int aW, int aC, int act_stride, bool flat,
                 const void* w, long long w_rows, long long w_inner, cudaStream_t stream) {
+    DataParams d = d0;
+    ConvMaps maps;
+    if (pl.im2col) {
+        if (int e = use_im2col(d, &maps.in[0], act, aN, aH, aW, aC, act_stride, kTileM, "conv (pair, im2col)")) return e;
+        for (int i = 1; i < 4; ++i) maps.in[i] = maps.in[0];
+    }
     PairParams p = {};
     p.out = d.out; p.partials = d.partials;
     p.ncls = d.ncls;
@@ -1183,8 +1281,10 @@ int launch_pair(bool b_mn, const DataParams& d, const PairPlan& pl, const void* 
     p.N = d.N; p.OHt = d.OHt; p.OWt = d.OWt; p.OHf = d.OHf; p.OWf = d.OWf; p.os = d.os; p.Cn = d.Cn;
     p.bw = pl.g.bw; p.bh = pl.g.bh; p.nb = pl.g.nb;
     p.tiles_w = pl.g.tiles_w; p.tiles_h = pl.g.tiles_h;
-    p.tiles_per_cls = pl.g.tiles();
+    p.tiles_per_cls = pl.im2col ? d.tiles_per_cls : pl.g.tiles();
     p.pair_tiles_per_cls = pl.pair_tiles_per_cls;
+    p.im2col = pl.im2col ? 1 : 0;
+    p.cstride = d.cstride; p.low_w = d.low_w; p.low_h = d.low_h; p.cls_pix = d.cls_pix;
     p.num_pair_tiles = pl.pair_tiles_per_cls * d.ncls;
     p.th = pl.th; p.pitch = pl.pitch; p.rows_img = pl.rows_img;
     p.num_n_blocks = d.num_n_blocks; p.bn = d.bn; p.groups = d.bn / 64;
@@ -1192,11 +1292,11 @@ int launch_pair(bool b_mn, const DataParams& d, const PairPlan& pl, const void* 
     p.halo = pl.halo ? 1 : 0;
     p.a_slot_bytes = pl.a_slot; p.a_stages = pl.a_stages; p.b_stages = pl.b_stages;
     p.bgroup = pl.bgroup;
-    p.a_bytes = (uint32_t)pl.g.pix() * 128u;
+    p.a_bytes = pl.im2col ? (uint32_t)kTileM * 128u : (uint32_t)pl.g.pix() * 128u;
     p.dbg = g_conv_dbg;
     p.ablate = g_conv_ablate;
-    ConvMaps maps;
-    if (int e = make_act_maps(maps.in, act, aN, aH, aW, aC, act_stride, flat, pl.g, "conv (pair) activations")) return e;
+    if (!pl.im2col)
+        if (int e = make_act_maps(maps.in, act, aN, aH, aW, aC, act_stride, flat, pl.g, "conv (pair) activations")) return e;
     if (int e = tma_host::encode_2d(&maps.w, w, w_rows, w_inner, w_inner * 2, b_mn ? 64 : d.bn / 2, "conv (pair) weights")) return e;
     const int smem = pl.a_stages * pl.a_slot + pl.b_stages * (d.bn / 2) * 128 + kEpiWarps * kStgBytes + 1024 + 1024;
     static int attr_smem[2] = {0, 0};
@@ -1222,32 +1322,10 @@ int launch_pair(bool b_mn, const DataParams& d, const PairPlan& pl, const void* 
     return 0;
 }
 
-// Turn a filled DataParams (classes, taps in INPUT-pixel offsets, class grid N x OHt x OWt) into im2col mode over the
-// activation [aN, aH, aW, aC] read with traversal stride `cstride`, and build its tensor map.
-int use_im2col(DataParams& p, CUtensorMap* map, const void* act, int aN, int aH, int aW, int aC, int cstride, int pixels, const char* what) {
-    int low_w = 127, low_h = 127;
-    for (int c = 0; c < p.ncls; ++c)
-        for (int i = 0; i < p.cls_ntaps[c]; ++i) {
-            low_w = p.taps[c][i].dw < low_w ? p.taps[c][i].dw : low_w;
-            low_h = p.taps[c][i].dh < low_h ? p.taps[c][i].dh : low_h;
-        }
-    p.im2col = 1;
-    p.cstride = cstride;
-    p.low_w = low_w; p.low_h = low_h;
-    p.cls_pix = (long long)p.N * p.OHt * p.OWt;
-    p.tiles_per_cls = (int)((p.cls_pix + pixels - 1) / pixels);
-    p.tiles_w = p.tiles_per_cls; p.tiles_h = 1;  // (unused by the im2col decode; kept non-zero)
-    p.num_tiles = p.ncls * p.tiles_per_cls;
-    p.a_bytes = (uint32_t)pixels * 128u;
-    // the base positions must number exactly OWt x OHt per image
-    const int up_w = (p.OWt - 1) * cstride + 1 + low_w - aW, up_h = (p.OHt - 1) * cstride + 1 + low_h - aH;
-    return make_im2col_map(map, act, aN, aH, aW, aC, low_w, low_h, up_w, up_h, cstride, pixels, what);
-}
-
 // classes / taps / grid of the forward convolution (shared by the launch and the partial-row query)
 void fill_fwd(DataParams& p, const ConvShape& s, const BoxGeo& g) {
     p.ncls = 1;
-    p.cls_ntaps[0] = forward_taps(s, p.taps[0]);
+    p.cls_ntaps[0] = (g_im2col && !s.flat) ? im2col_fwd_taps(s, p.taps[0]) : forward_taps(s, p.taps[0]);
     fill_geo(p, g);
     p.OHf = g.GH; p.OWf = g.GW; p.os = 1;
     p.Cn = s.Cout;
@@ -1264,12 +1342,13 @@ int fwd_partial_rows(const ConvShape& s) {
     DataParams p = {};
     fill_fwd(p, s, g);
     PairPlan pl;
-    if (plan_pair(p, s.R == 3 && s.stride == 1, pl)) return 2 * pl.pgroups;
+    if (plan_pair(p, s.R == 3 && s.stride == 1, s.flat, pl)) return 2 * pl.pgroups;
     return fwd_m_groups(s);
 }
 
 // weight-gradient launch plan (shared by the scratch-size query and the launch)
 struct WgradPlan {
+    bool im2col;
     BoxGeo g;
     int bn, nblk, U, G, mgroups, ksteps, slot_bytes, stages, ksplit, cps;
 };
@@ -1278,31 +1357,34 @@ bool plan_wgrad(const ConvShape& s, WgradPlan& w) {
     w.bn = s.Cout <= 256 ? s.Cout : 256;
     w.nblk = s.Cout / w.bn;
     w.U = s.R * s.S * (s.C / 64);
-    int G = 512 / w.bn;
-    if (G > (w.U + 1) / 2) G = (w.U + 1) / 2;
+    int Gmax = 512 / w.bn;
+    if (Gmax > (w.U + 1) / 2) Gmax = (w.U + 1) / 2;
     const int avail = 227 * 1024 - 1024 - 512;
-    for (;; --G) {
-        if (G < 1) return false;
-        const int nslots = w.bn / 64 + 2 * G;
-        int rows_opts[2] = {128, 64};
-        bool found = false;
-        for (int o = 0; o < 2 && !found; ++o) {
-            const int rows = g_wgrad_rows ? g_wgrad_rows : rows_opts[o];
-            const BoxGeo g = s.flat ? choose_box(1, 1, s.N * s.OH * s.OW, rows) : choose_box(s.N, s.OH, s.OW, rows);
-            const int ksteps = (g.pix() + 15) / 16;
-            const int slot = ksteps * 2048;
-            int stages = avail / (nslots * slot);
+    // 128-pixel chunks first (with as many accumulator pairs as still leave two stages), 64-pixel chunks only when even one
+    // pair does not fit: the cost per chunk (barrier round trip, commit) outweighs both a shallower prefetch and fewer
+    // accumulators per CTA (measured, benchmarks/conv_bench.py --wgrad-rows)
+    int G = 0;
+    const int rows_opts[2] = {128, 64};
+    for (int o = 0; o < 2 && G == 0; ++o) {
+        const int rows = g_wgrad_rows ? g_wgrad_rows : rows_opts[o];
+        // im2col mode chunks the flattened output positions exactly like a 1x1 layer does
+        const BoxGeo g = (s.flat || g_im2col) ? choose_box(1, 1, s.N * s.OH * s.OW, rows) : choose_box(s.N, s.OH, s.OW, rows);
+        const int ksteps = (g.pix() + 15) / 16;
+        const int slot = ksteps * 2048;
+        for (int gg = Gmax; gg >= 1; --gg) {
+            int stages = avail / ((w.bn / 64 + 2 * gg) * slot);
             if (stages > 4) stages = 4;
-            const bool last = (o == 1) || g_wgrad_rows != 0;
-            if (stages >= 3 || (last && stages >= 2)) {
+            if (stages >= 2) {
+                G = gg;
                 w.g = g; w.ksteps = ksteps; w.slot_bytes = slot; w.stages = stages;
-                found = true;
+                break;
             }
-            if (g_wgrad_rows) break;
         }
-        if (found) break;
+        if (g_wgrad_rows) break;
     }
+    if (G == 0) return false;
     w.G = G;
+    w.im2col = g_im2col && !s.flat;
     w.mgroups = (w.U + 2 * G - 1) / (2 * G);
     const int items = w.nblk * w.mgroups;
     const int chunks = w.g.tiles();
@@ -1359,12 +1441,11 @@ DDL_API int ddl_conv_fwd(const void* x, const void* w, void* y, float* partials,
     fill_fwd(p, s, g);
     cudaStream_t stream = (cudaStream_t)stream_;
     PairPlan pl;
-    const bool pair_shape = plan_pair(p, R == 3 && stride == 1, pl);
+    const bool pair_shape = plan_pair(p, R == 3 && stride == 1, s.flat, pl);
     if (pair_shape && ptr_is_local(x) && ptr_is_local(w))
         return launch_pair(false, p, pl, x, N, H, W, C, stride, s.flat, w, Cout, (long long)R * S * C, stream);
     ConvMaps maps;
     if (g_im2col && !s.flat) {
-        p.cls_ntaps[0] = im2col_fwd_taps(s, p.taps[0]);
         if (int e = use_im2col(p, &maps.in[0], x, N, H, W, C, stride, kTileM, "conv fwd (im2col)")) return e;
         for (int i = 1; i < 4; ++i) maps.in[i] = maps.in[0];
     } else {
@@ -1444,7 +1525,7 @@ DDL_API int ddl_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H
     }
     p.num_tiles = p.ncls * p.tiles_per_cls;
     PairPlan pl;
-    if (plan_pair(p, R == 3 && stride == 1, pl) && ptr_is_local(dy) && ptr_is_local(w))
+    if (plan_pair(p, R == 3 && stride == 1, s.flat, pl) && ptr_is_local(dy) && ptr_is_local(w))
         return launch_pair(true, p, pl, dy, N, s.OH, s.OW, Cout, 1, s.flat, w, Cout, (long long)R * S * C, stream);
     ConvMaps maps;
     if (g_im2col && !s.flat) {
@@ -1475,7 +1556,7 @@ DDL_API int ddl_conv_wgrad(const void* x, const void* dy, void* dw, long long sk
     DDL_REQUIRE(scratch_bytes >= ddl_conv_wgrad_scratch_bytes(N, H, W, C, Cout, R, S, stride, pad), "conv wgrad: scratch too small");
     WgradParams p = {};
     p.partials = (float*)scratch;
-    p.ntaps = forward_taps(s, p.taps);
+    p.ntaps = w.im2col ? im2col_fwd_taps(s, p.taps) : forward_taps(s, p.taps);
     p.N = w.g.N; p.OHt = w.g.GH; p.OWt = w.g.GW;
     p.bw = w.g.bw; p.bh = w.g.bh; p.nb = w.g.nb;
     p.tiles_w = w.g.tiles_w; p.tiles_h = w.g.tiles_h;
@@ -1486,10 +1567,19 @@ DDL_API int ddl_conv_wgrad(const void* x, const void* dy, void* dw, long long sk
     p.slot_bytes = w.slot_bytes; p.ksteps = w.ksteps; p.stages = w.stages; p.pix = w.g.pix();
     p.Mtot = (long long)w.U * 64;
     ConvMaps maps;
-    if (int e = make_act_maps(maps.in, x, N, H, W, C, stride, s.flat, w.g, "conv wgrad x")) return e;
+    if (w.im2col) {
+        p.im2col = 1;
+        p.cstride = stride; p.low_w = -pad; p.low_h = -pad;
+        p.OHt = s.OH; p.OWt = s.OW;
+        const int up_w = (s.OW - 1) * stride + 1 - pad - W, up_h = (s.OH - 1) * stride + 1 - pad - H;
+        if (int e = make_im2col_map(&maps.in[0], x, N, H, W, C, -pad, -pad, up_w, up_h, stride, w.g.pix(), "conv wgrad x (im2col)")) return e;
+        for (int i = 1; i < 4; ++i) maps.in[i] = maps.in[0];
+    } else {
+        if (int e = make_act_maps(maps.in, x, N, H, W, C, stride, s.flat, w.g, "conv wgrad x")) return e;
+    }
     {
         CUtensorMap tmp[4];
-        if (int e = make_act_maps(tmp, dy, N, s.OH, s.OW, Cout, 1, s.flat, w.g, "conv wgrad dy")) return e;
+        if (int e = make_act_maps(tmp, dy, N, s.OH, s.OW, Cout, 1, s.flat || w.im2col, w.g, "conv wgrad dy")) return e;
         maps.w = tmp[0];
     }
     const int smem = p.stages * (p.bn / 64 + 2 * p.G) * p.slot_bytes + 512 + 1024;
