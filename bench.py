@@ -419,7 +419,7 @@ class StockRunner:
         if self.want_graph and self.world > 1:
             raise RuntimeError("stock-graphed is a one-GPU arm")
         self.opt = torch.optim.AdamW(self.model.parameters(), lr=wl.optim.lr, weight_decay=wl.optim.weight_decay,
-                                     **({"capturable": True} if self.want_graph else {"fused": True}))
+                                     **({"fused": True, "capturable": True} if self.want_graph else {"fused": True}))
         self.graphed = self.want_graph
         self.graph = None
         self.static = None

@@ -35,8 +35,8 @@ def main():
     torch.backends.cudnn.benchmark = True
     wl = get_workload(args.workload)
     batch = args.batch or wl.per_gpu_batch
-    ns = argparse.Namespace(workload=args.workload, dropout=args.dropout, no_graph=True, comm="auto", bucket_mb=25.0)
-    runner = bench.OursRunner(ns, wl, dev) if args.impl == "ours" else bench.StockRunner(ns, wl, dev)
+    ns = argparse.Namespace(workload=args.workload, dropout=args.dropout, no_graph=True, comm="auto", bucket_mb=25.0, reshard=False)
+    runner = bench.OursRunner(ns, wl, args.workload, dev) if args.impl == "ours" else bench.StockRunner(ns, wl, args.workload, dev)
     loader = bench.build_batches(args.workload, batch, 0, 1, pool=1)
     b = bench.to_device(next(iter(loader)), dev)
     for _ in range(4):

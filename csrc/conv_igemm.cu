@@ -782,8 +782,9 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_kernel(const __grid_
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     constexpr uint32_t kTmemCols = 512;
 
-    // zero every slot once: the rows behind each box (K padding up to a multiple of 16 pixels) must read as zeros
-    if (!p.im2col) {
+    // zero every slot once when a chunk is not a whole number of 16-pixel k-steps: the rows behind each box (K padding)
+    // must read as zeros
+    if (p.pix * 128 != p.slot_bytes) {
         const int n16 = p.stages * stage_bytes / 16;
         uint4* s4 = reinterpret_cast<uint4*>(smem);
         for (int i = threadIdx.x; i < n16; i += kWgThreads) s4[i] = make_uint4(0, 0, 0, 0);

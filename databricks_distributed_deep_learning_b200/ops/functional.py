@@ -667,9 +667,7 @@ class _ConvNative(torch.autograd.Function):
             else:
                 L.call("ddl_conv_dgrad", dy.data_ptr(), _weight_krsc(weight).data_ptr(), dx.data_ptr(), *geom, st)
         if ctx.needs_input_grad[1]:
-            dw = torch.empty_like(weight)
-            if not dw.is_non_overlapping_and_dense():
-                dw = torch.empty(weight.shape, dtype=weight.dtype, device=dev, memory_format=torch.channels_last)
+            dw = torch.empty_like(weight)  # same (dense) layout as the parameter: the copy into the gradient bucket is flat
             scratch = _scratch(L.lib().ddl_conv_wgrad_scratch_bytes(*geom), dev)
             sk, sc, sr, ss = dw.stride()
             L.call("ddl_conv_wgrad", x.data_ptr(), dy.data_ptr(), dw.data_ptr(), sk, sc, sr, ss, scratch.data_ptr(), scratch.numel(), *geom, st)
