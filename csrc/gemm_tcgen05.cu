@@ -477,8 +477,15 @@ __global__ void __launch_bounds__(kThreads, 1) gemm2sm_bf16_kernel(const __grid_
             }
         }
     } else if (warp == 1) {
-        if (lane == 0 && leader) {
+        // The whole warp runs the loop (stage addresses and descriptors stay warp-uniform: they are computed in uniform
+        // registers and feed UTCHMMA without an ELECT / R2UR round trip per instruction); one elected lane issues.  A stage's
+        // descriptors are a constant plus the 14-bit address field, a k-step adds 32 B (K-major) or 2048 B (MN-major).
+        if (leader) {
             constexpr uint32_t idesc = make_idesc(2 * BM, BN, A_MN, B_MN);
+            const uint64_t da_const = A_MN ? make_smem_desc(0, BK * 128, 1024) : make_smem_desc(0, 16, 1024);
+            const uint64_t db_const = B_MN ? make_smem_desc(0, BK * 128, 1024) : make_smem_desc(0, 16, 1024);
+            constexpr uint32_t kStepA = (A_MN ? 2048 : 32) >> 4, kStepB = (B_MN ? 2048 : 32) >> 4;
+            const uint32_t smem_base = smem_u32(smem);
             int stage = 0;
             uint32_t phase = 0;
             int acc_stage = 0;
@@ -493,18 +500,19 @@ __global__ void __launch_bounds__(kThreads, 1) gemm2sm_bf16_kernel(const __grid_
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
-                    const uint32_t sa = smem_u32(smem + stage * kStageBytes);
-                    const uint32_t sb = sa + kABytes;
+                    const uint32_t sa = smem_base + (uint32_t)stage * (uint32_t)kStageBytes;
+                    const uint64_t da = da_const | (uint64_t)(sa >> 4), db = db_const | (uint64_t)((sa + kABytes) >> 4);
+                    if (elect_one()) {
+                        umma_bf16_2sm(d_tmem, da, db, idesc, kb > kb0 ? 1u : 0u);
 #pragma unroll
-                    for (int k = 0; k < BK / UMMA_K; ++k) {
-                        const uint64_t da = A_MN ? make_smem_desc(sa + k * 2048, BK * 128, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
-                        const uint64_t db = B_MN ? make_smem_desc(sb + k * 2048, BK * 128, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
-                        umma_bf16_2sm(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        for (int k = 1; k < BK / UMMA_K; ++k) umma_bf16_2sm(d_tmem, da + k * kStepA, db + k * kStepB, idesc, 1u);
+                        umma_commit_2sm(&empty_bar[stage]);
                     }
-                    umma_commit_2sm(&empty_bar[stage]);
+                    __syncwarp();
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
-                umma_commit_2sm(&tmem_full[acc_stage]);
+                if (elect_one()) umma_commit_2sm(&tmem_full[acc_stage]);
+                __syncwarp();
                 if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
             }
         }
@@ -746,6 +754,18 @@ __global__ void f32_to_bf16_kernel(float* __restrict__ in, bf16* __restrict__ ou
             for (int j = 0; j < 8; ++j) f[j] += g[j];
         }
         st_global_v4(out + i * 8, float_to_bf16x8(f));
+    }
+}
+
+// out = dy * gelu'(pre), 8 elements per thread (the stand-alone form of the DDL_EPI_DGELU epilogue)
+__global__ void dgelu_mul_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ pre, bf16* __restrict__ out, size_t n8) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+        float g[8], p[8];
+        bf16x8_to_float(ld_stream_v4(dy + i * 8), g);
+        bf16x8_to_float(ld_stream_v4(pre + i * 8), p);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] *= dgelu_f(p[j]);
+        st_global_v4(out + i * 8, float_to_bf16x8(g));
     }
 }
 
@@ -1044,6 +1064,16 @@ DDL_API int ddl_f32_to_bf16(const float* in, void* out, size_t numel, int flags,
     int blocks = ddl_ceil_div((long long)(numel / 8), 256);
     if (blocks > DDL_SM_COUNT * 8) blocks = DDL_SM_COUNT * 8;
     f32_to_bf16_kernel<<<blocks, 256, 0, (cudaStream_t)stream_>>>(const_cast<float*>(in), (bf16*)out, numel / 8, flags);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+DDL_API int ddl_dgelu_mul(const void* dy, const void* pre, void* out, size_t numel, void* stream_) {
+    DDL_REQUIRE(numel % 8 == 0, "ddl_dgelu_mul: numel must be a multiple of 8");
+    if (numel == 0) return 0;
+    int blocks = ddl_ceil_div((long long)(numel / 8), 256);
+    if (blocks > DDL_SM_COUNT * 8) blocks = DDL_SM_COUNT * 8;
+    dgelu_mul_kernel<<<blocks, 256, 0, (cudaStream_t)stream_>>>((const bf16*)dy, (const bf16*)pre, (bf16*)out, numel / 8);
     DDL_LAUNCH_CHECK();
     return 0;
 }

@@ -110,6 +110,7 @@ _PROTOS = {
     "ddl_allgather_gemm_bf16": ([C.POINTER(CommT), C.POINTER(_vp), _vp, _vp, _vp, _ll, _vp, _ll, _i, _i, _i, _vp, _vp, _vp, _i, _vp], _i),
     "ddl_gemm_set_cluster": ([_i], _i),
     "ddl_f32_to_bf16": ([_vp, _vp, _sz, _i, _vp], _i),
+    "ddl_dgelu_mul": ([_vp, _vp, _vp, _sz, _vp], _i),
     "ddl_colsum_scratch_bytes": ([_i, _i], _sz),
     "ddl_colsum_bf16": ([_vp, _i, _i, _ll, _vp, _vp, _sz, _vp], _i),
 }

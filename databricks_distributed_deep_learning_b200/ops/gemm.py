@@ -126,6 +126,13 @@ def colsum(x: torch.Tensor) -> torch.Tensor:
 # flat gradient bucket), registered by the DDP / FSDP wrappers.  The weight-gradient GEMM then writes there directly,
 # autograd adopts that view as .grad, and the wrapper's gradient collection has nothing left to copy for this parameter.
 _grad_dest = {}
+# destinations already handed out during the current backward pass: a weight used by two linear nodes (tied weights) must
+# not have both weight-gradient GEMMs write the same view (autograd would then sum two aliases of one buffer)
+_handed_out = set()
+
+
+def _clear_handed_out() -> None:
+    _handed_out.clear()
 
 
 def register_grad_destination(weight: torch.Tensor, view: torch.Tensor) -> None:
@@ -141,8 +148,14 @@ def _grad_destination(weight: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
     ent = _grad_dest.get(id(weight))
     if ent is None or ent[0]() is not weight:
         return None
-    # only when nothing has been accumulated yet (first backward after zero_grad(set_to_none=True))
-    return ent[1] if weight.grad is None else None
+    # only when nothing has been accumulated yet (first backward after zero_grad(set_to_none=True)) and only ONCE per
+    # backward pass: a second use of the same weight gets a fresh tensor and autograd sums the two
+    if weight.grad is not None or id(weight) in _handed_out:
+        return None
+    if not _handed_out:
+        torch.autograd.Variable._execution_engine.queue_callback(_clear_handed_out)
+    _handed_out.add(id(weight))
+    return ent[1]
 
 
 def _wgrad(dy: torch.Tensor, x: torch.Tensor, weight: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -235,9 +248,11 @@ class _Linear(torch.autograd.Function):
 
 
 def _dgelu_mul(dy: torch.Tensor, pre: torch.Tensor) -> torch.Tensor:
-    p = pre.float()
-    cdf = 0.5 * (1 + torch.erf(p * 0.70710678))
-    return (dy.float() * (cdf + p * torch.exp(-0.5 * p * p) * 0.39894228)).to(dy.dtype)
+    """``dy * gelu'(pre)`` in one native pass (the fused-into-the-GEMM form lives in :func:`ffn`)."""
+    dy, pre = dy.contiguous(), pre.contiguous()
+    out = torch.empty_like(dy)
+    L.call("ddl_dgelu_mul", dy.data_ptr(), pre.data_ptr(), out.data_ptr(), dy.numel(), L.stream_ptr(dy.device))
+    return out
 
 
 def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, activation: Optional[str] = None,

@@ -280,6 +280,8 @@ int ddl_gemm_set_cluster(int cluster);
 /* flags: bit 0 = add to the existing bf16 output, bit 1 = write zeros back to `in` after reading it (a cached split-K
  * accumulator is then ready for the next GEMM without a memset) */
 int ddl_f32_to_bf16(const float* in, void* out, size_t numel, int flags, void* stream);
+/* out = dy * GELU'(pre) elementwise on bf16 (numel a multiple of 8): the stand-alone form of the DDL_EPI_DGELU epilogue */
+int ddl_dgelu_mul(const void* dy, const void* pre, void* out, size_t numel, void* stream);
 size_t ddl_colsum_scratch_bytes(int rows, int cols);
 /* out[c] = sum_r x[r,c] (bias gradients), deterministic two-stage fold */
 int ddl_colsum_bf16(const void* x, int rows, int cols, long long ld, void* out, void* scratch, size_t scratch_bytes, void* stream);

@@ -198,7 +198,7 @@ def w_fsdp_gpu(steps):
     for mode, kw in (("ddp", {}), ("fsdp", {}), ("fsdp_reshard", {"reshard_after_forward": True})):
         torch.manual_seed(3)
         model = bert_tiny(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0)
-        tr = Trainer(model, lr=1e-3, device=dev, use_graph=(mode != "fsdp_reshard"), parallelism=mode.split("_")[0], bucket_cap_mb=1.0, **kw)
+        tr = Trainer(model, lr=1e-3, device=dev, use_graph=True, parallelism=mode.split("_")[0], bucket_cap_mb=1.0, **kw)
         loader = SyntheticTokenLoader(8, seq_len=128, vocab_size=512, rank=rank, world_size=world, seed=4, steps=steps, pool=steps)
         out = tr.fit(loader)
         sd = tr.ddp.full_state_dict() if mode.startswith("fsdp") else {k: v.detach().cpu() for k, v in tr.model.state_dict().items()}

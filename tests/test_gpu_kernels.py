@@ -885,3 +885,22 @@ def test_b200_inference_runner_matches_eager_fp32():
     scale = np.abs(want).max()
     assert np.abs(got - want).max() < 0.08 * scale, (np.abs(got - want).max(), scale)
     assert np.corrcoef(got.ravel(), want.ravel())[0, 1] > 0.99
+
+
+def test_linear_tied_weight_gradients_are_summed_not_aliased():
+    """A weight used by two linear nodes in one backward pass (tied weights) with a registered bucket destination: the
+    second weight-gradient GEMM must not write the view the first one already handed to autograd."""
+    from databricks_distributed_deep_learning_b200.ops import gemm as G
+
+    torch.manual_seed(0)
+    w = (torch.randn(256, 128, device="cuda") * 0.05).to(torch.bfloat16).requires_grad_()
+    x1 = torch.randn(64, 128, device="cuda").to(torch.bfloat16)
+    x2 = torch.randn(64, 128, device="cuda").to(torch.bfloat16)
+    slot = torch.zeros(256, 128, dtype=torch.bfloat16, device="cuda")
+    G.register_grad_destination(w, slot)
+    try:
+        (G.linear(x1, w).float().sum() + 2.0 * G.linear(x2, w).float().sum()).backward()
+    finally:
+        G._grad_dest.pop(id(w), None)
+    ref = torch.ones(64, 256, device="cuda").t() @ x1.float() + 2.0 * torch.ones(64, 256, device="cuda").t() @ x2.float()
+    assert torch.allclose(w.grad.float(), ref, rtol=2e-2, atol=2e-1), (w.grad.float() - ref).abs().max().item()
