@@ -311,6 +311,82 @@ __global__ void __launch_bounds__(kThreads) allreduce_nvls_kernel(Ctx c, char* m
     epoch_end(c, epoch);
 }
 
+// ---- hybrid all-reduce: switch reduction and peer loads / stores in one launch -----------------
+// The NVLS kernel alone moves S bytes per direction per GPU but keeps the links only about half busy (the multimem
+// reduce / broadcast rate of the switch is the limit: 16 MB take ~39 us of data phase at 8 GPUs); the two-shot kernel
+// moves 1.75 S per direction through plain loads and stores.  Running both on disjoint parts of ONE message at the same
+// time fills the links: CTAs [0, nb_a) reduce granules [0, n_a) through the multicast address, CTAs [nb_a, gridDim)
+// two-shot granules [n_a, n_a + n_b).  Every CTA does its own pairwise flag barriers (as in the other kernels), so the two
+// parts need no synchronisation with each other.  bf16 in place; every replica gets bit-identical results (each granule is
+// reduced once - by the switch or by its owner rank - and broadcast).
+template <int W, int UNR_A, int UNR_B>
+__global__ void __launch_bounds__(kThreads) allreduce_hybrid_kernel(Ctx c, char* mc_in, char* mc_out, PeerPtrs in, PeerPtrs out, size_t n_a,
+                                                                    size_t n_b, int nb_a, float scale) {
+    uint32_t epoch = epoch_begin(c);
+    block_barrier(c, epoch, false);
+    if ((int)blockIdx.x < nb_a) {
+        const size_t slice = n_a / W, base = slice * c.rank;
+        const size_t stride = (size_t)nb_a * blockDim.x;
+        for (size_t g0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g0 < slice; g0 += stride * UNR_A) {
+            uint4 v[UNR_A];
+#pragma unroll
+            for (int k = 0; k < UNR_A; ++k) {
+                const size_t g = g0 + k * stride;
+                if (g < slice) v[k] = multimem_ld_reduce_bf16x8(mc_in + (base + g) * 16);
+            }
+#pragma unroll
+            for (int k = 0; k < UNR_A; ++k) {
+                const size_t g = g0 + k * stride;
+                if (g < slice) {
+                    float f[8];
+                    bf16x8_to_float(v[k], f);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) f[j] *= scale;
+                    multimem_st_bf16x8(mc_out + (base + g) * 16, float_to_bf16x8(f));
+                }
+            }
+        }
+    } else {
+        const int vb = blockIdx.x - nb_a, vn = gridDim.x - nb_a;
+        const size_t slice = n_b / W, base = n_a + slice * c.rank;
+        const size_t stride = (size_t)vn * blockDim.x;
+        for (size_t g0 = (size_t)vb * blockDim.x + threadIdx.x; g0 < slice; g0 += stride * UNR_B) {
+            uint4 raw[UNR_B][W][1];
+#pragma unroll
+            for (int k = 0; k < UNR_B; ++k) {
+                const size_t g = g0 + k * stride;
+                if (g < slice) {
+#pragma unroll
+                    for (int r = 0; r < W; ++r) {
+                        int peer = c.rank + r;
+                        if (peer >= W) peer -= W;
+                        g8_load_raw<bf16>(in.p[peer], base + g, raw[k][r]);
+                    }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < UNR_B; ++k) {
+                const size_t g = g0 + k * stride;
+                if (g < slice) {
+                    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int r = 0; r < W; ++r) g8_accumulate<bf16>(raw[k][r], acc);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[j] *= scale;
+#pragma unroll
+                    for (int r = 0; r < W; ++r) {
+                        int peer = c.rank + r;
+                        if (peer >= W) peer -= W;
+                        G8<bf16>::store(out.p[peer], base + g, acc);
+                    }
+                }
+            }
+        }
+    }
+    block_barrier(c, epoch, true);
+    epoch_end(c, epoch);
+}
+
 // ---- all-gather / reduce-scatter / broadcast ------------------------------------------
 // all-gather: out[r * shard + i] = peer r's shard[i]   (pull; 16-byte vectors)
 __global__ void __launch_bounds__(kThreads) allgather_kernel(Ctx c, PeerPtrs shard, char* out, size_t shard16) {
@@ -571,6 +647,34 @@ DDL_API int ddl_allreduce(const ddl_comm_t* comm, void* const* in_ptrs, void* co
     } else {
         DDL_REQUIRE(false, "unknown all-reduce algorithm %d", algo);
     }
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+// bf16, in place (in == out buffers).  nvls_permille of the message goes through the switch with nvls_blocks CTAs, the
+// rest through two-shot peer loads / stores with p2p_blocks CTAs.  World size 2, 4 or 8.
+DDL_API int ddl_allreduce_hybrid(const ddl_comm_t* comm, void* const* buf_ptrs, size_t numel, float scale, void* mc_buf, int nvls_permille,
+                                 int nvls_blocks, int p2p_blocks, void* stream_) {
+    Ctx c;
+    if (int e = make_ctx(comm, &c)) return e;
+    DDL_REQUIRE(mc_buf != nullptr, "hybrid all-reduce needs the multicast address of the buffer");
+    DDL_REQUIRE(c.world == 2 || c.world == 4 || c.world == 8, "hybrid all-reduce: world size must be 2, 4 or 8");
+    DDL_REQUIRE(numel % (8 * (size_t)c.world) == 0, "hybrid all-reduce: numel %zu must be a multiple of 8*world", numel);
+    DDL_REQUIRE(nvls_permille >= 0 && nvls_permille <= 1000 && nvls_blocks >= 1 && p2p_blocks >= 1, "hybrid all-reduce: bad split");
+    DDL_REQUIRE(nvls_blocks + p2p_blocks <= DDL_COMM_MAX_BLOCKS, "hybrid all-reduce: too many blocks");
+    PeerPtrs io;
+    if (int e = fill_ptrs(&io, buf_ptrs, c.world, "buf")) return e;
+    const size_t n8 = numel / 8, unit = (size_t)c.world;
+    size_t n_a = (size_t)((double)n8 * nvls_permille / 1000.0) / unit * unit;
+    if (n_a > n8) n_a = n8;
+    const size_t n_b = n8 - n_a;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int nb = nvls_blocks + p2p_blocks;
+#define HYB(W_, UB_) allreduce_hybrid_kernel<W_, 8, UB_><<<nb, kThreads, 0, stream>>>(c, (char*)mc_buf, (char*)mc_buf, io, io, n_a, n_b, nvls_blocks, scale)
+    if (c.world == 2) HYB(2, 8);
+    else if (c.world == 4) HYB(4, 4);
+    else HYB(8, 2);
+#undef HYB
     DDL_LAUNCH_CHECK();
     return 0;
 }

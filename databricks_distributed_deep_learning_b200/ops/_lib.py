@@ -49,6 +49,7 @@ _PROTOS = {
     "ddl_comm_epoch_bytes": ([], _sz),
     "ddl_allreduce_oneshot_max_bytes": ([_i, _i], _sz),
     "ddl_allreduce": ([C.POINTER(CommT), C.POINTER(_vp), C.POINTER(_vp), _sz, _i, _i, _f, _i, _vp, _vp, _i, _vp], _i),
+    "ddl_allreduce_hybrid": ([C.POINTER(CommT), C.POINTER(_vp), _sz, _f, _vp, _i, _i, _i, _vp], _i),
     "ddl_allgather": ([C.POINTER(CommT), C.POINTER(_vp), _vp, _sz, _i, _vp], _i),
     "ddl_reducescatter": ([C.POINTER(CommT), C.POINTER(_vp), _vp, _sz, _i, _i, _f, _i, _vp], _i),
     "ddl_reducescatter_adamw": ([C.POINTER(CommT), C.POINTER(_vp), _sz, _i, _f, _vp, _vp, _vp, _vp, _vp, _i, _vp], _i),

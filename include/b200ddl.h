@@ -58,6 +58,12 @@ size_t ddl_allreduce_oneshot_max_bytes(int dtype, int num_blocks);
  * BASELINE.json:5; the reference has no collective. */
 int ddl_allreduce(const ddl_comm_t* comm, void* const* in_ptrs, void* const* out_ptrs, size_t numel, int in_dtype, int out_dtype,
                   float scale, int algo, void* mc_in, void* mc_out, int num_blocks, void* stream);
+/* Hybrid all-reduce (bf16, in place): nvls_permille / 1000 of the message is reduced by the switch (multimem, nvls_blocks
+ * CTAs), the rest by two-shot peer loads / stores (p2p_blocks CTAs), in ONE kernel - the two paths use different link
+ * resources and overlap.  buf_ptrs[r] = the buffer in rank r's heap, mc_buf its multicast address.  BASELINE.json:5
+ * (">= 80 % of the NVLink roofline for buckets >= 16 MB"); no counterpart in the reference. */
+int ddl_allreduce_hybrid(const ddl_comm_t* comm, void* const* buf_ptrs, size_t numel, float scale, void* mc_buf, int nvls_permille,
+                         int nvls_blocks, int p2p_blocks, void* stream);
 int ddl_allgather(const ddl_comm_t* comm, void* const* shard_ptrs, void* out_full, size_t shard_bytes, int num_blocks, void* stream);
 int ddl_reducescatter(const ddl_comm_t* comm, void* const* full_ptrs, void* out_shard, size_t shard_numel, int in_dtype,
                       int out_dtype, float scale, int num_blocks, void* stream);
