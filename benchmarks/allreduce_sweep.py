@@ -88,6 +88,15 @@ def main():
             if nvls:
                 cands.append(("nvls", blocks))
         res = {}
+        if nvls and dtype == torch.bfloat16 and nbytes >= (2 << 20) and world in (2, 4, 8):
+            # hybrid: part of the message through the switch, the rest over peer loads / stores, one kernel
+            for permille in (500, 600, 700, 800):
+                for nvb, p2b in ((8, 32), (8, 64), (16, 48)):
+                    key = f"hybrid{permille}/{nvb}+{p2b}"
+                    try:
+                        res[key] = {"ms": timeit(lambda: comm.all_reduce_hybrid_(view, permille, nvb, p2b), nbytes)}
+                    except Exception as ex:
+                        res[key] = {"error": str(ex)[:200]}
         for algo, blocks in cands:
             if algo == "oneshot" and nbytes > comm_oneshot_max(dtype, blocks):
                 continue
@@ -112,7 +121,7 @@ def main():
         row["speedup_vs_nccl"] = ms_nccl / res[best_key]["ms"]
         rows.append(row)
         if rank == 0:
-            print(f"{nbytes:>12d} B  best {best_key:<12s} {row['best_ms']*1e3:9.1f} us  busbw {row['best_busbw_gbs']:7.1f} GB/s "
+            print(f"{nbytes:>12d} B  best {best_key:<18s} {row['best_ms']*1e3:9.1f} us  busbw {row['best_busbw_gbs']:7.1f} GB/s "
                   f"({row['frac_of_900']*100:5.1f}% of 900) | nccl {ms_nccl*1e3:9.1f} us busbw {row['nccl_busbw_gbs']:7.1f} GB/s "
                   f"| x{row['speedup_vs_nccl']:.2f}", flush=True)
         size *= 2
@@ -134,7 +143,11 @@ def main():
             table = []
             for r in rows:
                 algo, blocks = r["best"].split("/")
-                table.append({"max_bytes": r["bytes"], "algo": algo, "blocks": int(blocks)})
+                if algo.startswith("hybrid"):
+                    nvb, p2b = blocks.split("+")
+                    table.append({"max_bytes": r["bytes"], "algo": "hybrid", "permille": int(algo[6:]), "blocks": int(nvb), "p2p_blocks": int(p2b)})
+                else:
+                    table.append({"max_bytes": r["bytes"], "algo": algo, "blocks": int(blocks)})
             table[-1]["max_bytes"] = 1 << 62
             tpath = os.path.join(ROOT, "gpurun_out", f"allreduce_table_w{world}.json")
             with open(tpath, "w") as fh:

@@ -104,6 +104,10 @@ class Trainer:
         self.ddp.zero_grad(set_to_none=True)
         loss = self.loss_fn(self.ddp, batch) if self.loss_fn else _default_loss(self.ddp, batch, self.fused)
         loss.backward()
+        if self.fused:
+            from .ops import functional as OF
+
+            OF.join_side_work()
         self.opt.step()
         if self.fused:
             from .ops import functional as OF

@@ -621,6 +621,35 @@ def _weight_krsc(weight: torch.Tensor) -> torch.Tensor:
     return weight.contiguous(memory_format=torch.channels_last)
 
 
+# ---- weight gradients on a side stream -------------------------------------------------------------------------
+# A convolution's weight gradient depends only on (x, dy) and nothing in the backward chain depends on it until the
+# gradient is collected.  Issued on a second stream it becomes - inside the whole-step CUDA graph - a parallel branch: its
+# persistent, latency-bound CTAs share the SMs with the small memory-bound BatchNorm-backward CTAs of the main branch.
+# Its inputs and scratch (x, dy, scratch) are kept alive - and dw lives on as the parameter's .grad - until `join_side_work()` has made the consuming stream wait
+# for it; the DDP / FSDP wrappers join before they collect a bucket's gradients, and a callback joins at the end of every
+# backward pass.  DDL_WGRAD_STREAM=0 keeps the weight gradients on the main stream.
+_WGRAD_STREAM = _os.environ.get("DDL_WGRAD_STREAM", "1") != "0"
+_side_streams = {}
+_side_pending = []
+
+
+def _side_stream(device: torch.device) -> torch.cuda.Stream:
+    key = (device.type, device.index)
+    if key not in _side_streams:
+        _side_streams[key] = torch.cuda.Stream(device)
+    return _side_streams[key]
+
+
+def join_side_work() -> None:
+    """Make the current stream wait for every weight gradient still running on the side stream."""
+    if not _side_pending:
+        return
+    cur = torch.cuda.current_stream()
+    for ev, _keep in _side_pending:
+        cur.wait_event(ev)
+    _side_pending.clear()
+
+
 class _ConvNative(torch.autograd.Function):
     """conv2d on NHWC bf16 through the implicit-GEMM kernels; returns (y, partial BatchNorm statistics of y)."""
 
@@ -670,7 +699,23 @@ class _ConvNative(torch.autograd.Function):
             dw = torch.empty_like(weight)  # same (dense) layout as the parameter: the copy into the gradient bucket is flat
             scratch = _scratch(L.lib().ddl_conv_wgrad_scratch_bytes(*geom), dev)
             sk, sc, sr, ss = dw.stride()
-            L.call("ddl_conv_wgrad", x.data_ptr(), dy.data_ptr(), dw.data_ptr(), sk, sc, sr, ss, scratch.data_ptr(), scratch.numel(), *geom, st)
+            # The side stream is only safe when nothing on the main stream reads dw before the join: a leaf parameter whose
+            # .grad is still None (AccumulateGrad then adopts dw without touching it).  The pending list must not hold dw
+            # itself - an extra reference makes AccumulateGrad clone it on the main stream, before the side stream wrote it.
+            if _WGRAD_STREAM and weight.is_leaf and weight.grad is None and not weight._backward_hooks:
+                main, side = torch.cuda.current_stream(dev), _side_stream(dev)
+                ready = torch.cuda.Event()
+                ready.record(main)       # dy (and x) are complete on the main stream here
+                side.wait_event(ready)
+                L.call("ddl_conv_wgrad", x.data_ptr(), dy.data_ptr(), dw.data_ptr(), sk, sc, sr, ss, scratch.data_ptr(), scratch.numel(), *geom,
+                       side.cuda_stream)
+                done = torch.cuda.Event()
+                done.record(side)
+                if not _side_pending:
+                    torch.autograd.Variable._execution_engine.queue_callback(join_side_work)
+                _side_pending.append((done, (x, dy, scratch)))
+            else:
+                L.call("ddl_conv_wgrad", x.data_ptr(), dy.data_ptr(), dw.data_ptr(), sk, sc, sr, ss, scratch.data_ptr(), scratch.numel(), *geom, st)
         return dx, dw, None, None, None
 
 

@@ -61,11 +61,19 @@ class VariantSelector:
                 return None
         return None
 
+    def pick_row(self, nbytes: int) -> dict:
+        for row in self.table:
+            if nbytes <= row["max_bytes"]:
+                return row
+        return {"algo": "twoshot", "blocks": 64}
+
     def pick(self, nbytes: int, same_dtype: bool) -> Tuple[int, int]:
         for row in self.table:
             if nbytes <= row["max_bytes"]:
                 algo = row["algo"]
                 blocks = int(row["blocks"])
+                if algo == "hybrid":  # callers that can run it ask pick_row(); everybody else gets the switch reduction
+                    algo = "nvls"
                 if algo == "nvls" and not (self.nvls and same_dtype):
                     # the switch is not doing the reduction: the SMs have to move (W-1)/W of the bytes
                     algo, blocks = "twoshot", max(blocks, 64 if nbytes >= (4 << 20) else 32)
@@ -142,6 +150,12 @@ class PeerMemoryComm(CommBackend):
         nbytes = n * buf.element_size()
         same = out_dtype == buf.dtype
         name = algo or self.force_algo
+        if name is None and same and buf.dtype == torch.bfloat16 and ob is sb and ooff == off and scale is None:
+            row = self.selector.pick_row(nbytes)
+            if row.get("algo") == "hybrid" and self.heap.multicast_supported and self.world_size in (2, 4, 8):
+                return self.all_reduce_hybrid_(buf, int(row.get("permille", 600)), int(row.get("blocks", 8)), int(row.get("p2p_blocks", 48)))
+        if name == "hybrid":
+            return self.all_reduce_hybrid_(buf, scale=scale)
         if name:
             a, nb = _ALGO_NAMES[name], num_blocks or self.num_blocks or 32
         else:
@@ -154,6 +168,18 @@ class PeerMemoryComm(CommBackend):
             L.dtype_code(out_dtype), float(scale if scale is not None else 1.0 / self.world_size), a, sb.mc(off), ob.mc(ooff), nb,
             L.stream_ptr(self.device),
         )
+        return _StreamOrdered()
+
+    def all_reduce_hybrid_(self, buf: torch.Tensor, permille: int = 600, nvls_blocks: int = 8, p2p_blocks: int = 48,
+                           scale: Optional[float] = None) -> CommHandle:
+        """In-place bf16 mean (or ``scale`` x sum): ``permille`` / 1000 of the message through the switch (NVLS), the rest
+        through two-shot peer loads / stores, in one kernel (``ddl_allreduce_hybrid``)."""
+        if buf.dtype != torch.bfloat16 or not self.heap.multicast_supported:
+            raise RuntimeError("hybrid all-reduce needs a bf16 buffer in multicast-mapped symmetric memory")
+        sb, off = self.lookup(buf)
+        L.call("ddl_allreduce_hybrid", C.byref(self._ct), sb.ptr_array(off), buf.numel(),
+               float(scale if scale is not None else 1.0 / self.world_size), sb.mc(off), int(permille), int(nvls_blocks), int(p2p_blocks),
+               L.stream_ptr(self.device))
         return _StreamOrdered()
 
     def broadcast_(self, buf: torch.Tensor, src: int = 0) -> None:

@@ -316,6 +316,10 @@ class DistributedDataParallel(nn.Module):
 
     def _launch_bucket(self, b: GradBucket) -> None:
         b.launched = True
+        if self.device.type == "cuda":
+            from ..ops import functional as OF
+
+            OF.join_side_work()  # weight gradients still running on the side stream (ops/functional.py)
         self._gather_grads(b)
         if self._comm_stream is not None:
             # the comm stream must see every gradient write of this bucket

@@ -273,6 +273,10 @@ class FullyShardedDataParallel(nn.Module):
 
     def _reduce_and_update(self, u: _Unit) -> None:
         u.reduced = True
+        if self.cuda:
+            from ..ops import functional as OF
+
+            OF.join_side_work()
         self._gather_grads(u)
         if self.cuda:
             self._comm_stream.wait_stream(torch.cuda.current_stream(self.device))

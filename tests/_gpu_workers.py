@@ -42,6 +42,22 @@ def w_allreduce_variants():
     src = comm.alloc_flat(n, torch.float32, dev)
     dst = comm.alloc_flat(n, torch.bfloat16, dev)
     report["nvls_tested"] = bool(comm.heap.multicast_supported)
+    if comm.heap.multicast_supported and world in (2, 4, 8):
+        # hybrid (switch reduction + peer loads / stores in one kernel) against the fp32 mean of the bf16 inputs
+        for n_h, permille in (((1 << 20) + 8192, 600), (8 * world * 64, 500), (1 << 22, 0), (1 << 21, 1000)):
+            n_h = n_h // (8 * world) * (8 * world)
+            hb = comm.alloc_flat(n_h, torch.bfloat16, dev)
+            for rep in range(2):
+                g = torch.Generator(device="cpu").manual_seed(300 + rep)
+                full = torch.randn(world, n_h, generator=g)
+                hb.copy_(full[rank].to(torch.bfloat16))
+                pg.barrier()
+                comm.all_reduce_hybrid_(hb, permille, 4, 8)
+                torch.cuda.synchronize()
+                err = (hb.float().cpu() - full.to(torch.bfloat16).float().mean(0)).abs().max().item()
+                report["cases"].append(("hybrid", n_h, permille, rep, err))
+                report["ok"] &= err < 2e-2
+                pg.barrier()
     for algo in ("oneshot", "twoshot"):
         g = torch.Generator(device="cpu").manual_seed(7)
         full = torch.randn(world, n, generator=g)
