@@ -51,6 +51,10 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--json", default=os.path.join(ROOT, "gpurun_out", "conv_bench.json"))
     ap.add_argument("--im2col", type=int, default=1)
+    ap.add_argument("--halo", default="1,0,28", help="halo-tile kernel for 3x3 / stride 1: on,mt,min_w")
+    ap.add_argument("--ablate", type=int, default=0, help="timing experiments (results are garbage): see ddl_conv_set_debug")
+    ap.add_argument("--no-lib", type=int, default=0, help="skip the library convolutions")
+    ap.add_argument("--only3x3", type=int, default=0, help="only the 3x3 / stride-1 layers")
     ap.add_argument("--pair", type=int, default=0, help="forward / data-gradient kernel: 0 one CTA, 1 CTA pairs + halo tiles, 2 CTA pairs")
     ap.add_argument("--wgrad-rows", type=int, default=0)
     args = ap.parse_args()
@@ -58,6 +62,8 @@ def main():
 
     L0.call("ddl_conv_set_tuning", args.wgrad_rows, args.pair)
     L0.call("ddl_conv_set_im2col", args.im2col)
+    L0.call("ddl_conv_set_halo", *[int(v) for v in args.halo.split(",")])
+    L0.call("ddl_conv_set_debug", None, args.ablate)
     torch.backends.cudnn.benchmark = True
     dev = torch.device("cuda")
     bf = torch.bfloat16
@@ -73,6 +79,8 @@ def main():
     tot = {"cudnn_fwd": 0.0, "cudnn_dgrad": 0.0, "cudnn_wgrad": 0.0, "floor": 0.0}
     print(f"{'layer':32s} {'x':>2s} {'fwd':>8s} {'dgrad':>8s} {'wgrad':>8s} {'floor':>7s} | {'n.fwd':>8s} {'n.dgrad':>8s} {'n.wgrad':>8s} {'ws.fwd /dgrad':>16s}   (us per call; n.* = csrc/conv_igemm.cu, n.fwd / ws.fwd include the BN statistics)")
     for cnt, cin, hw, cout, k, s in LAYERS:
+        if args.only3x3 and not (k == 3 and s == 1):
+            continue
         pad = k // 2
         x = torch.randn(N, cin, hw, hw, device=dev).to(bf).contiguous(memory_format=torch.channels_last)
         w = torch.randn(cout, cin, k, k, device=dev).to(bf).contiguous(memory_format=torch.channels_last)

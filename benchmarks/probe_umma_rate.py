@@ -14,7 +14,7 @@ NAMES = {0: "one thread, divergent region", 1: "uniform warp + elect", 3: "+ com
          5: "+ wait for the commit of 6 groups ago", 6: "+ wait for the commit of the previous group"}
 out = torch.zeros(148, 2, dtype=torch.int64, device="cuda")
 for mode in (0, 1, 3, 4, 5, 6):
-    for n in (128, 256):
+    for n in (32, 64, 128, 256):
         for it in range(2):
             L.call("ddl_probe_umma_rate", out.data_ptr(), n, 2048, 148, mode, 2, L.stream_ptr())
             torch.cuda.synchronize()

@@ -86,8 +86,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv1x1_fwd_kernel(const __grid_c
     const uint32_t tmem_base = *tmem_ptr_smem;
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
+        // ===================== TMA producer (warp-uniform loop, one elected lane issues) =====================
+        if (elect_one()) {
             mbar_expect_tx(w_bar, (uint32_t)w_bytes);
             for (int kb = 0; kb < p.kblocks; ++kb) {
                 if (!B_MN) {
@@ -97,46 +97,53 @@ __global__ void __launch_bounds__(kThreads, 1) conv1x1_fwd_kernel(const __grid_c
                         tma_load_2d(w_smem + (size_t)kb * p.n_cta * 128 + j * 8192, &tma_w, w_bar, col_block + j * 64, kb * 64);
                 }
             }
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-                for (int kb = 0; kb < p.kblocks; ++kb) {
-                    mbar_wait(&empty_bar[stage], phase ^ 1);
+        }
+        __syncwarp();
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+            for (int kb = 0; kb < p.kblocks; ++kb) {
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                if (elect_one()) {
                     mbar_expect_tx(&full_bar[stage], kStageBytes);
                     tma_load_2d(a_smem + stage * kStageBytes, &tma_x, &full_bar[stage], kb * 64, tile * kTileM);  // OOB rows: zeros
-                    if (++stage == p.stages) { stage = 0; phase ^= 1; }
                 }
+                __syncwarp();
+                if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
-            const uint32_t idesc = make_idesc(kTileM, p.n_cta, false, B_MN);
-            mbar_wait(w_bar, 0);
+        // ===================== MMA issue: the whole warp runs the loop, one elected lane issues =====================
+        // (descriptors = constant | address >> 4, a k-step only adds to the address field: csrc/conv_igemm.cu)
+        const uint32_t idesc = make_idesc(kTileM, p.n_cta, false, B_MN);
+        constexpr uint32_t kStepA = 32 >> 4, kStepB = (B_MN ? 2048 : 32) >> 4;
+        const uint64_t da0 = make_smem_desc(0, 16, 1024) | (uint64_t)(smem_u32(a_smem) >> 4);
+        const uint64_t db0 = (B_MN ? make_smem_desc(0, 8192, 1024) : make_smem_desc(0, 16, 1024)) | (uint64_t)(smem_u32(w_smem) >> 4);
+        const uint32_t w_kb16 = (uint32_t)(p.n_cta * 128) >> 4;
+        const int kblocks = p.kblocks, stages = p.stages, nbuf = p.nbuf;
+        mbar_wait(w_bar, 0);
+        tc_fence_after();
+        int stage = 0, acc = 0;
+        uint32_t phase = 0, acc_phase = 0;
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+            mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
             tc_fence_after();
-            int stage = 0, acc = 0;
-            uint32_t phase = 0, acc_phase = 0;
-            const uint32_t sw = smem_u32(w_smem);
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-                mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+            const uint32_t d_tmem = tmem_base + acc * p.n_cta;
+            for (int kb = 0; kb < kblocks; ++kb) {
+                mbar_wait(&full_bar[stage], phase);
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + acc * p.n_cta;
-                for (int kb = 0; kb < p.kblocks; ++kb) {
-                    mbar_wait(&full_bar[stage], phase);
-                    tc_fence_after();
-                    const uint32_t sa = smem_u32(a_smem + stage * kStageBytes);
-                    const uint32_t sb = sw + kb * (p.n_cta * 128);
+                const uint64_t da = da0 + (uint32_t)stage * (uint32_t)(kStageBytes >> 4), db = db0 + (uint32_t)kb * w_kb16;
+                if (elect_one()) {
+                    umma_bf16(d_tmem, da, db, idesc, kb > 0 ? 1u : 0u);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        umma_bf16(d_tmem, make_smem_desc(sa + k * 32, 16, 1024),
-                                  B_MN ? make_smem_desc(sb + k * 2048, 8192, 1024) : make_smem_desc(sb + k * 32, 16, 1024), idesc,
-                                  (kb > 0 || k > 0) ? 1u : 0u);
+                    for (int k = 1; k < 4; ++k) umma_bf16(d_tmem, da + k * kStepA, db + k * kStepB, idesc, 1u);
                     umma_commit(&empty_bar[stage]);
-                    if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                    if (kb == kblocks - 1) umma_commit(&tmem_full[acc]);
                 }
-                umma_commit(&tmem_full[acc]);
-                if (++acc == p.nbuf) { acc = 0; acc_phase ^= 1; }
+                __syncwarp();
+                if (++stage == stages) { stage = 0; phase ^= 1; }
             }
+            if (++acc == nbuf) { acc = 0; acc_phase ^= 1; }
         }
     } else {
         // ===================== epilogue warps =====================

@@ -138,9 +138,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
 
     if (warp == 0) {
         // ===================== TMA producer =====================
-        if (lane == 0) {
+        // (the whole warp runs the loop and one elected lane issues, as in the MMA warp below: inside an `if (lane == 0)`
+        // region every TMA instruction is wrapped in an ELECT / R2UR.BROADCAST loop and the B_MN layers, with up to five
+        // loads per k-block, ran producer-bound)
+        {
             int stage = 0;
             uint32_t phase = 0;
+            const uint32_t tx_bytes = p.a_bytes + (uint32_t)stage_b;
             for (int tile = m_group; tile < p.num_tiles; tile += m_groups) {
                 const int cls = tile / p.tiles_per_cls, t = tile - cls * p.tiles_per_cls;
                 const int ng = t / tiles_hw, rem = t - ng * tiles_hw;
@@ -157,19 +161,22 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
                 }
                 for (int ti = 0; ti < ntaps; ++ti) {
                     const Tap tp = p.taps[cls][ti];
+                    const int wcol = tp.wtap * p.w_tap_stride;
                     for (int cb = 0; cb < p.cblocks; ++cb) {
                         mbar_wait(&empty_bar[stage], phase ^ 1);
                         uint8_t* sa = smem + (size_t)stage * stage_bytes;
                         uint8_t* sb = sa + kStageA;
-                        mbar_expect_tx(&full_bar[stage], p.a_bytes + (uint32_t)stage_b);
-                        if (p.im2col) tma_load_im2col(sa, &maps.in[0], &full_bar[stage], cb * 64, iw, ih, in_, tp.dw - p.low_w, tp.dh - p.low_h);
-                        else tma_load_4d(sa, &maps.in[tp.map], &full_bar[stage], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
-                        if (!B_MN) {
-                            tma_load_2d(sb, &maps.w, &full_bar[stage], tp.wtap * p.w_tap_stride + cb * 64, n_blk * p.bn);
-                        } else {
-                            for (int j = 0; j < p.groups; ++j)
-                                tma_load_2d(sb + j * 8192, &maps.w, &full_bar[stage], tp.wtap * p.w_tap_stride + n_blk * p.bn + j * 64, cb * 64);
+                        if (elect_one()) {
+                            mbar_expect_tx(&full_bar[stage], tx_bytes);
+                            if (p.im2col) tma_load_im2col(sa, &maps.in[0], &full_bar[stage], cb * 64, iw, ih, in_, tp.dw - p.low_w, tp.dh - p.low_h);
+                            else tma_load_4d(sa, &maps.in[tp.map], &full_bar[stage], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
+                            if (!B_MN) {
+                                tma_load_2d(sb, &maps.w, &full_bar[stage], wcol + cb * 64, n_blk * p.bn);
+                            } else {
+                                for (int j = 0; j < p.groups; ++j) tma_load_2d(sb + j * 8192, &maps.w, &full_bar[stage], wcol + n_blk * p.bn + j * 64, cb * 64);
+                            }
                         }
+                        __syncwarp();
                         if (++stage == p.stages) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -744,6 +751,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_pair_kernel(const __grid_con
     }
 }
 
+#include "conv_halo.cuh"
+
 // ------------------------------------------------------------------------------------------------ weight gradient
 // D[m = (tap, c)][n = k] = sum over pixels of x_tap[pix][c] * dy[pix][k].  Both operands are MN-major: a pixel's
 // 64-channel slice is one 128-byte row, the reduction index (pixel) walks the rows.  The (tap, c) axis is cut into
@@ -753,6 +762,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_pair_kernel(const __grid_con
 // fixed order.  Slots hold ceil16(pixels) rows; the rows past the box are zeroed once and never written again, so the
 // K padding multiplies zeros.
 constexpr int kWgThreads = 192;  // TMA, MMA, 4 epilogue warps
+constexpr int kWgMaxUnits = 8;    // 64-channel units (two per accumulator pair) a CTA may own
 
 struct WgradParams {
     float* partials;  // [ksplit][Mtot][Cout]
@@ -815,41 +825,48 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_kernel(const __grid_
     const int tiles_hw = p.tiles_h * p.tiles_w;
 
     if (warp == 0) {
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            const uint32_t tx_bytes = (uint32_t)(dy_slots + nu) * (uint32_t)p.pix * 128u;
-            for (int chunk = c0; chunk < c1; ++chunk) {
-                const int ng = chunk / tiles_hw, rem = chunk - ng * tiles_hw;
-                const int hb = rem / p.tiles_w, wb = rem - hb * p.tiles_w;
-                const int n0 = ng * p.nb, oh0 = hb * p.bh, ow0 = wb * p.bw;
-                mbar_wait(&empty_bar[stage], phase ^ 1);
-                uint8_t* st = smem + (size_t)stage * stage_bytes;
+        // producer: warp-uniform loop, one elected lane issues the (up to 4 + 8) loads of a chunk; the unit -> (tap, channel
+        // block) decode is hoisted out of the chunk loop
+        int stage = 0;
+        uint32_t phase = 0;
+        const uint32_t tx_bytes = (uint32_t)(dy_slots + nu) * (uint32_t)p.pix * 128u;
+        int u_c[kWgMaxUnits], u_dw[kWgMaxUnits], u_dh[kWgMaxUnits], u_map[kWgMaxUnits];
+#pragma unroll
+        for (int i = 0; i < kWgMaxUnits; ++i) {
+            const int u = u0 + (i < nu ? i : 0);
+            const int ti = u / p.cblocks;
+            const Tap tp = p.taps[ti];
+            u_c[i] = (u - ti * p.cblocks) * 64;
+            u_dw[i] = tp.dw; u_dh[i] = tp.dh; u_map[i] = tp.map;
+        }
+        for (int chunk = c0; chunk < c1; ++chunk) {
+            const int ng = chunk / tiles_hw, rem = chunk - ng * tiles_hw;
+            const int hb = rem / p.tiles_w, wb = rem - hb * p.tiles_w;
+            const int n0 = ng * p.nb, oh0 = hb * p.bh, ow0 = wb * p.bw;
+            const int m0 = chunk * p.pix, t2 = p.im2col ? m0 / p.OWt : 0;
+            const int iw = p.im2col ? (m0 % p.OWt) * p.cstride + p.low_w : 0, ih = p.im2col ? (t2 % p.OHt) * p.cstride + p.low_h : 0;
+            const int in_ = p.im2col ? t2 / p.OHt : 0;
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            uint8_t* st = smem + (size_t)stage * stage_bytes;
+            if (elect_one()) {
                 mbar_expect_tx(&full_bar[stage], tx_bytes);
                 if (p.im2col) {
-                    const int m0 = chunk * p.pix, t2 = m0 / p.OWt;
-                    const int iw = (m0 % p.OWt) * p.cstride + p.low_w, ih = (t2 % p.OHt) * p.cstride + p.low_h, in_ = t2 / p.OHt;
-                    for (int j = 0; j < dy_slots; ++j)
-                        tma_load_4d(st + j * p.slot_bytes, &maps.w, &full_bar[stage], nb_ * p.bn + j * 64, m0, 0, 0);
-                    for (int i = 0; i < nu; ++i) {
-                        const int u = u0 + i;
-                        const int ti = u / p.cblocks, cb = u - ti * p.cblocks;
-                        const Tap tp = p.taps[ti];
-                        tma_load_im2col(st + (dy_slots + i) * p.slot_bytes, &maps.in[0], &full_bar[stage], cb * 64, iw, ih, in_, tp.dw - p.low_w,
-                                        tp.dh - p.low_h);
-                    }
+                    for (int j = 0; j < dy_slots; ++j) tma_load_4d(st + j * p.slot_bytes, &maps.w, &full_bar[stage], nb_ * p.bn + j * 64, m0, 0, 0);
+#pragma unroll
+                    for (int i = 0; i < kWgMaxUnits; ++i)
+                        if (i < nu)
+                            tma_load_im2col(st + (dy_slots + i) * p.slot_bytes, &maps.in[0], &full_bar[stage], u_c[i], iw, ih, in_, u_dw[i] - p.low_w,
+                                            u_dh[i] - p.low_h);
                 } else {
-                    for (int j = 0; j < dy_slots; ++j)
-                        tma_load_4d(st + j * p.slot_bytes, &maps.w, &full_bar[stage], nb_ * p.bn + j * 64, ow0, oh0, n0);
-                    for (int i = 0; i < nu; ++i) {
-                        const int u = u0 + i;
-                        const int ti = u / p.cblocks, cb = u - ti * p.cblocks;
-                        const Tap tp = p.taps[ti];
-                        tma_load_4d(st + (dy_slots + i) * p.slot_bytes, &maps.in[tp.map], &full_bar[stage], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
-                    }
+                    for (int j = 0; j < dy_slots; ++j) tma_load_4d(st + j * p.slot_bytes, &maps.w, &full_bar[stage], nb_ * p.bn + j * 64, ow0, oh0, n0);
+#pragma unroll
+                    for (int i = 0; i < kWgMaxUnits; ++i)
+                        if (i < nu)
+                            tma_load_4d(st + (dy_slots + i) * p.slot_bytes, &maps.in[u_map[i]], &full_bar[stage], u_c[i], ow0 + u_dw[i], oh0 + u_dh[i], n0);
                 }
-                if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
+            __syncwarp();
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
     } else if (warp == 1) {
         // whole warp runs the loop (uniform addresses / descriptors), one elected lane issues; a k-step of 16 pixels is
@@ -868,7 +885,13 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_kernel(const __grid_
                 for (int g = 0; g < npairs; ++g) {
                     const uint64_t da0 = d_const | (uint64_t)((sdy + (uint32_t)(dy_slots + 2 * g) * (uint32_t)p.slot_bytes) >> 4);
                     const uint32_t d_tmem = tmem_base + g * p.bn;
-                    for (int k = 0; k < p.ksteps; ++k) umma_bf16(d_tmem, da0 + k * 128, db0 + k * 128, idesc, (chunk > c0 || k > 0) ? 1u : 0u);
+                    if (p.ksteps == 8) {
+                        umma_bf16(d_tmem, da0, db0, idesc, chunk > c0 ? 1u : 0u);
+#pragma unroll
+                        for (int k = 1; k < 8; ++k) umma_bf16(d_tmem, da0 + k * 128, db0 + k * 128, idesc, 1u);
+                    } else {
+                        for (int k = 0; k < p.ksteps; ++k) umma_bf16(d_tmem, da0 + k * 128, db0 + k * 128, idesc, (chunk > c0 || k > 0) ? 1u : 0u);
+                    }
                 }
                 umma_commit(&empty_bar[stage]);
             }
@@ -1323,6 +1346,99 @@ int launch_pair(bool b_mn, const DataParams& d0, const PairPlan& pl, const void*
     return 0;
 }
 
+// ---- halo kernel launch plan (conv_halo.cuh) -------------------------------------------------------------
+int g_halo = 1;        // 3x3 / stride-1 / pad-1 layers on halo tiles; 0 = im2col kernel
+int g_halo_mt = 0;     // pixel tiles per weight tile: 0 = auto, 1 / 2 forced (benchmarks)
+int g_halo_min_w = 28; // narrower images fill too few of the 128 MMA rows per tile
+
+struct HaloPlan {
+    int th, pitch, tiles_h, num_tiles, mt, bn, nblk, cblocks, a_stages, b_stages, a_slot, box_rows, m_groups, smem;
+};
+
+// Cred = reduction channels (forward: C, data gradient: Cout), Cn = output channels of the contraction
+bool plan_halo(int N, int H, int W, int Cred, int Cn, int R, int stride, int pad, HaloPlan& h) {
+    if (!g_halo || R != 3 || stride != 1 || pad != 1) return false;
+    if (W < g_halo_min_w || W + 1 > 128 || Cn > 256 || (long long)N * H > (1 << 28)) return false;
+    h.pitch = W + 1;
+    int th = 128 / h.pitch;
+    if (th > H) th = H;
+    h.tiles_h = (H + th - 1) / th;
+    h.th = (H + h.tiles_h - 1) / h.tiles_h;
+    h.num_tiles = N * h.tiles_h;
+    h.bn = Cn;
+    h.nblk = 1;
+    h.cblocks = Cred / 64;
+    h.box_rows = (h.th + 2) * h.pitch;
+    int slot_rows = h.box_rows + 1;
+    if (slot_rows < 2 * h.pitch + 2 + 128) slot_rows = 2 * h.pitch + 2 + 128;
+    h.a_slot = (slot_rows * 128 + 1023) / 1024 * 1024;
+    const int b_slot = h.bn * 128, b_all = 9 * h.cblocks * b_slot;
+    for (int mt = 2; mt >= 1; --mt) {
+        if (g_halo_mt && mt != g_halo_mt) continue;
+        if (2 * mt * h.bn > 512) continue;
+        const int fixed = 4 * (h.bn / 64) * mt * kStgBytes + 512 + 1024;
+        const int avail = 227 * 1024 - fixed;
+        const bool stay = b_all + 2 * mt * h.a_slot <= avail;
+        int a_stages, b_stages;
+        if (stay) {
+            b_stages = 0;
+            a_stages = (avail - b_all) / (mt * h.a_slot);
+            if (a_stages > 4) a_stages = 4;
+        } else {
+            a_stages = 2;
+            b_stages = (avail - 2 * mt * h.a_slot) / b_slot;
+            if (b_stages > kHaloMaxStages) b_stages = kHaloMaxStages;
+            if (b_stages < 3) continue;
+        }
+        h.mt = mt; h.a_stages = a_stages; h.b_stages = b_stages;
+        h.smem = fixed + a_stages * mt * h.a_slot + (b_stages ? b_stages : 9 * h.cblocks) * b_slot;
+        const int units = (h.num_tiles + mt - 1) / mt;
+        h.m_groups = DDL_SM_COUNT < units ? DDL_SM_COUNT : units;
+        return true;
+    }
+    return false;
+}
+
+// act [N, H, W, Cact] NHWC; w [w_rows][w_inner]; out [N, H, W, Cn]
+int launch_halo(bool b_mn, const HaloPlan& h, const void* act, int N, int H, int W, int Cact, const void* w, long long w_rows, long long w_inner,
+                int w_tap_stride, void* out, float* partials, int Cn, cudaStream_t stream) {
+    ConvMaps maps;
+    {
+        const cuuint64_t dims[4] = {(cuuint64_t)Cact, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+        const cuuint64_t str[3] = {(cuuint64_t)Cact * 2, (cuuint64_t)W * Cact * 2, (cuuint64_t)H * W * Cact * 2};
+        const cuuint32_t box[4] = {64u, (cuuint32_t)h.pitch, (cuuint32_t)(h.th + 2), 1u};
+        if (int e = make_map4(&maps.in[0], act, dims, str, box, "conv (halo) activations")) return e;
+        for (int i = 1; i < 4; ++i) maps.in[i] = maps.in[0];
+    }
+    if (int e = tma_host::encode_2d(&maps.w, w, w_rows, w_inner, w_inner * 2, b_mn ? 64 : h.bn, "conv (halo) weights")) return e;
+    HaloParams p = {};
+    p.out = (bf16*)out; p.partials = partials;
+    p.N = N; p.H = H; p.W = W; p.Cn = Cn;
+    p.th = h.th; p.pitch = h.pitch; p.tiles_h = h.tiles_h; p.num_tiles = h.num_tiles;
+    p.mt = h.mt; p.num_units = (h.num_tiles + h.mt - 1) / h.mt;
+    p.num_n_blocks = h.nblk; p.bn = h.bn; p.groups = h.bn / 64;
+    p.cblocks = h.cblocks; p.w_tap_stride = w_tap_stride;
+    p.flip = b_mn ? 1 : 0;
+    p.a_stages = h.a_stages; p.b_stages = h.b_stages;
+    p.ablate = g_conv_ablate;
+    p.a_slot = (uint32_t)h.a_slot; p.box_rows = (uint32_t)h.box_rows; p.a_box_bytes = (uint32_t)h.box_rows * 128u;
+    const bool stay = h.b_stages == 0;
+    void (*kern)(const ConvMaps, const HaloParams) = nullptr;
+    if (b_mn) kern = h.mt == 2 ? (stay ? conv_halo_kernel<true, 2, true> : conv_halo_kernel<true, 2, false>)
+                               : (stay ? conv_halo_kernel<true, 1, true> : conv_halo_kernel<true, 1, false>);
+    else kern = h.mt == 2 ? (stay ? conv_halo_kernel<false, 2, true> : conv_halo_kernel<false, 2, false>)
+                          : (stay ? conv_halo_kernel<false, 1, true> : conv_halo_kernel<false, 1, false>);
+    static int attr_smem[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const int variant = (b_mn ? 4 : 0) + (h.mt == 2 ? 2 : 0) + (stay ? 1 : 0);
+    if (h.smem > attr_smem[variant]) {
+        DDL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, h.smem));
+        attr_smem[variant] = h.smem;
+    }
+    kern<<<h.m_groups * h.nblk, kThreads, h.smem, stream>>>(maps, p);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
 // classes / taps / grid of the forward convolution (shared by the launch and the partial-row query)
 void fill_fwd(DataParams& p, const ConvShape& s, const BoxGeo& g) {
     p.ncls = 1;
@@ -1340,6 +1456,8 @@ void fill_fwd(DataParams& p, const ConvShape& s, const BoxGeo& g) {
 // rows of BatchNorm partials the forward writes (the pair kernel when the shape allows it, else the one-CTA kernel)
 int fwd_partial_rows(const ConvShape& s) {
     const BoxGeo g = s.flat ? choose_box(1, 1, s.N * s.OH * s.OW, kTileM) : choose_box(s.N, s.OH, s.OW, kTileM);
+    HaloPlan hp;
+    if (plan_halo(s.N, s.OH, s.OW, s.C, s.Cout, s.R, s.stride, s.pad, hp)) return hp.m_groups;
     DataParams p = {};
     fill_fwd(p, s, g);
     PairPlan pl;
@@ -1359,6 +1477,7 @@ bool plan_wgrad(const ConvShape& s, WgradPlan& w) {
     w.nblk = s.Cout / w.bn;
     w.U = s.R * s.S * (s.C / 64);
     int Gmax = 512 / w.bn;
+    if (Gmax > kWgMaxUnits / 2) Gmax = kWgMaxUnits / 2;
     if (Gmax > (w.U + 1) / 2) Gmax = (w.U + 1) / 2;
     const int avail = 227 * 1024 - 1024 - 512;
     // 128-pixel chunks first (with as many accumulator pairs as still leave two stages), 64-pixel chunks only when even one
@@ -1421,6 +1540,14 @@ DDL_API int ddl_conv_set_tuning(int wgrad_rows, int pair_mode) {
     return 0;
 }
 
+DDL_API int ddl_conv_set_halo(int on, int mt, int min_w) {
+    DDL_REQUIRE(mt >= 0 && mt <= 2, "conv tuning: halo mt must be 0 (auto), 1 or 2");
+    g_halo = on ? 1 : 0;
+    g_halo_mt = mt;
+    g_halo_min_w = min_w > 0 ? min_w : 28;
+    return 0;
+}
+
 // development aid: device buffer of [296][8] int64 that the next pair-kernel launches fill with per-CTA wait-cycle counters
 // (producer: total, wait A slot, wait B slot; MMA issuer: total, wait A data, wait B data, wait accumulator); null = off
 DDL_API int ddl_conv_set_debug(void* buf, int ablate) {
@@ -1435,6 +1562,11 @@ DDL_API int ddl_conv_fwd(const void* x, const void* w, void* y, float* partials,
                 H, W, C, Cout, R, stride, pad);
     DDL_REQUIRE(x && w && y, "conv fwd: null pointer");
     const ConvShape s = make_shape(N, H, W, C, Cout, R, S, stride, pad);
+    {
+        HaloPlan hp;
+        if (plan_halo(N, s.OH, s.OW, C, Cout, R, stride, pad, hp))
+            return launch_halo(false, hp, x, N, H, W, C, w, Cout, (long long)R * S * C, C, y, partials, Cout, (cudaStream_t)stream_);
+    }
     const BoxGeo g = s.flat ? choose_box(1, 1, N * s.OH * s.OW, kTileM) : choose_box(N, s.OH, s.OW, kTileM);
     DataParams p = {};
     p.out = (bf16*)y;
@@ -1470,6 +1602,11 @@ DDL_API int ddl_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H
     DDL_REQUIRE(dy && w && dx, "conv dgrad: null pointer");
     const ConvShape s = make_shape(N, H, W, C, Cout, R, S, stride, pad);
     cudaStream_t stream = (cudaStream_t)stream_;
+    {
+        HaloPlan hp;
+        if (plan_halo(N, H, W, Cout, C, R, stride, pad, hp))
+            return launch_halo(true, hp, dy, N, s.OH, s.OW, Cout, w, Cout, (long long)R * S * C, C, dx, nullptr, C, stream);
+    }
     // boxes walk the dy grid; a class of the stride-2 case covers H/2 x W/2 = OH x OW input pixels
     const BoxGeo g = s.flat ? choose_box(1, 1, N * s.OH * s.OW, kTileM) : choose_box(N, s.OH, s.OW, kTileM);
     DataParams p = {};

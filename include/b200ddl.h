@@ -248,6 +248,9 @@ int ddl_conv_wgrad(const void* x, const void* dy, void* dw, long long sk, long l
 int ddl_conv_set_tuning(int wgrad_rows, int pair_mode);
 /* activation tiles through im2col-mode TMA (1, default: dense 128-pixel tiles) or through tiled boxes (0; comparison runs) */
 int ddl_conv_set_im2col(int on);
+/* 3x3 / stride-1 / pad-1 layers (forward and data gradient) on halo tiles (csrc/conv_halo.cuh): on = 1 (default) / 0; mt =
+ * pixel tiles per weight tile (0 = auto, 1, 2); min_w = narrowest image that takes this kernel (0 = default 28) */
+int ddl_conv_set_halo(int on, int mt, int min_w);
 /* development aid: device buffer [296][8] int64 that following forward / data-gradient launches of the CTA-pair kernel fill
  * with per-CTA wait-cycle counters (which barrier each role waits on); NULL switches it off.  ablate (timing experiments
  * only, results are garbage): bit 0 = epilogue drops its staging and stores, bit 1 = no TMA loads are issued */
