@@ -283,8 +283,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
     const int kb_per_split = (p.k_blocks_total + p.split_k - 1) / p.split_k;
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
+        // ===================== TMA producer (warp-uniform loop, one elected lane issues) =====================
+        {
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = sched_id; tile < num_tiles; tile += sched_n) {
@@ -296,6 +296,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * L::kStageBytes;
                     uint8_t* sb = sa + L::kABytes;
+                    if (elect_one()) {
                     mbar_expect_tx(&full_bar[stage], L::kStageBytes);
                     if (A_MN) {
 #pragma unroll
@@ -323,14 +324,21 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
                             tma_load_2d_mcast(sb + cta_rank * (kHalf * 128), &tma_b_half, &full_bar[stage], kb * BK, n_blk * BN + cta_rank * kHalf, 0x3);
                         }
                     }
+                    }
+                    __syncwarp();
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
+        // ===================== MMA issue: the whole warp runs the loop, one elected lane issues =====================
+        // (stage descriptors = constant | address >> 4, a k-step adds 32 B (K-major) or 2048 B (MN-major) to the address)
+        {
             constexpr uint32_t idesc = make_idesc(BM, BN, A_MN, B_MN);
+            const uint64_t da_const = A_MN ? make_smem_desc(0, BK * 128, 1024) : make_smem_desc(0, 16, 1024);
+            const uint64_t db_const = B_MN ? make_smem_desc(0, BK * 128, 1024) : make_smem_desc(0, 16, 1024);
+            constexpr uint32_t kStepA = (A_MN ? 2048 : 32) >> 4, kStepB = (B_MN ? 2048 : 32) >> 4;
+            const uint32_t smem_base = smem_u32(smem);
             int stage = 0;
             uint32_t phase = 0;
             int acc_stage = 0;
@@ -345,22 +353,22 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_bf16_kernel(const __grid_con
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
-                    const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
-                    const uint32_t sb = sa + L::kABytes;
+                    // (the address field is 14 bits of (address >> 4); in a cluster the shared-window address carries the CTA rank above it)
+                    const uint32_t sa = (smem_base + (uint32_t)stage * (uint32_t)L::kStageBytes) & 0x3FFFFu;
+                    const uint64_t da = da_const | (uint64_t)(sa >> 4), db = db_const | (uint64_t)((sa + L::kABytes) >> 4);
+                    if (elect_one()) {
+                        umma_bf16(d_tmem, da, db, idesc, kb > kb0 ? 1u : 0u);
 #pragma unroll
-                    for (int k = 0; k < BK / UMMA_K; ++k) {
-                        // K-major: +32 B per 16 elements inside the 128 B swizzle span
-                        // MN-major: +2 k-groups (8 rows of 128 B each) = 2048 B
-                        const uint64_t da = A_MN ? make_smem_desc(sa + k * 2048, BK * 128, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
-                        const uint64_t db = B_MN ? make_smem_desc(sb + k * 2048, BK * 128, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
-                        umma_bf16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        for (int k = 1; k < BK / UMMA_K; ++k) umma_bf16(d_tmem, da + k * kStepA, db + k * kStepB, idesc, 1u);
+                        // frees the smem stage once these MMAs retire (in both CTAs when B is shared)
+                        if (kCluster > 1) umma_commit_mcast(&empty_bar[stage], 0x3);
+                        else umma_commit(&empty_bar[stage]);
                     }
-                    // frees the smem stage once these MMAs retire (in both CTAs when B is shared)
-                    if (kCluster > 1) umma_commit_mcast(&empty_bar[stage], 0x3);
-                    else umma_commit(&empty_bar[stage]);
+                    __syncwarp();
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(&tmem_full[acc_stage]);  // accumulator complete -> epilogue
+                if (elect_one()) umma_commit(&tmem_full[acc_stage]);  // accumulator complete -> epilogue
+                __syncwarp();
                 if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
             }
         }
@@ -446,7 +454,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm2sm_bf16_kernel(const __grid_
     const int kb_per_split = (p.k_blocks_total + p.split_k - 1) / p.split_k;
 
     if (warp == 0) {
-        if (lane == 0) {
+        // producer: warp-uniform loop, one elected lane issues
+        {
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = sched_id; tile < num_tiles; tile += sched_n) {
@@ -458,6 +467,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm2sm_bf16_kernel(const __grid_
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * kStageBytes;
                     uint8_t* sb = sa + kABytes;
+                    if (elect_one()) {
                     if (leader) mbar_expect_tx(&full_bar[stage], 2 * kStageBytes);
                     if (A_MN) {
 #pragma unroll
@@ -472,6 +482,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm2sm_bf16_kernel(const __grid_
                     } else {
                         tma_load_2d_2sm(sb, &tma_b, &full_bar[stage], kb * BK, n0);
                     }
+                    }
+                    __syncwarp();
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
             }
@@ -622,7 +634,7 @@ __global__ void __launch_bounds__(kGatherThreads, 1) gemm_allgather_kernel(const
     };
 
     if (warp == 0) {
-        if (lane == 0) {
+        {   // warp-uniform loop (every lane polls the shard flag), one elected lane issues the loads
             int stage = 0;
             uint32_t phase = 0, ready = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -634,6 +646,7 @@ __global__ void __launch_bounds__(kGatherThreads, 1) gemm_allgather_kernel(const
                     do {
                         asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(g.flags + sh) : "memory");
                     } while (v < copiers_total);
+                    __syncwarp();
                     fence_proxy_async_all();  // copiers wrote with ordinary stores; TMA reads through the async proxy
                     ready |= 1u << sh;
                 }
@@ -641,16 +654,21 @@ __global__ void __launch_bounds__(kGatherThreads, 1) gemm_allgather_kernel(const
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * L::kStageBytes;
                     uint8_t* sb = sa + L::kABytes;
-                    mbar_expect_tx(&full_bar[stage], L::kStageBytes);
-                    tma_load_2d(sa, &tma_a, &full_bar[stage], kb * BK, m_blk * BM);
-                    tma_load_2d(sb, &tma_b, &full_bar[stage], kb * BK, n_blk * BN);
+                    if (elect_one()) {
+                        mbar_expect_tx(&full_bar[stage], L::kStageBytes);
+                        tma_load_2d(sa, &tma_a, &full_bar[stage], kb * BK, m_blk * BM);
+                        tma_load_2d(sb, &tma_b, &full_bar[stage], kb * BK, n_blk * BN);
+                    }
+                    __syncwarp();
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        {   // warp-uniform loop, one elected lane issues
             constexpr uint32_t idesc = make_idesc(BM, BN, false, false);
+            const uint64_t d_const = make_smem_desc(0, 16, 1024);
+            const uint32_t smem_base = smem_u32(smem);
             int stage = 0, acc_stage = 0;
             uint32_t phase = 0, acc_phase = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -660,16 +678,19 @@ __global__ void __launch_bounds__(kGatherThreads, 1) gemm_allgather_kernel(const
                 for (int kb = 0; kb < p.k_blocks_total; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
-                    const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
-                    const uint32_t sb = sa + L::kABytes;
+                    const uint32_t sa = smem_base + (uint32_t)stage * (uint32_t)L::kStageBytes;
+                    const uint64_t da = d_const | (uint64_t)(sa >> 4), db = d_const | (uint64_t)((sa + L::kABytes) >> 4);
+                    if (elect_one()) {
+                        umma_bf16(d_tmem, da, db, idesc, kb > 0 ? 1u : 0u);
 #pragma unroll
-                    for (int k = 0; k < BK / UMMA_K; ++k)
-                        umma_bf16(d_tmem, make_smem_desc(sa + k * 32, 16, 1024), make_smem_desc(sb + k * 32, 16, 1024), idesc,
-                                  (kb > 0 || k > 0) ? 1u : 0u);
-                    umma_commit(&empty_bar[stage]);
+                        for (int k = 1; k < BK / UMMA_K; ++k) umma_bf16(d_tmem, da + k * 2, db + k * 2, idesc, 1u);
+                        umma_commit(&empty_bar[stage]);
+                    }
+                    __syncwarp();
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(&tmem_full[acc_stage]);
+                if (elect_one()) umma_commit(&tmem_full[acc_stage]);
+                __syncwarp();
                 if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1; }
             }
         }

@@ -149,54 +149,57 @@ __global__ void __launch_bounds__(kFwdThreads, 1) stem_fwd_kernel(const __grid_c
     const uint32_t tmem_base = *tmem_ptr_smem;
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
+        // ===================== TMA producer (warp-uniform loop, one elected lane issues) =====================
+        if (elect_one()) {
             mbar_expect_tx(w_bar, kFwdWBytes);
             tma_load_2d(w_smem, &tma_w, w_bar, 0, 0);
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-                const long long p0 = (long long)tile * kTileM;
+        }
+        __syncwarp();
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+            const long long p0 = (long long)tile * kTileM;
 #pragma unroll
-                for (int a = 0; a < kTaps; ++a) {
-                    mbar_wait(&empty_bar[stage], phase ^ 1);
+            for (int a = 0; a < kTaps; ++a) {
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                if (elect_one()) {
                     mbar_expect_tx(&full_bar[stage], kFwdStageBytes);
                     // rows past the end of z are zero-filled by TMA (they only feed dropped outputs)
                     tma_load_2d(a_smem + stage * kFwdStageBytes, &tma_z, &full_bar[stage], 0, (int)(p0 + (long long)a * p.Wp));
-                    if (++stage == kFwdStages) { stage = 0; phase ^= 1; }
                 }
+                __syncwarp();
+                if (++stage == kFwdStages) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
-            constexpr uint32_t idesc = make_idesc(kTileM, kCout, false, false);
-            mbar_wait(w_bar, 0);
+        // ===================== MMA issue: the whole warp runs the loop, one elected lane issues =====================
+        constexpr uint32_t idesc = make_idesc(kTileM, kCout, false, false);
+        const uint64_t d_const = make_smem_desc(0, 16, 1024);
+        const uint64_t da0 = d_const | (uint64_t)(smem_u32(a_smem) >> 4), db0 = d_const | (uint64_t)(smem_u32(w_smem) >> 4);
+        mbar_wait(w_bar, 0);
+        tc_fence_after();
+        int stage = 0, acc = 0;
+        uint32_t phase = 0, acc_phase = 0;
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+            mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
             tc_fence_after();
-            int stage = 0, acc = 0;
-            uint32_t phase = 0, acc_phase = 0;
-            const uint32_t sw = smem_u32(w_smem);
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-                mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+            const uint32_t d_tmem = tmem_base + acc * kCout;
+#pragma unroll
+            for (int a = 0; a < kTaps; ++a) {
+                mbar_wait(&full_bar[stage], phase);
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + acc * kCout;
+                const uint64_t da = da0 + (uint32_t)stage * (uint32_t)(kFwdStageBytes >> 4), db = db0 + (uint32_t)a * (uint32_t)((kCout * 128) >> 4);
+                if (elect_one()) {
+                    umma_bf16(d_tmem, da, db, idesc, a > 0 ? 1u : 0u);
 #pragma unroll
-                for (int a = 0; a < kTaps; ++a) {
-                    mbar_wait(&full_bar[stage], phase);
-                    tc_fence_after();
-                    const uint32_t sa = smem_u32(a_smem + stage * kFwdStageBytes);
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const uint64_t da = make_smem_desc(sa + k * 32, 16, 1024);
-                        const uint64_t db = make_smem_desc(sw + a * (kCout * 128) + k * 32, 16, 1024);
-                        umma_bf16(d_tmem, da, db, idesc, (a > 0 || k > 0) ? 1u : 0u);
-                    }
+                    for (int k = 1; k < 4; ++k) umma_bf16(d_tmem, da + k * 2, db + k * 2, idesc, 1u);
                     umma_commit(&empty_bar[stage]);
-                    if (++stage == kFwdStages) { stage = 0; phase ^= 1; }
+                    if (a == kTaps - 1) umma_commit(&tmem_full[acc]);
                 }
-                umma_commit(&tmem_full[acc]);
-                if (++acc == kAccBufs) { acc = 0; acc_phase ^= 1; }
+                __syncwarp();
+                if (++stage == kFwdStages) { stage = 0; phase ^= 1; }
             }
+            if (++acc == kAccBufs) { acc = 0; acc_phase ^= 1; }
         }
     } else {
         // ===================== epilogue warps (2..5) =====================
@@ -334,48 +337,51 @@ __global__ void __launch_bounds__(kWgThreads, 1) stem_wgrad_kernel(const __grid_
     const bool has_work = (int)blockIdx.x < p.num_rows;
 
     if (warp == 0) {
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int row = blockIdx.x; row < p.num_rows; row += gridDim.x) {
-                const int n = row / p.OH, oh = row - n * p.OH;
-                mbar_wait(&empty_bar[stage], phase ^ 1);
-                uint8_t* st = smem + (size_t)stage * stage_bytes;
+        // producer: warp-uniform loop, one elected lane issues
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int row = blockIdx.x; row < p.num_rows; row += gridDim.x) {
+            const int n = row / p.OH, oh = row - n * p.OH;
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            uint8_t* st = smem + (size_t)stage * stage_bytes;
+            if (elect_one()) {
                 mbar_expect_tx(&full_bar[stage], stage_bytes);
                 tma_load_2d(st, &tma_dy, &full_bar[stage], 0, row * p.OW);
 #pragma unroll
-                for (int a = 0; a < kTaps; ++a)
-                    tma_load_2d(st + (1 + a) * box_bytes, &tma_z, &full_bar[stage], 0, (n * p.Hp + oh + a) * p.Wp);
-                if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                for (int a = 0; a < kTaps; ++a) tma_load_2d(st + (1 + a) * box_bytes, &tma_z, &full_bar[stage], 0, (n * p.Hp + oh + a) * p.Wp);
             }
+            __syncwarp();
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // A: z boxes, MN-major, M = 128 = taps (a, a+1) x 64; B: dy box, MN-major, N = 64; K = pixels of the row
-            constexpr uint32_t idesc = make_idesc(128, kCout, true, true);
-            int stage = 0;
-            uint32_t phase = 0;
-            bool first = true;
-            const int ksteps = p.OW / 16;
-            for (int row = blockIdx.x; row < p.num_rows; row += gridDim.x) {
-                mbar_wait(&full_bar[stage], phase);
-                tc_fence_after();
-                const uint32_t sdy = smem_u32(smem + (size_t)stage * stage_bytes);
+        // A: z boxes, MN-major, M = 128 = taps (a, a+1) x 64; B: dy box, MN-major, N = 64; K = pixels of the row.  The
+        // whole warp runs the loop, one elected lane issues; a k-step of 16 pixels adds 2048 B to both descriptors.
+        constexpr uint32_t idesc = make_idesc(128, kCout, true, true);
+        const uint64_t d_const = make_smem_desc(0, box_bytes, 1024);
+        const uint32_t smem_base = smem_u32(smem);
+        int stage = 0;
+        uint32_t phase = 0;
+        bool first = true;
+        const int ksteps = p.OW / 16;
+        for (int row = blockIdx.x; row < p.num_rows; row += gridDim.x) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            const uint32_t sdy = smem_base + (uint32_t)stage * (uint32_t)stage_bytes;
+            const uint64_t db0 = d_const | (uint64_t)(sdy >> 4);
+            if (elect_one()) {
 #pragma unroll
                 for (int pair = 0; pair < 2; ++pair) {
-                    const uint32_t sz = sdy + (1 + 2 * pair) * box_bytes;
-                    for (int k = 0; k < ksteps; ++k) {
-                        const uint64_t da = make_smem_desc(sz + k * 2048, box_bytes, 1024);
-                        const uint64_t db = make_smem_desc(sdy + k * 2048, box_bytes, 1024);
-                        umma_bf16(tmem_base + pair * kCout, da, db, idesc, (!first || k > 0) ? 1u : 0u);
-                    }
+                    const uint64_t da0 = d_const | (uint64_t)((sdy + (1 + 2 * pair) * box_bytes) >> 4);
+                    for (int k = 0; k < ksteps; ++k) umma_bf16(tmem_base + pair * kCout, da0 + k * 128, db0 + k * 128, idesc, (!first || k > 0) ? 1u : 0u);
                 }
-                first = false;
                 umma_commit(&empty_bar[stage]);
-                if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
-            umma_commit(done_bar);
+            __syncwarp();
+            first = false;
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
+        if (elect_one()) umma_commit(done_bar);
+        __syncwarp();
     } else {
         // epilogue: TMEM -> this CTA's fp32 partial (rows m = 32*quarter + lane)
         const int quarter = warp & 3;
