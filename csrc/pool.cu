@@ -2,8 +2,8 @@
 // the ResNet stem (112^2 -> 56^2, reference model at notebooks/cv/onnx_experiments.py:19) and
 // the global average pool before the classifier (7^2 -> 1), forward and backward.
 //
-// Max pool: one thread per output pixel x 8 channels (one 16-byte vector): 9 vector loads,
-// one vector store, plus one byte per element recording which of the 9 taps won.  Backward
+// Max pool (odd image sizes; even sizes: see the *_even_* kernels below): one thread per output pixel x 8 channels (one
+// 16-byte vector): 9 vector loads, one vector store, plus one byte per element recording which of the 9 taps won.  Backward
 // is a gather: one thread per INPUT pixel x 8 channels looks at the (at most 4) windows that
 // contain it and sums the gradients of those whose recorded tap points here - no atomics,
 // every dx element written exactly once.
@@ -109,6 +109,121 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_bwd_kernel(const bf16* __res
     }
 }
 
+// ---- even H and W (the ResNet stem: 112^2 -> 56^2): the same two passes with a fraction of the instructions ---------
+// The generic kernels above spend ~600 instructions per 16-byte vector on 64-bit index divisions and per-element float
+// compares and ran at 2.5 - 4x their memory time.  Here a block owns one output row (forward) or one pair of input rows
+// (backward) of one image, so that no division is left; the maximum is taken on packed bf16 pairs (HMNMX2) and the
+// winning tap is found by comparing the taps with it, last to first (the lowest tap index wins a tie, as in ATen); the
+// tap codes are stored as 4 bits per element (one 32-bit word per 8 channels).  The backward pass handles a 2 x 2 patch
+// of input pixels per thread: the four windows that reach it are loaded once (the generic kernel loads nine per patch).
+__device__ __forceinline__ uint32_t hmax2_u32(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+// 0xffff in each half where a == b
+__device__ __forceinline__ uint32_t heq2_mask(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm("set.eq.u32.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+
+__global__ void __launch_bounds__(256) maxpool3x3s2_even_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y,
+                                                                     uint32_t* __restrict__ idx, int H, int W, int C, int OH, int OW) {
+    const int vc = C >> 3, oh = blockIdx.x, n = blockIdx.y;
+    const bf16* xin = x + (size_t)n * H * W * C;
+    const size_t orow = ((size_t)n * OH + oh) * OW;
+    for (int t = threadIdx.x; t < OW * vc; t += blockDim.x) {
+        const int ow = t / vc, c8 = t - ow * vc;
+        uint4 v[9];
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
+            const int ih = oh * 2 - 1 + kh;
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
+                const int iw = ow * 2 - 1 + kw;
+                // out of the image: -inf in every element (0xff80 = bf16 -inf); never wins, never ties with a finite value
+                v[kh * 3 + kw] = (ih >= 0 && iw >= 0) ? ld_global_v4(xin + ((size_t)ih * W + iw) * C + c8 * 8)
+                                                      : make_uint4(0xff80ff80u, 0xff80ff80u, 0xff80ff80u, 0xff80ff80u);
+            }
+        }
+        uint32_t m[4], arg[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t* w0 = reinterpret_cast<const uint32_t*>(&v[0]);
+            uint32_t mm = w0[q];
+#pragma unroll
+            for (int tap = 1; tap < 9; ++tap) mm = hmax2_u32(mm, reinterpret_cast<const uint32_t*>(&v[tap])[q]);
+            uint32_t a = 0;
+#pragma unroll
+            for (int tap = 8; tap >= 0; --tap) {
+                const uint32_t eq = heq2_mask(reinterpret_cast<const uint32_t*>(&v[tap])[q], mm);
+                a = (a & ~eq) | ((uint32_t)tap * 0x00010001u & eq);
+            }
+            m[q] = mm;
+            arg[q] = a;
+        }
+        const size_t o = orow + ow;
+        st_global_v4(y + o * C + c8 * 8, make_uint4(m[0], m[1], m[2], m[3]));
+        // element 2q -> bits [8q, 8q+4), element 2q+1 -> bits [8q+4, 8q+8)
+        uint32_t packed = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) packed |= ((arg[q] & 0xfu) | ((arg[q] >> 12) & 0xf0u)) << (8 * q);
+        idx[o * vc + c8] = packed;
+    }
+}
+
+__global__ void __launch_bounds__(256) maxpool3x3s2_even_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ dy2,
+                                                                     const uint32_t* __restrict__ idx, bf16* __restrict__ dx, int H, int W, int C,
+                                                                     int OH, int OW) {
+    const int vc = C >> 3, a = blockIdx.x, n = blockIdx.y;  // input rows 2a, 2a + 1
+    bf16* dxn = dx + (size_t)n * H * W * C;
+    for (int t = threadIdx.x; t < OW * vc; t += blockDim.x) {
+        const int b = t / vc, c8 = t - b * vc;  // input columns 2b, 2b + 1
+        float acc[4][8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[i][e] = 0.f;
+#pragma unroll
+        for (int di = 0; di < 2; ++di) {
+#pragma unroll
+            for (int dj = 0; dj < 2; ++dj) {
+                const int oh = a + di, ow = b + dj;
+                if (oh >= OH || ow >= OW) continue;
+                const size_t o = ((size_t)n * OH + oh) * OW + ow;
+                const uint32_t codes = idx[o * vc + c8];
+                float g[8];
+                bf16x8_to_float(ld_global_v4(dy + o * C + c8 * 8), g);
+                if (dy2) {
+                    float g2[8];
+                    bf16x8_to_float(ld_global_v4(dy2 + o * C + c8 * 8), g2);
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) g[e] += g2[e];
+                }
+                // pixel (i, j) of the patch is tap (i + 1 - 2 di, j + 1 - 2 dj) of this window when that lies in [0, 2]
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    if (di == 1 && i == 0) continue;
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {
+                        if (dj == 1 && j == 0) continue;
+                        const uint32_t code = (uint32_t)((i + 1 - 2 * di) * 3 + (j + 1 - 2 * dj));
+#pragma unroll
+                        for (int e = 0; e < 8; ++e)
+                            if (((codes >> (4 * e)) & 0xfu) == code) acc[i * 2 + j][e] += g[e];
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+                st_global_v4(dxn + ((size_t)(2 * a + i) * W + 2 * b + j) * C + c8 * 8, float_to_bf16x8(acc[i * 2 + j]));
+    }
+}
+
 // global average pool: y[n, c] = mean_hw x[n, hw, c]
 __global__ void __launch_bounds__(256) avgpool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int N, int HW, int C) {
     const int vc = C >> 3;
@@ -160,6 +275,9 @@ __global__ void __launch_bounds__(256) nchw_to_nhwc8_kernel(const T* __restrict_
     }
 }
 
+// even image sizes take the row-per-block kernels (their index format differs: forward and backward decide alike)
+bool maxpool_even(int N, int H, int W) { return H % 2 == 0 && W % 2 == 0 && N <= 65535 && H >= 2 && W >= 2; }
+
 int grid_for(size_t total) {
     long long b = (long long)((total + 255) / 256);
     const long long cap = DDL_SM_COUNT * 16;
@@ -172,6 +290,12 @@ DDL_API int ddl_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, int H
     DDL_REQUIRE(C % 8 == 0, "maxpool: channels must be a multiple of 8");
     DDL_REQUIRE(x && y && idx, "maxpool: null pointer");
     const int OH = (H + 2 - 3) / 2 + 1, OW = (W + 2 - 3) / 2 + 1;
+    if (maxpool_even(N, H, W)) {  // idx: 4-bit tap codes, C / 2 bytes per output pixel (the buffer holds C)
+        DDL_REQUIRE(((uintptr_t)idx & 3) == 0, "maxpool: index buffer must be 4-byte aligned");
+        maxpool3x3s2_even_fwd_kernel<<<dim3(OH, N), 256, 0, (cudaStream_t)stream_>>>((const bf16*)x, (bf16*)y, (uint32_t*)idx, H, W, C, OH, OW);
+        DDL_LAUNCH_CHECK();
+        return 0;
+    }
     const size_t total = (size_t)N * OH * OW * (C / 8);
     maxpool3x3s2_fwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream_>>>((const bf16*)x, (bf16*)y, (unsigned char*)idx, N, H, W, C,
                                                                                OH, OW);
@@ -184,6 +308,12 @@ DDL_API int ddl_maxpool3x3s2_bwd_ex(const void* dy, const void* dy2, const void*
     DDL_REQUIRE(C % 8 == 0, "maxpool: channels must be a multiple of 8");
     DDL_REQUIRE(dy && dx && idx, "maxpool: null pointer");
     const int OH = (H + 2 - 3) / 2 + 1, OW = (W + 2 - 3) / 2 + 1;
+    if (maxpool_even(N, H, W)) {
+        maxpool3x3s2_even_bwd_kernel<<<dim3(H / 2, N), 256, 0, (cudaStream_t)stream_>>>((const bf16*)dy, (const bf16*)dy2, (const uint32_t*)idx,
+                                                                                        (bf16*)dx, H, W, C, OH, OW);
+        DDL_LAUNCH_CHECK();
+        return 0;
+    }
     const size_t total = (size_t)N * H * W * (C / 8);
     maxpool3x3s2_bwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream_>>>((const bf16*)dy, (const bf16*)dy2, (const unsigned char*)idx,
                                                                                (bf16*)dx, N, H, W, C, OH, OW);

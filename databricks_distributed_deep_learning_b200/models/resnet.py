@@ -150,6 +150,14 @@ class ResNet(nn.Module):
         return self
 
     def forward(self, x):
+        if self.impl == "fused" and x.is_cuda:
+            from ..ops import functional as OF
+
+            with OF.batches_counted_once(self):  # one kernel for all num_batches_tracked counters
+                return self._forward(x)
+        return self._forward(x)
+
+    def _forward(self, x):
         fused = self.impl == "fused" and x.is_cuda
         if fused:
             from ..ops import functional as OF

@@ -257,6 +257,33 @@ def residual_fork(x: torch.Tensor):
 
 
 # ----------------------------------------------------------------------------- batch norm
+_batches_counted_by_model = False
+
+
+class batches_counted_once:
+    """``with batches_counted_once(model):`` - the ``num_batches_tracked`` counters of every training-mode BatchNorm of
+    ``model`` are advanced by ONE multi-tensor kernel here instead of one tiny kernel per layer inside :func:`bn_act`
+    (53 launches per ResNet-50 step)."""
+
+    def __init__(self, model: nn.Module):
+        # (collected on every call: buffers are replaced by model.to(...) / load_state_dict(assign=True))
+        self.counters = [m.num_batches_tracked for m in model.modules()
+                         if isinstance(m, nn.modules.batchnorm._BatchNorm) and m.training and m.num_batches_tracked is not None]
+
+    def __enter__(self):
+        global _batches_counted_by_model
+        self.prev = _batches_counted_by_model
+        if self.counters and not self.prev:
+            torch._foreach_add_(self.counters, 1)
+        _batches_counted_by_model = True
+        return self
+
+    def __exit__(self, *exc):
+        global _batches_counted_by_model
+        _batches_counted_by_model = self.prev
+        return False
+
+
 class _BnAct(torch.autograd.Function):
     """x: NCHW-shaped tensor in channels_last memory (i.e. an NHWC matrix [M, C])."""
 
@@ -339,7 +366,7 @@ def bn_act(x, bn: nn.BatchNorm2d, relu: bool = True, residual: Optional[torch.Te
     if bn.running_mean is not None and (bn.running_mean.dtype != torch.float32 or bn.running_var.dtype != torch.float32):
         raise L.DdlError("fused BatchNorm keeps running_mean / running_var in float32 (got "
                          f"{bn.running_mean.dtype}); convert the model with models.prepare_for_fused() instead of .to(bfloat16)")
-    if training and bn.num_batches_tracked is not None:
+    if training and bn.num_batches_tracked is not None and not _batches_counted_by_model:
         bn.num_batches_tracked.add_(1)
     y = _BnAct.apply(x, residual, bn.weight, bn.bias, bn.running_mean, bn.running_var, training,
                      0.1 if bn.momentum is None else bn.momentum, bn.eps, relu, sums if training else None,
@@ -443,11 +470,14 @@ class _StemConv(torch.autograd.Function):
         ctx.geom = (N, H, W)
         ctx.wlike = weight  # only its shape / strides are used
         ctx.mark_non_differentiable(partials)
+        ctx.set_materialize_grads(False)  # no zero-filled gradient tensor for the statistics output on every backward
         return y, partials
 
     @staticmethod
     @once_differentiable
     def backward(ctx, dy, _unused):
+        if dy is None:  # (grads are not materialised: the convolution's output did not reach the loss)
+            return (None,) * 2
         (z,) = ctx.saved_tensors
         N, H, W = ctx.geom
         dev = z.device
@@ -511,12 +541,15 @@ class _Conv1x1(torch.autograd.Function):
         y = y2.view(N, H, W, Cout).permute(0, 3, 1, 2)       # NCHW-shaped, channels-last strides
         if want_stats:
             ctx.mark_non_differentiable(sums)
+            ctx.set_materialize_grads(False)
             return y, sums
         return y, None
 
     @staticmethod
     @once_differentiable
     def backward(ctx, dy, _dsums):
+        if dy is None:  # (grads are not materialised: the convolution's output did not reach the loss)
+            return (None,) * 3
         from . import gemm as G
 
         x2, w2 = ctx.saved_tensors
@@ -581,11 +614,14 @@ class _Conv1x1WS(torch.autograd.Function):
         L.call("ddl_conv1x1_fwd", x.data_ptr(), w2.data_ptr(), y.data_ptr(), partials.data_ptr(), M, Cout, Cin, L.stream_ptr(dev))
         ctx.save_for_backward(x, weight)
         ctx.mark_non_differentiable(partials)
+        ctx.set_materialize_grads(False)  # no zero-filled gradient tensor for the statistics output on every backward
         return y, partials
 
     @staticmethod
     @once_differentiable
     def backward(ctx, dy, _unused):
+        if dy is None:  # (grads are not materialised: the convolution's output did not reach the loss)
+            return (None,) * 2
         x, weight = ctx.saved_tensors
         if not dy.is_contiguous(memory_format=torch.channels_last):
             dy = dy.contiguous(memory_format=torch.channels_last)
@@ -675,11 +711,14 @@ class _ConvNative(torch.autograd.Function):
         ctx.save_for_backward(x, weight)
         ctx.geom = geom
         ctx.mark_non_differentiable(partials)
+        ctx.set_materialize_grads(False)  # no zero-filled gradient tensor for the statistics output on every backward
         return y, partials
 
     @staticmethod
     @once_differentiable
     def backward(ctx, dy, _unused):
+        if dy is None:  # (grads are not materialised: the convolution's output did not reach the loss)
+            return (None,) * 5
         x, weight = ctx.saved_tensors
         geom = ctx.geom
         dev = x.device
