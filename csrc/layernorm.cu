@@ -136,25 +136,30 @@ __global__ void __launch_bounds__(kLnThreads, (VPL <= 4 ? 2 : 1)) add_ln_fwd_ker
 // before the current one is processed (software pipeline across the row loop; without it each row paid a full memory
 // latency: 7 400 cycles per row measured).  To have registers for that, the dgamma / dbeta column sums of a warp live
 // in shared memory ([warp][which][k][half][lane] float4: conflict-free 512-byte rows) instead of 2 * VPL * 8 registers.
-template <int VPL>
+// COLSUM: a third column sum, of the gradient that leaves through the first input (dx when dropout is active, else dz):
+// that is the bias gradient of the linear layer in front of this LayerNorm, which then needs no column-sum pass of its own.
+template <int VPL, bool COLSUM>
 __global__ void __launch_bounds__(kLnThreads, (VPL <= 4 ? 2 : 1)) ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z,
                                                                const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
                                                                const bf16* __restrict__ gamma, bf16* __restrict__ dz,
                                                                bf16* __restrict__ dx, float* __restrict__ partials, int rows, int H,
                                                                DropCfg drop) {
     resolve_seed(drop);
-    extern __shared__ float4 ln_acc[];  // [kWarpsPerBlock][2][VPL][2][32]
+    extern __shared__ float4 ln_acc[];  // [kWarpsPerBlock][kAcc][VPL][2][32]
+    constexpr int kAcc = COLSUM ? 3 : 2;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nv = H >> 3;
     const float inv_h = 1.f / (float)H;
-    float4* acc_g = ln_acc + (size_t)(warp * 2 + 0) * VPL * 64;  // dgamma: [k][half][lane]
-    float4* acc_b = ln_acc + (size_t)(warp * 2 + 1) * VPL * 64;  // dbeta
+    float4* acc_g = ln_acc + (size_t)(warp * kAcc + 0) * VPL * 64;  // dgamma: [k][half][lane]
+    float4* acc_b = ln_acc + (size_t)(warp * kAcc + 1) * VPL * 64;  // dbeta
+    float4* acc_x = ln_acc + (size_t)(warp * kAcc + (COLSUM ? 2 : 0)) * VPL * 64;  // column sum of dx (COLSUM only)
 #pragma unroll
     for (int k = 0; k < VPL; ++k)
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             acc_g[(k * 2 + h) * 32 + lane] = make_float4(0.f, 0.f, 0.f, 0.f);
             acc_b[(k * 2 + h) * 32 + lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (COLSUM) acc_x[(k * 2 + h) * 32 + lane] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
     uint4 gam[VPL];
 #pragma unroll
@@ -226,10 +231,22 @@ __global__ void __launch_bounds__(kLnThreads, (VPL <= 4 ? 2 : 1)) ln_bwd_kernel(
                 bf16x8_to_float(gam[k], gm);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) o[j] = rstd * (d[j] * gm[j] - c1 - (zz[j] - mean) * rstd * c2);
-                st_global_v4(dz + off, float_to_bf16x8(o));
+                uint4 ov = float_to_bf16x8(o);
+                st_global_v4(dz + off, ov);
                 if (dx != nullptr && drop.thr) {
                     apply_dropout8(o, drop, ((size_t)row * nv + c));
-                    st_global_v4(dx + off, float_to_bf16x8(o));
+                    ov = float_to_bf16x8(o);
+                    st_global_v4(dx + off, ov);
+                }
+                if (COLSUM) {  // of the values as stored (bf16-rounded), like a column-sum pass over the tensor would see them
+                    float r[8];
+                    bf16x8_to_float(ov, r);
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        float4 a = acc_x[(k * 2 + h) * 32 + lane];
+                        a.x += r[4 * h + 0]; a.y += r[4 * h + 1]; a.z += r[4 * h + 2]; a.w += r[4 * h + 3];
+                        acc_x[(k * 2 + h) * 32 + lane] = a;
+                    }
                 }
             }
         }
@@ -241,18 +258,18 @@ __global__ void __launch_bounds__(kLnThreads, (VPL <= 4 ? 2 : 1)) ln_bwd_kernel(
         mean = nmean;
         rstd = nrstd;
     }
-    // block fold of the 8 warps' column sums -> this block's partial row [2][H]
+    // block fold of the 8 warps' column sums -> this block's partial row [kAcc][H]
     __syncthreads();
-    float* out = partials + (size_t)blockIdx.x * 2 * H;
+    float* out = partials + (size_t)blockIdx.x * kAcc * H;
     const float* accf = reinterpret_cast<const float*>(ln_acc);
-    for (int idx = threadIdx.x; idx < 2 * H; idx += blockDim.x) {
+    for (int idx = threadIdx.x; idx < kAcc * H; idx += blockDim.x) {
         const int which = idx / H, col = idx - which * H;
         const int c = col >> 3, e8 = col & 7;       // vector index, element inside the vector
         const int k = c >> 5, ln = c & 31, h = e8 >> 2, e = e8 & 3;
         float a = 0.f;
 #pragma unroll
         for (int w = 0; w < kWarpsPerBlock; ++w)
-            a += accf[((((size_t)(w * 2 + which) * VPL + k) * 2 + h) * 32 + ln) * 4 + e];
+            a += accf[((((size_t)(w * kAcc + which) * VPL + k) * 2 + h) * 32 + ln) * 4 + e];
         out[idx] = a;
     }
 }
@@ -262,31 +279,35 @@ __global__ void __launch_bounds__(kLnThreads, (VPL <= 4 ? 2 : 1)) ln_bwd_kernel(
 constexpr int kLnFoldWarps = 32;
 __global__ void __launch_bounds__(kLnFoldWarps * 32) ln_bwd_finalize_kernel(const float* __restrict__ partials, int nblocks, int H,
                                                                             bf16* __restrict__ dgamma, bf16* __restrict__ dbeta,
-                                                                            float* __restrict__ dgamma_f32, float* __restrict__ dbeta_f32) {
+                                                                            float* __restrict__ dgamma_f32, float* __restrict__ dbeta_f32,
+                                                                            int nacc, bf16* __restrict__ dxsum) {
     __shared__ float sh[kLnFoldWarps][33];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int i = blockIdx.x * 32 + lane;
+    const int tot = nacc * H;
     float a[4] = {0.f, 0.f, 0.f, 0.f};
-    if (i < 2 * H) {
+    if (i < tot) {
         int b = w;
         for (; b + 3 * kLnFoldWarps < nblocks; b += 4 * kLnFoldWarps) {
 #pragma unroll
-            for (int u = 0; u < 4; ++u) a[u] += partials[(size_t)(b + u * kLnFoldWarps) * 2 * H + i];
+            for (int u = 0; u < 4; ++u) a[u] += partials[(size_t)(b + u * kLnFoldWarps) * tot + i];
         }
-        for (; b < nblocks; b += kLnFoldWarps) a[0] += partials[(size_t)b * 2 * H + i];
+        for (; b < nblocks; b += kLnFoldWarps) a[0] += partials[(size_t)b * tot + i];
     }
     sh[w][lane] = (a[0] + a[1]) + (a[2] + a[3]);
     __syncthreads();
-    if (w != 0 || i >= 2 * H) return;
+    if (w != 0 || i >= tot) return;
     float acc = 0.f;
 #pragma unroll
     for (int k = 0; k < kLnFoldWarps; ++k) acc += sh[k][lane];
     if (i < H) {
         if (dgamma) dgamma[i] = __float2bfloat16(acc);
         if (dgamma_f32) dgamma_f32[i] = acc;
-    } else {
+    } else if (i < 2 * H) {
         if (dbeta) dbeta[i - H] = __float2bfloat16(acc);
         if (dbeta_f32) dbeta_f32[i - H] = acc;
+    } else if (dxsum) {
+        dxsum[i - 2 * H] = __float2bfloat16(acc);
     }
 }
 
@@ -422,35 +443,55 @@ DDL_API int ddl_add_layernorm_fwd(const void* x, const void* residual, const voi
 }
 
 DDL_API size_t ddl_layernorm_bwd_scratch_bytes(int rows, int H) { return (size_t)ln_grid(rows) * 2 * H * sizeof(float); }
+DDL_API size_t ddl_layernorm_bwd_colsum_scratch_bytes(int rows, int H) { return (size_t)ln_grid(rows) * 3 * H * sizeof(float); }
 
-DDL_API int ddl_layernorm_bwd(const void* dy, const void* z, const float* mean, const float* rstd, const void* gamma, void* dz,
-                              void* dx, void* dgamma, void* dbeta, int param_grad_dtype, void* scratch, size_t scratch_bytes, int rows,
-                              int H, float dropout_p, unsigned long long seed, const unsigned long long* seed_dev, void* stream_) {
+template <bool COLSUM>
+static int ln_bwd_impl(const void* dy, const void* z, const float* mean, const float* rstd, const void* gamma, void* dz, void* dx, void* dgamma,
+                       void* dbeta, void* dxsum, int param_grad_dtype, void* scratch, size_t scratch_bytes, int rows, int H, float dropout_p,
+                       unsigned long long seed, const unsigned long long* seed_dev, void* stream_) {
+    constexpr int kAcc = COLSUM ? 3 : 2;
     DDL_REQUIRE(H % 8 == 0 && H >= 8 && H <= 2048, "layernorm: hidden size %d must be a multiple of 8 and <= 2048", H);
-    DDL_REQUIRE(dy && z && mean && rstd && gamma && dz && scratch, "layernorm bwd: null pointer");
-    DDL_REQUIRE(scratch_bytes >= ddl_layernorm_bwd_scratch_bytes(rows, H), "layernorm bwd: scratch too small (%zu < %zu)", scratch_bytes,
-                ddl_layernorm_bwd_scratch_bytes(rows, H));
+    DDL_REQUIRE(dy && z && mean && rstd && gamma && dz && scratch && (!COLSUM || dxsum), "layernorm bwd: null pointer");
+    const size_t need = (size_t)ln_grid(rows) * kAcc * H * sizeof(float);
+    DDL_REQUIRE(scratch_bytes >= need, "layernorm bwd: scratch too small (%zu < %zu)", scratch_bytes, need);
     if (rows == 0) return 0;
     const DropCfg d = make_drop(dropout_p, seed, seed_dev);
     const int grid = ln_grid(rows);
     cudaStream_t s = (cudaStream_t)stream_;
     LN_DISPATCH(H, ({
-                    const int smem = kWarpsPerBlock * 2 * VPL * 64 * (int)sizeof(float4);
-                    static bool attr_set = false;  // one per VPL instantiation
+                    const int smem = kWarpsPerBlock * kAcc * VPL * 64 * (int)sizeof(float4);
+                    static bool attr_set = false;  // one per (VPL, COLSUM) instantiation
                     if (!attr_set) {
-                        DDL_CHECK(cudaFuncSetAttribute(ln_bwd_kernel<VPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+                        DDL_CHECK(cudaFuncSetAttribute(ln_bwd_kernel<VPL, COLSUM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
                         attr_set = true;
                     }
-                    ln_bwd_kernel<VPL><<<grid, kLnThreads, smem, s>>>((const bf16*)dy, (const bf16*)z, mean, rstd, (const bf16*)gamma,
-                                                                      (bf16*)dz, (bf16*)dx, (float*)scratch, rows, H, d);
+                    ln_bwd_kernel<VPL, COLSUM><<<grid, kLnThreads, smem, s>>>((const bf16*)dy, (const bf16*)z, mean, rstd, (const bf16*)gamma,
+                                                                              (bf16*)dz, (bf16*)dx, (float*)scratch, rows, H, d);
                 }));
     DDL_LAUNCH_CHECK();
     const bool f32 = param_grad_dtype == DDL_F32;
-    ln_bwd_finalize_kernel<<<ddl_ceil_div(2 * H, 32), kLnFoldWarps * 32, 0, s>>>((const float*)scratch, grid, H, f32 ? nullptr : (bf16*)dgamma,
-                                                                    f32 ? nullptr : (bf16*)dbeta, f32 ? (float*)dgamma : nullptr,
-                                                                    f32 ? (float*)dbeta : nullptr);
+    ln_bwd_finalize_kernel<<<ddl_ceil_div(kAcc * H, 32), kLnFoldWarps * 32, 0, s>>>(
+        (const float*)scratch, grid, H, f32 ? nullptr : (bf16*)dgamma, f32 ? nullptr : (bf16*)dbeta, f32 ? (float*)dgamma : nullptr,
+        f32 ? (float*)dbeta : nullptr, kAcc, (bf16*)dxsum);
     DDL_LAUNCH_CHECK();
     return 0;
+}
+
+DDL_API int ddl_layernorm_bwd(const void* dy, const void* z, const float* mean, const float* rstd, const void* gamma, void* dz,
+                              void* dx, void* dgamma, void* dbeta, int param_grad_dtype, void* scratch, size_t scratch_bytes, int rows,
+                              int H, float dropout_p, unsigned long long seed, const unsigned long long* seed_dev, void* stream_) {
+    return ln_bwd_impl<false>(dy, z, mean, rstd, gamma, dz, dx, dgamma, dbeta, nullptr, param_grad_dtype, scratch, scratch_bytes, rows, H,
+                              dropout_p, seed, seed_dev, stream_);
+}
+
+// as ddl_layernorm_bwd, plus dxsum [H] bf16 = column sums of the gradient of the first input (dx if dropout is active, else dz) =
+// the bias gradient of a linear layer that produced that input.  scratch: ddl_layernorm_bwd_colsum_scratch_bytes(rows, H).
+DDL_API int ddl_layernorm_bwd_colsum(const void* dy, const void* z, const float* mean, const float* rstd, const void* gamma, void* dz,
+                                     void* dx, void* dgamma, void* dbeta, void* dxsum, int param_grad_dtype, void* scratch,
+                                     size_t scratch_bytes, int rows, int H, float dropout_p, unsigned long long seed,
+                                     const unsigned long long* seed_dev, void* stream_) {
+    return ln_bwd_impl<true>(dy, z, mean, rstd, gamma, dz, dx, dgamma, dbeta, dxsum, param_grad_dtype, scratch, scratch_bytes, rows, H,
+                             dropout_p, seed, seed_dev, stream_);
 }
 
 DDL_API int ddl_embed_layernorm_fwd(const long long* ids, const long long* token_types, const void* word, const void* pos,

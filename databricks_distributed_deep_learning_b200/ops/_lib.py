@@ -61,6 +61,8 @@ _PROTOS = {
     "ddl_add_layernorm_fwd": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _f, _f, _u64, _vp, _vp], _i),
     "ddl_layernorm_bwd_scratch_bytes": ([_i, _i], _sz),
     "ddl_layernorm_bwd": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _i, _i, _f, _u64, _vp, _vp], _i),
+    "ddl_layernorm_bwd_colsum_scratch_bytes": ([_i, _i], _sz),
+    "ddl_layernorm_bwd_colsum": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _i, _i, _f, _u64, _vp, _vp], _i),
     "ddl_embed_layernorm_fwd": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _f, _u64, _vp, _vp], _i),
     "ddl_dropout": ([_vp, _vp, _sz, _f, _u64, _vp, _vp], _i),
     "ddl_cross_entropy": ([_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _f, _ll, _vp], _i),

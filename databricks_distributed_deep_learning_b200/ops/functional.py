@@ -115,12 +115,23 @@ class _AddLayerNorm(torch.autograd.Function):
         dz = torch.empty_like(z)
         dx = torch.empty_like(z) if ctx.p > 0 else None
         dgamma, dbeta = torch.empty_like(gamma), torch.empty_like(gamma)
-        nbytes = L.lib().ddl_layernorm_bwd_scratch_bytes(rows, H)
-        scratch = _scratch(nbytes, dev)
         sw = seed_word(dev) if ctx.p > 0 else None
-        L.call("ddl_layernorm_bwd", dy.data_ptr(), z.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(), dz.data_ptr(),
-               L.ptr(dx), dgamma.data_ptr(), dbeta.data_ptr(), L.DDL_BF16, scratch.data_ptr(), scratch.numel(), rows, H,
-               float(ctx.p), ctx.salt, L.ptr(sw), L.stream_ptr(dev))
+        if ctx.needs_input_grad[0]:
+            # the column sums of the first input's gradient come out of the same pass: if that input was produced by a
+            # linear layer, this IS its bias gradient (ops/gemm.py picks it up instead of running a column-sum pass)
+            from . import gemm as G
+
+            dxsum = torch.empty_like(gamma)
+            scratch = _scratch(L.lib().ddl_layernorm_bwd_colsum_scratch_bytes(rows, H), dev)
+            L.call("ddl_layernorm_bwd_colsum", dy.data_ptr(), z.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(),
+                   dz.data_ptr(), L.ptr(dx), dgamma.data_ptr(), dbeta.data_ptr(), dxsum.data_ptr(), L.DDL_BF16, scratch.data_ptr(),
+                   scratch.numel(), rows, H, float(ctx.p), ctx.salt, L.ptr(sw), L.stream_ptr(dev))
+            G.offer_colsum(dx if dx is not None else dz, dxsum)
+        else:
+            scratch = _scratch(L.lib().ddl_layernorm_bwd_scratch_bytes(rows, H), dev)
+            L.call("ddl_layernorm_bwd", dy.data_ptr(), z.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(), dz.data_ptr(),
+                   L.ptr(dx), dgamma.data_ptr(), dbeta.data_ptr(), L.DDL_BF16, scratch.data_ptr(), scratch.numel(), rows, H,
+                   float(ctx.p), ctx.salt, L.ptr(sw), L.stream_ptr(dev))
         dres = dz if (ctx.has_res and ctx.needs_input_grad[1]) else None
         if dres is not None and ctx.res_slot is not None:
             ctx.res_slot.put(dres)  # added in the epilogue of the data-gradient GEMM that owns the slot (ops/gemm.py::GradSlot)

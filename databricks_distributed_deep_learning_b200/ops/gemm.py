@@ -122,6 +122,30 @@ def colsum(x: torch.Tensor) -> torch.Tensor:
     return out
 
 
+# Column sums that an upstream backward kernel produced together with a gradient tensor (LayerNorm backward: the sums of
+# the gradient of its first input).  Keyed by the gradient's address; the entry keeps the tensor alive until it is taken or
+# the backward pass ends, so the address cannot be handed to another tensor in between.
+_colsum_offers = {}
+
+
+def _clear_colsum_offers() -> None:
+    _colsum_offers.clear()
+
+
+def offer_colsum(grad: torch.Tensor, sums: torch.Tensor) -> None:
+    if not _colsum_offers:
+        torch.autograd.Variable._execution_engine.queue_callback(_clear_colsum_offers)
+    _colsum_offers[grad.data_ptr()] = (grad, sums)
+
+
+def _bias_grad(dy: torch.Tensor) -> torch.Tensor:
+    """Column sums of ``dy``: taken from the kernel that produced ``dy`` when it offered them, else a column-sum pass."""
+    ent = _colsum_offers.pop(dy.data_ptr(), None)
+    if ent is not None and ent[0].shape == dy.shape and ent[0].stride() == dy.stride() and ent[1].shape[0] == dy.shape[1]:
+        return ent[1]
+    return colsum(dy)
+
+
 # Where a weight's gradient should be written: id(parameter) -> (weak reference to it, 2-D bf16 view of its slot in the
 # flat gradient bucket), registered by the DDP / FSDP wrappers.  The weight-gradient GEMM then writes there directly,
 # autograd adopts that view as .grad, and the wrapper's gradient collection has nothing left to copy for this parameter.
@@ -243,7 +267,7 @@ class _Linear(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = gemm_nt(dy, weight, M, K, N, b_mn=True, residual=addend)  # + skip gradient in the epilogue
         dw = _wgrad(dy, x, weight) if ctx.needs_input_grad[1] else None
-        db = colsum(dy) if ctx.has_bias and ctx.needs_input_grad[2] else None
+        db = _bias_grad(dy) if ctx.has_bias and ctx.needs_input_grad[2] else None
         return dx, dw, db, dres, None, None, None
 
 
@@ -291,10 +315,12 @@ class _FFN(torch.autograd.Function):
         I = w1.shape[0]
         O = w2.shape[0]
         dw2 = _wgrad(dy, h, w2)
-        db2 = colsum(dy)
-        dpre = gemm_nt(dy, w2, M, I, O, b_mn=True, aux=pre, epilogue=EPI_DGELU)  # (dy W2) * gelu'(pre)
+        db2 = _bias_grad(dy)
+        # (dy W2) * gelu'(pre); the epilogue also accumulates the column sums of what it stores = the bias gradient of W1
+        stats = torch.zeros(2, I, dtype=torch.float32, device=x.device)
+        dpre = gemm_nt(dy, w2, M, I, O, b_mn=True, aux=pre, epilogue=EPI_DGELU, col_stats=stats)
         dw1 = _wgrad(dpre, x, w1)
-        db1 = colsum(dpre)
+        db1 = stats[0].to(torch.bfloat16)
         dres = dy if (ctx.has_res and ctx.needs_input_grad[5]) else None
         addend = ctx.in_slot.take() if ctx.in_slot is not None else None
         if dres is not None and ctx.res_is_input and addend is None and ctx.needs_input_grad[0]:

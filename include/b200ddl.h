@@ -92,6 +92,12 @@ size_t ddl_layernorm_bwd_scratch_bytes(int rows, int H);
 int ddl_layernorm_bwd(const void* dy, const void* z, const float* mean, const float* rstd, const void* gamma, void* dz, void* dx,
                       void* dgamma, void* dbeta, int param_grad_dtype, void* scratch, size_t scratch_bytes, int rows, int H,
                       float dropout_p, unsigned long long seed, const unsigned long long* seed_dev, void* stream);
+/* as ddl_layernorm_bwd, plus dxsum [H] bf16 = column sums of the gradient of the first input (dx when dropout is active, else
+ * dz): the bias gradient of the linear layer that produced that input.  scratch: ddl_layernorm_bwd_colsum_scratch_bytes. */
+size_t ddl_layernorm_bwd_colsum_scratch_bytes(int rows, int H);
+int ddl_layernorm_bwd_colsum(const void* dy, const void* z, const float* mean, const float* rstd, const void* gamma, void* dz, void* dx,
+                             void* dgamma, void* dbeta, void* dxsum, int param_grad_dtype, void* scratch, size_t scratch_bytes, int rows,
+                             int H, float dropout_p, unsigned long long seed, const unsigned long long* seed_dev, void* stream);
 int ddl_embed_layernorm_fwd(const long long* ids, const long long* token_types, const void* word, const void* pos,
                             const void* type, const void* gamma, const void* beta, void* z_out, void* y, float* mean, float* rstd,
                             int rows, int S, int H, float eps, float dropout_p, unsigned long long seed,
