@@ -17,7 +17,8 @@ LIB = os.path.join(ROOT, "databricks_distributed_deep_learning_b200", "ops", "li
 OUT = os.path.join(ROOT, "profiles", "sass")
 KEY = re.compile(r"^(UTC\w+|UTMA\w+|LDTM|STTM|SYNCS|UBLKCP|MULTIMEM|LDGMC|RED|ATOM|HMMA|LDGSTS|LDG|STG|LDS|STS|BAR|MEMBAR|ERRBAR|UTCBAR|FFMA|MUFU|SHFL|CCTL)")
 FULL = ("gemm_bf16_kernelILi256ELb0ELb0ELi4ELi2", "attn_fwd_kernelILi1", "attn_bwd_kernel", "allreduce_nvls_kernelILb1",
-        "allreduce_twoshot_kernelI13__nv_bfloat16S1_Li8", "gemm2sm_bf16_kernelILb0ELb0", "stem_fwd_kernel", "stem_wgrad_kernel", "conv1x1_fwd_kernel", "attn_fwd_stream_kernel")
+        "allreduce_twoshot_kernelI13__nv_bfloat16S1_Li8", "gemm2sm_bf16_kernelILb0ELb0", "stem_fwd_kernel", "stem_wgrad_kernel", "conv1x1_fwd_kernel", "attn_fwd_stream_kernel",
+        "conv_halo_kernelILb0ELi2ELb1", "conv_halo_kernelILb1ELi2ELb0", "conv_data_kernelILb0", "conv_data_kernelILb1", "conv_wgrad_kernel")
 
 
 def main():
