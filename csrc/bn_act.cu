@@ -359,6 +359,249 @@ __global__ void __launch_bounds__(kBnMaxThreads) bn_bwd_apply_kernel(const bf16*
     }
 }
 
+// ---- stem: BatchNorm + ReLU + 3x3/2 max pool in one forward and two backward kernels --------------------------------------
+// relu(maxpool(bn(x))) = maxpool(relu(bn(x))): the normalised 112 x 112 activation (411 MB at batch 256) is never written or
+// read; the pooled tensor and a 4-bit code per pooled element (winning tap 0..8, or 15 = "pooled value is 0: no gradient")
+// carry everything the backward needs.  Even H and W only (every window starts at an even pixel - 1).
+//   forward : block = one output row of one image; z = x * scale + shift in fp32 for the 9 taps, lowest tap wins a tie
+//   reduce  : elementwise over the pooled tensors: g = (dy + dy2) where y > 0; partial sum(g), sum(g * (x - mean)) per channel in
+//             the layout of bn_bwd_reduce_kernel, with (x - mean) recovered from y (see the kernel)
+//   apply   : thread = 2 x 2 input patch x 8 channels; the gradient of a pixel is the sum of g over the (at most four) windows
+//             whose winning tap is that pixel; dx = a * (g - b - (x - mean) * c) with the coefficients of bn_bwd_finalize_kernel
+
+__device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+__device__ __forceinline__ uint32_t bf16x2_min(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm("min.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+// 0xffff in each half where a == b
+__device__ __forceinline__ uint32_t bf16x2_eq_mask(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm("set.eq.u32.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+
+// z = x * scale + shift is monotonic in x per channel, so the window's winner is the largest x where scale > 0 and the
+// smallest x where scale < 0: maximum AND minimum are taken on packed bf16 pairs, the winner's tap is found by comparing the
+// taps with it, last to first (lowest tap wins a tie, as ATen does on equal values), and z is evaluated once per element.
+__global__ void __launch_bounds__(256) bn_relu_pool_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ scale,
+                                                                const float* __restrict__ shift, bf16* __restrict__ y,
+                                                                uint32_t* __restrict__ codes, int H, int W, int C, int OH, int OW) {
+    const int vc = C >> 3, oh = blockIdx.x, n = blockIdx.y;
+    const bf16* xin = x + (size_t)n * H * W * C;
+    const size_t orow = ((size_t)n * OH + oh) * OW;
+    const int c8 = threadIdx.x % vc;  // blockDim.x is a multiple of vc: the same for every item of this thread
+    float sc[8], sf[8];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        *reinterpret_cast<float4*>(&sc[4 * h]) = *reinterpret_cast<const float4*>(scale + c8 * 8 + 4 * h);
+        *reinterpret_cast<float4*>(&sf[4 * h]) = *reinterpret_cast<const float4*>(shift + c8 * 8 + 4 * h);
+    }
+    uint32_t use_max[4];  // 0xffff in the halves whose channel has scale >= 0
+#pragma unroll
+    for (int q = 0; q < 4; ++q) use_max[q] = (sc[2 * q] >= 0.f ? 0x0000ffffu : 0u) | (sc[2 * q + 1] >= 0.f ? 0xffff0000u : 0u);
+    for (int t = threadIdx.x; t < OW * vc; t += blockDim.x) {
+        const int ow = t / vc;
+        const bool top = oh == 0, left = ow == 0;  // taps of row 0 / column 0 lie outside the image there
+        uint4 v[9];
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
+                // an outside tap is replaced by the centre tap: a duplicate changes neither the maximum nor the minimum
+                const int ih = oh * 2 - 1 + ((kh == 0 && top) ? 1 : kh), iw = ow * 2 - 1 + ((kw == 0 && left) ? 1 : kw);
+                v[kh * 3 + kw] = ld_global_v4(xin + ((size_t)ih * W + iw) * C + c8 * 8);
+            }
+        float best[8];
+        uint32_t packed = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint32_t mx = reinterpret_cast<const uint32_t*>(&v[0])[q], mn = mx;
+#pragma unroll
+            for (int tap = 1; tap < 9; ++tap) {
+                const uint32_t w = reinterpret_cast<const uint32_t*>(&v[tap])[q];
+                mx = bf16x2_max(mx, w);
+                mn = bf16x2_min(mn, w);
+            }
+            const uint32_t win = (mx & use_max[q]) | (mn & ~use_max[q]);
+            uint32_t a = 0;
+#pragma unroll
+            for (int tap = 8; tap >= 0; --tap) {
+                if ((tap < 3 && top) || (tap % 3 == 0 && left)) continue;  // not a tap of this window
+                const uint32_t eq = bf16x2_eq_mask(reinterpret_cast<const uint32_t*>(&v[tap])[q], win);
+                a = (a & ~eq) | ((uint32_t)tap * 0x00010001u & eq);
+            }
+            const float z0 = fmaf(__uint_as_float(win << 16), sc[2 * q], sf[2 * q]);
+            const float z1 = fmaf(__uint_as_float(win & 0xffff0000u), sc[2 * q + 1], sf[2 * q + 1]);
+            best[2 * q] = z0 > 0.f ? z0 : 0.f;
+            best[2 * q + 1] = z1 > 0.f ? z1 : 0.f;
+            packed |= ((z0 > 0.f ? (a & 0xfu) : 15u) | ((z1 > 0.f ? ((a >> 16) & 0xfu) : 15u) << 4)) << (8 * q);
+        }
+        const size_t o = orow + ow;
+        st_global_v4(y + o * C + c8 * 8, float_to_bf16x8(best));
+        codes[o * vc + c8] = packed;
+    }
+}
+
+// The winning tap's x never has to be fetched: where a gradient passes, the pooled value IS the normalised winner,
+// y = (x - mean) * invstd * gamma + beta, so (x - mean) = (y - beta) / (gamma * invstd) (y carries bf16 rounding, 2^-9
+// relative - noise for a sum over ~10^5 pixels per channel; a channel with gamma == 0 contributes 0 to sum(g * (x - mean)),
+// its dx is 0 anyway).  The pass is then elementwise over the POOLED tensors only.
+__global__ void __launch_bounds__(kBnMaxThreads) bn_relu_pool_bwd_reduce_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ dy2,
+                                                                                 const bf16* __restrict__ y, const bf16* __restrict__ gamma,
+                                                                                 const bf16* __restrict__ beta, const float* __restrict__ invstd,
+                                                                                 float* __restrict__ partials, size_t nvec, int vec_cols,
+                                                                                 int C) {
+    extern __shared__ float sh[];
+    const int vc = (int)(((size_t)blockIdx.x * blockDim.x + threadIdx.x) % vec_cols);
+    float bt[8], rs[8], s[8], q[8];
+    {
+        float gm[8], is[8];
+        bf16x8_to_float(ld_global_v4(gamma + vc * 8), gm);
+        bf16x8_to_float(ld_global_v4(beta + vc * 8), bt);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) *reinterpret_cast<float4*>(&is[4 * h]) = *reinterpret_cast<const float4*>(invstd + vc * 8 + 4 * h);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float d = gm[j] * is[j];
+            rs[j] = d != 0.f ? 1.f / d : 0.f;
+            s[j] = q[j] = 0.f;
+        }
+    }
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t v0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v0 < nvec; v0 += stride * kUnroll) {
+        uint4 ud[kUnroll], u2[kUnroll], uy[kUnroll];
+#pragma unroll
+        for (int k = 0; k < kUnroll; ++k)
+            if (v0 + k * stride < nvec) {
+                ud[k] = ld_stream_v4(dy + (v0 + k * stride) * 8);
+                if (dy2) u2[k] = ld_stream_v4(dy2 + (v0 + k * stride) * 8);
+                uy[k] = ld_stream_v4(y + (v0 + k * stride) * 8);
+            }
+#pragma unroll
+        for (int k = 0; k < kUnroll; ++k)
+            if (v0 + k * stride < nvec) {
+                float g[8], yy[8];
+                bf16x8_to_float(ud[k], g);
+                bf16x8_to_float(uy[k], yy);
+                if (dy2) {
+                    float g2[8];
+                    bf16x8_to_float(u2[k], g2);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) g[j] += g2[j];
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float gj = yy[j] > 0.f ? g[j] : 0.f;
+                    s[j] += gj;
+                    q[j] = fmaf(gj, yy[j] - bt[j], q[j]);
+                }
+            }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) q[j] *= rs[j];
+    fold_to_partials(s, q, vec_cols, C, partials + (size_t)blockIdx.x * 2 * C, sh);
+}
+
+__global__ void __launch_bounds__(256, 2) bn_relu_pool_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ dy2,
+                                                                      const uint32_t* __restrict__ codes, const bf16* __restrict__ x,
+                                                                      const float* __restrict__ mean, const float* __restrict__ coef,
+                                                                      bf16* __restrict__ dx, int H, int W, int C, int OH, int OW) {
+    const int vc = C >> 3, a_ = blockIdx.x, n = blockIdx.y;  // input rows 2 a_, 2 a_ + 1
+    const int c8 = threadIdx.x % vc;
+    // dx = a * (g - b - (x - mean) * c) = ka * g + kx * x + k0   (three coefficient vectors in registers instead of four)
+    float ka[8], kx[8], k0[8];
+    {
+        float mu[8], kb[8], kc[8];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            *reinterpret_cast<float4*>(&mu[4 * h]) = *reinterpret_cast<const float4*>(mean + c8 * 8 + 4 * h);
+            *reinterpret_cast<float4*>(&ka[4 * h]) = *reinterpret_cast<const float4*>(coef + c8 * 8 + 4 * h);
+            *reinterpret_cast<float4*>(&kb[4 * h]) = *reinterpret_cast<const float4*>(coef + C + c8 * 8 + 4 * h);
+            *reinterpret_cast<float4*>(&kc[4 * h]) = *reinterpret_cast<const float4*>(coef + 2 * C + c8 * 8 + 4 * h);
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            kx[e] = -ka[e] * kc[e];
+            k0[e] = ka[e] * (kc[e] * mu[e] - kb[e]);
+        }
+    }
+    const bf16* xin = x + (size_t)n * H * W * C;
+    bf16* dxn = dx + (size_t)n * H * W * C;
+    for (int t = threadIdx.x; t < OW * vc; t += blockDim.x) {
+        const int b = t / vc;  // input columns 2b, 2b + 1
+        uint4 xv[4];
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int j = 0; j < 2; ++j) xv[i * 2 + j] = ld_stream_v4(xin + ((size_t)(2 * a_ + i) * W + 2 * b + j) * C + c8 * 8);
+        // all loads of the item first (the four windows' codes and gradients are independent of each other and of x):
+        // with the loads behind per-window branches this kernel ran latency-bound at 2.4x its memory time
+        uint32_t cdw[4];
+        uint4 gv[4], g2v[4];
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            const int oh = a_ + (w >> 1), ow = b + (w & 1);
+            const bool ok = oh < OH && ow < OW;
+            const size_t o = ((size_t)n * OH + (ok ? oh : a_)) * OW + (ok ? ow : b);
+            const uint32_t c = codes[o * vc + c8];
+            cdw[w] = ok ? c : 0xffffffffu;  // 15 in every nibble matches no tap
+            gv[w] = ld_global_v4(dy + o * C + c8 * 8);
+            if (dy2) g2v[w] = ld_global_v4(dy2 + o * C + c8 * 8);
+        }
+        float acc[4][8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[i][e] = 0.f;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            const int di = w >> 1, dj = w & 1;
+            const uint32_t cd = cdw[w];
+            float g[8];
+            bf16x8_to_float(gv[w], g);
+            if (dy2) {
+                float g2[8];
+                bf16x8_to_float(g2v[w], g2);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) g[e] += g2[e];
+            }
+            // pixel (i, j) of the patch is tap (i + 1 - 2 di, j + 1 - 2 dj) of this window when that lies in [0, 2]
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                if (di == 1 && i == 0) continue;
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    if (dj == 1 && j == 0) continue;
+                    // bit 4e + 3 of m is set where nibble e of the code word equals this tap (exact: no carry crosses a nibble)
+                    const uint32_t t_ = cd ^ ((uint32_t)((i + 1 - 2 * di) * 3 + (j + 1 - 2 * dj)) * 0x11111111u);
+                    const uint32_t m = ~(((t_ & 0x77777777u) + 0x77777777u) | t_) & 0x88888888u;
+#pragma unroll
+                    for (int e = 0; e < 8; ++e)
+                        if (m & (8u << (4 * e))) acc[i * 2 + j][e] += g[e];
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float xx[8], o8[8];
+            bf16x8_to_float(xv[i], xx);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) o8[e] = fmaf(ka[e], acc[i][e], fmaf(kx[e], xx[e], k0[e]));
+            st_global_v4(dxn + ((size_t)(2 * a_ + (i >> 1)) * W + 2 * b + (i & 1)) * C + c8 * 8, float_to_bf16x8(o8));
+        }
+    }
+}
+
+bool bn_pool_ok(int N, int H, int W, int C) {
+    return N >= 1 && N <= 65535 && H >= 2 && W >= 2 && H % 2 == 0 && W % 2 == 0 && C % 8 == 0 && C >= 8 && C <= 2048 && 256 % (C / 8) == 0;
+}
+
 size_t smem_bytes(const BnGeom& g) { return (size_t)g.threads * 17 * sizeof(float); }
 
 }  // namespace
@@ -502,6 +745,59 @@ DDL_API int ddl_bn_act_bwd(const void* dy, const void* y, const void* x, const v
                              scratch_bytes, M, C, relu, stream_);
 }
 
+// ---- stem: BatchNorm + ReLU + max pool (see the kernels above) ----------------------------------------------------------
+DDL_API int ddl_bn_relu_maxpool_supported(int N, int H, int W, int C) { return bn_pool_ok(N, H, W, C) ? 1 : 0; }
+
+// scratch of the backward: the partials + coefficients of a BatchNorm backward over the pooled tensor
+DDL_API size_t ddl_bn_relu_maxpool_bwd_scratch_bytes(int N, int H, int W, int C) {
+    if (!bn_pool_ok(N, H, W, C)) return 0;
+    return ddl_bn_scratch_bytes((long long)N * (H / 2) * (W / 2), C);
+}
+
+// x [N, H, W, C] bf16 = the convolution output; statistics as per-CTA partials [nblocks][2][C] (as for
+// ddl_bn_act_fwd_train_from_partials); y [N, H/2, W/2, C] bf16 = maxpool3x3s2(relu(bn(x))); codes: N * H/2 * W/2 * C/2 bytes.
+DDL_API int ddl_bn_relu_maxpool_fwd_train(const void* x, const void* gamma, const void* beta, float* running_mean, float* running_var,
+                                          void* y, void* codes, float* mean, float* invstd, float* scale, float* shift,
+                                          const float* partials, int nblocks, int N, int H, int W, int C, float eps, float momentum,
+                                          void* stream_) {
+    DDL_REQUIRE(bn_pool_ok(N, H, W, C), "bn + relu + maxpool: unsupported shape (N %d, %d x %d, C %d)", N, H, W, C);
+    DDL_REQUIRE(x && y && codes && mean && invstd && scale && shift && partials && nblocks >= 1, "bn + relu + maxpool fwd: null pointer");
+    DDL_REQUIRE(((uintptr_t)codes & 3) == 0, "bn + relu + maxpool: code buffer must be 4-byte aligned");
+    cudaStream_t s = (cudaStream_t)stream_;
+    const long long M = (long long)N * H * W;
+    bn_fwd_finalize_kernel<<<ddl_ceil_div(C, 32), kFoldThreads, 0, s>>>(partials, nblocks, M, C, (const bf16*)gamma, (const bf16*)beta,
+                                                                        running_mean, running_var, momentum, eps, mean, invstd, scale, shift);
+    DDL_LAUNCH_CHECK();
+    bn_relu_pool_fwd_kernel<<<dim3(H / 2, N), 256, 0, s>>>((const bf16*)x, scale, shift, (bf16*)y, (uint32_t*)codes, H, W, C, H / 2, W / 2);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+// dy (+ optional dy2) and y (the forward's output) [N, H/2, W/2, C] -> dx [N, H, W, C], dgamma, dbeta
+DDL_API int ddl_bn_relu_maxpool_bwd(const void* dy, const void* dy2, const void* y, const void* codes, const void* x, const void* gamma,
+                                    const void* beta, const float* mean, const float* invstd, void* dx, void* dgamma, void* dbeta,
+                                    int param_grad_dtype, void* scratch, size_t scratch_bytes, int N, int H, int W, int C, void* stream_) {
+    DDL_REQUIRE(bn_pool_ok(N, H, W, C), "bn + relu + maxpool: unsupported shape (N %d, %d x %d, C %d)", N, H, W, C);
+    DDL_REQUIRE(dy && y && codes && x && gamma && beta && mean && invstd && dx && scratch, "bn + relu + maxpool bwd: null pointer");
+    DDL_REQUIRE(scratch_bytes >= ddl_bn_relu_maxpool_bwd_scratch_bytes(N, H, W, C), "bn + relu + maxpool bwd: scratch too small");
+    cudaStream_t s = (cudaStream_t)stream_;
+    const int OH = H / 2, OW = W / 2;
+    BnGeom g;
+    if (int e = make_geom((long long)N * OH * OW, C, &g)) return e;
+    float* partials = (float*)scratch;
+    float* coef = partials + (size_t)g.grid * 2 * C;
+    bn_relu_pool_bwd_reduce_kernel<<<g.grid, g.threads, smem_bytes(g), s>>>((const bf16*)dy, (const bf16*)dy2, (const bf16*)y, (const bf16*)gamma,
+                                                                            (const bf16*)beta, invstd, partials, g.nvec, g.vec_cols, C);
+    DDL_LAUNCH_CHECK();
+    bn_bwd_finalize_kernel<<<ddl_ceil_div(C, 32), kFoldThreads, 0, s>>>(partials, g.grid, (long long)N * H * W, C, (const bf16*)gamma, invstd,
+                                                                        dgamma, dbeta, param_grad_dtype, coef);
+    DDL_LAUNCH_CHECK();
+    bn_relu_pool_bwd_apply_kernel<<<dim3(H / 2, N), 256, 0, s>>>((const bf16*)dy, (const bf16*)dy2, (const uint32_t*)codes, (const bf16*)x, mean,
+                                                                 coef, (bf16*)dx, H, W, C, OH, OW);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
 // ---------------------------------------------------------------------------------------
 // Allocation-free variant of ddl_bn_act_fwd_train.
 //
@@ -527,6 +823,7 @@ DDL_API int ddl_bn_act_bwd(const void* dy, const void* y, const void* x, const v
 //    threads) race on the array and corrupt each other's statistics: serialise them.
 //  * No cudaMalloc / cudaFree / allocating library routine is called on this path.
 #define DDL_BN_NOALLOC_MAX_FLOATS (DDL_BN_NOALLOC_MAX_BYTES / sizeof(float))
+
 static __device__ __align__(256) float g_bn_noalloc_scratch[DDL_BN_NOALLOC_MAX_FLOATS];
 
 namespace {

@@ -180,39 +180,49 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_even_bwd_kernel(const bf16* 
     bf16* dxn = dx + (size_t)n * H * W * C;
     for (int t = threadIdx.x; t < OW * vc; t += blockDim.x) {
         const int b = t / vc, c8 = t - b * vc;  // input columns 2b, 2b + 1
+        // all loads of the item first (with them behind per-window branches the kernel ran latency-bound)
+        uint32_t cdw[4];
+        uint4 gv[4], g2v[4];
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            const int oh = a + (w >> 1), ow = b + (w & 1);
+            const bool ok = oh < OH && ow < OW;
+            const size_t o = ((size_t)n * OH + (ok ? oh : a)) * OW + (ok ? ow : b);
+            const uint32_t c = idx[o * vc + c8];
+            cdw[w] = ok ? c : 0xffffffffu;  // 15 in every nibble matches no tap
+            gv[w] = ld_global_v4(dy + o * C + c8 * 8);
+            if (dy2) g2v[w] = ld_global_v4(dy2 + o * C + c8 * 8);
+        }
         float acc[4][8];
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
             for (int e = 0; e < 8; ++e) acc[i][e] = 0.f;
 #pragma unroll
-        for (int di = 0; di < 2; ++di) {
+        for (int w = 0; w < 4; ++w) {
+            const int di = w >> 1, dj = w & 1;
+            const uint32_t codes = cdw[w];
+            float g[8];
+            bf16x8_to_float(gv[w], g);
+            if (dy2) {
+                float g2[8];
+                bf16x8_to_float(g2v[w], g2);
 #pragma unroll
-            for (int dj = 0; dj < 2; ++dj) {
-                const int oh = a + di, ow = b + dj;
-                if (oh >= OH || ow >= OW) continue;
-                const size_t o = ((size_t)n * OH + oh) * OW + ow;
-                const uint32_t codes = idx[o * vc + c8];
-                float g[8];
-                bf16x8_to_float(ld_global_v4(dy + o * C + c8 * 8), g);
-                if (dy2) {
-                    float g2[8];
-                    bf16x8_to_float(ld_global_v4(dy2 + o * C + c8 * 8), g2);
+                for (int e = 0; e < 8; ++e) g[e] += g2[e];
+            }
+            // pixel (i, j) of the patch is tap (i + 1 - 2 di, j + 1 - 2 dj) of this window when that lies in [0, 2]
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) g[e] += g2[e];
-                }
-                // pixel (i, j) of the patch is tap (i + 1 - 2 di, j + 1 - 2 dj) of this window when that lies in [0, 2]
+            for (int i = 0; i < 2; ++i) {
+                if (di == 1 && i == 0) continue;
 #pragma unroll
-                for (int i = 0; i < 2; ++i) {
-                    if (di == 1 && i == 0) continue;
+                for (int j = 0; j < 2; ++j) {
+                    if (dj == 1 && j == 0) continue;
+                    // bit 4e + 3 of m is set where nibble e of the code word equals this tap (exact: no carry crosses a nibble)
+                    const uint32_t t_ = codes ^ ((uint32_t)((i + 1 - 2 * di) * 3 + (j + 1 - 2 * dj)) * 0x11111111u);
+                    const uint32_t m = ~(((t_ & 0x77777777u) + 0x77777777u) | t_) & 0x88888888u;
 #pragma unroll
-                    for (int j = 0; j < 2; ++j) {
-                        if (dj == 1 && j == 0) continue;
-                        const uint32_t code = (uint32_t)((i + 1 - 2 * di) * 3 + (j + 1 - 2 * dj));
-#pragma unroll
-                        for (int e = 0; e < 8; ++e)
-                            if (((codes >> (4 * e)) & 0xfu) == code) acc[i * 2 + j][e] += g[e];
-                    }
+                    for (int e = 0; e < 8; ++e)
+                        if (m & (8u << (4 * e))) acc[i * 2 + j][e] += g[e];
                 }
             }
         }

@@ -165,6 +165,9 @@ class ResNet(nn.Module):
             if OF.stem_usable(x, self.conv1):
                 # native stem: space-to-depth + tcgen05 implicit GEMM, BatchNorm statistics from its epilogue
                 y, partials = OF.stem_conv(x, self.conv1.weight)
+                if not self.small_input and OF.bn_relu_maxpool_usable(y, self.bn1):
+                    # BatchNorm + ReLU + max pool in one pass: the normalised 112 x 112 activation is never written
+                    return self._trunk(OF.bn_relu_maxpool(y, self.bn1, partials), fused, pooled=True)
                 x = OF.bn_act(y, self.bn1, relu=True, partials=partials)
                 return self._trunk(x, fused)
             x = OF.to_nhwc_bf16(x, pad_channels=self.stem_pad)
@@ -179,10 +182,10 @@ class ResNet(nn.Module):
             x = _conv_bn_act(x, self.conv1, self.bn1, True, None, self.impl)
         return self._trunk(x, fused)
 
-    def _trunk(self, x, fused: bool):
+    def _trunk(self, x, fused: bool, pooled: bool = False):
         if fused:
             from ..ops import functional as OF
-        if not self.small_input:
+        if not self.small_input and not pooled:
             x = OF.maxpool3x3s2(x) if fused else F.max_pool2d(x, 3, 2, 1)
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         if fused:

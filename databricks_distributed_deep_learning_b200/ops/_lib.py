@@ -73,6 +73,10 @@ _PROTOS = {
     "ddl_bn_act_bwd": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _ll, _i, _i, _vp], _i),
     "ddl_bn_act_fwd_train_mask": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _ll, _i, _f, _f, _i, _vp], _i),
     "ddl_bn_act_bwd_ex": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _ll, _i, _i, _vp], _i),
+    "ddl_bn_relu_maxpool_supported": ([_i, _i, _i, _i], _i),
+    "ddl_bn_relu_maxpool_bwd_scratch_bytes": ([_i, _i, _i, _i], _sz),
+    "ddl_bn_relu_maxpool_fwd_train": ([_vp] * 12 + [_i] * 5 + [_f, _f, _vp], _i),
+    "ddl_bn_relu_maxpool_bwd": ([_vp] * 12 + [_i, _vp, _sz, _i, _i, _i, _i, _vp], _i),
     "ddl_maxpool3x3s2_bwd_ex": ([_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp], _i),
     "ddl_bn_act_fwd_train_from_partials": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _ll, _i, _f, _f, _i, _vp], _i),
     "ddl_stem_z_bytes": ([_i, _i, _i], _sz),

@@ -415,6 +415,67 @@ class _MaxPool3x3s2(torch.autograd.Function):
         return dx
 
 
+class _BnReluMaxPool(torch.autograd.Function):
+    """maxpool3x3s2(relu(batch_norm(x))) for the ResNet stem in one pass (csrc/bn_act.cu): the normalised full-resolution
+    activation is never materialised; statistics come from the convolution epilogue's per-CTA partials."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, running_mean, running_var, momentum, eps, partials):
+        _req_bf16(x, gamma, beta)
+        N, Cc, H, W = x.shape
+        if not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        dev = x.device
+        y = torch.empty((N, Cc, H // 2, W // 2), dtype=x.dtype, device=dev, memory_format=torch.channels_last)
+        codes = torch.empty(N * (H // 2) * (W // 2) * Cc // 2, dtype=torch.uint8, device=dev)
+        mean, invstd, scale, shift = (torch.empty(Cc, dtype=torch.float32, device=dev) for _ in range(4))
+        L.call("ddl_bn_relu_maxpool_fwd_train", x.data_ptr(), gamma.data_ptr(), beta.data_ptr(), L.ptr(running_mean), L.ptr(running_var),
+               y.data_ptr(), codes.data_ptr(), mean.data_ptr(), invstd.data_ptr(), scale.data_ptr(), shift.data_ptr(), partials.data_ptr(),
+               partials.numel() // (2 * Cc), N, H, W, Cc, float(eps), float(momentum), L.stream_ptr(dev))
+        ctx.save_for_backward(x, gamma, beta, mean, invstd, codes, y)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        x, gamma, beta, mean, invstd, codes, y = ctx.saved_tensors
+        N, Cc, H, W = x.shape
+        dev = x.device
+        dy2 = _take_addend(dy)
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dx = torch.empty_like(x, memory_format=torch.channels_last)
+        dgamma, dbeta = torch.empty_like(gamma), torch.empty_like(gamma)
+        scratch = _scratch(L.lib().ddl_bn_relu_maxpool_bwd_scratch_bytes(N, H, W, Cc), dev)
+        L.call("ddl_bn_relu_maxpool_bwd", dy.data_ptr(), L.ptr(dy2), y.data_ptr(), codes.data_ptr(), x.data_ptr(), gamma.data_ptr(),
+               beta.data_ptr(), mean.data_ptr(), invstd.data_ptr(), dx.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), L.DDL_BF16,
+               scratch.data_ptr(), scratch.numel(), N, H, W, Cc, L.stream_ptr(dev))
+        return dx, dgamma, dbeta, None, None, None, None, None
+
+
+_BN_POOL_FUSED = os.environ.get("DDL_BN_POOL", "fused") == "fused"  # DDL_BN_POOL=split: bn_act followed by maxpool3x3s2
+
+
+def bn_relu_maxpool_usable(x: torch.Tensor, bn: nn.BatchNorm2d) -> bool:
+    if not (_BN_POOL_FUSED and x.is_cuda and x.dim() == 4 and x.dtype == torch.bfloat16):
+        return False
+    if not (bn.training and bn.running_mean is not None and bn.weight is not None and bn.bias is not None):
+        return False
+    N, Cc, H, W = x.shape
+    return bool(L.lib().ddl_bn_relu_maxpool_supported(N, H, W, Cc))
+
+
+def bn_relu_maxpool(x: torch.Tensor, bn: nn.BatchNorm2d, partials: torch.Tensor) -> torch.Tensor:
+    """``max_pool2d(relu(batch_norm(x)), 3, 2, 1)`` in training mode with the statistics taken from ``partials`` (the stem
+    convolution's epilogue); torch's running-statistics semantics as in :func:`bn_act`."""
+    if bn.running_mean.dtype != torch.float32 or bn.running_var.dtype != torch.float32:
+        raise L.DdlError("fused BatchNorm keeps running_mean / running_var in float32; convert the model with models.prepare_for_fused()")
+    if bn.num_batches_tracked is not None and not _batches_counted_by_model:
+        bn.num_batches_tracked.add_(1)
+    return _accepts_second_grad(_BnReluMaxPool.apply(x, bn.weight, bn.bias, bn.running_mean, bn.running_var,
+                                                     0.1 if bn.momentum is None else bn.momentum, bn.eps, partials))
+
+
 def maxpool3x3s2(x: torch.Tensor) -> torch.Tensor:
     """``F.max_pool2d(x, 3, 2, 1)`` on channels-last bf16 (K14)."""
     return _accepts_second_grad(_MaxPool3x3s2.apply(x))

@@ -171,6 +171,18 @@ int ddl_bn_act_bwd(const void* dy, const void* y, const void* x, const void* gam
 int ddl_bn_act_bwd_ex(const void* dy, const void* dy2, const void* y, const void* relu_mask, const void* x, const void* gamma,
                       const float* mean, const float* invstd, void* dx, void* dres, void* dgamma, void* dbeta,
                       int param_grad_dtype, void* scratch, size_t scratch_bytes, long long M, int C, int relu, void* stream);
+/* Stem: BatchNorm (batch statistics from per-CTA partials, as ddl_bn_act_fwd_train_from_partials) + ReLU + 3x3/2 max pool in
+ * ONE pass over x [N, H, W, C] (even H, W; 256 % (C / 8) == 0): y [N, H/2, W/2, C]; codes = N * H/2 * W/2 * C/2 bytes (4 bits per
+ * pooled element: winning tap, or 15 where the pooled value is 0).  Backward: dx, dgamma, dbeta from dy (+ optional dy2), y, the
+ * codes and x; scratch from ddl_bn_relu_maxpool_bwd_scratch_bytes. */
+int ddl_bn_relu_maxpool_supported(int N, int H, int W, int C);
+size_t ddl_bn_relu_maxpool_bwd_scratch_bytes(int N, int H, int W, int C);
+int ddl_bn_relu_maxpool_fwd_train(const void* x, const void* gamma, const void* beta, float* running_mean, float* running_var, void* y,
+                                  void* codes, float* mean, float* invstd, float* scale, float* shift, const float* partials, int nblocks,
+                                  int N, int H, int W, int C, float eps, float momentum, void* stream);
+int ddl_bn_relu_maxpool_bwd(const void* dy, const void* dy2, const void* y, const void* codes, const void* x, const void* gamma,
+                            const void* beta, const float* mean, const float* invstd, void* dx, void* dgamma, void* dbeta,
+                            int param_grad_dtype, void* scratch, size_t scratch_bytes, int N, int H, int W, int C, void* stream);
 
 /* ---- self-attention on tcgen05 (csrc/attention.cu), K11 ---------------------------------- */
 /* qkv: packed projections [B*S, 3*heads*64] bf16 (q | k | v); seqlens[B] = valid (right-padded)

@@ -904,3 +904,48 @@ def test_linear_tied_weight_gradients_are_summed_not_aliased():
         G._grad_dest.pop(id(w), None)
     ref = torch.ones(64, 256, device="cuda").t() @ x1.float() + 2.0 * torch.ones(64, 256, device="cuda").t() @ x2.float()
     assert torch.allclose(w.grad.float(), ref, rtol=2e-2, atol=2e-1), (w.grad.float() - ref).abs().max().item()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,H,C", [(4, 112, 64), (3, 20, 64), (2, 16, 128)])
+def test_bn_relu_maxpool_fused_matches_fp32_reference(N, H, C):
+    """Stem BatchNorm + ReLU + max pool in one pass (csrc/bn_act.cu) vs max_pool2d(relu(batch_norm(x))) in fp32, forward,
+    running statistics and all three gradients, including the second (skip-branch) gradient summed inside the kernel."""
+    OF = _OF()
+    from databricks_distributed_deep_learning_b200.ops import _lib as L
+
+    torch.manual_seed(5)
+    x = (torch.randn(N, C, H, H, device="cuda") * 1.5 + 0.3).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    bn = torch.nn.BatchNorm2d(C).cuda()
+    with torch.no_grad():
+        bn.weight.copy_(torch.randn(C) * 0.5 + 1.0)
+        bn.bias.copy_(torch.randn(C) * 0.3)
+    bn.weight.data = bn.weight.data.to(torch.bfloat16)
+    bn.bias.data = bn.bias.data.to(torch.bfloat16)
+    ref_bn = torch.nn.BatchNorm2d(C).cuda()
+    ref_bn.weight.data = bn.weight.data.float().clone()
+    ref_bn.bias.data = bn.bias.data.float().clone()
+    # statistics as ONE partial row [2][C] of the bf16 values
+    xf = x.float()
+    partials = torch.stack([xf.sum((0, 2, 3)), (xf * xf).sum((0, 2, 3))]).contiguous()
+    assert L.lib().ddl_bn_relu_maxpool_supported(N, H, H, C)
+    xg = x.clone().requires_grad_()
+    y = OF.bn_relu_maxpool(xg, bn, partials)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xr = xf.clone().requires_grad_()
+    yr = F.max_pool2d(F.relu(ref_bn(xr)), 3, 2, 1)
+    yr.backward(dy.float())
+    assert y.shape == yr.shape
+    assert (y.float() - yr).abs().max().item() < 0.04 * max(1.0, yr.abs().max().item())
+    assert torch.allclose(bn.running_mean, ref_bn.running_mean, atol=1e-3) and torch.allclose(bn.running_var, ref_bn.running_var, rtol=1e-3, atol=1e-3)
+    rel = lambda a, b: ((a.float() - b).norm() / b.norm().clamp_min(1e-6)).item()
+    # ties / rounding may route a few gradients to a neighbouring tap: compare in norm
+    assert rel(xg.grad, xr.grad) < 0.05, rel(xg.grad, xr.grad)
+    assert rel(bn.weight.grad, ref_bn.weight.grad) < 0.02 and rel(bn.bias.grad, ref_bn.bias.grad) < 0.02
+    # against the split path of this library (same bf16 roundings): forward identical
+    bn2 = torch.nn.BatchNorm2d(C).cuda()
+    bn2.weight.data = bn.weight.data.clone()
+    bn2.bias.data = bn.bias.data.clone()
+    y2 = OF.maxpool3x3s2(OF.bn_act(x, bn2, relu=True, partials=partials))
+    assert torch.equal(y, y2)
