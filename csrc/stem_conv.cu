@@ -40,8 +40,8 @@ constexpr int kCout = 64;       // output channels
 constexpr int kZC = 16;         // space-to-depth channels (12 used)
 constexpr int kTaps = 4;        // vertical taps a (each covers 4 horizontal taps x 16 channels = K 64)
 constexpr int kTileM = 128;
-constexpr int kFwdStages = 8;   // 16 KB each
-constexpr int kFwdThreads = 192;
+constexpr int kFwdStages = 2;   // one whole tile each: 4 vertical taps x 16 KB
+constexpr int kFwdThreads = 320;  // TMA warp, MMA warp, 8 epilogue warps
 constexpr int kAccBufs = 4;
 
 // ------------------------------------------------------------------------------------------------ prep kernels
@@ -107,8 +107,9 @@ struct StemFwdParams {
 };
 
 constexpr int kFwdWBytes = kTaps * kCout * 128;                         // 32 KB packed weights
-constexpr int kFwdStageBytes = kTileM * 128;                            // 16 KB
-constexpr int kFwdStgOffset = kFwdWBytes + kFwdStages * kFwdStageBytes; // 4 epilogue warps x 4 KB
+constexpr int kFwdTapBytes = kTileM * 128;                              // 16 KB: [128 positions x 64] of one vertical tap
+constexpr int kFwdStageBytes = kTaps * kFwdTapBytes;                    // 64 KB
+constexpr int kFwdStgOffset = kFwdWBytes + kFwdStages * kFwdStageBytes; // 8 epilogue warps x 2 KB
 constexpr int kFwdBarOffset = kFwdStgOffset + 4 * 4096;
 constexpr int kFwdSmem = kFwdBarOffset + 512 + 1024;
 
@@ -137,7 +138,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) stem_fwd_kernel(const __grid_c
         }
         for (int s = 0; s < kAccBufs; ++s) {
             mbar_init(&tmem_full[s], 1);
-            mbar_init(&tmem_empty[s], 4);
+            mbar_init(&tmem_empty[s], 8);
         }
         mbar_init(w_bar, 1);
         fence_barrier_init();
@@ -155,21 +156,25 @@ __global__ void __launch_bounds__(kFwdThreads, 1) stem_fwd_kernel(const __grid_c
             tma_load_2d(w_smem, &tma_w, w_bar, 0, 0);
         }
         __syncwarp();
-        int stage = 0;
-        uint32_t phase = 0;
-        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        // A stage holds all four taps of a tile and is handed back by the SAME commit that publishes the tile's accumulator
+        // (the producer waits on tmem_full of the tile that used the stage, two tiles back): one tcgen05.commit per tile.
+        // With a commit per tap the kernel ran commit-bound - 5 x ~450 cycles per tile against 16 x 48 cycles of MMAs.
+        int it = 0;
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
             const long long p0 = (long long)tile * kTileM;
-#pragma unroll
-            for (int a = 0; a < kTaps; ++a) {
-                mbar_wait(&empty_bar[stage], phase ^ 1);
-                if (elect_one()) {
-                    mbar_expect_tx(&full_bar[stage], kFwdStageBytes);
-                    // rows past the end of z are zero-filled by TMA (they only feed dropped outputs)
-                    tma_load_2d(a_smem + stage * kFwdStageBytes, &tma_z, &full_bar[stage], 0, (int)(p0 + (long long)a * p.Wp));
-                }
-                __syncwarp();
-                if (++stage == kFwdStages) { stage = 0; phase ^= 1; }
+            const int stage = it & 1;
+            if (it >= kFwdStages) {
+                const int j = it - kFwdStages;  // (its barrier cannot complete again before this stage is refilled)
+                mbar_wait(&tmem_full[j % kAccBufs], (uint32_t)((j / kAccBufs) & 1));
             }
+            if (elect_one()) {
+                mbar_expect_tx(&full_bar[stage], kFwdStageBytes);
+                // rows past the end of z are zero-filled by TMA (they only feed dropped outputs)
+#pragma unroll
+                for (int a = 0; a < kTaps; ++a)
+                    tma_load_2d(a_smem + stage * kFwdStageBytes + a * kFwdTapBytes, &tma_z, &full_bar[stage], 0, (int)(p0 + (long long)a * p.Wp));
+            }
+            __syncwarp();
         }
     } else if (warp == 1) {
         // ===================== MMA issue: the whole warp runs the loop, one elected lane issues =====================
@@ -178,112 +183,119 @@ __global__ void __launch_bounds__(kFwdThreads, 1) stem_fwd_kernel(const __grid_c
         const uint64_t da0 = d_const | (uint64_t)(smem_u32(a_smem) >> 4), db0 = d_const | (uint64_t)(smem_u32(w_smem) >> 4);
         mbar_wait(w_bar, 0);
         tc_fence_after();
-        int stage = 0, acc = 0;
-        uint32_t phase = 0, acc_phase = 0;
-        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        int it = 0, acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+            const int stage = it & 1;
             mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+            mbar_wait(&full_bar[stage], (uint32_t)((it >> 1) & 1));
             tc_fence_after();
             const uint32_t d_tmem = tmem_base + acc * kCout;
+            if (elect_one()) {
 #pragma unroll
-            for (int a = 0; a < kTaps; ++a) {
-                mbar_wait(&full_bar[stage], phase);
-                tc_fence_after();
-                const uint64_t da = da0 + (uint32_t)stage * (uint32_t)(kFwdStageBytes >> 4), db = db0 + (uint32_t)a * (uint32_t)((kCout * 128) >> 4);
-                if (elect_one()) {
-                    umma_bf16(d_tmem, da, db, idesc, a > 0 ? 1u : 0u);
+                for (int a = 0; a < kTaps; ++a) {
+                    const uint64_t da = da0 + (uint32_t)(stage * (kFwdStageBytes >> 4) + a * (kFwdTapBytes >> 4));
+                    const uint64_t db = db0 + (uint32_t)(a * ((kCout * 128) >> 4));
 #pragma unroll
-                    for (int k = 1; k < 4; ++k) umma_bf16(d_tmem, da + k * 2, db + k * 2, idesc, 1u);
-                    umma_commit(&empty_bar[stage]);
-                    if (a == kTaps - 1) umma_commit(&tmem_full[acc]);
+                    for (int k = 0; k < 4; ++k) umma_bf16(d_tmem, da + k * 2, db + k * 2, idesc, (a | k) ? 1u : 0u);
                 }
-                __syncwarp();
-                if (++stage == kFwdStages) { stage = 0; phase ^= 1; }
+                umma_commit(&tmem_full[acc]);
             }
+            __syncwarp();
             if (++acc == kAccBufs) { acc = 0; acc_phase ^= 1; }
         }
     } else {
-        // ===================== epilogue warps (2..5) =====================
-        const int quarter = warp & 3;  // TMEM lanes 32*quarter .. +31
-        uint8_t* stg = smem + kFwdStgOffset + (warp - 2) * 4096;
-        float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;  // channels 2*lane, 2*lane+1
+        // ===================== epilogue warps (2..9): TMEM lane quarter x 32-column half =====================
+        // (with four warps the epilogue - ~1500 cycles per tile per warp - was what bounded the kernel, not the 768 cycles
+        // of MMAs; offsets are 32-bit, checked on the host)
+        const int ew = warp - 2, quarter = warp & 3, h = ew >> 2;
+        uint8_t* stg = smem + kFwdStgOffset + ew * 2048;
+        float cs[8], cq[8];  // columns h * 32 + t_ch * 8 + q
+#pragma unroll
+        for (int q = 0; q < 8; ++q) cs[q] = cq[q] = 0.f;
+        const int t_row = lane >> 2, t_ch = lane & 3;
+        const int img = p.Hp * p.Wp, total = (int)p.total_pos;
         int acc = 0;
         uint32_t acc_phase = 0;
-        const long long img = (long long)p.Hp * p.Wp;
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+            // my row: flattened padded position -> element offset of the output row (or -1: dropped)
+            const int pos = tile * kTileM + quarter * 32 + lane;
+            int out_off = -1;
+            if (pos < total) {
+                const int n = pos / img, rem = pos - n * img;
+                const int oh = rem / p.Wp, ow = rem - oh * p.Wp;
+                if (oh < p.OH && ow < p.OW) out_off = ((n * p.OH + oh) * p.OW + ow) * kCout;
+            }
             mbar_wait(&tmem_full[acc], acc_phase);
             tc_fence_after();
-            uint32_t r0[32], r1[32];
-            const uint32_t taddr = tmem_base + acc * kCout + ((uint32_t)(quarter * 32) << 16);
-            tmem_ld_32x32(taddr, r0);
-            tmem_ld_32x32(taddr + 32, r1);
+            uint32_t r[32];
+            tmem_ld_32x32(tmem_base + acc * kCout + h * 32 + ((uint32_t)(quarter * 32) << 16), r);
             tmem_ld_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tmem_empty[acc]);
             if (++acc == kAccBufs) { acc = 0; acc_phase ^= 1; }
-
-            // my row: flattened padded position -> output offset (or invalid)
-            const long long pos = (long long)tile * kTileM + quarter * 32 + lane;
-            long long out_off = -1;
-            if (pos < p.total_pos) {
-                const long long n = pos / img;
-                const int rem = (int)(pos - n * img);
-                const int oh = rem / p.Wp, ow = rem - oh * p.Wp;
-                if (oh < p.OH && ow < p.OW) out_off = ((n * p.OH + oh) * (long long)p.OW + ow) * kCout;
-            }
-            // bf16 row into the warp's staging tile (16-byte chunks XOR-swizzled by row: conflict-free both ways);
-            // dropped rows are written as zeros so that they do not disturb the statistics
-            const bool valid = out_off >= 0;
+            // bf16 row into the warp's staging tile (16-byte chunks XOR-swizzled: conflict-free both ways)
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
+            for (int j = 0; j < 4; ++j) {
                 float f[8];
 #pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const uint32_t bits = j < 4 ? r0[j * 8 + e] : r1[(j - 4) * 8 + e];
-                    f[e] = valid ? __uint_as_float(bits) : 0.f;
-                }
-                *reinterpret_cast<uint4*>(stg + lane * 128 + ((j ^ (lane & 7)) * 16)) = float_to_bf16x8(f);
+                for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[j * 8 + e]);
+                *reinterpret_cast<uint4*>(stg + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4)) = float_to_bf16x8(f);
             }
             __syncwarp();
-            // statistics: lane owns channels 2*lane, 2*lane+1 (one 4-byte word per row)
-#pragma unroll 8
-            for (int r = 0; r < 32; ++r) {
-                const uint32_t wv = *reinterpret_cast<const uint32_t*>(stg + r * 128 + (((lane >> 2) ^ (r & 7)) * 16) + (lane & 3) * 4);
-                const float a0 = __uint_as_float(wv << 16), a1 = __uint_as_float(wv & 0xffff0000u);
-                s0 += a0;
-                q0 += a0 * a0;
-                s1 += a1;
-                q1 += a1 * a1;
-            }
-            // coalesced stores: 4 rows (4 x 128 B) per instruction
+            // transposed domain: 4 lanes = one 64-byte row piece; coalesced stores, statistics of the stored values
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int row = i * 4 + (lane >> 3), chunk = lane & 7;
-                const long long off = __shfl_sync(0xffffffffu, out_off, row);
-                const uint4 v = *reinterpret_cast<const uint4*>(stg + row * 128 + ((chunk ^ (row & 7)) * 16));
-                if (off >= 0) st_global_v4(p.y + off + chunk * 8, v);
+            for (int it = 0; it < 4; ++it) {
+                const int rr = it * 8 + t_row;
+                const uint4 v = *reinterpret_cast<const uint4*>(stg + rr * 64 + ((t_ch ^ ((rr >> 1) & 3)) << 4));
+                const int off = __shfl_sync(0xffffffffu, out_off, rr);
+                if (off >= 0) {
+                    st_global_v4(p.y + off + h * 32 + t_ch * 8, v);
+                    float f[8];
+                    bf16x8_to_float(v, f);
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        cs[q] += f[q];
+                        cq[q] = fmaf(f[q], f[q], cq[q]);
+                    }
+                }
             }
             __syncwarp();
         }
-        // fold the four epilogue warps in fixed order -> this CTA's partial statistics
-        float* mine = reinterpret_cast<float*>(stg);  // each warp's own staging area, free after its last tile
-        __syncwarp();
-        mine[lane * 4 + 0] = s0;
-        mine[lane * 4 + 1] = s1;
-        mine[lane * 4 + 2] = q0;
-        mine[lane * 4 + 3] = q1;
-        asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
-        if (warp == 2) {
-            float t[4] = {0.f, 0.f, 0.f, 0.f};
+        // fold the 8 row groups of the warp, then - in fixed order - the four lane-quarter warps of each column half
 #pragma unroll
-            for (int w = 0; w < 4; ++w)
+        for (int q = 0; q < 8; ++q) {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) t[e] += reinterpret_cast<const float*>(smem + kFwdStgOffset + w * 4096)[lane * 4 + e];
+            for (int o = 4; o < 32; o <<= 1) {
+                cs[q] += __shfl_xor_sync(0xffffffffu, cs[q], o);
+                cq[q] += __shfl_xor_sync(0xffffffffu, cq[q], o);
+            }
+        }
+        float* mine = reinterpret_cast<float*>(stg);  // own staging area, free now: [32 columns][2]
+        if (t_row == 0) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                mine[(t_ch * 8 + q) * 2] = cs[q];
+                mine[(t_ch * 8 + q) * 2 + 1] = cq[q];
+            }
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");  // the eight epilogue warps only
+        if (ew == 0) {
+            // lane -> columns lane (half 0) and 32 + lane (half 1)
             float* out = p.partials + (size_t)blockIdx.x * 2 * kCout;
-            out[2 * lane] = t[0];
-            out[2 * lane + 1] = t[1];
-            out[kCout + 2 * lane] = t[2];
-            out[kCout + 2 * lane + 1] = t[3];
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+                float ts = 0.f, tq = 0.f;
+#pragma unroll
+                for (int qw = 0; qw < 4; ++qw) {
+                    const float* src = reinterpret_cast<const float*>(smem + kFwdStgOffset + (hh * 4 + qw) * 2048);
+                    ts += src[lane * 2];
+                    tq += src[lane * 2 + 1];
+                }
+                out[hh * 32 + lane] = ts;
+                out[kCout + hh * 32 + lane] = tq;
+            }
         }
     }
     tc_fence_before();
@@ -497,6 +509,7 @@ DDL_API int ddl_stem_conv_fwd(const void* z, const void* w, long long sk, long l
     p.OH = H / 2;
     p.OW = W / 2;
     p.total_pos = (long long)N * p.Hp * p.Wp;
+    DDL_REQUIRE(p.total_pos < (1ll << 31) - kTileM && (long long)N * p.OH * p.OW * kCout < (1ll << 31), "stem conv: batch too large for 32-bit offsets");
     p.num_tiles = (int)((p.total_pos + kTileM - 1) / kTileM);
     CUtensorMap tz, tw;
     if (int e = make_rows_map(&tz, z, p.total_pos - 3, kZC * 2, kTileM)) return e;
