@@ -87,9 +87,12 @@ def main():
         y = F.conv2d(x, w, None, s, pad)
         dy = torch.randn_like(y).contiguous(memory_format=torch.channels_last)
         ho = y.shape[2]
-        t_f = timeit(lambda: F.conv2d(x, w, None, s, pad), flush)
-        t_d = timeit(lambda: torch.ops.aten.convolution_backward(dy, x, w, None, (s, s), (pad, pad), (1, 1), False, (0, 0), 1, (True, False, False)), flush) if cin > 3 else 0.0
-        t_w = timeit(lambda: torch.ops.aten.convolution_backward(dy, x, w, None, (s, s), (pad, pad), (1, 1), False, (0, 0), 1, (False, True, False)), flush)
+        if args.no_lib:
+            t_f = t_d = t_w = 0.0
+        else:
+            t_f = timeit(lambda: F.conv2d(x, w, None, s, pad), flush)
+        t_d = 0.0 if args.no_lib else timeit(lambda: torch.ops.aten.convolution_backward(dy, x, w, None, (s, s), (pad, pad), (1, 1), False, (0, 0), 1, (True, False, False)), flush) if cin > 3 else 0.0
+        t_w = 0.0 if args.no_lib else timeit(lambda: torch.ops.aten.convolution_backward(dy, x, w, None, (s, s), (pad, pad), (1, 1), False, (0, 0), 1, (False, True, False)), flush)
         flops = 2.0 * N * ho * ho * cout * cin * k * k
         bytes_io = 2.0 * (x.numel() + y.numel())
         floor = max(flops / (peaks["bf16_tflops"] * 1e12), bytes_io / (peaks["hbm_gbs"] * 1e9)) * 1e6
