@@ -54,6 +54,7 @@ def main():
     ap.add_argument("--halo", default="1,0,28", help="halo-tile kernel for 3x3 / stride 1: on,mt,min_w")
     ap.add_argument("--ablate", type=int, default=0, help="timing experiments (results are garbage): see ddl_conv_set_debug")
     ap.add_argument("--no-lib", type=int, default=0, help="skip the library convolutions")
+    ap.add_argument("--stay", type=int, default=1, help="resident weight panels in the data kernel")
     ap.add_argument("--only3x3", type=int, default=0, help="only the 3x3 / stride-1 layers")
     ap.add_argument("--pair", type=int, default=0, help="forward / data-gradient kernel: 0 one CTA, 1 CTA pairs + halo tiles, 2 CTA pairs")
     ap.add_argument("--wgrad-rows", type=int, default=0)
@@ -62,6 +63,7 @@ def main():
 
     L0.call("ddl_conv_set_tuning", args.wgrad_rows, args.pair)
     L0.call("ddl_conv_set_im2col", args.im2col)
+    L0.call("ddl_conv_set_stay", args.stay)
     L0.call("ddl_conv_set_halo", *[int(v) for v in args.halo.split(",")])
     L0.call("ddl_conv_set_debug", None, args.ablate)
     torch.backends.cudnn.benchmark = True

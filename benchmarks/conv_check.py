@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--only", type=int, default=-1)
     ap.add_argument("--im2col", type=int, default=1)
     ap.add_argument("--halo", default="1,0,28", help="halo-tile kernel for 3x3 / stride 1: on,mt,min_w")
+    ap.add_argument("--stay", type=int, default=1, help="resident weight panels in the data kernel")
     ap.add_argument("--only3x3", type=int, default=0, help="only the 3x3 / stride-1 layers")
     ap.add_argument("--pair", type=int, default=0, help="0 = one-CTA data kernel, 1 = CTA pairs + halo tiles, 2 = CTA pairs")
     args = ap.parse_args()
@@ -32,6 +33,7 @@ def main():
 
     L.call("ddl_conv_set_tuning", 0, args.pair)
     L.call("ddl_conv_set_im2col", args.im2col)
+    L.call("ddl_conv_set_stay", args.stay)
     L.call("ddl_conv_set_halo", *[int(v) for v in args.halo.split(",")])
     print(f"pair mode {args.pair}", flush=True)
     bad = 0

@@ -95,6 +95,11 @@ struct DataParams {
     // taps[].dw / dh are offsets in input pixels, the base pixel of output (a, b) is (b * cstride + low_w, a * cstride + low_h)
     int im2col, cstride, low_w, low_h;
     long long cls_pix;  // N * OHt * OWt
+    // stay: all weight tiles of the CTA's column block (ntaps * cblocks * bn * 128 bytes <= 128 KB, one class) are loaded once
+    // and stay in shared memory; the ring then carries activation tiles only (launch_data decides)
+    int stay;
+    uint32_t panel_bytes;
+    int ablate;  // timing experiments only (ddl_conv_set_debug): 1 = no epilogue staging / stores, 2 = no activation loads
 };
 
 template <bool B_MN>
@@ -102,13 +107,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     const int stage_b = p.bn * 128;
-    const int stage_bytes = kStageA + stage_b;
-    uint8_t* stg_base = smem + (size_t)p.stages * stage_bytes;
+    const int stage_bytes = p.stay ? kStageA : kStageA + stage_b;
+    uint8_t* ring = smem + (p.stay ? p.panel_bytes : 0u);  // (the resident weight panel, if any, comes first)
+    uint8_t* stg_base = ring + (size_t)p.stages * stage_bytes;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(stg_base + kEpiWarps * kStgBytes);
     uint64_t* empty_bar = full_bar + kMaxStages;
     uint64_t* tmem_full = empty_bar + kMaxStages;  // [2]
     uint64_t* tmem_empty = tmem_full + 2;           // [2]
-    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    uint64_t* w_bar = tmem_empty + 2;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(w_bar + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     constexpr uint32_t kTmemCols = 512;
@@ -128,6 +135,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
             mbar_init(&tmem_full[s], 1);
             mbar_init(&tmem_empty[s], 4 * p.groups);
         }
+        mbar_init(w_bar, 1);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(tmem_ptr_smem, kTmemCols);
@@ -142,9 +150,26 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
         // region every TMA instruction is wrapped in an ELECT / R2UR.BROADCAST loop and the B_MN layers, with up to five
         // loads per k-block, ran producer-bound)
         {
+            auto load_b = [&](uint8_t* sb, uint64_t* bar, int wcol, int cb) {
+                if (!B_MN) {
+                    tma_load_2d(sb, &maps.w, bar, wcol + cb * 64, n_blk * p.bn);
+                } else {
+                    for (int j = 0; j < p.groups; ++j) tma_load_2d(sb + j * 8192, &maps.w, bar, wcol + n_blk * p.bn + j * 64, cb * 64);
+                }
+            };
+            if (p.stay) {
+                // the weight panel of this column block, once: tile (tap ti, channel block cb) at index ti * cblocks + cb
+                if (elect_one()) {
+                    mbar_expect_tx(w_bar, p.panel_bytes);
+                    for (int ti = 0; ti < p.cls_ntaps[0]; ++ti)
+                        for (int cb = 0; cb < p.cblocks; ++cb)
+                            load_b(smem + (size_t)(ti * p.cblocks + cb) * stage_b, w_bar, p.taps[0][ti].wtap * p.w_tap_stride, cb);
+                }
+                __syncwarp();
+            }
             int stage = 0;
             uint32_t phase = 0;
-            const uint32_t tx_bytes = p.a_bytes + (uint32_t)stage_b;
+            const uint32_t tx_bytes = p.a_bytes + (p.stay ? 0u : (uint32_t)stage_b);
             for (int tile = m_group; tile < p.num_tiles; tile += m_groups) {
                 const int cls = tile / p.tiles_per_cls, t = tile - cls * p.tiles_per_cls;
                 const int ng = t / tiles_hw, rem = t - ng * tiles_hw;
@@ -164,16 +189,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
                     const int wcol = tp.wtap * p.w_tap_stride;
                     for (int cb = 0; cb < p.cblocks; ++cb) {
                         mbar_wait(&empty_bar[stage], phase ^ 1);
-                        uint8_t* sa = smem + (size_t)stage * stage_bytes;
-                        uint8_t* sb = sa + kStageA;
+                        uint8_t* sa = ring + (size_t)stage * stage_bytes;
                         if (elect_one()) {
-                            mbar_expect_tx(&full_bar[stage], tx_bytes);
-                            if (p.im2col) tma_load_im2col(sa, &maps.in[0], &full_bar[stage], cb * 64, iw, ih, in_, tp.dw - p.low_w, tp.dh - p.low_h);
-                            else tma_load_4d(sa, &maps.in[tp.map], &full_bar[stage], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
-                            if (!B_MN) {
-                                tma_load_2d(sb, &maps.w, &full_bar[stage], wcol + cb * 64, n_blk * p.bn);
+                            if (p.ablate & 2) {
+                                mbar_arrive(&full_bar[stage]);
                             } else {
-                                for (int j = 0; j < p.groups; ++j) tma_load_2d(sb + j * 8192, &maps.w, &full_bar[stage], wcol + n_blk * p.bn + j * 64, cb * 64);
+                                mbar_expect_tx(&full_bar[stage], tx_bytes);
+                                if (p.im2col) tma_load_im2col(sa, &maps.in[0], &full_bar[stage], cb * 64, iw, ih, in_, tp.dw - p.low_w, tp.dh - p.low_h);
+                                else tma_load_4d(sa, &maps.in[tp.map], &full_bar[stage], cb * 64, ow0 + tp.dw, oh0 + tp.dh, n0);
+                                if (!p.stay) load_b(sa + kStageA, &full_bar[stage], wcol, cb);
                             }
                         }
                         __syncwarp();
@@ -192,7 +216,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
             const uint64_t da_const = make_smem_desc(0, 16, 1024);
             const uint64_t db_const = B_MN ? make_smem_desc(0, 8192, 1024) : make_smem_desc(0, 16, 1024);
             constexpr uint32_t kStepA = 32 >> 4, kStepB = (B_MN ? 2048 : 32) >> 4;
-            const uint32_t smem_base = smem_u32(smem);
+            const uint32_t ring_base = smem_u32(ring), panel_base = smem_u32(smem);
+            const bool stay = p.stay != 0;
+            if (stay) {
+                mbar_wait(w_bar, 0);
+                tc_fence_after();
+            }
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
             for (int tile = m_group; tile < p.num_tiles; tile += m_groups) {
@@ -204,8 +233,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
                 for (int kb = 0; kb < nkb; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
-                    const uint32_t sa = smem_base + (uint32_t)stage * (uint32_t)stage_bytes;
-                    const uint64_t da = da_const | (uint64_t)(sa >> 4), db = db_const | (uint64_t)((sa + kStageA) >> 4);
+                    const uint32_t sa = ring_base + (uint32_t)stage * (uint32_t)stage_bytes;
+                    const uint32_t sb = stay ? panel_base + (uint32_t)kb * (uint32_t)stage_b : sa + kStageA;
+                    const uint64_t da = da_const | (uint64_t)(sa >> 4), db = db_const | (uint64_t)(sb >> 4);
                     if (elect_one()) {
                         umma_bf16(d_tmem, da, db, idesc, kb > 0 ? 1u : 0u);
 #pragma unroll
@@ -279,6 +309,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
                         __syncwarp();
                         if (lane == 0) mbar_arrive(&tmem_empty[acc]);
                     }
+                    if (p.ablate & 1) continue;
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         float f[8];
@@ -1124,15 +1155,33 @@ int g_im2col = 1;  // activation tiles through im2col-mode TMA (dense 128-pixel 
 int g_ring_group = 1;  // ring slots released per tcgen05.commit (1 = every k-block; larger values measured slower)
 int g_wgrad_rows = 0;  // 0 = auto, 64 / 128 = forced pixel-chunk size of the weight gradient (benchmarks)
 
+int g_stay = 1;  // resident weight panel where it fits (ddl_conv_set_stay)
+long long* g_conv_dbg = nullptr;  // ddl_conv_set_debug
+int g_conv_ablate = 0;
+
 int launch_data(bool b_mn, const ConvMaps& maps, DataParams& p, cudaStream_t stream) {
     p.groups = p.bn / 64;
-    const int stage_bytes = kStageA + p.bn * 128;
     const int fixed = kEpiWarps * kStgBytes + 512 + 1024;
-    p.stages = (227 * 1024 - fixed) / stage_bytes;
+    // Resident weights: one class, 256-column blocks, the whole [ntaps * cblocks] x bn panel within 128 KB (K <= 256) and four
+    // activation stages beside it.  Measured gain is small (256 -> 1024 at 14 x 14: 49.2 -> 47.1 us forward; narrower column
+    // blocks got slower): these short-K layers are not bound by the weight re-loads but by draining the accumulator - with
+    // neither loads nor stores the kernel still takes 32.8 us, i.e. ~5500 cycles per 128 x 256 tile against 2048 cycles of
+    // MMAs (tcgen05.ld of the 128 KB fp32 tile) - and by the staging + stores of the epilogue (another 16 us);
+    // benchmarks/conv_ablate.py.
+    const long long panel = (long long)p.cls_ntaps[0] * p.cblocks * p.bn * 128;
+    p.stay = 0;
+    p.panel_bytes = 0;
+    if (g_stay && p.ncls == 1 && p.bn == 256 && panel <= 128 * 1024 && (227 * 1024 - fixed - panel) / kStageA >= 4) {
+        p.stay = 1;
+        p.panel_bytes = (uint32_t)panel;
+    }
+    const int stage_bytes = p.stay ? kStageA : kStageA + p.bn * 128;
+    p.ablate = g_conv_ablate;
+    p.stages = (227 * 1024 - fixed - (int)p.panel_bytes) / stage_bytes;
     if (p.stages > kMaxStages) p.stages = kMaxStages;
     p.group = 1;
     DDL_REQUIRE(p.stages >= 2, "conv: tile does not fit in shared memory");
-    const int smem = fixed + p.stages * stage_bytes;
+    const int smem = fixed + (int)p.panel_bytes + p.stages * stage_bytes;
     static int attr_smem[2] = {0, 0};
     if (smem > attr_smem[b_mn ? 1 : 0]) {
         if (b_mn) DDL_CHECK(cudaFuncSetAttribute(conv_data_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -1201,8 +1250,6 @@ int use_im2col(DataParams& p, CUtensorMap* map, const void* act, int aN, int aH,
 }
 
 // ---- pair kernel launch plan -----------------------------------------------------------------------------
-long long* g_conv_dbg = nullptr;  // ddl_conv_set_debug
-int g_conv_ablate = 0;
 int g_pair_mode = 0;  // 0 = never use the CTA-pair kernel, 1 = pair kernel (halo tiles where possible), 2 = pair kernel, no halo
 
 bool ptr_is_local(const void* ptr) {
@@ -1537,6 +1584,11 @@ DDL_API int ddl_conv_set_tuning(int wgrad_rows, int pair_mode) {
     DDL_REQUIRE(pair_mode >= 0 && pair_mode <= 2, "conv tuning: pair_mode must be 0 (one-CTA kernel), 1 (CTA pairs + halo tiles) or 2 (CTA pairs)");
     g_wgrad_rows = wgrad_rows;
     g_pair_mode = pair_mode;
+    return 0;
+}
+
+DDL_API int ddl_conv_set_stay(int on) {
+    g_stay = on ? 1 : 0;
     return 0;
 }
 

@@ -100,6 +100,7 @@ _PROTOS = {
     "ddl_conv_set_debug": ([_vp, _i], _i),
     "ddl_conv_set_im2col": ([_i], _i),
     "ddl_conv_set_halo": ([_i, _i, _i], _i),
+    "ddl_conv_set_stay": ([_i], _i),
     "ddl_probe_umma_shift": ([_vp, _vp, _vp, _i, _i, _i, _vp], _i),
     "ddl_probe_umma_rate": ([_vp, _i, _i, _i, _i, _i, _vp], _i),
     "ddl_embed_bwd_scratch_bytes": ([_i, _i], _sz),

@@ -269,6 +269,8 @@ int ddl_conv_set_im2col(int on);
 /* 3x3 / stride-1 / pad-1 layers (forward and data gradient) on halo tiles (csrc/conv_halo.cuh): on = 1 (default) / 0; mt =
  * pixel tiles per weight tile (0 = auto, 1, 2); min_w = narrowest image that takes this kernel (0 = default 28) */
 int ddl_conv_set_halo(int on, int mt, int min_w);
+/* weight panel of a CTA's column block resident in shared memory where it fits (1, default) or streamed with every tile (0) */
+int ddl_conv_set_stay(int on);
 /* development aid: device buffer [296][8] int64 that following forward / data-gradient launches of the CTA-pair kernel fill
  * with per-CTA wait-cycle counters (which barrier each role waits on); NULL switches it off.  ablate (timing experiments
  * only, results are garbage): bit 0 = epilogue drops its staging and stores, bit 1 = no TMA loads are issued */
