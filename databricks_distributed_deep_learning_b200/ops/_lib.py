@@ -15,7 +15,8 @@ from typing import Optional
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200ddl.so")
+# DDL_LIB_PATH: an alternative build of the library (A/B timing of kernel variants in one gpurun call; benchmarks only)
+LIB_PATH = os.environ.get("DDL_LIB_PATH") or os.path.join(_HERE, "libb200ddl.so")
 
 DDL_F32, DDL_BF16 = 0, 1
 ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS = 0, 1, 2, 3
