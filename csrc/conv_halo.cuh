@@ -2,9 +2,9 @@
 // anonymous namespace (it uses that file's ConvMaps, tma_load_4d and epilogue constants).
 //
 // What the im2col kernel (conv_data_kernel) pays for on these layers, per 128-pixel tile: nine activation tiles (the same
-// pixels nine times over through L2 and shared memory), nine weight tiles, and one tcgen05.commit per 64-deep k-block - a
-// commit costs the tensor pipe ~450 cycles (csrc/probe_umma.cu), four 128 x 64 x 16 MMAs take 128: the 64-channel layers of
-// ResNet-50's first stage ran commit-bound at 2.7x the library's time.  Here
+// pixels nine times over through L2 and shared memory), nine weight tiles, one tcgen05.commit per 64-deep k-block (~450
+// cycles of tensor-pipe time each, csrc/probe_umma.cu, against 128 - 256 cycles of MMAs) and one trip of the MMA warp through
+// its per-k-block loop: the 64-channel layers of ResNet-50's first stage ran at 2.7x the library's time.  Here
 //   * the activation tile is loaded ONCE per 64-channel block as a box [64, W + 1, th + 2, 1] that starts at column -1 and
 //     row oh0 - 1; TMA zero-fills everything outside the image - that is the padding.  With a row pitch of W + 1 the zero
 //     column of image row h + 1 doubles as the right-hand padding of row h.  MMA row m = a * (W + 1) + b, and tap (r, s)

@@ -2,11 +2,12 @@
 // 3x3 layers (stride 1 and 2) of the reference's ResNet-50 (notebooks/cv/onnx_experiments.py:19; shapes in SURVEY.md
 // section 2.E.2; K9 in section 2.E.3, BASELINE.json:5 "conv-BN-ReLU epilogues ... no cuBLAS/cuDNN on these paths").
 //
-// No im2col buffer exists anywhere.  The activation tensor is described to TMA as a 4-D tensor [C, W, H, N]; the operand
-// tile of a filter tap is ONE box [64 channels, bw, bh, nb] whose start coordinate is shifted by the tap offset.
-// Coordinates outside the image are zero-filled by TMA - that IS the padding.  Stride-2 layers use four "parity" maps
-// (base pointer shifted by (ph, pw), strides doubled), so that a tap again reads a dense box.  1x1 / stride-1 layers
-// are flattened to [C, N*H*W] and tiled 128 pixels at a time.
+// No im2col buffer exists anywhere.  The activation tensor is described to TMA as a 4-D tensor [C, W, H, N].  By default the
+// operand tile of a filter tap is ONE im2col-mode load (cuTensorMapEncodeIm2col): 128 consecutive output positions x 64
+// channels, displaced by the tap offset, zero-filled outside the image - that IS the padding - with the convolution stride as
+// traversal stride; tiles are dense across image rows and images.  (ddl_conv_set_im2col(0) goes back to tiled boxes
+// [64 channels, bw, bh, nb] with four "parity" maps for stride 2.)  3x3 / stride-1 layers on wide images take the halo-tile
+// kernel of conv_halo.cuh; 256-column blocks with K <= 256 keep their weight panel in shared memory (DataParams::stay).
 //
 //   data kernel   out[pix, n] = sum_taps  A_tap[pix, :] . W_tap[n, :]           (forward and data gradient)
 //       forward : A = x boxes,  W_tap = w[n][tap][:]  (K-major rows of the channels-last weight),  BatchNorm statistics
@@ -20,8 +21,9 @@
 //       the CTA's whole pixel range, fp32 partials per pixel split, folded in fixed order (and transposed to the weight
 //       layout) by a second kernel.
 //
-// Structure of both kernels as in gemm_tcgen05.cu / conv1x1.cu: warp 0 = TMA producer, warp 1 = MMA issuer (one thread),
-// remaining warps = epilogue; mbarrier ring between producer and MMA, tcgen05.commit releases stages.
+// Structure of all kernels as in gemm_tcgen05.cu / conv1x1.cu: warp 0 = TMA producer, warp 1 = MMA issue (both run their loops
+// warp-uniform, elect.sync picks the issuing lane), remaining warps = epilogue; mbarrier ring between producer and MMA,
+// tcgen05.commit releases stages.
 #include <cuda.h>
 
 #include <algorithm>

@@ -238,21 +238,23 @@ def test_trainer_graph_matches_eager_resnet18():
         assert abs(a - b) < 0.05 * max(1.0, abs(a)), (losses[False], losses[True])
 
 
-def test_fused_resnet_matches_torch_impl_one_step():
-    """Fused NHWC/bf16 ResNet forward+backward vs the ATen implementation of the same module."""
+@pytest.mark.parametrize("small,size,batch", [(True, 32, 32), (False, 64, 16)])
+def test_fused_resnet_matches_torch_impl_one_step(small, size, batch):
+    """Fused NHWC/bf16 ResNet forward+backward vs the ATen implementation of the same module; the ImageNet-style stem
+    (7x7/2 native convolution, BatchNorm + ReLU + max pool in one pass) is exercised by the second case."""
     from databricks_distributed_deep_learning_b200.models import resnet18
 
     torch.manual_seed(2)
-    a = resnet18(num_classes=10, small_input=True).cuda().to(torch.bfloat16).to(memory_format=torch.channels_last)
-    b = resnet18(num_classes=10, small_input=True).cuda()
+    a = resnet18(num_classes=10, small_input=small).cuda().to(torch.bfloat16).to(memory_format=torch.channels_last)
+    b = resnet18(num_classes=10, small_input=small).cuda()
     b.load_state_dict({k: v.float() for k, v in a.state_dict().items()})
     for m in a.modules():
         if isinstance(m, torch.nn.BatchNorm2d):
             m.running_mean.data = m.running_mean.data.float()
             m.running_var.data = m.running_var.data.float()
     a.set_impl("fused")
-    x = torch.randn(32, 3, 32, 32, device="cuda")
-    y = torch.randint(0, 10, (32,), device="cuda")
+    x = torch.randn(batch, 3, size, size, device="cuda")
+    y = torch.randint(0, 10, (batch,), device="cuda")
     OF = _OF()
     la = OF.cross_entropy(a(x), y)
     la.backward()
@@ -949,3 +951,23 @@ def test_bn_relu_maxpool_fused_matches_fp32_reference(N, H, C):
     bn2.bias.data = bn.bias.data.clone()
     y2 = OF.maxpool3x3s2(OF.bn_act(x, bn2, relu=True, partials=partials))
     assert torch.equal(y, y2)
+
+
+@pytest.mark.gpu
+def test_fused_resnet_counts_batches_once_per_forward():
+    """All BatchNorm num_batches_tracked counters advance by exactly one per training forward of the fused model (one
+    multi-tensor add for the whole model), and not at all in eval mode."""
+    from databricks_distributed_deep_learning_b200.models import prepare_for_fused, resnet18
+
+    m = prepare_for_fused(resnet18(num_classes=10, small_input=True, impl="fused"), "cuda")
+    x = torch.randn(4, 3, 32, 32, device="cuda")
+    m.train()
+    m(x)
+    m(x)
+    counts = {int(b.num_batches_tracked) for b in m.modules() if isinstance(b, torch.nn.BatchNorm2d)}
+    assert counts == {2}, counts
+    m.eval()
+    with torch.no_grad():
+        m(x)
+    counts = {int(b.num_batches_tracked) for b in m.modules() if isinstance(b, torch.nn.BatchNorm2d)}
+    assert counts == {2}, counts
