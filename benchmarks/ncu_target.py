@@ -74,6 +74,19 @@ def main():
         for _ in range(2):
             y, _ = OF.stem_conv(x, w)
             y.backward(torch.randn_like(y))
+    elif mode == "stempool":
+        # the whole ImageNet-style stem: space-to-depth + 7x7/2 convolution (+ statistics), BatchNorm + ReLU + max pool in one pass, backward
+        from databricks_distributed_deep_learning_b200.ops import functional as OF
+
+        w = torch.randn(64, 3, 7, 7, device="cuda").to(bf).contiguous(memory_format=torch.channels_last).requires_grad_()
+        bn = torch.nn.BatchNorm2d(64).cuda()
+        bn.weight.data = bn.weight.data.to(bf)
+        bn.bias.data = bn.bias.data.to(bf)
+        x = torch.randn(256, 3, 224, 224, device="cuda")
+        for _ in range(2):
+            y, part = OF.stem_conv(x, w)
+            p = OF.bn_relu_maxpool(y, bn, part)
+            p.backward(torch.randn_like(p))
     elif mode == "conv1x1":
         from databricks_distributed_deep_learning_b200.ops import functional as OF
 
