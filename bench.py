@@ -104,6 +104,32 @@ def heap_bytes(device):
         return 0
 
 
+# Model FLOPs per sample for one training step (forward + backward = 3 x forward; 2 FLOPs per MAC; matmul / convolution
+# work only): ResNet-50 4.09 GMAC forward (torchvision's count at 224 x 224); BERT: 6 x non-embedding parameters per token
+# plus the attention score / context matmuls.
+_MODEL_GFLOP_PER_SAMPLE = {
+    "resnet50": 3 * 2 * 4.09,
+    "bert-base": (6 * 85.1e6 * 128 + 3 * 4 * 128 * 128 * 768 * 12) / 1e9,
+    "bert-large": (6 * 302.3e6 * 512 + 3 * 4 * 512 * 512 * 1024 * 24) / 1e9,
+}
+
+
+def roofline_block(workload, per_gpu_value):
+    """Achieved model TFLOP/s per GPU against the measured cuBLAS bf16 throughput (MEASURED_PEAKS.json, else the recipe's
+    fallback) - the fraction the profiling recipe asks to report."""
+    from databricks_distributed_deep_learning_b200.utils.timing import load_measured_peaks
+
+    g = _MODEL_GFLOP_PER_SAMPLE.get(workload)
+    if g is None:
+        return None
+    peaks = load_measured_peaks()
+    tf = per_gpu_value * g / 1e3
+    den = peaks.get("bf16_tflops_sustained") or peaks.get("bf16_tflops")
+    return {"model_tflops_per_gpu": round(tf, 1), "of_measured_bf16_tflops": round(tf / den, 3) if den else None,
+            "bf16_tflops_denominator": den, "hbm_gbs": peaks.get("hbm_gbs"), "peaks_source": peaks.get("source"),
+            "gflop_per_sample": round(g, 2)}
+
+
 def measure(args, workload, impl, device, rank, world):
     """One (workload, arm): device-resident and end-to-end throughput.  Returns the result dict (same on every rank)."""
     import torch
@@ -167,6 +193,18 @@ def measure(args, workload, impl, device, rank, world):
         }
     peak = torch.cuda.max_memory_allocated(device) + (heap_bytes(device) - heap0)
     value = batch * world * K / (ms / 1e3)
+    # per-bucket communication time / bus bandwidth (a few eager steps outside the timed region; state rolled back)
+    comm_stats = None
+    if impl == "ours" and world > 1 and not runner.fsdp:
+        try:
+            comm_stats = runner.trainer.profile_comm(host_batches[0], steps=3)
+            for b in comm_stats["buckets"]:  # time = max over ranks; bandwidths follow from it
+                b["us"] = round(pg.max_over_ranks(b["us"]), 3)
+                b["busbw_gbs"] = round(b["bytes"] / b["us"] * 1e-3 * 2.0 * (world - 1) / world, 1)
+                b["frac_of_900"] = round(b["busbw_gbs"] / 900.0, 3)
+            comm_stats["comm_us_per_step"] = round(sum(b["us"] for b in comm_stats["buckets"]), 1)
+        except Exception as ex:  # noqa: BLE001 - a metrics pass must never take the bench line down
+            comm_stats = {"error": f"{type(ex).__name__}: {ex}"[:200]}
     out = {
         "metric": f"{workload} training throughput ({wl.unit}), device-timed, max over ranks",
         "value": round(value, 2), "unit": wl.unit, "n_gpus": world, "steps": K, "warmup": W,
@@ -184,7 +222,10 @@ def measure(args, workload, impl, device, rank, world):
         "e2e": e2e, "gpu_launches": int(launches), "final_loss": final_loss,
         "peak_mem_gb": round(peak / 2**30, 2),
         "wall_s_timed_region": round(wall, 3),
+        "roofline": roofline_block(workload, value / world),
     }
+    if comm_stats is not None:
+        out["comm_per_bucket"] = comm_stats
     runner.close()
     del runner, dev_batches
     gc.collect()

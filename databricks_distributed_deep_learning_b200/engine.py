@@ -184,6 +184,50 @@ class Trainer:
         torch.cuda.synchronize(self.device)
         pg.barrier()
 
+    # ---- communication metrics --------------------------------------------------------------
+    def profile_comm(self, batch, steps: int = 3) -> dict:
+        """Per-bucket all-reduce time and bus bandwidth of this model's gradient buckets (SURVEY.md section 5 "metrics").
+
+        Runs ``steps`` EAGER steps (timed events cannot live inside the whole-step CUDA graph) on ``batch`` and rolls the
+        training state back afterwards, like the warm-up of the graph capture.  Returns ``{"buckets": [{bucket, bytes,
+        us, busbw_gbs, frac_of_900}, ...] (mean over steps), "comm_us_per_step", "bytes_per_step"}``; DDP only."""
+        if self.parallelism != "ddp":
+            return {"buckets": [], "note": "per-bucket timing is implemented for the DDP wrapper"}
+        dev_batch = batch
+        if self.cuda:
+            self._ensure_static(batch)
+            self._copy_into(self.static_batch, batch, non_blocking=False)
+            dev_batch = self.static_batch
+        state = self._training_state()
+        snap = [t.detach().clone() for t in state]
+        py_step = getattr(self.opt, "_step", None)
+        self.ddp.comm_timing(True)
+        per_bucket: dict = {}
+        try:
+            for _ in range(steps):
+                self._step_impl(dev_batch)
+                if self.cuda:
+                    torch.cuda.synchronize(self.device)
+                for r in self.ddp.comm_stats():
+                    per_bucket.setdefault(r["bucket"], []).append(r)
+        finally:
+            self.ddp.comm_timing(False)
+            with torch.no_grad():
+                for t, c in zip(state, snap):
+                    t.copy_(c)
+            if py_step is not None:
+                self.opt._step = py_step
+        buckets = []
+        for k in sorted(per_bucket):
+            rs = per_bucket[k]
+            d = {"bucket": k, "bytes": rs[0]["bytes"], "us": sum(r["us"] for r in rs) / len(rs),
+                 "busbw_gbs": sum(r["busbw_gbs"] for r in rs) / len(rs)}
+            if "frac_of_900" in rs[0]:
+                d["frac_of_900"] = d["busbw_gbs"] / 900.0
+            buckets.append(d)
+        return {"buckets": buckets, "comm_us_per_step": sum(b["us"] for b in buckets),
+                "bytes_per_step": sum(b["bytes"] for b in buckets), "world": pg.world_size()}
+
     # ---- public API ------------------------------------------------------------------------
     def step(self, batch) -> torch.Tensor:
         """One step.  ``batch`` holds host (ideally pinned) or device tensors.  Returns the

@@ -169,6 +169,9 @@ class DistributedDataParallel(nn.Module):
         self._callback_queued = False
         self._grads_detached = False  # True after zero_grad(set_to_none=True): buckets are not pre-zeroed
         self._comm_stream = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" else None
+        # per-bucket communication timing (SURVEY.md section 5 "metrics"): off by default, see comm_timing() / comm_stats()
+        self._comm_timing = False
+        self._comm_records: list = []
         self._next_bucket = 0  # buckets are launched strictly in index order (see _grad_ready)
         self._param_listeners: List[Callable] = []
         # lets checkpoint loaders that only see the bare module find the wrapper (utils/checkpoint.py); a plain
@@ -321,16 +324,66 @@ class DistributedDataParallel(nn.Module):
 
             OF.join_side_work()  # weight gradients still running on the side stream (ops/functional.py)
         self._gather_grads(b)
+        rec = self._comm_record_start(b) if self._comm_timing else None
         if self._comm_stream is not None:
             # the comm stream must see every gradient write of this bucket
             self._comm_stream.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(self._comm_stream):
+                if rec is not None:
+                    rec["start"].record(self._comm_stream)
                 b.handle = self.comm.all_reduce_mean_(b.buffer, self._reduce_out(b))
+                if rec is not None:
+                    rec["end"].record(self._comm_stream)
                 if self.on_bucket_reduced is not None:
                     b.handle.wait()
                     self.on_bucket_reduced(b)
         else:
             b.handle = self.comm.all_reduce_mean_(b.buffer, self._reduce_out(b))
+
+    # ------------------------------------------------------------------ per-bucket communication metrics
+    def comm_timing(self, on: bool = True) -> None:
+        """Record, for every bucket all-reduce from now on, its size and duration (CUDA events on the comm stream; wall
+        clock from launch to completion on the CPU / gloo path).  Not under CUDA-graph capture (events inside a graph
+        cannot be timed): :meth:`engine.Trainer.profile_comm` runs a few eager steps for that."""
+        self._comm_timing = bool(on)
+        self._comm_records = []
+
+    def _comm_record_start(self, b: GradBucket):
+        import time
+
+        if self._comm_stream is not None:
+            if torch.cuda.is_current_stream_capturing():
+                return None
+            rec = {"bucket": b.index, "bytes": b.padded_numel * b.buffer.element_size(),
+                   "start": torch.cuda.Event(enable_timing=True), "end": torch.cuda.Event(enable_timing=True)}
+        else:
+            rec = {"bucket": b.index, "bytes": b.padded_numel * b.buffer.element_size(), "t0": time.perf_counter(), "t1": None,
+                   "b": b}
+        self._comm_records.append(rec)
+        return rec
+
+    def comm_stats(self, reset: bool = True):
+        """One dict per recorded bucket all-reduce: bucket index, bytes, microseconds, bus bandwidth (algorithm bandwidth x
+        2 (W - 1) / W) and - on NVLink - its fraction of the nominal 900 GB/s per direction."""
+        import time
+
+        out = []
+        W = self.comm.world_size if hasattr(self.comm, "world_size") else pg.world_size()
+        f = 2.0 * (W - 1) / W if W > 1 else 0.0
+        for r in self._comm_records:
+            if "start" in r:
+                r["end"].synchronize()
+                us = r["start"].elapsed_time(r["end"]) * 1e3
+            else:
+                us = ((r["t1"] if r["t1"] is not None else time.perf_counter()) - r["t0"]) * 1e6
+            bus = r["bytes"] / max(us, 1e-3) * 1e-3 * f  # GB/s
+            d = {"bucket": r["bucket"], "bytes": r["bytes"], "us": us, "busbw_gbs": bus}
+            if "start" in r:
+                d["frac_of_900"] = bus / 900.0
+            out.append(d)
+        if reset:
+            self._comm_records = []
+        return out
 
     def _reduce_out(self, b: GradBucket) -> Optional[torch.Tensor]:
         return None  # in place; subclasses / fused optimizers may redirect
@@ -350,9 +403,14 @@ class DistributedDataParallel(nn.Module):
                             b.handle.wait()
             torch.cuda.current_stream(self.device).wait_stream(self._comm_stream)
         else:
+            import time
+
             for b in self.buckets:
                 if b.handle is not None:
                     b.handle.wait()
+                    for r in self._comm_records:
+                        if r.get("b") is b and r["t1"] is None:
+                            r["t1"] = time.perf_counter()
                     if self.on_bucket_reduced is not None:
                         self.on_bucket_reduced(b)
         for b in self.buckets:

@@ -197,3 +197,21 @@ def w_fsdp_resume(reshard):
     load_err = max(float((sr[k].float() - sc[k].float()).abs().max()) for k in sr)
     errs = pg.all_gather_object((resume_err, load_err))
     return {"resume_err": max(e[0] for e in errs), "load_err": max(e[1] for e in errs)}
+
+
+def w_profile_comm(steps):
+    """Trainer.profile_comm on the gloo path: per-bucket all-reduce records, and the training state is rolled back."""
+    from databricks_distributed_deep_learning_b200.engine import Trainer
+    from databricks_distributed_deep_learning_b200.parallel import process_group as pg
+
+    torch.set_num_threads(2)
+    torch.manual_seed(0)
+    tr = Trainer(_make_resnet18(), lr=1e-3, device=torch.device("cpu"), bucket_cap_mb=1.0)
+    x = torch.randn(4, 3, 32, 32)
+    y = torch.randint(0, 10, (4,))
+    before = torch.cat([p.detach().flatten() for p in tr.model.parameters()]).clone()
+    out = tr.profile_comm((x, y), steps=steps)
+    after = torch.cat([p.detach().flatten() for p in tr.model.parameters()])
+    loss = float(tr.step((x, y)))
+    return {"stats": out, "rolled_back": bool(torch.equal(before, after)), "nbuckets": len(tr.ddp.buckets), "loss": loss,
+            "rank": pg.rank()}

@@ -59,3 +59,14 @@ def test_single_process_wrapper_and_grad_views():
     ddp.zero_grad()
     assert all(float(b.buffer.abs().sum()) == 0 for b in ddp.buckets)
     assert set(k[len("module."):] for k in ddp.state_dict()) == set(m.state_dict())
+
+
+def test_profile_comm_reports_every_bucket_and_rolls_back():
+    """SURVEY.md section 5 "metrics": per-bucket communication time / bytes / bus bandwidth from a few eager steps."""
+    out = Distributor(num_processes=2, use_gpu=False, timeout_s=600).run(W.w_profile_comm, 2)
+    st = out["stats"]
+    assert out["rolled_back"] and out["nbuckets"] > 1
+    assert [b["bucket"] for b in st["buckets"]] == list(range(out["nbuckets"]))
+    assert all(b["bytes"] > 0 and b["us"] > 0 and b["busbw_gbs"] > 0 for b in st["buckets"])
+    assert st["bytes_per_step"] == sum(b["bytes"] for b in st["buckets"]) and st["world"] == 2
+    assert abs(st["comm_us_per_step"] - sum(b["us"] for b in st["buckets"])) < 1e-6
