@@ -38,7 +38,20 @@ def main():
             torch.cuda.synchronize()
             ts.append(a.elapsed_time(b) * 1e3)
         ts = sorted(ts[3:])
-        print(f"{cin}x{hw}^2 -> {cout} k{k}/s{s} ablate {ab}: {ts[len(ts) // 2]:7.1f} us", flush=True)
+        # one more run with the cycle counters on (im2col / tiled data kernel only)
+        dbg = torch.zeros(296, 8, dtype=torch.int64, device="cuda")
+        L.call("ddl_conv_set_debug", dbg.data_ptr(), ab)
+        L.call("ddl_conv_fwd", x.data_ptr(), w.data_ptr(), y.data_ptr(), part.data_ptr(), *geom, L.stream_ptr())
+        torch.cuda.synchronize()
+        L.call("ddl_conv_set_debug", None, ab)
+        d = dbg.cpu()
+        d = d[d[:, 0] > 0].float()
+        extra = ""
+        if len(d):
+            m = [int(v) for v in d.median(0).values.tolist()]
+            extra = (f" | cycles (median over {len(d)} CTAs): MMA warp total {m[0]}, waiting for a free accumulator {m[1]}, for operands {m[2]}; "
+                     f"epilogue warp total {m[3]}, waiting for a finished accumulator {m[4]}")
+        print(f"{cin}x{hw}^2 -> {cout} k{k}/s{s} ablate {ab}: {ts[len(ts) // 2]:7.1f} us{extra}", flush=True)
     L.call("ddl_conv_set_debug", None, 0)
 
 

@@ -68,6 +68,17 @@ __device__ __forceinline__ void tma_load_im2col(void* smem_dst, const CUtensorMa
         : "memory");
 }
 
+// mbarrier wait that adds the cycles spent waiting to *acc when timing is on
+__device__ __forceinline__ void mbar_wait_timed(uint64_t* bar, uint32_t parity, bool timing, long long& acc) {
+    if (!timing) {
+        mbar_wait(bar, parity);
+        return;
+    }
+    const long long t0 = clock64();
+    mbar_wait(bar, parity);
+    acc += clock64() - t0;
+}
+
 // ------------------------------------------------------------------------------------------------ data kernel
 constexpr int kTileM = 128;
 constexpr int kEpiWarps = 16;  // 4 TMEM lane quarters x 4 column groups of 64
@@ -102,6 +113,9 @@ struct DataParams {
     int stay;
     uint32_t panel_bytes;
     int ablate;  // timing experiments only (ddl_conv_set_debug): 1 = no epilogue staging / stores, 2 = no activation loads
+    int dense;       // output position of MMA row r of tile t is t * 128 + r (set by launch_data)
+    long long* dbg;  // optional [gridDim.x][8] cycle counters (ddl_conv_set_debug): MMA warp total / wait accumulator / wait
+                     // operands, first epilogue warp total / wait accumulator
 };
 
 template <bool B_MN>
@@ -226,14 +240,17 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
             }
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
+            const bool timing = p.dbg != nullptr;
+            long long w_te = 0, w_full = 0;
+            const long long t_start = timing ? clock64() : 0;
             for (int tile = m_group; tile < p.num_tiles; tile += m_groups) {
                 const int cls = tile / p.tiles_per_cls;
                 const int nkb = p.cls_ntaps[cls] * p.cblocks;
-                mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+                mbar_wait_timed(&tmem_empty[acc], acc_phase ^ 1, timing, w_te);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * p.bn;
                 for (int kb = 0; kb < nkb; ++kb) {
-                    mbar_wait(&full_bar[stage], phase);
+                    mbar_wait_timed(&full_bar[stage], phase, timing, w_full);
                     tc_fence_after();
                     const uint32_t sa = ring_base + (uint32_t)stage * (uint32_t)stage_bytes;
                     const uint32_t sb = stay ? panel_base + (uint32_t)kb * (uint32_t)stage_b : sa + kStageA;
@@ -251,6 +268,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
                 __syncwarp();
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
+            if (timing && lane == 0) {
+                long long* d = p.dbg + (size_t)blockIdx.x * 8;
+                d[0] = clock64() - t_start;
+                d[1] = w_te;
+                d[2] = w_full;
+            }
         }
     } else {
         // ===================== epilogue warps =====================
@@ -260,6 +283,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
         if (group < p.groups) {
             uint8_t* stg = stg_base + ew * kStgBytes;
             const bool stats = p.partials != nullptr;
+            const bool timing = p.dbg != nullptr && ew == 0;
+            long long w_tf = 0;
+            const long long t_start = timing ? clock64() : 0;
             float cs[16], cq[16];  // columns col0 + h * 32 + t_ch * 8 + q  at index h * 8 + q
 #pragma unroll
             for (int i = 0; i < 16; ++i) cs[i] = cq[i] = 0.f;
@@ -268,19 +294,30 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
             const int rows_img = p.bw * p.bh, rows_box = rows_img * p.nb;
             int acc = 0;
             uint32_t acc_phase = 0;
+            // dense: MMA row r of tile t IS output position t * 128 + r (1x1 / stride-1 layers and every stride-1 class in im2col
+            // mode).  No division per tile then: a chain of ~13 integer divisions in front of every accumulator (the tiled-box
+            // decode) cost ~2000 cycles per tile and made the epilogue, not the mainloop, the bottleneck of the short-K layers.
+            const bool dense = p.dense != 0;
             for (int tile = m_group; tile < p.num_tiles; tile += m_groups) {
-                const int cls = tile / p.tiles_per_cls, t = tile - cls * p.tiles_per_cls;
-                const int ng = t / tiles_hw, rem = t - ng * tiles_hw;
-                const int hb = rem / p.tiles_w, wb = rem - hb * p.tiles_w;
-                const int n0 = ng * p.nb, oh0 = hb * p.bh, ow0 = wb * p.bw;
-                const int oph = p.cls_oph[cls], opw = p.cls_opw[cls];
+                int cls = 0, t = tile, n0 = 0, oh0 = 0, ow0 = 0, oph = 0, opw = 0;
+                if (!dense) {
+                    cls = tile / p.tiles_per_cls;
+                    t = tile - cls * p.tiles_per_cls;
+                    const int ng = t / tiles_hw, rem = t - ng * tiles_hw;
+                    const int hb = rem / p.tiles_w, wb = rem - hb * p.tiles_w;
+                    n0 = ng * p.nb; oh0 = hb * p.bh; ow0 = wb * p.bw;
+                    oph = p.cls_oph[cls]; opw = p.cls_opw[cls];
+                }
                 // element offset of the 16-byte piece this lane stores for each of its 4 rows per 32-column half
                 long long off[4];
 #pragma unroll
                 for (int it = 0; it < 4; ++it) {
                     const int r = quarter * 32 + it * 8 + t_row;
                     off[it] = -1;
-                    if (p.im2col) {
+                    if (dense) {
+                        const int m = t * kTileM + r;
+                        if (m < (int)p.cls_pix) off[it] = (long long)m * p.Cn + col0 + t_ch * 8;
+                    } else if (p.im2col) {
                         const int m = t * kTileM + r;
                         if (m < (int)p.cls_pix) {
                             if (p.os == 1) {  // dense output: position m IS the pixel index
@@ -298,7 +335,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
                             off[it] = (((long long)(n0 + j) * p.OHf + (oh0 + a) * p.os + oph) * p.OWf + (ow0 + b) * p.os + opw) * p.Cn + col0 + t_ch * 8;
                     }
                 }
-                mbar_wait(&tmem_full[acc], acc_phase);
+                mbar_wait_timed(&tmem_full[acc], acc_phase, timing, w_tf);
                 tc_fence_after();
                 const uint32_t taddr = tmem_base + acc * p.bn + group * 64 + ((uint32_t)(quarter * 32) << 16);
 #pragma unroll
@@ -340,6 +377,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
                     __syncwarp();
                 }
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+            if (timing && lane == 0) {
+                long long* d = p.dbg + (size_t)blockIdx.x * 8;
+                d[3] = clock64() - t_start;
+                d[4] = w_tf;
             }
             if (stats) {
                 // fold the 8 row groups of the warp (lanes with equal t_ch), then the 4 lane-quarter warps of this
@@ -428,17 +470,6 @@ struct PairParams {
     long long* dbg;  // optional [gridDim.x][8] cycle counters (ddl_conv_set_debug): where each role of a CTA waits
     int ablate;      // development only: bit 0 = epilogue drops its staging / stores, bit 1 = producer issues no TMA loads
 };
-
-// mbarrier wait that adds the cycles spent waiting to *acc when timing is on
-__device__ __forceinline__ void mbar_wait_timed(uint64_t* bar, uint32_t parity, bool timing, long long& acc) {
-    if (!timing) {
-        mbar_wait(bar, parity);
-        return;
-    }
-    const long long t0 = clock64();
-    mbar_wait(bar, parity);
-    acc += clock64() - t0;
-}
 
 __device__ __forceinline__ void tma_load_im2col_2sm(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c, int w, int h, int n, int off_w,
                                                     int off_h) {
@@ -1179,6 +1210,14 @@ int launch_data(bool b_mn, const ConvMaps& maps, DataParams& p, cudaStream_t str
     }
     const int stage_bytes = p.stay ? kStageA : kStageA + p.bn * 128;
     p.ablate = g_conv_ablate;
+    p.dbg = g_conv_dbg;
+    // dense tiles: one class whose positions are stored with pixel stride 1 and that is tiled 128 positions at a time, either by
+    // im2col-mode loads or as a flat 1x1 layer (one box row of 128 pixels per tile)
+    p.dense = 0;
+    if (p.ncls == 1 && p.os == 1 && (p.im2col || (p.N == 1 && p.OHt == 1 && p.bw == kTileM && p.bh == 1 && p.nb == 1))) {
+        p.dense = 1;
+        if (!p.im2col) p.cls_pix = p.OWt;
+    }
     p.stages = (227 * 1024 - fixed - (int)p.panel_bytes) / stage_bytes;
     if (p.stages > kMaxStages) p.stages = kMaxStages;
     p.group = 1;

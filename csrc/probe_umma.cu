@@ -173,6 +173,73 @@ __global__ void __launch_bounds__(128, 1) probe_umma_rate_kernel(long long* __re
         tmem_dealloc(tmem, 512);
     }
 }
+// How fast can an epilogue drain TMEM, and does a running mainloop slow it down?  `nwarps` warps (4 per TMEM lane quarter) read
+// 32 lanes x 32 columns (4 KB per tcgen05.ld) `iters` times each from columns [256, 512) while - if mma_on - one warp keeps
+// issuing 128 x 256 x 16 MMAs into columns [0, 256) until the readers are done.  out[cta] = {cycles of the read phase, MMAs
+// issued meanwhile}.
+__global__ void __launch_bounds__(64 + 16 * 32, 1) probe_tmem_drain_kernel(long long* __restrict__ out, int nwarps, int iters, int mma_on) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* done = reinterpret_cast<uint64_t*>(smem + 128 * 128 + 256 * 128);
+    uint32_t* tptr = reinterpret_cast<uint32_t*>(done + 1);
+    volatile int* flag = reinterpret_cast<volatile int*>(tptr + 1);  // readers still running
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < (128 * 128 + 256 * 128) / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+    fence_proxy_async();
+    if (threadIdx.x == 0) {
+        mbar_init(done, 1);
+        *flag = nwarps;
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tptr, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tptr;
+    long long mmas = 0;
+    if (warp == 0) {
+        if (mma_on) {
+            const uint32_t idesc = make_idesc(128, 256, false, false);
+            const uint64_t da = make_smem_desc(smem_u32(smem), 16, 1024), db = make_smem_desc(smem_u32(smem) + 128 * 128, 16, 1024);
+            while (*flag > 0) {
+                if (elect_one()) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) umma_bf16(tmem, da + k * 2, db + k * 2, idesc, 1u);
+                }
+                __syncwarp();
+                mmas += 4;
+            }
+            if (elect_one()) umma_commit(done);
+            __syncwarp();
+            mbar_wait(done, 0);
+        }
+    } else if (warp >= 2 && warp < 2 + nwarps) {
+        const int quarter = warp & 3;
+        uint32_t r[32];
+        uint32_t sink = 0;
+        __syncwarp();
+        const long long t0 = clock64();
+        for (int i = 0; i < iters; ++i) {
+            tmem_ld_32x32(tmem + 256 + (uint32_t)((i & 7) * 32) + ((uint32_t)(quarter * 32) << 16), r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int e = 0; e < 32; ++e) sink ^= r[e];
+        }
+        const long long t1 = clock64();
+        if (lane == 0) {
+            atomicSub(const_cast<int*>(flag), 1);
+            if (warp == 2) out[blockIdx.x * 2] = t1 - t0;
+            if (sink == 0x12345678u) out[blockIdx.x * 2] = 0;  // keep the loads alive
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0 && lane == 0) out[blockIdx.x * 2 + 1] = mmas;
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem, 512);
+    }
+}
 }  // namespace
 
 // out: int64 [grid][2] = {issue cycles, completion cycles} of `iters` MMAs 128 x n x 16 per CTA
@@ -204,6 +271,20 @@ DDL_API int ddl_probe_umma_shift(const void* X, const void* B, float* D, int shi
         attr = true;
     }
     probe_umma_kernel<<<1, 128, smem, (cudaStream_t)stream_>>>(tx, tb, D, shift, variant, mn);
+    DDL_LAUNCH_CHECK();
+    return 0;
+}
+
+// out: int64 [grid][2] = {cycles the first reader warp needed for `iters` tcgen05.ld of 4 KB each, MMAs issued meanwhile}
+DDL_API int ddl_probe_tmem_drain(long long* out, int nwarps, int iters, int mma_on, int grid, void* stream_) {
+    DDL_REQUIRE(out && nwarps >= 1 && nwarps <= 16 && iters >= 1 && grid >= 1, "probe drain: bad arguments");
+    const int smem = 128 * 128 + 256 * 128 + 256 + 1024;
+    static bool attr = false;
+    if (!attr) {
+        DDL_CHECK(cudaFuncSetAttribute(probe_tmem_drain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr = true;
+    }
+    probe_tmem_drain_kernel<<<grid, 64 + 16 * 32, smem, (cudaStream_t)stream_>>>(out, nwarps, iters, mma_on);
     DDL_LAUNCH_CHECK();
     return 0;
 }

@@ -104,6 +104,7 @@ _PROTOS = {
     "ddl_conv_set_stay": ([_i], _i),
     "ddl_probe_umma_shift": ([_vp, _vp, _vp, _i, _i, _i, _vp], _i),
     "ddl_probe_umma_rate": ([_vp, _i, _i, _i, _i, _i, _vp], _i),
+    "ddl_probe_tmem_drain": ([_vp, _i, _i, _i, _i, _vp], _i),
     "ddl_embed_bwd_scratch_bytes": ([_i, _i], _sz),
     "ddl_embed_bwd": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i, _i, _i, _i, _i, _i, _vp], _i),
     "ddl_attention_fwd": ([_vp, _vp, _vp, _vp, _i, _i, _i, _f, _u64, _vp, _vp], _i),

@@ -276,6 +276,13 @@ int ddl_conv_set_stay(int on);
  * only, results are garbage): bit 0 = epilogue drops its staging and stores, bit 1 = no TMA loads are issued */
 int ddl_conv_set_debug(void* buf, int ablate);
 
+/* ---- hardware probes (csrc/probe_umma.cu; benchmarks/probe_umma*.py, probe_tmem_drain.py; not on any training path) ---- */
+int ddl_probe_umma_shift(const void* X, const void* B, float* D, int shift, int variant, int mn, void* stream);
+int ddl_probe_umma_rate(long long* out, int n, int iters, int grid, int mode, int nacc, void* stream);
+/* cycles for `iters` tcgen05.ld (32 lanes x 32 columns) per warp with `nwarps` reader warps, with or without a concurrent stream
+ * of 128 x 256 x 16 MMAs on other TMEM columns; out: int64 [grid][2] = {cycles, MMAs issued meanwhile} */
+int ddl_probe_tmem_drain(long long* out, int nwarps, int iters, int mma_on, int grid, void* stream);
+
 /* ---- tcgen05 / TMEM / TMA GEMM (csrc/gemm_tcgen05.cu), K8 ------------------------------ */
 /* C[M,N] = epilogue(A . B^T), bf16 operands, fp32 accumulation in tensor memory.
  * A is [M,K] row-major (a_mn = 0) or stored as [K,M] (a_mn = 1); B is [N,K] (b_mn = 0) or stored
