@@ -79,6 +79,9 @@ __device__ __forceinline__ void mbar_wait_timed(uint64_t* bar, uint32_t parity, 
     acc += clock64() - t0;
 }
 
+// x / d through a host-computed multiplier M = ceil(2^40 / d): exact while x * d < 2^40 (checked where M is computed)
+__device__ __forceinline__ int fast_div(int x, unsigned long long M) { return (int)(((unsigned long long)(unsigned)x * M) >> 40); }
+
 // ------------------------------------------------------------------------------------------------ data kernel
 constexpr int kTileM = 128;
 constexpr int kEpiWarps = 16;  // 4 TMEM lane quarters x 4 column groups of 64
@@ -114,6 +117,7 @@ struct DataParams {
     uint32_t panel_bytes;
     int ablate;  // timing experiments only (ddl_conv_set_debug): 1 = no epilogue staging / stores, 2 = no activation loads
     int dense;       // output position of MMA row r of tile t is t * 128 + r (set by launch_data)
+    unsigned long long mul_ow, mul_oh, mul_tpc;  // fast_div multipliers of OWt, OHt, tiles_per_cls (0 = use the plain division)
     long long* dbg;  // optional [gridDim.x][8] cycle counters (ddl_conv_set_debug): MMA warp total / wait accumulator / wait
                      // operands, first epilogue warp total / wait accumulator
 };
@@ -301,7 +305,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
             for (int tile = m_group; tile < p.num_tiles; tile += m_groups) {
                 int cls = 0, t = tile, n0 = 0, oh0 = 0, ow0 = 0, oph = 0, opw = 0;
                 if (!dense) {
-                    cls = tile / p.tiles_per_cls;
+                    cls = p.mul_tpc ? fast_div(tile, p.mul_tpc) : tile / p.tiles_per_cls;
                     t = tile - cls * p.tiles_per_cls;
                     const int ng = t / tiles_hw, rem = t - ng * tiles_hw;
                     const int hb = rem / p.tiles_w, wb = rem - hb * p.tiles_w;
@@ -323,8 +327,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
                             if (p.os == 1) {  // dense output: position m IS the pixel index
                                 off[it] = (long long)m * p.Cn + col0 + t_ch * 8;
                             } else {
-                                const int b = m % p.OWt, t2 = m / p.OWt;
-                                const int a = t2 % p.OHt, nn = t2 / p.OHt;
+                                const int t2 = p.mul_ow ? fast_div(m, p.mul_ow) : m / p.OWt, b = m - t2 * p.OWt;
+                                const int nn = p.mul_oh ? fast_div(t2, p.mul_oh) : t2 / p.OHt, a = t2 - nn * p.OHt;
                                 off[it] = (((long long)nn * p.OHf + a * p.os + oph) * p.OWf + b * p.os + opw) * p.Cn + col0 + t_ch * 8;
                             }
                         }
@@ -1211,6 +1215,14 @@ int launch_data(bool b_mn, const ConvMaps& maps, DataParams& p, cudaStream_t str
     const int stage_bytes = p.stay ? kStageA : kStageA + p.bn * 128;
     p.ablate = g_conv_ablate;
     p.dbg = g_conv_dbg;
+    auto magic = [](long long xmax, int d) -> unsigned long long {  // 0 when the exactness bound x * d < 2^40 does not hold
+        if (d <= 0 || xmax * (long long)d >= (1ll << 40) || xmax / d >= (1ll << 23)) return 0ull;  // (second bound: no 64-bit overflow)
+        return ((1ull << 40) + (unsigned long long)d - 1) / (unsigned long long)d;
+    };
+    const long long max_pos = (long long)p.N * p.OHt * p.OWt + kTileM;
+    p.mul_ow = magic(max_pos, p.OWt);
+    p.mul_oh = magic(max_pos, p.OHt);
+    p.mul_tpc = magic((long long)p.num_tiles + 1, p.tiles_per_cls);
     // dense tiles: one class whose positions are stored with pixel stride 1 and that is tiled 128 positions at a time, either by
     // im2col-mode loads or as a flat 1x1 layer (one box row of 128 pixels per tile)
     p.dense = 0;
