@@ -1201,10 +1201,8 @@ int launch_data(bool b_mn, const ConvMaps& maps, DataParams& p, cudaStream_t str
     const int fixed = kEpiWarps * kStgBytes + 512 + 1024;
     // Resident weights: one class, 256-column blocks, the whole [ntaps * cblocks] x bn panel within 128 KB (K <= 256) and four
     // activation stages beside it.  Measured gain is small (256 -> 1024 at 14 x 14: 49.2 -> 47.1 us forward; narrower column
-    // blocks got slower): these short-K layers are not bound by the weight re-loads but by draining the accumulator - with
-    // neither loads nor stores the kernel still takes 32.8 us, i.e. ~5500 cycles per 128 x 256 tile against 2048 cycles of
-    // MMAs (tcgen05.ld of the 128 KB fp32 tile) - and by the staging + stores of the epilogue (another 16 us);
-    // benchmarks/conv_ablate.py.
+    // blocks got slower): what bounded these short-K layers was the index arithmetic of the epilogue (see `dense` below and
+    // benchmarks/conv_ablate.py), not the weight re-loads.
     const long long panel = (long long)p.cls_ntaps[0] * p.cblocks * p.bn * 128;
     p.stay = 0;
     p.panel_bytes = 0;
