@@ -191,19 +191,23 @@ __global__ void __launch_bounds__(kThreads, 1) conv_data_kernel(const __grid_con
             uint32_t phase = 0;
             const uint32_t tx_bytes = p.a_bytes + (p.stay ? 0u : (uint32_t)stage_b);
             for (int tile = m_group; tile < p.num_tiles; tile += m_groups) {
-                const int cls = tile / p.tiles_per_cls, t = tile - cls * p.tiles_per_cls;
-                const int ng = t / tiles_hw, rem = t - ng * tiles_hw;
-                const int hb = rem / p.tiles_w, wb = rem - hb * p.tiles_w;
-                const int n0 = ng * p.nb, oh0 = hb * p.bh, ow0 = wb * p.bw;
-                const int ntaps = p.cls_ntaps[cls];
-                int iw = 0, ih = 0, in_ = 0;  // im2col mode: base pixel of the tile's first position
+                // (divisions through the host-computed multipliers where they exist; none at all for flat dense tiles)
+                const int cls = p.ncls == 1 ? 0 : (p.mul_tpc ? fast_div(tile, p.mul_tpc) : tile / p.tiles_per_cls);
+                const int t = tile - cls * p.tiles_per_cls;
+                int n0 = 0, oh0 = 0, ow0 = t * kTileM;  // flat dense tiles: one box row of 128 pixels per tile
+                int iw = 0, ih = 0, in_ = 0;             // im2col mode: base pixel of the tile's first position
                 if (p.im2col) {
                     const int m0 = t * kTileM;  // < 2^31 (checked on the host)
-                    const int b0 = m0 % p.OWt, t2 = m0 / p.OWt;
+                    const int t2 = p.mul_ow ? fast_div(m0, p.mul_ow) : m0 / p.OWt, b0 = m0 - t2 * p.OWt;
+                    in_ = p.mul_oh ? fast_div(t2, p.mul_oh) : t2 / p.OHt;
                     iw = b0 * p.cstride + p.low_w;
-                    ih = (t2 % p.OHt) * p.cstride + p.low_h;
-                    in_ = t2 / p.OHt;
+                    ih = (t2 - in_ * p.OHt) * p.cstride + p.low_h;
+                } else if (!p.dense) {
+                    const int ng = t / tiles_hw, rem = t - ng * tiles_hw;
+                    const int hb = rem / p.tiles_w, wb = rem - hb * p.tiles_w;
+                    n0 = ng * p.nb; oh0 = hb * p.bh; ow0 = wb * p.bw;
                 }
+                const int ntaps = p.cls_ntaps[cls];
                 for (int ti = 0; ti < ntaps; ++ti) {
                     const Tap tp = p.taps[cls][ti];
                     const int wcol = tp.wtap * p.w_tap_stride;
@@ -845,6 +849,7 @@ struct WgradParams {
     // im2col mode: chunk = `pix` consecutive output positions (dense, spanning rows and images); x taps through the im2col
     // map maps.in[0], dy through the flattened map maps.w; nothing needs zero-filling (TMA fills what lies past the end)
     int im2col, cstride, low_w, low_h;
+    unsigned long long mul_ow, mul_oh;  // fast_div multipliers of OWt, OHt (0 = plain division)
 };
 
 __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_kernel(const __grid_constant__ ConvMaps maps, const WgradParams p) {
@@ -908,12 +913,19 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_kernel(const __grid_
             u_dw[i] = tp.dw; u_dh[i] = tp.dh; u_map[i] = tp.map;
         }
         for (int chunk = c0; chunk < c1; ++chunk) {
-            const int ng = chunk / tiles_hw, rem = chunk - ng * tiles_hw;
-            const int hb = rem / p.tiles_w, wb = rem - hb * p.tiles_w;
-            const int n0 = ng * p.nb, oh0 = hb * p.bh, ow0 = wb * p.bw;
-            const int m0 = chunk * p.pix, t2 = p.im2col ? m0 / p.OWt : 0;
-            const int iw = p.im2col ? (m0 % p.OWt) * p.cstride + p.low_w : 0, ih = p.im2col ? (t2 % p.OHt) * p.cstride + p.low_h : 0;
-            const int in_ = p.im2col ? t2 / p.OHt : 0;
+            // (a chain of plain integer divisions here is ~1000 cycles of dependent latency per chunk - as much as the chunk's MMAs)
+            int n0 = 0, oh0 = 0, ow0 = 0, iw = 0, ih = 0, in_ = 0;
+            const int m0 = chunk * p.pix;
+            if (p.im2col) {
+                const int t2 = p.mul_ow ? fast_div(m0, p.mul_ow) : m0 / p.OWt;
+                in_ = p.mul_oh ? fast_div(t2, p.mul_oh) : t2 / p.OHt;
+                iw = (m0 - t2 * p.OWt) * p.cstride + p.low_w;
+                ih = (t2 - in_ * p.OHt) * p.cstride + p.low_h;
+            } else {
+                const int ng = chunk / tiles_hw, rem = chunk - ng * tiles_hw;
+                const int hb = rem / p.tiles_w, wb = rem - hb * p.tiles_w;
+                n0 = ng * p.nb; oh0 = hb * p.bh; ow0 = wb * p.bw;
+            }
             mbar_wait(&empty_bar[stage], phase ^ 1);
             uint8_t* st = smem + (size_t)stage * stage_bytes;
             if (elect_one()) {
@@ -1812,6 +1824,15 @@ DDL_API int ddl_conv_wgrad(const void* x, const void* dy, void* dw, long long sk
         p.im2col = 1;
         p.cstride = stride; p.low_w = -pad; p.low_h = -pad;
         p.OHt = s.OH; p.OWt = s.OW;
+        {
+            const long long xmax = (long long)N * s.OH * s.OW + 256;
+            auto magic = [&](int d) -> unsigned long long {
+                if (d <= 0 || xmax * (long long)d >= (1ll << 40) || xmax / d >= (1ll << 23)) return 0ull;
+                return ((1ull << 40) + (unsigned long long)d - 1) / (unsigned long long)d;
+            };
+            p.mul_ow = magic(s.OW);
+            p.mul_oh = magic(s.OH);
+        }
         const int up_w = (s.OW - 1) * stride + 1 - pad - W, up_h = (s.OH - 1) * stride + 1 - pad - H;
         if (int e = make_im2col_map(&maps.in[0], x, N, H, W, C, -pad, -pad, up_w, up_h, stride, w.g.pix(), "conv wgrad x (im2col)")) return e;
         for (int i = 1; i < 4; ++i) maps.in[i] = maps.in[0];
