@@ -198,8 +198,12 @@ def measure(args, workload, impl, device, rank, world):
     if impl == "ours" and world > 1 and not runner.fsdp:
         try:
             comm_stats = runner.trainer.profile_comm(host_batches[0], steps=3)
-            for b in comm_stats["buckets"]:  # time = max over ranks; bandwidths follow from it
-                b["us"] = round(pg.max_over_ranks(b["us"]), 3)
+            # A rank that enters a collective early waits inside it for the last one: the LAST rank's time (min over ranks) is the
+            # transfer itself and gives the bandwidth; the max over ranks additionally holds the arrival skew of these eager steps.
+            for b in comm_stats["buckets"]:
+                us_max = pg.max_over_ranks(b["us"])
+                b["us"] = round(-pg.max_over_ranks(-b["us"]), 3)
+                b["us_incl_skew_wait"] = round(us_max, 3)
                 b["busbw_gbs"] = round(b["bytes"] / b["us"] * 1e-3 * 2.0 * (world - 1) / world, 1)
                 b["frac_of_900"] = round(b["busbw_gbs"] / 900.0, 3)
             comm_stats["comm_us_per_step"] = round(sum(b["us"] for b in comm_stats["buckets"]), 1)
