@@ -287,17 +287,41 @@ class Trainer:
         n = min(last, self.steps_done, 1024)
         return [float(self._loss_ring[(self.steps_done - n + i) % 1024]) for i in range(n)]
 
-    def fit(self, loader: Iterable, steps: Optional[int] = None, log_every: int = 0, logger=None) -> Dict[str, Any]:
+    def fit(self, loader: Iterable, steps: Optional[int] = None, log_every: int = 0, logger=None,
+            log_comm: bool = False) -> Dict[str, Any]:
+        """Run ``steps`` optimisation steps over ``loader``.  With a ``logger`` (``utils.timing.JsonlLogger``) every
+        ``log_every``-th step is logged with its loss and the throughput since the previous record; ``log_comm=True`` first logs
+        one ``comm`` record with the per-bucket all-reduce time / bytes / bus bandwidth of this model (:meth:`profile_comm`, run
+        on the first batch, state rolled back)."""
+        import time
+
         losses = []
-        for i, batch in enumerate(loader):
+        it = iter(loader)
+        first = None
+        if log_comm and logger is not None and pg.world_size() > 1:
+            first = next(it, None)
+            if first is not None:
+                logger.log(kind="comm", **self.profile_comm(first))
+        t_last, n_last = time.perf_counter(), 0
+
+        def batches():
+            if first is not None:
+                yield first
+            yield from it
+
+        for i, batch in enumerate(batches()):
             if steps is not None and i >= steps:
                 break
             loss = self.step(batch)
             if not self.cuda:
                 losses.append(float(loss))
             if log_every and (i + 1) % log_every == 0 and logger is not None:
-                val = self.loss_history(1)[0] if self.cuda else losses[-1]
-                logger.log(step=i + 1, loss=val)
+                val = self.loss_history(1)[0] if self.cuda else losses[-1]  # (the read-back synchronises: the rate below is real)
+                now = time.perf_counter()
+                x0 = batch[next(iter(batch))] if isinstance(batch, dict) else batch[0]
+                per_step = int(x0.shape[0]) * pg.world_size()
+                logger.log(kind="step", step=i + 1, loss=val, samples_per_s=round(per_step * (i + 1 - n_last) / max(now - t_last, 1e-9), 2))
+                t_last, n_last = now, i + 1
         if self.cuda:
             losses = self.loss_history(min(self.steps_done, 1024))
         return {"steps": self.steps_done, "losses": losses}

@@ -215,3 +215,18 @@ def w_profile_comm(steps):
     loss = float(tr.step((x, y)))
     return {"stats": out, "rolled_back": bool(torch.equal(before, after)), "nbuckets": len(tr.ddp.buckets), "loss": loss,
             "rank": pg.rank()}
+
+
+def w_fit_with_logging(path):
+    """Trainer.fit with a JSONL logger: one comm record (per-bucket all-reduce metrics) and step records with throughput."""
+    from databricks_distributed_deep_learning_b200.engine import Trainer
+    from databricks_distributed_deep_learning_b200.utils.data import cifar_shape_loader
+    from databricks_distributed_deep_learning_b200.utils.timing import JsonlLogger
+    from databricks_distributed_deep_learning_b200.parallel import process_group as pg
+
+    torch.set_num_threads(2)
+    torch.manual_seed(0)
+    tr = Trainer(_make_resnet18(), lr=1e-3, device=torch.device("cpu"), bucket_cap_mb=1.0)
+    loader = cifar_shape_loader(4, rank=pg.rank(), world_size=pg.world_size(), seed=1, steps=4, pin_memory=False)
+    out = tr.fit(loader, log_every=2, logger=JsonlLogger(path), log_comm=True)
+    return {"steps": out["steps"], "nlosses": len(out["losses"])}

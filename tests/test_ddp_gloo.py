@@ -70,3 +70,16 @@ def test_profile_comm_reports_every_bucket_and_rolls_back():
     assert all(b["bytes"] > 0 and b["us"] > 0 and b["busbw_gbs"] > 0 for b in st["buckets"])
     assert st["bytes_per_step"] == sum(b["bytes"] for b in st["buckets"]) and st["world"] == 2
     assert abs(st["comm_us_per_step"] - sum(b["us"] for b in st["buckets"])) < 1e-6
+
+
+def test_fit_logs_comm_and_throughput(tmp_path):
+    import json
+
+    path = str(tmp_path / "run.jsonl")
+    out = Distributor(num_processes=2, use_gpu=False, timeout_s=600).run(W.w_fit_with_logging, path)
+    assert out["steps"] == 4 and out["nlosses"] == 4
+    recs = [json.loads(l) for l in open(path)]
+    comm = [r for r in recs if r.get("kind") == "comm"]
+    steps = [r for r in recs if r.get("kind") == "step"]
+    assert len(comm) == 1 and comm[0]["world"] == 2 and len(comm[0]["buckets"]) > 1
+    assert [r["step"] for r in steps] == [2, 4] and all(r["samples_per_s"] > 0 and r["loss"] > 0 for r in steps)
