@@ -23,7 +23,8 @@ def train_fn(model_name, image_size, num_classes, batch, steps, ckpt):
     trainer = Trainer(model, lr=1e-3)  # bf16 + fused kernels + CUDA graph on GPU, fp32 eager on CPU
     loader = SyntheticImageLoader(batch, image_size=image_size, num_classes=num_classes, steps=steps,
                                   rank=pg.rank(), world_size=pg.world_size())
-    out = trainer.fit(loader, log_every=max(1, steps // 5), logger=JsonlLogger(also_print=True))
+    # step records (loss, samples/s) plus one record with the per-bucket all-reduce time / bytes / bus bandwidth of this model
+    out = trainer.fit(loader, log_every=max(1, steps // 5), logger=JsonlLogger(also_print=True), log_comm=True)
     if ckpt:
         save_checkpoint(ckpt, trainer.ddp, trainer.opt, step=out["steps"])  # rank 0 writes, everyone syncs
     return {"final_loss": out["losses"][-1] if out["losses"] else None, "world": pg.world_size()}
